@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE config C3: batched collision check of 1M Reeds-Shepp edges (disc
+footprint r = 1.0 m) on a 2000x2000 occupancy grid at 0.1 m.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode check|solve_check]
+
+One "step" = one pass of StateValidatorOccupancyMap::IsPathValid over one batch of 1M pre-solved
+Reeds-Shepp edges (mode check, default) or PathConnectionReedsShepp::Connect + IsPathValid over 1M
+start/goal pairs (mode solve_check).  Rank r of N owns its own batch (weak scaling, no data-path
+collective; NCCL only reduces the timing).  Prints ONE JSON line on rank 0.
+
+  value     edges/s with the edge records already resident in HBM (CUDA events on the launch stream)
+  e2e       edges/s through the host-buffer C-ABI call (pinned host memory, H2D + kernel + D2H)
+  roofline  algorithmic bytes (80 + 4*S per edge, S = samples visited) / kernel time vs measured HBM peak
+  cpu_baseline / --impl reference: the UNMODIFIED reference (oracle/_ref/libpp_ref.so) timed on all
+            host cores, one process per core, on a bounded sample of the same edges.
+"""
+import argparse
+import ctypes
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+N_EDGES = 1_000_000
+N_BATCHES = 4  # rotating batches: 4 x 72 MB of edge records > 126 MB L2
+RMIN = 2.0
+RADIUS, MIN_STEP = 1.0, 0.1
+WORKLOAD = "C3: 1M Reeds-Shepp edges x disc footprint r=1.0m on 2000x2000 grid @0.1m (parking lot, p=0.5)"
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# --------------------------------------------------------------------------------------------------
+# Reference arm: the compiled reference on the host cores (test infrastructure, see oracle/)
+def _ref_world():
+    import refapi
+    from pathplanning_b200 import synth
+    cfg = synth.C3
+    w = refapi.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    for r in synth.config_rects(cfg):
+        w.add_rectangle(*r)
+    w.update()
+    w.set_validator_params(RADIUS, MIN_STEP)
+    return w
+
+
+def _ref_worker(w, starts, goals, mode, reps, conn):
+    """Child process: solve (untimed for mode check) then time the reference loop."""
+    import refapi
+    try:
+        if mode == "check":
+            r = w.check_rs_edges(starts, goals, RMIN)
+            times = [w.check_rs_segments(starts, r["steer"], r["dir"], r["len"], RMIN)["seconds"] for _ in range(reps)]
+        else:
+            times = [w.check_rs_edges(starts, goals, RMIN, full=False)["seconds"] for _ in range(reps)]
+        conn.send(times)
+    except Exception as e:  # pragma: no cover
+        conn.send(e)
+    conn.close()
+
+
+def run_reference(args, per_core):
+    """Times the reference's own CPU implementation with one process per host core.
+    Returns (edges_per_s, ms_per_step, cores, sample description)."""
+    import multiprocessing as mp
+    from pathplanning_b200 import synth
+    cores = host_cores()
+    w = _ref_world()  # built once, inherited by fork (process-global Random<> statics stay per process)
+    n = per_core * cores
+    starts, goals = synth.random_rs_queries(n, seed=1000)
+    reps = args.warmup + args.steps
+    ctxmp = mp.get_context("fork")
+    procs, pipes = [], []
+    for c in range(cores):
+        a, b = ctxmp.Pipe(duplex=False)
+        sl = slice(c * per_core, (c + 1) * per_core)
+        p = ctxmp.Process(target=_ref_worker, args=(w, starts[sl], goals[sl], args.mode, reps, b))
+        p.start()
+        procs.append(p)
+        pipes.append(a)
+    results = [a.recv() for a in pipes]
+    for p in procs:
+        p.join()
+    for r in results:
+        if isinstance(r, Exception):
+            raise r
+    # all cores run concurrently; a step takes as long as the slowest core
+    per_step = np.max(np.array(results)[:, args.warmup:], axis=0)
+    sec = float(np.mean(per_step))
+    sample = f"{n} edges of the workload ({per_core}/core), {args.steps} timed passes, one process per core"
+    return n / sec, sec * 1e3, cores, sample
+
+
+def reference_main(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import refapi
+    if not refapi.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libpp_ref.so not built"}))
+        return
+    value, ms, cores, sample = run_reference(args, per_core=args.cpu_edges_per_core)
+    line = {
+        "impl": "reference", "metric": "collision-checked RS edges/s", "value": value, "unit": "edges/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "mode": args.mode},
+        "cpu_baseline": {"value": value, "unit": "edges/s", "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons through NVML while the timed regions run."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self.active = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            if self.active.is_set():
+                try:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for bit, name in names.items():
+                        if mask & bit:
+                            self.reasons.add(name)
+                except Exception:
+                    pass
+            time.sleep(0.002)
+
+    def stop(self):
+        self._stop.set()
+
+    def summary(self):
+        return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def ours_main(args):
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    # CPU baseline first (rank 0, N=1 only), in a subprocess, before this process touches CUDA
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--mode", args.mode,
+                                  "--steps", "3", "--warmup", "1", "--cpu-edges-per-core", str(args.cpu_edges_per_core)],
+                                 capture_output=True, text=True, timeout=900)
+            ref_line = json.loads(out.stdout.strip().splitlines()[-1])
+            cpu_baseline = ref_line.get("cpu_baseline") or {"unavailable": ref_line.get("unavailable")}
+        except Exception as e:  # pragma: no cover
+            cpu_baseline = {"unavailable": f"{type(e).__name__}: {e}"}
+
+    import torch
+    import torch.distributed as dist
+    import pathplanning_b200 as pp
+    from pathplanning_b200 import synth
+    from pathplanning_b200.lib import ppx
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = pp.Context(local_rank)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+
+    # world model: replicated on every rank (setup, untimed)
+    cfg = synth.C3
+    occ = synth.rasterize_rectangles(synth.config_rects(cfg), cfg["lb"], cfg["ub"], cfg["resolution"])
+    sq = synth.exact_sqdist(occ)
+    rows, cols, origin = synth.map_geometry(cfg["lb"], cfg["ub"], cfg["resolution"])
+    desc = pp.MapDesc(rows=rows, cols=cols, resolution=cfg["resolution"], world_origin=origin, lb=cfg["lb"], ub=cfg["ub"])
+    ctx.upload_map(desc, sq, occ, None)
+    vp = pp.ValidatorParams(RADIUS, MIN_STEP).to_c()
+    cp = pp.RSCostParams(RMIN).to_c()
+
+    # this rank's edge batches, resident in HBM.  Batch 0 of rank 0 is the edge set the CPU arm samples.
+    n = N_EDGES
+    dev = torch.device("cuda", local_rank)
+    d_starts, d_goals, d_edges = [], [], []
+    for b in range(N_BATCHES):
+        s, g = synth.random_rs_queries(n, seed=1000 + 17 * (rank * N_BATCHES + b))
+        d_starts.append(torch.from_numpy(s).to(dev))
+        d_goals.append(torch.from_numpy(g).to(dev))
+        e = torch.empty(n * 72, dtype=torch.uint8, device=dev)
+        rc = ppx.ppx_rs_solve_dev(ctx.handle, n, d_starts[b].data_ptr(), d_goals[b].data_ptr(), ctypes.byref(cp),
+                                  e.data_ptr(), None, None, None)
+        assert rc == 0, ppx.ppx_last_error(ctx.handle)
+        d_edges.append(e)
+    d_valid = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_last = torch.empty(n, dtype=torch.float32, device=dev)
+    d_samples = torch.empty(n, dtype=torch.int32, device=dev)
+    d_word = torch.empty(n, dtype=torch.int32, device=dev)
+
+    def step(b, samples=False):
+        if args.mode == "check":
+            rc = ppx.ppx_check_edges_rs_dev(ctx.handle, n, d_edges[b].data_ptr(), RMIN, ctypes.byref(vp), d_valid.data_ptr(),
+                                            d_last.data_ptr(), d_samples.data_ptr() if samples else None)
+        else:
+            rc = ppx.ppx_connect_check_rs_dev(ctx.handle, n, d_starts[b].data_ptr(), d_goals[b].data_ptr(), ctypes.byref(cp),
+                                              ctypes.byref(vp), d_valid.data_ptr(), d_last.data_ptr(), d_word.data_ptr(), None, None)
+        assert rc == 0, ppx.ppx_last_error(ctx.handle)
+
+    # S: mean samples visited per edge (measured once, untimed) -> algorithmic bytes per edge
+    if args.mode == "check":
+        step(0, samples=True)
+        torch.cuda.synchronize()
+        mean_samples = float(d_samples.float().mean().item())
+    else:
+        rc = ppx.ppx_check_edges_rs_dev(ctx.handle, n, d_edges[0].data_ptr(), RMIN, ctypes.byref(vp), d_valid.data_ptr(),
+                                        d_last.data_ptr(), d_samples.data_ptr())
+        torch.cuda.synchronize()
+        mean_samples = float(d_samples.float().mean().item())
+    valid_frac = float(d_valid.float().mean().item())
+    in_bytes = 72 if args.mode == "check" else 48
+    bytes_per_edge = in_bytes + 8 + 4.0 * mean_samples
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(i % N_BATCHES)
+    barrier()
+    launches0 = ctx.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.active.set()
+    ev0.record(stream)
+    for i in range(args.steps):
+        step(i % N_BATCHES)
+    ev1.record(stream)
+    barrier()
+    sampler.active.clear()
+    launches = ctx.launch_count - launches0
+    ms = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    ms_per_step = ms_total / args.steps
+    value = world * n / (ms_per_step * 1e-3)
+
+    # e2e: the host-buffer C-ABI call a reference-side caller makes (pinned host memory)
+    if args.mode == "check":
+        h_in = [d_edges[b].cpu().pin_memory() for b in range(2)]
+        h2d = n * 72
+    else:
+        h_in = [(d_starts[b].cpu().pin_memory(), d_goals[b].cpu().pin_memory()) for b in range(2)]
+        h2d = n * 48
+    h_valid = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h_last = torch.empty(n, dtype=torch.float32).pin_memory()
+    d2h = n * 5
+
+    def e2e_step(b):
+        if args.mode == "check":
+            rc = ppx.ppx_check_edges_rs(ctx.handle, n, h_in[b].data_ptr(), RMIN, ctypes.byref(vp), h_valid.data_ptr(),
+                                        h_last.data_ptr(), None)
+        else:
+            rc = ppx.ppx_connect_check_rs(ctx.handle, n, h_in[b][0].data_ptr(), h_in[b][1].data_ptr(), ctypes.byref(cp),
+                                          ctypes.byref(vp), h_valid.data_ptr(), h_last.data_ptr(), None, None, None)
+        assert rc == 0, ppx.ppx_last_error(ctx.handle)
+
+    for i in range(3):
+        e2e_step(i % 2)
+    barrier()
+    e2e_steps = max(3, min(args.steps, 20))
+    sampler.active.set()
+    t0 = time.perf_counter()
+    for i in range(e2e_steps):
+        e2e_step(i % 2)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    sampler.active.clear()
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * n * e2e_steps / float(te.item())
+    sampler.stop()
+
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+        else:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        achieved = bytes_per_edge * n / (ms_per_step * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath):
+            traffic = json.load(open(tpath)).get(args.mode)
+        line = {
+            "metric": "collision-checked RS edges/s", "value": value, "unit": "edges/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "mode": args.mode, "edges_per_gpu_per_step": n,
+                       "mean_samples_per_edge": mean_samples, "valid_fraction": valid_frac,
+                       "l2": f"{N_BATCHES} rotating edge batches ({N_BATCHES * n * in_bytes / 1e6:.0f} MB) > 126 MB L2; the 16 MB clearance grid is meant to stay L2-resident"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src, "bytes_per_edge": bytes_per_edge,
+                         "note": "FP64-issue / dependent-L2-latency bound, not HBM bound (DESIGN.md)"},
+            "cpu_baseline": cpu_baseline,
+            "e2e": {"value": e2e_value, "unit": "edges/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": e2e_steps},
+            "gpu_launches": launches,
+            "clocks": sampler.summary(),
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    ctx.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="check", choices=["check", "solve_check"])
+    ap.add_argument("--cpu-edges-per-core", type=int, default=250_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_main(args)
+    else:
+        ours_main(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,895 @@
+// TEST INFRASTRUCTURE ONLY -- never linked into, imported by, or executed from the product path.
+//
+// C-callable harness over the UNMODIFIED reference sources (compiled where they lie under
+// /root/reference by oracle/Makefile into oracle/_ref/libpp_ref.so).  It exists so that tests,
+// __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference arm can run the
+// reference's own C++ path on the same inputs as the CUDA path.
+//
+// Harness-side definitions that the reference leaves undefined (traps):
+//  * H4  the reference seeds one process-global mt19937_64 from std::random_device
+//        (utils/random.h:14-16); the harness re-seeds it explicitly before each search.
+//  * H3  NonHolonomicHeuristic::GetHeuristicValue reads m_values[i][j][k] with k<0
+//        (algo/heuristics.cpp:84-94, out of bounds).  The harness re-points every m_values[i][j]
+//        into a padded copy where index k<0 aliases k+numAngular, which makes the read defined
+//        without touching reference source.  The CUDA path implements the same wrap.
+//  * H1/H2 are properties of how the reference compiles (abs overload, int WrapTheta); the
+//        harness asserts both at load time (ref_selfcheck).
+//
+// Private members are reached with the usual test-only access macro trick; all standard headers
+// are included first so the macros only affect reference headers.
+#include <stdlib.h>
+#include <math.h>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <cstdio>
+#include <memory>
+#include <vector>
+#include <array>
+#include <tuple>
+#include <set>
+#include <map>
+#include <queue>
+#include <random>
+#include <string>
+#include <chrono>
+#include <limits>
+#include <numeric>
+#include <fstream>
+#include <sstream>
+#include <iostream>
+#include <algorithm>
+#include <functional>
+#include <filesystem>
+#include <unordered_map>
+#include <unordered_set>
+#include <mutex>
+#include <thread>
+#include <signal.h>
+#include <eigen3/Eigen/Dense>
+#include <flann/flann.hpp>
+
+#define private public
+#define protected public
+#include "core/base.h"
+#include "algo/hybrid_a_star.h"
+#include "algo/heuristics.h"
+#include "algo/a_star_n2.h"
+#include "algo/rrt.h"
+#include "algo/rrt_star.h"
+#include "geometry/2dplane.h"
+#include "geometry/reeds_shepp.h"
+#include "models/kinematic_bicycle_model.h"
+#include "paths/path_constant_steer.h"
+#include "paths/path_reeds_shepp.h"
+#include "paths/path_se2.h"
+#include "paths/path_r2.h"
+#include "paths/path_composite.h"
+#include "state_space/state_space_se2.h"
+#include "state_space/state_space_r2.h"
+#include "state_validator/gvd.h"
+#include "state_validator/obstacle.h"
+#include "state_validator/obstacle_list_occupancy_map.h"
+#include "state_validator/occupancy_map.h"
+#include "state_validator/state_validator_occupancy_map.h"
+#include "state_validator/state_validator_free.h"
+#include "utils/tree.h"
+#undef private
+#undef protected
+
+using namespace Planner;
+
+namespace {
+
+// Counts IsStateValid calls (= samples visited by IsPathValid, which calls the virtual).
+class CountingValidator : public StateValidatorOccupancyMap {
+public:
+	using StateValidatorOccupancyMap::StateValidatorOccupancyMap;
+	bool IsStateValid(const Pose2d& state) override
+	{
+		samples++;
+		return StateValidatorOccupancyMap::IsStateValid(state);
+	}
+	long samples = 0;
+};
+
+struct RefWorld {
+	Ref<StateSpaceSE2> space;
+	Ref<ObstacleListOccupancyMap> map;
+	Ref<CountingValidator> validator;
+	Ref<GVD> gvd;
+	std::vector<Ref<Obstacle>> obstacles;
+};
+
+void SeedRandom(uint64_t seed)
+{
+	Random<double>::Init();
+	*Random<double>::s_engine = std::mt19937_64(seed);
+	Random<double>::s_uniformDistribution.reset();
+}
+
+ReedsShepp::PathSegment MakeSegment(const int* steer, const int* dir, const double* len)
+{
+	ReedsShepp::PathSegment seg;
+	for (int i = 0; i < 5; i++) {
+		if (dir[i] == (int)Direction::NoMotion)
+			break;
+		seg.AddMotion((Steer)steer[i], (Direction)dir[i], len[i]);
+	}
+	return seg;
+}
+
+void DumpSegment(const ReedsShepp::PathSegment& seg, int* steer, int* dir, double* len)
+{
+	for (int i = 0; i < 5; i++) {
+		const auto& m = seg.GetMotion(i);
+		steer[i] = (int)m.steer;
+		dir[i] = (int)m.direction;
+		len[i] = m.length;
+	}
+}
+
+}
+
+extern "C" {
+
+// ---------------------------------------------------------------------------------------------
+// Self check of the compile-dependent traps H1 / H2.  Returns 0 when the build behaves like an
+// upstream build (curved primitives, int-arithmetic heading wrap), else a bit mask.
+int ref_selfcheck(int* wrapped_out /* 75 ints: k=-37..37 -> wrapped k */)
+{
+	int bad = 0;
+	KinematicBicycleModel model(2.6, 0.0);
+	Pose2d to = model.ConstantSteer(Pose2d(0, 0, 0), 0.3, 1.5, Direction::Forward);
+	if (to.theta == 0.0)
+		bad |= 1; // H1: abs(int) picked
+	HybridAStar::SearchParameters p;
+	HybridAStar::StatePropagator prop(p);
+	for (int k = -37; k <= 37; k++) {
+		// pose whose heading falls in bin k
+		double th = (k + (k >= 0 ? 0.5 : -0.5)) * p.angularResolution;
+		Pose2d pose;
+		pose.position = Point2d(0.5, 0.5);
+		pose.theta = th;
+		Pose2i d = prop.DiscretizePose(pose);
+		if (wrapped_out)
+			wrapped_out[k + 37] = d.theta;
+	}
+	return bad;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Reeds-Shepp
+int ref_rs_optimal(const double* start, const double* goal, double rmin, float rev, float fwd, float sw,
+	int* steer, int* dir, double* len, double* total_len, float* cost)
+{
+	ReedsShepp::PathWords word = ReedsShepp::PathWords::NoPath;
+	auto seg = ReedsShepp::Solver::GetOptimalPath(Pose2d(start[0], start[1], start[2]), Pose2d(goal[0], goal[1], goal[2]),
+		rmin, rev, fwd, sw, &word);
+	DumpSegment(seg, steer, dir, len);
+	if (total_len)
+		*total_len = seg.GetLength(rmin);
+	if (cost)
+		*cost = seg.ComputeCost(rmin, rev, fwd, sw);
+	return (int)word;
+}
+
+// start/goal are passed verbatim (no Pose2d ctor wrap) when raw != 0
+int ref_rs_shortest(const double* start, const double* goal, double rmin,
+	int* steer, int* dir, double* len, double* total_len, double* final_pose)
+{
+	ReedsShepp::PathWords word = ReedsShepp::PathWords::NoPath;
+	Pose2d s(start[0], start[1], start[2]), g(goal[0], goal[1], goal[2]);
+	auto seg = ReedsShepp::Solver::GetShortestPath(s, g, rmin, &word);
+	DumpSegment(seg, steer, dir, len);
+	if (total_len)
+		*total_len = seg.GetLength(rmin);
+	if (final_pose) {
+		PathReedsShepp path(s, seg, rmin);
+		final_pose[0] = path.GetFinalState().x();
+		final_pose[1] = path.GetFinalState().y();
+		final_pose[2] = path.GetFinalState().theta;
+	}
+	return (int)word;
+}
+
+void ref_rs_optimal_batch(long n, const double* starts, const double* goals, double rmin, float rev, float fwd, float sw,
+	int* words, int* steer, int* dir, double* len, double* total_len, float* cost)
+{
+	for (long i = 0; i < n; i++)
+		words[i] = ref_rs_optimal(starts + 3 * i, goals + 3 * i, rmin, rev, fwd, sw,
+			steer + 5 * i, dir + 5 * i, len + 5 * i, total_len ? total_len + i : nullptr, cost ? cost + i : nullptr);
+}
+
+// Interpolate an RS path (optionally truncated first; truncate_ratio<0 => no truncation)
+void ref_rs_interpolate(const double* start, const int* steer, const int* dir, const double* len, double rmin,
+	double truncate_ratio, int nratios, const double* ratios, double* poses, double* out_length, double* final_pose)
+{
+	Pose2d s;
+	s.position = Point2d(start[0], start[1]);
+	s.theta = start[2];
+	PathReedsShepp path(s, MakeSegment(steer, dir, len), rmin);
+	if (truncate_ratio >= 0)
+		path.Truncate(truncate_ratio);
+	for (int i = 0; i < nratios; i++) {
+		Pose2d p = path.Interpolate(ratios[i]);
+		poses[3 * i + 0] = p.x();
+		poses[3 * i + 1] = p.y();
+		poses[3 * i + 2] = p.theta;
+	}
+	if (out_length)
+		*out_length = path.GetLength();
+	if (final_pose) {
+		final_pose[0] = path.GetFinalState().x();
+		final_pose[1] = path.GetFinalState().y();
+		final_pose[2] = path.GetFinalState().theta;
+	}
+}
+
+void ref_csteer_interpolate(const double* start, double steering, double length, int direction, double wheelbase,
+	int nratios, const double* ratios, double* poses)
+{
+	auto model = makeRef<KinematicBicycleModel>(wheelbase, 0.0);
+	Pose2d s;
+	s.position = Point2d(start[0], start[1]);
+	s.theta = start[2];
+	PathConstantSteer path(model, s, steering, length, (Direction)direction);
+	for (int i = 0; i < nratios; i++) {
+		Pose2d p = path.Interpolate(ratios[i]);
+		poses[3 * i + 0] = p.x();
+		poses[3 * i + 1] = p.y();
+		poses[3 * i + 2] = p.theta;
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// World: state space + obstacle-list occupancy map + validator
+void* ref_world_create(const double* lb, const double* ub, float resolution)
+{
+	auto* w = new RefWorld();
+	std::array<Pose2d, 2> bounds = { Pose2d(lb[0], lb[1], lb[2]), Pose2d(ub[0], ub[1], ub[2]) };
+	w->space = makeRef<StateSpaceSE2>(bounds);
+	w->map = makeRef<ObstacleListOccupancyMap>(resolution);
+	w->validator = makeRef<CountingValidator>(w->space, w->map);
+	return w;
+}
+
+void ref_world_destroy(void* h) { delete (RefWorld*)h; }
+
+void ref_world_set_position(void* h, double x, double y)
+{
+	// OccupancyMap::SetPosition only stores m_localOrigin; the grid origin is fixed at
+	// InitializeSize time (occupancy_map.cpp:8-9), so re-run it like a user would have to.
+	auto* w = (RefWorld*)h;
+	w->map->SetPosition(Point2d(x, y));
+}
+
+int ref_world_add_rectangle(void* h, double dx, double dy, double x, double y, double theta)
+{
+	auto* w = (RefWorld*)h;
+	auto obstacle = makeRef<Obstacle>();
+	obstacle->SetShape(makeRef<RectangleShape>(dx, dy));
+	obstacle->SetPose(Pose2d(x, y, theta));
+	w->obstacles.push_back(obstacle);
+	return w->map->AddObstacle(obstacle) ? 1 : 0;
+}
+
+// Mark single cells occupied (id>=0) the way AddObstacle does for each boundary cell
+// (obstacle_list_occupancy_map.cpp:39-42).
+void ref_world_set_cells(void* h, long n, const int* rows, const int* cols, int id)
+{
+	auto* w = (RefWorld*)h;
+	for (long i = 0; i < n; i++) {
+		(*w->map->m_occupancyMatrix)[rows[i]][cols[i]] = id;
+		w->map->m_obstacleDistanceMap->SetObstacle(GridCellPosition(rows[i], cols[i]));
+	}
+}
+
+void ref_world_update(void* h) { ((RefWorld*)h)->map->Update(); }
+
+void ref_world_info(void* h, int* rows, int* cols, double* origin_xy, float* resolution)
+{
+	auto* w = (RefWorld*)h;
+	*rows = w->map->Rows();
+	*cols = w->map->Columns();
+	origin_xy[0] = w->map->m_worldGridOrigin.x();
+	origin_xy[1] = w->map->m_worldGridOrigin.y();
+	origin_xy[2] = w->map->m_localOrigin.x();
+	origin_xy[3] = w->map->m_localOrigin.y();
+	*resolution = w->map->resolution;
+}
+
+void ref_world_copy_grids(void* h, int* occupancy, int* sqdist)
+{
+	auto* w = (RefWorld*)h;
+	long n = (long)w->map->Rows() * w->map->Columns();
+	if (occupancy)
+		memcpy(occupancy, w->map->m_occupancyMatrix->m_data, n * sizeof(int));
+	if (sqdist)
+		memcpy(sqdist, w->map->m_obstacleDistanceMap->m_distance.m_data, n * sizeof(int));
+}
+
+void ref_world_set_validator_params(void* h, float minSafeRadius, float minPathInterpolationDistance)
+{
+	auto* w = (RefWorld*)h;
+	w->validator->minSafeRadius = minSafeRadius;
+	w->validator->minPathInterpolationDistance = minPathInterpolationDistance;
+}
+
+// GVD::Update (obstacle brushfire + Voronoi brushfire + potential), copies out the float
+// potential (GVD::PathCostMap) and the squared Voronoi-edge distance.
+void ref_world_gvd_update(void* h, float* pathcost, int* voro_sqdist)
+{
+	auto* w = (RefWorld*)h;
+	if (!w->gvd)
+		w->gvd = makeRef<GVD>(w->map);
+	w->gvd->Update();
+	long n = (long)w->map->Rows() * w->map->Columns();
+	if (pathcost)
+		memcpy(pathcost, w->gvd->m_pathCostMap.m_data, n * sizeof(float));
+	if (voro_sqdist)
+		memcpy(voro_sqdist, w->gvd->m_voronoiMap->m_distance.m_data, n * sizeof(int));
+}
+
+int ref_is_state_valid(void* h, const double* pose)
+{
+	auto* w = (RefWorld*)h;
+	Pose2d p;
+	p.position = Point2d(pose[0], pose[1]);
+	p.theta = pose[2];
+	return w->validator->IsStateValid(p) ? 1 : 0;
+}
+
+void ref_is_state_valid_batch(void* h, long n, const double* poses, uint8_t* valid)
+{
+	for (long i = 0; i < n; i++)
+		valid[i] = (uint8_t)ref_is_state_valid(h, poses + 3 * i);
+}
+
+// Solve (GetOptimalPath) + build PathReedsShepp + IsPathValid for n start/goal pairs.
+// Any output pointer may be null.  Returns wall seconds of the loop.
+double ref_check_rs_edges(void* h, long n, const double* starts, const double* goals, double rmin,
+	float rev, float fwd, float sw,
+	uint8_t* valid, float* last, int* samples, int* words, int* steer, int* dir, double* len,
+	double* total_len, float* cost)
+{
+	auto* w = (RefWorld*)h;
+	auto t0 = std::chrono::steady_clock::now();
+	for (long i = 0; i < n; i++) {
+		Pose2d s(starts[3 * i], starts[3 * i + 1], starts[3 * i + 2]);
+		Pose2d g(goals[3 * i], goals[3 * i + 1], goals[3 * i + 2]);
+		ReedsShepp::PathWords word = ReedsShepp::PathWords::NoPath;
+		auto seg = ReedsShepp::Solver::GetOptimalPath(s, g, rmin, rev, fwd, sw, &word);
+		PathReedsShepp path(s, seg, rmin);
+		float l = 0.0f;
+		long before = w->validator->samples;
+		bool ok = w->validator->IsPathValid(path, &l);
+		if (valid) valid[i] = ok;
+		if (last) last[i] = l;
+		if (samples) samples[i] = (int)(w->validator->samples - before);
+		if (words) words[i] = (int)word;
+		if (steer) DumpSegment(seg, steer + 5 * i, dir + 5 * i, len + 5 * i);
+		if (total_len) total_len[i] = seg.GetLength(rmin);
+		if (cost) cost[i] = seg.ComputeCost(rmin, rev, fwd, sw);
+	}
+	return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// Check-only: pre-solved segments.  starts are taken verbatim (no wrap).
+double ref_check_rs_segments(void* h, long n, const double* starts, const int* steer, const int* dir, const double* len,
+	double rmin, uint8_t* valid, float* last, int* samples)
+{
+	auto* w = (RefWorld*)h;
+	std::vector<PathReedsShepp> paths;
+	paths.reserve(n);
+	for (long i = 0; i < n; i++) {
+		Pose2d s;
+		s.position = Point2d(starts[3 * i], starts[3 * i + 1]);
+		s.theta = starts[3 * i + 2];
+		paths.emplace_back(s, MakeSegment(steer + 5 * i, dir + 5 * i, len + 5 * i), rmin);
+	}
+	auto t0 = std::chrono::steady_clock::now();
+	for (long i = 0; i < n; i++) {
+		float l = 0.0f;
+		long before = w->validator->samples;
+		bool ok = w->validator->IsPathValid(paths[i], &l);
+		if (valid) valid[i] = ok;
+		if (last) last[i] = l;
+		if (samples) samples[i] = (int)(w->validator->samples - before);
+	}
+	return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+// Constant-steer primitives (A2): validity, last ratio, final pose (after truncation when invalid,
+// exactly as GetConstantSteerChild does, hybrid_a_star.cpp:117-123).
+void ref_check_csteer(void* h, long n, const double* starts, const double* steering, const double* length,
+	const int* direction, double wheelbase, uint8_t* valid, float* last, double* final_pose, double* final_len)
+{
+	auto* w = (RefWorld*)h;
+	auto model = makeRef<KinematicBicycleModel>(wheelbase, 0.0);
+	for (long i = 0; i < n; i++) {
+		Pose2d s;
+		s.position = Point2d(starts[3 * i], starts[3 * i + 1]);
+		s.theta = starts[3 * i + 2];
+		PathConstantSteer path(model, s, steering[i], length[i], (Direction)direction[i]);
+		float l = 0.0f;
+		bool ok = w->validator->IsPathValid(path, &l);
+		if (!ok)
+			path.Truncate(l);
+		if (valid) valid[i] = ok;
+		if (last) last[i] = l;
+		if (final_pose) {
+			final_pose[3 * i + 0] = path.GetFinalState().x();
+			final_pose[3 * i + 1] = path.GetFinalState().y();
+			final_pose[3 * i + 2] = path.GetFinalState().theta;
+		}
+		if (final_len) final_len[i] = path.GetLength();
+	}
+}
+
+// Straight SE(2) segments (paths/path_se2.cpp), used by RRT with PathConnectionSE2.
+void ref_check_line_edges(void* h, long n, const double* from, const double* to, uint8_t* valid, float* last)
+{
+	auto* w = (RefWorld*)h;
+	for (long i = 0; i < n; i++) {
+		Pose2d a, b;
+		a.position = Point2d(from[3 * i], from[3 * i + 1]);
+		a.theta = from[3 * i + 2];
+		b.position = Point2d(to[3 * i], to[3 * i + 1]);
+		b.theta = to[3 * i + 2];
+		PathSE2 path(a, b);
+		float l = 0.0f;
+		bool ok = w->validator->IsPathValid(path, &l);
+		if (valid) valid[i] = ok;
+		if (last) last[i] = l;
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// Holonomic-with-obstacles wavefront (A8).  Returns wall seconds of Update().
+double ref_wavefront(void* h, const double* goal, double rev, double fwd, float* cost, uint8_t* explored)
+{
+	auto* w = (RefWorld*)h;
+	ObstaclesHeuristic heur(w->map, rev, fwd);
+	Pose2d g(goal[0], goal[1], goal[2]);
+	auto t0 = std::chrono::steady_clock::now();
+	heur.Update(g);
+	double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	long n = (long)w->map->Rows() * w->map->Columns();
+	if (cost)
+		memcpy(cost, heur.m_cost.m_data, n * sizeof(float));
+	if (explored)
+		for (long i = 0; i < n; i++)
+			explored[i] = heur.m_explored.m_data[i] ? 1 : 0;
+	return dt;
+}
+
+// Heuristic lookups for n poses after a wavefront from `goal`
+void ref_obstacle_heuristic_values(void* h, const double* goal, double rev, double fwd, long n, const double* poses, double* values)
+{
+	auto* w = (RefWorld*)h;
+	ObstaclesHeuristic heur(w->map, rev, fwd);
+	Pose2d g(goal[0], goal[1], goal[2]);
+	heur.Update(g);
+	heur.SetGoal(g);
+	for (long i = 0; i < n; i++) {
+		Pose2d p;
+		p.position = Point2d(poses[3 * i], poses[3 * i + 1]);
+		p.theta = poses[3 * i + 2];
+		values[i] = heur.GetHeuristicValue(p);
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// Non-holonomic-without-obstacles table (A9).  values may be null to query the dimensions.
+double ref_nonholo_build(const double* lb, const double* ub, double spatialRes, double angRes, double rmin,
+	double rev, double fwd, double sw, int* dims /*nx,ny,na*/, double* offsets /*ox,oy*/, double* values)
+{
+	std::array<Pose2d, 2> bounds = { Pose2d(lb[0], lb[1], lb[2]), Pose2d(ub[0], ub[1], ub[2]) };
+	auto t0 = std::chrono::steady_clock::now();
+	auto heur = NonHolonomicHeuristic::Build(bounds, spatialRes, angRes, rmin, rev, fwd, sw);
+	double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	dims[0] = heur->numSpatialX;
+	dims[1] = heur->numSpatialY;
+	dims[2] = heur->numAngular;
+	if (offsets) {
+		offsets[0] = heur->offsetX;
+		offsets[1] = heur->offsetY;
+	}
+	if (values)
+		for (unsigned i = 0; i < heur->numSpatialX; i++)
+			for (unsigned j = 0; j < heur->numSpatialY; j++)
+				for (unsigned k = 0; k < heur->numAngular; k++)
+					values[((size_t)i * heur->numSpatialY + j) * heur->numAngular + k] = heur->m_values[i][j][k];
+	return dt;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Hybrid A*
+namespace {
+struct ExpansionRecord {
+	int ix, iy, ik, direction;
+	double x, y, theta;
+};
+
+class RecordingPropagator : public HybridAStar::StatePropagator {
+public:
+	RecordingPropagator(const HybridAStar::SearchParameters& p) :
+		HybridAStar::StatePropagator(p) { }
+	std::vector<std::tuple<HybridAStar::State, HybridAStar::Action, double>> GetNeighborStates(const HybridAStar::State& state) override
+	{
+		if (record)
+			expansions.push_back({ state.discretePose.x(), state.discretePose.y(), state.discretePose.theta, (int)state.direction,
+				state.continuousPose.x(), state.continuousPose.y(), state.continuousPose.theta });
+		auto out = HybridAStar::StatePropagator::GetNeighborStates(state);
+		numChildren += out.size();
+		return out;
+	}
+	bool record = true;
+	std::vector<ExpansionRecord> expansions;
+	size_t numChildren = 0;
+};
+
+struct RefHybrid {
+	RefWorld* world;
+	std::unique_ptr<HybridAStar> planner;
+	Ref<RecordingPropagator> propagator;
+	std::vector<double*> paddedBlocks; // H3 padding
+	std::vector<double*> originalBlocks;
+};
+}
+
+void* ref_hybrid_create(void* hw, double minTurningRadius, double directionSwitchingCost, double reverseCostMultiplier,
+	double forwardCostMultiplier, double voronoiCostMultiplier, unsigned numGeneratedMotion, double spatialResolution,
+	double angularResolution)
+{
+	auto* h = new RefHybrid();
+	h->world = (RefWorld*)hw;
+	HybridAStar::SearchParameters p(minTurningRadius, directionSwitchingCost, reverseCostMultiplier, forwardCostMultiplier,
+		voronoiCostMultiplier, numGeneratedMotion, spatialResolution, angularResolution);
+	h->planner = std::make_unique<HybridAStar>(p);
+	// validator handed to the planner is the counting subclass (same virtual behaviour)
+	Ref<StateValidatorOccupancyMap> validator = h->world->validator;
+	if (!h->planner->Initialize(validator)) {
+		delete h;
+		return nullptr;
+	}
+	h->world->gvd = h->planner->m_gvd;
+	// Swap in the recording propagator (same parameters / same base behaviour).
+	h->propagator = makeRef<RecordingPropagator>(p);
+	h->propagator->Initialize(validator, h->planner->m_graphSearch.m_heuristic, h->planner->m_gvd);
+	h->planner->m_propagator = h->propagator;
+	h->planner->m_graphSearch.Initialize(h->propagator, h->planner->m_graphSearch.m_heuristic);
+	// H3: make negative-k reads defined (alias k+numAngular)
+	auto& nh = *h->planner->m_nonHoloHeuristic;
+	const unsigned na = nh.numAngular;
+	for (unsigned i = 0; i < nh.numSpatialX; i++)
+		for (unsigned j = 0; j < nh.numSpatialY; j++) {
+			double* orig = nh.m_values[i][j];
+			double* padded = new double[2 * na];
+			for (unsigned k = 0; k < na; k++) {
+				padded[k] = orig[k];
+				padded[na + k] = orig[k];
+			}
+			h->originalBlocks.push_back(orig);
+			h->paddedBlocks.push_back(padded);
+			nh.m_values[i][j] = padded + na;
+		}
+	return h;
+}
+
+void ref_hybrid_destroy(void* hh)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& nh = *h->planner->m_nonHoloHeuristic;
+	size_t idx = 0;
+	for (unsigned i = 0; i < nh.numSpatialX; i++)
+		for (unsigned j = 0; j < nh.numSpatialY; j++)
+			nh.m_values[i][j] = h->originalBlocks[idx++];
+	for (double* p : h->paddedBlocks)
+		delete[] p;
+	delete h;
+}
+
+void ref_hybrid_table(void* hh, int* dims, double* offsets, double* values)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& nh = *h->planner->m_nonHoloHeuristic;
+	dims[0] = nh.numSpatialX;
+	dims[1] = nh.numSpatialY;
+	dims[2] = nh.numAngular;
+	if (offsets) {
+		offsets[0] = nh.offsetX;
+		offsets[1] = nh.offsetY;
+	}
+	if (values)
+		for (unsigned i = 0; i < nh.numSpatialX; i++)
+			for (unsigned j = 0; j < nh.numSpatialY; j++)
+				for (unsigned k = 0; k < nh.numAngular; k++)
+					values[((size_t)i * nh.numSpatialY + j) * nh.numAngular + k] = nh.m_values[i][j][k];
+}
+
+// Graph search only (wavefront + GVD update + A*), no smoothing: the part of
+// HybridAStar::SearchPath at hybrid_a_star.cpp:248-257.
+// times: [0] wavefront s, [1] gvd s, [2] graph search s
+// Returns status (0 success, -1 failure).
+int ref_hybrid_search(void* hh, const double* start, const double* goal, uint64_t seed, int do_wavefront,
+	double* cost, long* num_expanded, long* num_children, long* num_samples, double* times)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& pl = *h->planner;
+	Pose2d s(start[0], start[1], start[2]), g(goal[0], goal[1], goal[2]);
+	pl.SetInitState(s);
+	pl.SetGoalState(g);
+	SeedRandom(seed);
+	h->propagator->expansions.clear();
+	h->propagator->numChildren = 0;
+	long samplesBefore = h->world->validator->samples;
+	auto t0 = std::chrono::steady_clock::now();
+	if (do_wavefront)
+		pl.m_obstacleHeuristic->Update(pl.m_goal);
+	auto t1 = std::chrono::steady_clock::now();
+	pl.m_gvd->Update();
+	auto t2 = std::chrono::steady_clock::now();
+	pl.m_graphSearch.SetInitState(pl.m_propagator->CreateStateFromPose(pl.m_init));
+	pl.m_graphSearch.SetGoalState(pl.m_propagator->SetGoalState(pl.m_goal));
+	Status st = pl.m_graphSearch.SearchPath();
+	auto t3 = std::chrono::steady_clock::now();
+	pl.m_stats.graphSearchStatus = st;
+	if (cost) *cost = pl.m_graphSearch.GetOptimalCost();
+	if (num_expanded) *num_expanded = (long)h->propagator->expansions.size();
+	if (num_children) *num_children = (long)h->propagator->numChildren;
+	if (num_samples) *num_samples = h->world->validator->samples - samplesBefore;
+	if (times) {
+		times[0] = std::chrono::duration<double>(t1 - t0).count();
+		times[1] = std::chrono::duration<double>(t2 - t1).count();
+		times[2] = std::chrono::duration<double>(t3 - t2).count();
+	}
+	return (int)st;
+}
+
+// Expansion-ordered node records of the last search: 4 ints + 3 doubles each
+long ref_hybrid_expansions(void* hh, long cap, int* keys /*4*cap: ix,iy,ik,dir*/, double* poses /*3*cap*/)
+{
+	auto* h = (RefHybrid*)hh;
+	long n = (long)h->propagator->expansions.size();
+	for (long i = 0; i < n && i < cap; i++) {
+		const auto& e = h->propagator->expansions[i];
+		if (keys) {
+			keys[4 * i + 0] = e.ix;
+			keys[4 * i + 1] = e.iy;
+			keys[4 * i + 2] = e.ik;
+			keys[4 * i + 3] = e.direction;
+		}
+		if (poses) {
+			poses[3 * i + 0] = e.x;
+			poses[3 * i + 1] = e.y;
+			poses[3 * i + 2] = e.theta;
+		}
+	}
+	return n;
+}
+
+// Solution of the last search as the node chain root..goal: continuous poses + per-action kind
+// (0 constant-steer, 1 Reeds-Shepp) and length.  Returns number of states (0 when no solution).
+long ref_hybrid_solution(void* hh, long cap, double* poses, int* kinds, double* lengths)
+{
+	auto* h = (RefHybrid*)hh;
+	auto states = h->planner->m_graphSearch.GetPath();
+	auto actions = h->planner->m_graphSearch.GetActions();
+	long n = (long)states.size();
+	for (long i = 0; i < n && i < cap; i++) {
+		poses[3 * i + 0] = states[i].continuousPose.x();
+		poses[3 * i + 1] = states[i].continuousPose.y();
+		poses[3 * i + 2] = states[i].continuousPose.theta;
+		if (i > 0) {
+			auto& path = actions[i - 1].path;
+			if (kinds) kinds[i] = dynamic_cast<PathReedsShepp*>(path.get()) ? 1 : 0;
+			if (lengths) lengths[i] = path->GetLength();
+		} else {
+			if (kinds) kinds[0] = -1;
+			if (lengths) lengths[0] = 0.0;
+		}
+	}
+	return n;
+}
+
+// Full reference SearchPath (wavefront + GVD + A* + resampling + smoothing): timing only.
+int ref_hybrid_search_full(void* hh, const double* start, const double* goal, uint64_t seed, double* seconds, long* path_len)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& pl = *h->planner;
+	pl.SetInitState(Pose2d(start[0], start[1], start[2]));
+	pl.SetGoalState(Pose2d(goal[0], goal[1], goal[2]));
+	SeedRandom(seed);
+	h->propagator->record = false;
+	auto t0 = std::chrono::steady_clock::now();
+	Status st = pl.SearchPath();
+	*seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	h->propagator->record = true;
+	if (path_len) *path_len = (long)pl.GetPath().size();
+	return (int)st;
+}
+
+// One call of StatePropagator::GetNeighborStates (A1) on an arbitrary parent, for unit-level
+// parity of the successor kernel.  The wavefront for `goal` must already be current
+// (call ref_hybrid_prepare_goal).  Children: pose(3), key(3), direction, cost, kind.
+void ref_hybrid_prepare_goal(void* hh, const double* goal)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& pl = *h->planner;
+	Pose2d g(goal[0], goal[1], goal[2]);
+	pl.SetGoalState(g);
+	pl.m_obstacleHeuristic->Update(g);
+	pl.m_gvd->Update();
+	auto goalState = pl.m_propagator->SetGoalState(g);
+	pl.m_graphSearch.SetGoalState(goalState);
+	pl.m_graphSearch.m_heuristic->SetGoal(goalState);
+}
+
+int ref_hybrid_expand(void* hh, const double* parent, uint64_t seed, double* poses /*3*11*/, int* keys /*3*11*/,
+	int* directions, double* costs, int* kinds, double* heuristics, double* parent_heuristic)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& pl = *h->planner;
+	Pose2d p;
+	p.position = Point2d(parent[0], parent[1]);
+	p.theta = parent[2];
+	auto state = pl.m_propagator->CreateStateFromPose(p);
+	SeedRandom(seed);
+	bool rec = h->propagator->record;
+	h->propagator->record = false;
+	auto children = h->propagator->GetNeighborStates(state);
+	h->propagator->record = rec;
+	if (parent_heuristic)
+		*parent_heuristic = pl.m_graphSearch.m_heuristic->GetHeuristicValue(state);
+	int n = 0;
+	for (auto& [child, action, cost] : children) {
+		poses[3 * n + 0] = child.continuousPose.x();
+		poses[3 * n + 1] = child.continuousPose.y();
+		poses[3 * n + 2] = child.continuousPose.theta;
+		keys[3 * n + 0] = child.discretePose.x();
+		keys[3 * n + 1] = child.discretePose.y();
+		keys[3 * n + 2] = child.discretePose.theta;
+		directions[n] = (int)child.direction;
+		costs[n] = cost;
+		kinds[n] = dynamic_cast<PathReedsShepp*>(action.path.get()) ? 1 : 0;
+		if (heuristics)
+			heuristics[n] = pl.m_graphSearch.m_heuristic->GetHeuristicValue(child);
+		n++;
+	}
+	return n;
+}
+
+// Combined heuristic (max of non-holonomic table and obstacle wavefront) for arbitrary poses.
+void ref_hybrid_heuristic(void* hh, long n, const double* poses, double* values, double* nonholo, double* obst)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& pl = *h->planner;
+	for (long i = 0; i < n; i++) {
+		Pose2d p;
+		p.position = Point2d(poses[3 * i], poses[3 * i + 1]);
+		p.theta = poses[3 * i + 2];
+		auto state = pl.m_propagator->CreateStateFromPose(p);
+		if (values) values[i] = pl.m_graphSearch.m_heuristic->GetHeuristicValue(state);
+		if (nonholo) nonholo[i] = pl.m_nonHoloHeuristic->GetHeuristicValue(p);
+		if (obst) obst[i] = pl.m_obstacleHeuristic->GetHeuristicValue(p);
+	}
+}
+
+// ---------------------------------------------------------------------------------------------
+// Grid A* (BASELINE config C1, CPU-only): Euclidean step cost and heuristic as C++ functors,
+// like interfaces/python/scripts/example_a_star_grid.py:46-52 does through Python callbacks.
+int ref_astar_n2(void* hw, int r0, int c0, int r1, int c1, double* cost, long* explored, double* seconds,
+	long cap, int* path_cells, long* path_len)
+{
+	auto* w = (RefWorld*)hw;
+	auto euclid = [](const GridCellPosition& a, const GridCellPosition& b) {
+		double dr = a.row - b.row, dc = a.col - b.col;
+		return std::sqrt(dr * dr + dc * dc);
+	};
+	Ref<OccupancyMap> map = w->map;
+	auto propagator = makeRef<AStarStatePropagatorFcnN2>(map, euclid);
+	auto heuristic = makeRef<AStarHeuristicFcnN2>(euclid);
+	AStarN2 astar;
+	astar.Initialize(propagator, heuristic);
+	astar.SetInitState(GridCellPosition(r0, c0));
+	astar.SetGoalState(GridCellPosition(r1, c1));
+	auto t0 = std::chrono::steady_clock::now();
+	Status st = astar.SearchPath();
+	*seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	*cost = astar.GetOptimalCost();
+	*explored = (long)astar.GetExploredStates().size();
+	auto path = astar.GetPath();
+	*path_len = (long)path.size();
+	for (long i = 0; i < (long)path.size() && i < cap; i++) {
+		path_cells[2 * i] = path[i].row;
+		path_cells[2 * i + 1] = path[i].col;
+	}
+	return (int)st;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tree / kNN (A10) through the reference's own utils/tree.h on top of the brute-force flann
+// stand-in (oracle/shim/flann/flann.hpp).  2-D points (the only instantiation that compiles
+// unmodified).
+void ref_tree_knn_r2(long npoints, const double* points, long nqueries, const double* queries, int k, int* indices)
+{
+	using VertexTree = Tree<Point2d, 2>;
+	VertexTree tree;
+	std::unordered_map<VertexTree::Node*, int> index;
+	VertexTree::Node* prev = tree.CreateRootNode(Point2d(points[0], points[1]));
+	index[prev] = 0;
+	for (long i = 1; i < npoints; i++) {
+		auto* node = tree.Extend(Point2d(points[2 * i], points[2 * i + 1]), prev);
+		if (index.find(node) == index.end())
+			index[node] = (int)i;
+		prev = node;
+	}
+	for (long q = 0; q < nqueries; q++) {
+		auto near = tree.GetNearestNodes(Point2d(queries[2 * q], queries[2 * q + 1]), k);
+		for (int j = 0; j < k; j++)
+			indices[q * k + j] = j < (int)near.size() ? index[near[j]] : -1;
+	}
+}
+
+// RRT / RRT* in R^2 with the reference templates (algo/rrt.h, algo/rrt_star.h) -- the aliases
+// the reference itself instantiates (RRTR2, RRTStarR2).  Free-space validator as in
+// planner/tests/test_rrt_star.cpp.  Returns status; nodes = tree size.
+int ref_rrtstar_r2_free(const double* lb, const double* ub, const double* start, const double* goal, uint64_t seed,
+	unsigned maxIteration, unsigned maxNodes, double maxConnectionDistance, double goalBias, int star,
+	long* nodes, long cap, double* path_xy, long* path_len)
+{
+	auto space = makeRef<StateSpaceR2>(std::array<Point2d, 2> { Point2d(lb[0], lb[1]), Point2d(ub[0], ub[1]) });
+	Ref<StateValidator<Point2d, 2, double>> validator = makeRef<StateValidatorFree<Point2d, 2, double>>(space);
+	Ref<PathConnection<Point2d>> conn = makeRef<PathConnectionR2>();
+	SeedRandom(seed);
+	std::vector<Point2d> path;
+	Status st;
+	if (star) {
+		RRTStarR2 rrt(space, validator, conn);
+		RRTStarParameters p;
+		p.maxIteration = maxIteration;
+		p.maxNumberTreeNode = maxNodes;
+		p.maxConnectionDistance = maxConnectionDistance;
+		p.goalBias = goalBias;
+		rrt.SetParameters(p);
+		rrt.SetInitState(Point2d(start[0], start[1]));
+		rrt.SetGoalState(Point2d(goal[0], goal[1]));
+		SeedRandom(seed);
+		st = rrt.SearchPath();
+		*nodes = (long)rrt.m_tree.Size();
+		path = rrt.GetPath();
+	} else {
+		RRTR2 rrt(space, validator, conn);
+		RRTParameters p;
+		p.maxIteration = maxIteration;
+		p.maxNumberTreeNode = maxNodes;
+		p.maxConnectionDistance = maxConnectionDistance;
+		p.goalBias = goalBias;
+		rrt.SetParameters(p);
+		rrt.SetInitState(Point2d(start[0], start[1]));
+		rrt.SetGoalState(Point2d(goal[0], goal[1]));
+		SeedRandom(seed);
+		st = rrt.SearchPath();
+		*nodes = (long)rrt.m_tree.Size();
+		path = rrt.GetPath();
+	}
+	*path_len = (long)path.size();
+	for (long i = 0; i < (long)path.size() && i < cap; i++) {
+		path_xy[2 * i] = path[i].x();
+		path_xy[2 * i + 1] = path[i].y();
+	}
+	return (int)st;
+}
+
+// Raw draws from the reference RNG wrapper after seeding (pins H4: one 64-bit draw per sample,
+// SampleUniform = lb + (ub-lb)*u).
+void ref_random_uniform(uint64_t seed, long n, double lb, double ub, double* out)
+{
+	SeedRandom(seed);
+	for (long i = 0; i < n; i++)
+		out[i] = Random<double>::SampleUniform(lb, ub);
+}
+
+} // extern "C"

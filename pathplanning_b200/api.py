@@ -1,0 +1,244 @@
+"""numpy-level host API over the C ABI (include/ppx.h).
+
+Mirrors, batched, the reference interfaces on the hot path:
+  StateValidatorOccupancyMap::IsStateValid / IsPathValid  (state_validator_occupancy_map.cpp:15-71)
+  ReedsShepp::Solver::GetOptimalPath / GetShortestPath     (geometry/reeds_shepp.cpp:608-683)
+  PathConnectionReedsShepp::Connect + IsPathValid          (paths/path_reeds_shepp.cpp:174-179)
+Everything here is argument marshalling; the arithmetic is in the CUDA kernels.
+"""
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from .lib import ppx, MapDescC, ValidatorParamsC, RSCostParamsC
+
+RS_EDGE = np.dtype([("start", "<f8", (3,)), ("len", "<f8", (5,)), ("code", "<u8")], align=True)
+CSTEER_EDGE = np.dtype([("start", "<f8", (3,)), ("length", "<f8"), ("beta", "<f8"), ("cos_beta", "<f8"),
+                        ("dtheta_ddist", "<f8"), ("direction", "<i4"), ("_pad", "<i4")], align=True)
+LINE_EDGE = np.dtype([("from", "<f8", (3,)), ("to", "<f8", (3,))], align=True)
+assert RS_EDGE.itemsize == 72 and CSTEER_EDGE.itemsize == 64 and LINE_EDGE.itemsize == 48
+
+
+class PPXError(RuntimeError):
+    pass
+
+
+@dataclass
+class MapDesc:
+    rows: int
+    cols: int
+    resolution: float
+    world_origin: tuple
+    local_origin: tuple = (0.0, 0.0)
+    lb: tuple = (-1.0, -1.0, -np.pi)
+    ub: tuple = (1.0, 1.0, np.pi)
+
+    def to_c(self):
+        d = MapDescC()
+        d.rows, d.cols, d.resolution = int(self.rows), int(self.cols), float(self.resolution)
+        d.world_origin[:] = self.world_origin
+        d.local_origin[:] = self.local_origin
+        d.lb[:] = self.lb
+        d.ub[:] = self.ub
+        return d
+
+
+@dataclass
+class ValidatorParams:
+    """StateValidatorOccupancyMap public fields (state_validator_occupancy_map.h:27-28)."""
+    min_safe_radius: float = 1.0
+    min_path_interpolation_distance: float = 0.1
+
+    def to_c(self):
+        return ValidatorParamsC(self.min_safe_radius, self.min_path_interpolation_distance)
+
+
+@dataclass
+class RSCostParams:
+    min_turning_radius: float = 1.0
+    reverse_cost_multiplier: float = 1.0
+    forward_cost_multiplier: float = 1.0
+    direction_switching_cost: float = 0.0
+    shortest: int = 0
+
+    def to_c(self):
+        return RSCostParamsC(self.min_turning_radius, self.reverse_cost_multiplier, self.forward_cost_multiplier,
+                             self.direction_switching_cost, self.shortest)
+
+
+def make_rs_edges(starts, steer, direction, lengths):
+    """Pack (n,3) starts, (n,5) steer / direction / length arrays into ppx_rs_edge records."""
+    n = len(starts)
+    e = np.zeros(n, dtype=RS_EDGE)
+    e["start"] = starts
+    e["len"] = lengths
+    code = np.zeros(n, dtype=np.uint64)
+    steer = np.asarray(steer, dtype=np.uint64)
+    direction = np.asarray(direction, dtype=np.uint64)
+    for i in range(5):
+        code |= ((steer[:, i] & 3) | ((direction[:, i] & 3) << 2)) << np.uint64(4 * i)
+    e["code"] = code
+    return e
+
+
+def make_csteer_edges(starts, steering, length, direction, wheelbase=2.6, rear_to_center=0.0):
+    """Host half of KinematicBicycleModel::ConstantSteer (kinematic_bicycle_model.cpp:14-20):
+    the per-steering constants are evaluated here with the host libm, like the reference does."""
+    n = len(starts)
+    e = np.zeros(n, dtype=CSTEER_EDGE)
+    e["start"] = starts
+    e["length"] = length
+    tan_s = np.tan(np.asarray(steering, dtype=np.float64))
+    beta = np.arctan(rear_to_center * tan_s / wheelbase)
+    cos_beta = np.cos(beta)
+    e["beta"] = beta
+    e["cos_beta"] = cos_beta
+    e["dtheta_ddist"] = cos_beta * tan_s / wheelbase
+    e["direction"] = direction
+    return e
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f64(a, shape_last=3):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if shape_last and (a.ndim != 2 or a.shape[1] != shape_last):
+        raise ValueError(f"expected (n,{shape_last}) float64, got {a.shape}")
+    return a
+
+
+class Context:
+    """One ppx_ctx (one GPU, one stream)."""
+
+    def __init__(self, device=0):
+        h = C.c_void_p()
+        rc = ppx.ppx_ctx_create(int(device), C.byref(h))
+        if rc != 0:
+            raise PPXError(f"ppx_ctx_create({device}) failed with {rc}: no usable CUDA device; "
+                           "libppx has no CPU fallback")
+        self._h = h
+        self.device = device
+        self.map = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            ppx.ppx_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise PPXError(f"ppx error {rc}: {ppx.ppx_last_error(self._h).decode()}")
+
+    @property
+    def handle(self):
+        return self._h
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(ppx.ppx_ctx_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
+
+    def synchronize(self):
+        self._check(ppx.ppx_ctx_synchronize(self._h))
+
+    @property
+    def launch_count(self):
+        return int(ppx.ppx_ctx_launch_count(self._h))
+
+    # ---- world model ------------------------------------------------------------------------
+    def upload_map(self, desc: MapDesc, sqdist=None, occupancy=None, pathcost=None):
+        cells = desc.rows * desc.cols
+        keep = []
+        for name, a, dt in (("sqdist", sqdist, np.int32), ("occupancy", occupancy, np.int32), ("pathcost", pathcost, np.float32)):
+            if a is not None:
+                a = np.ascontiguousarray(a, dtype=dt).reshape(-1)
+                if a.size != cells:
+                    raise ValueError(f"{name} has {a.size} cells, expected {cells}")
+            keep.append(a)
+        d = desc.to_c()
+        self._check(ppx.ppx_map_upload(self._h, C.byref(d), _ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2])))
+        self.map = desc
+
+    # ---- A7 -----------------------------------------------------------------------------------
+    def is_state_valid(self, poses, vp: ValidatorParams):
+        poses = _f64(poses)
+        out = np.empty(len(poses), dtype=np.uint8)
+        v = vp.to_c()
+        self._check(ppx.ppx_is_state_valid(self._h, len(poses), _ptr(poses), C.byref(v), _ptr(out)))
+        return out.astype(bool)
+
+    def check_edges_rs(self, edges, min_turning_radius, vp: ValidatorParams, want_samples=False):
+        edges = np.ascontiguousarray(edges, dtype=RS_EDGE)
+        n = len(edges)
+        valid = np.empty(n, dtype=np.uint8)
+        last = np.empty(n, dtype=np.float32)
+        samples = np.empty(n, dtype=np.uint32) if want_samples else None
+        v = vp.to_c()
+        self._check(ppx.ppx_check_edges_rs(self._h, n, _ptr(edges), float(min_turning_radius), C.byref(v),
+                                           _ptr(valid), _ptr(last), _ptr(samples)))
+        return (valid.astype(bool), last, samples) if want_samples else (valid.astype(bool), last)
+
+    def check_edges_csteer(self, edges, vp: ValidatorParams, want_final=False):
+        edges = np.ascontiguousarray(edges, dtype=CSTEER_EDGE)
+        n = len(edges)
+        valid = np.empty(n, dtype=np.uint8)
+        last = np.empty(n, dtype=np.float32)
+        final = np.empty((n, 3), dtype=np.float64) if want_final else None
+        v = vp.to_c()
+        self._check(ppx.ppx_check_edges_csteer(self._h, n, _ptr(edges), C.byref(v), _ptr(valid), _ptr(last), _ptr(final)))
+        return (valid.astype(bool), last, final) if want_final else (valid.astype(bool), last)
+
+    def check_edges_line(self, edges, vp: ValidatorParams):
+        edges = np.ascontiguousarray(edges, dtype=LINE_EDGE)
+        n = len(edges)
+        valid = np.empty(n, dtype=np.uint8)
+        last = np.empty(n, dtype=np.float32)
+        v = vp.to_c()
+        self._check(ppx.ppx_check_edges_line(self._h, n, _ptr(edges), C.byref(v), _ptr(valid), _ptr(last)))
+        return valid.astype(bool), last
+
+    # ---- A3 / A4 ------------------------------------------------------------------------------
+    def rs_solve(self, starts, goals, cp: RSCostParams):
+        """-> dict(edges, word, length, cost)"""
+        starts, goals = _f64(starts), _f64(goals)
+        n = len(starts)
+        edges = np.zeros(n, dtype=RS_EDGE)
+        word = np.empty(n, dtype=np.int32)
+        length = np.empty(n, dtype=np.float64)
+        cost = np.empty(n, dtype=np.float32)
+        c = cp.to_c()
+        self._check(ppx.ppx_rs_solve(self._h, n, _ptr(starts), _ptr(goals), C.byref(c), _ptr(edges), _ptr(word),
+                                     _ptr(length), _ptr(cost)))
+        return dict(edges=edges, word=word, length=length, cost=cost)
+
+    def connect_check_rs(self, starts, goals, cp: RSCostParams, vp: ValidatorParams):
+        """-> dict(valid, last, word, length, cost)"""
+        starts, goals = _f64(starts), _f64(goals)
+        n = len(starts)
+        valid = np.empty(n, dtype=np.uint8)
+        last = np.empty(n, dtype=np.float32)
+        word = np.empty(n, dtype=np.int32)
+        length = np.empty(n, dtype=np.float64)
+        cost = np.empty(n, dtype=np.float32)
+        c, v = cp.to_c(), vp.to_c()
+        self._check(ppx.ppx_connect_check_rs(self._h, n, _ptr(starts), _ptr(goals), C.byref(c), C.byref(v), _ptr(valid),
+                                             _ptr(last), _ptr(word), _ptr(length), _ptr(cost)))
+        return dict(valid=valid.astype(bool), last=last, word=word, length=length, cost=cost)
+
+    def rs_interpolate(self, edges, min_turning_radius, ratios):
+        edges = np.ascontiguousarray(edges, dtype=RS_EDGE)
+        ratios = np.ascontiguousarray(ratios, dtype=np.float64)
+        n = len(edges)
+        if ratios.ndim == 1:
+            ratios = np.tile(ratios, (n, 1))
+        nr = ratios.shape[1]
+        poses = np.empty((n, nr, 3), dtype=np.float64)
+        self._check(ppx.ppx_rs_interpolate(self._h, n, _ptr(edges), float(min_turning_radius), nr, _ptr(ratios), _ptr(poses)))
+        return poses

@@ -1,0 +1,94 @@
+// Host-side context shared by the translation units of libppx.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+#include "ppx.h"
+#include "ppx_device.cuh"
+
+struct ppx_ctx {
+	int device = 0;
+	cudaStream_t own_stream = nullptr;
+	cudaStream_t stream = nullptr;
+	int num_sms = 0;
+	std::string error;
+	int64_t launches = 0;
+
+	// world model
+	bool has_map = false;
+	ppx_map_desc desc {};
+	int32_t* d_sqdist = nullptr;
+	int32_t* d_occupancy = nullptr;
+	float* d_pathcost = nullptr;
+	float* d_clearance = nullptr;
+	size_t cells = 0;
+
+	// grow-only device scratch for the host-buffer entry points
+	struct Scratch {
+		void* ptr = nullptr;
+		size_t bytes = 0;
+	};
+	Scratch scratch[8];
+
+	// non-holonomic table (A9)
+	bool has_nonholo = false;
+	double* d_nonholo = nullptr;
+
+	// resident wavefronts (A8)
+	int32_t wf_slots = 0;
+	float* d_wf_cost = nullptr;
+	uint8_t* d_wf_explored = nullptr;
+	double* d_wf_goals = nullptr;
+
+	ppx::MapDev map_dev() const
+	{
+		ppx::MapDev m;
+		m.rows = desc.rows;
+		m.cols = desc.cols;
+		m.res = desc.resolution;
+		m.resd = (double)desc.resolution;
+		m.ox = desc.world_origin[0];
+		m.oy = desc.world_origin[1];
+		m.lox = desc.local_origin[0];
+		m.loy = desc.local_origin[1];
+		m.lbx = desc.lb[0]; m.lby = desc.lb[1]; m.lbt = desc.lb[2];
+		m.ubx = desc.ub[0]; m.uby = desc.ub[1]; m.ubt = desc.ub[2];
+		m.clearance = d_clearance;
+		m.occupancy = d_occupancy;
+		m.pathcost = d_pathcost;
+		return m;
+	}
+};
+
+int ppx_fail(ppx_ctx* ctx, int code, const char* fmt, ...);
+int ppx_scratch(ppx_ctx* ctx, int slot, size_t bytes, void** out);
+
+#define PPX_CUDA(ctx, call)                                                                           \
+	do {                                                                                              \
+		cudaError_t e_ = (call);                                                                      \
+		if (e_ != cudaSuccess)                                                                        \
+			return ppx_fail(ctx, PPX_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+	} while (0)
+
+#define PPX_CHECK(expr)      \
+	do {                     \
+		int rc_ = (expr);    \
+		if (rc_ != PPX_OK)   \
+			return rc_;      \
+	} while (0)
+
+#define PPX_REQUIRE(ctx, cond, msg) \
+	do {                            \
+		if (!(cond))                \
+			return ppx_fail(ctx, PPX_ERR_INVALID, "%s", msg); \
+	} while (0)
+
+#define PPX_LAUNCHED(ctx)                                                                             \
+	do {                                                                                              \
+		(ctx)->launches++;                                                                            \
+		cudaError_t e_ = cudaGetLastError();                                                          \
+		if (e_ != cudaSuccess)                                                                        \
+			return ppx_fail(ctx, PPX_ERR_CUDA, "%s:%d launch: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+	} while (0)

@@ -1,0 +1,678 @@
+// Device-side restatement of the reference's geometry / path / validator arithmetic.
+// Every function cites the reference lines it follows and keeps the reference's operation ORDER
+// and its float/double mixing, because collision verdicts and `last` ratios are compared
+// bit-for-bit with the reference.  Compiled with -fmad=false (no FMA contraction).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "ppx.h"
+
+#define PPX_PI 3.14159265358979323846
+#define PPX_PI_2 1.57079632679489661923
+#define PPX_2PI (2 * PPX_PI)
+#define PPX_INF (__longlong_as_double(0x7ff0000000000000LL))
+
+namespace ppx {
+
+// World model as the kernels see it (passed by value as a kernel parameter).
+struct MapDev {
+	int rows, cols;
+	float res; // OccupancyMap::resolution
+	double resd; // (double)res: the reference divides a double by the float field
+	double ox, oy; // m_worldGridOrigin
+	double lox, loy; // m_localOrigin
+	double lbx, lby, lbt, ubx, uby, ubt; // StateSpaceSE2::bounds
+	const float* __restrict__ clearance; // (float)(sqrt((double)sqdist) * res), gvd.h:38
+	const int* __restrict__ occupancy;
+	const float* __restrict__ pathcost;
+};
+
+struct Pose {
+	double x, y, th;
+};
+
+// Pose2<double>::WrapTheta, geometry/2dplane.h:36-45.  Non-finite / astronomically large
+// headings would spin forever in the reference; the kernel returns them unchanged instead.
+__device__ __forceinline__ double wrap_theta(double t)
+{
+	if (!(fabs(t) < 1e15))
+		return t;
+	while (t > PPX_PI)
+		t -= 2 * PPX_PI;
+	while (t < -PPX_PI)
+		t += 2 * PPX_PI;
+	return t;
+}
+
+// static_cast<int>(double) as x86-64 cvttsd2si does it (out of range / NaN -> INT_MIN),
+// occupancy_map.h:108-109.
+__device__ __forceinline__ int trunc_i32(double v)
+{
+	if (!(v > -2147483649.0 && v < 2147483648.0))
+		return INT_MIN;
+	return __double2int_rz(v);
+}
+
+// std::min(a,b) / std::max(a,b) with the library's comparison direction (matters for NaN).
+__device__ __forceinline__ double std_min(double a, double b) { return (b < a) ? b : a; }
+__device__ __forceinline__ float std_minf(float a, float b) { return (b < a) ? b : a; }
+__device__ __forceinline__ float std_maxf(float a, float b) { return (a < b) ? b : a; }
+
+// Maths::Modulo, utils/maths.h:9-16
+__device__ __forceinline__ double modulo(double in, double mod)
+{
+	double out = fmod(in, mod);
+	if (out < 0)
+		out += mod;
+	return out;
+}
+
+// StateValidatorOccupancyMap::IsStateValid, state_validator_occupancy_map.cpp:15-26.
+// Returns validity; *dist receives the clearance of the pose's cell when it is inside the map.
+__device__ __forceinline__ bool is_state_valid(const MapDev& m, double x, double y, double th, float minSafeRadius, float* dist)
+{
+	// Pose2d localState(WorldPositionToLocalPosition(position), theta): the ctor wraps theta
+	double lx = x - m.lox;
+	double ly = y - m.loy;
+	double lth = wrap_theta(th);
+	// WorldPositionToGridCell(position) (bounded), occupancy_map.h:106-117,180-183
+	int row = trunc_i32((x - m.ox) / m.resd);
+	int col = trunc_i32((y - m.oy) / m.resd);
+	bool inside = row >= 0 && row < m.rows && col >= 0 && col < m.cols;
+	// StateSpaceSE2::ValidateBounds, state_space_se2.cpp:15-25
+	bool inBounds = !(lx < m.lbx || lx > m.ubx) && !(ly < m.lby || ly > m.uby) && !(lth < m.lbt || lth > m.ubt);
+	if (!inBounds || !inside)
+		return false;
+	float d = __ldg(m.clearance + (size_t)row * m.cols + col);
+	*dist = d;
+	return d >= minSafeRadius;
+}
+
+// The step of IsPathValid after a valid sample, state_validator_occupancy_map.cpp:54-65.
+__device__ __forceinline__ double next_step(const MapDev& m, double x, double y, float distance, float minSafeRadius, float minStep)
+{
+	// std::min({a,b,c,d}) keeps the first element unless a later one compares less
+	double b0 = x - m.lbx;
+	double b1 = m.ubx - x;
+	double b2 = y - m.lby;
+	double b3 = m.uby - y;
+	double mn = b0;
+	if (b1 < mn) mn = b1;
+	if (b2 < mn) mn = b2;
+	if (b3 < mn) mn = b3;
+	float distToMapBorder = (float)mn;
+	float deltaLength = distance - minSafeRadius;
+	deltaLength = std_minf(deltaLength, distToMapBorder);
+	return (double)std_maxf(deltaLength, minStep);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Reeds-Shepp path (paths/path_reeds_shepp.cpp)
+
+struct RSSeg {
+	double len[5];
+	uint32_t code; // 4 bits per motion: steer | dir<<2
+	__device__ __forceinline__ int steer(int i) const { return (code >> (4 * i)) & 3; }
+	__device__ __forceinline__ int dir(int i) const { return (code >> (4 * i + 2)) & 3; }
+	// Motion::IsValid, reeds_shepp.cpp:305-308
+	__device__ __forceinline__ bool valid(int i) const { return i < 5 && len[i] != PPX_INF && dir(i) != 2; }
+};
+
+// PathSegment::m_length as AddMotion accumulates it (reeds_shepp.cpp:319-335)
+__device__ __forceinline__ double rs_total_length(const RSSeg& s)
+{
+	double total = 0.0;
+	for (int i = 0; i < 5; i++) {
+		if (!s.valid(i))
+			break;
+		total += fabs(s.len[i]);
+	}
+	return total;
+}
+
+// Pose2 operator+ (2dplane.h:49-62) with the rotation of the left pose cached (sL, cL).
+__device__ __forceinline__ Pose pose_compose(const Pose& l, double sL, double cL, double rx, double ry, double rth)
+{
+	Pose out;
+	out.x = (cL * rx + (-sL) * ry) + l.x;
+	out.y = (sL * rx + cL * ry) + l.y;
+	out.th = wrap_theta(wrap_theta(l.th + rth));
+	return out;
+}
+
+// PathReedsShepp::Straight / Turn (path_reeds_shepp.cpp:121-151) applied to a knot pose whose
+// sin/cos are cached.  `amount` = motion.length * motionRatio.
+__device__ __forceinline__ Pose rs_advance(const Pose& k, double sK, double cK, int steer, int dir, double amount, double r)
+{
+	if (steer == 1) { // Straight
+		double length = amount;
+		if (dir == 1)
+			length = -length;
+		length *= r;
+		Pose e;
+		e.x = k.x + length * cK;
+		e.y = k.y + length * sK;
+		e.th = wrap_theta(k.th); // Pose2d ctor
+		return e;
+	}
+	double turnAngle = amount;
+	if (dir == 1)
+		turnAngle = -turnAngle;
+	double phi = turnAngle / 2;
+	double sinPhi, cosPhi;
+	sincos(phi, &sinPhi, &cosPhi);
+	double L = 2 * sinPhi * r;
+	double x = L * cosPhi;
+	double y = L * sinPhi;
+	if (steer == 2) {
+		y *= -1;
+		turnAngle *= -1;
+	}
+	// start + Pose2d(x, y, turnAngle): the temporary's ctor wraps turnAngle first
+	return pose_compose(k, sK, cK, x, y, wrap_theta(turnAngle));
+}
+
+// Incremental walker over an RS path.  PathReedsShepp::Interpolate (path_reeds_shepp.cpp:12-47)
+// re-walks all motions from the start for every ratio; motions that end before the target are
+// always applied with motionRatio == 1.0 exactly, so their end poses ("knots") do not depend on
+// the target and can be kept while targets are non-decreasing ("knot caching").
+struct RSWalker {
+	Pose k; // pose at the start of motion m
+	double sK, cK; // sin/cos of k.th
+	double lenAcc; // `length` accumulated over completed motions
+	int m;
+
+	__device__ __forceinline__ void init(const Pose& start)
+	{
+		k = start;
+		sincos(k.th, &sK, &cK);
+		lenAcc = 0.0;
+		m = 0;
+	}
+
+	// Pose at `target` = ratio * totalLength (targets must be non-decreasing across calls).
+	__device__ __forceinline__ Pose at(const RSSeg& s, double r, double target)
+	{
+		while (true) {
+			if (!s.valid(m))
+				return k; // ran off the end: interp is the end of the last applied motion
+			double motionLength = s.len[m] * r;
+			if (motionLength == 0) {
+				m++;
+				continue;
+			}
+			double motionRatio = (target - lenAcc) / motionLength;
+			motionRatio = std_min(motionRatio, 1.0);
+			Pose p = rs_advance(k, sK, cK, s.steer(m), s.dir(m), s.len[m] * motionRatio, r);
+			double lenEnd = lenAcc + motionLength;
+			if (lenEnd >= target)
+				return p;
+			k = p;
+			sincos(k.th, &sK, &cK);
+			lenAcc = lenEnd;
+			m++;
+		}
+	}
+};
+
+// StateValidatorOccupancyMap::IsPathValid on a PathReedsShepp,
+// state_validator_occupancy_map.cpp:28-71.
+__device__ __forceinline__ bool rs_is_path_valid(const MapDev& map, const Pose& start, const RSSeg& seg, double r,
+	float minSafeRadius, float minStep, float* last, unsigned* samples)
+{
+	const double pathLength = rs_total_length(seg) * r; // PathSegment::GetLength(r)
+	unsigned ns = 0;
+	float dist = 0.0f;
+	if (pathLength == 0.0) {
+		*last = 1.0f;
+		bool ok = is_state_valid(map, start.x, start.y, start.th, minSafeRadius, &dist);
+		if (samples) *samples = 1;
+		return ok;
+	}
+	RSWalker w;
+	w.init(start);
+	double lastValidLength = 0.0;
+	double length = 0.0;
+	bool ok = true;
+	while (length < pathLength) {
+		double ratio = length / pathLength;
+		Pose p = w.at(seg, r, ratio * pathLength);
+		ns++;
+		if (!is_state_valid(map, p.x, p.y, p.th, minSafeRadius, &dist)) {
+			*last = (float)(lastValidLength / pathLength);
+			ok = false;
+			break;
+		}
+		lastValidLength = length;
+		length += next_step(map, p.x, p.y, dist, minSafeRadius, minStep);
+	}
+	if (ok)
+		*last = 1.0f;
+	if (samples) *samples = ns;
+	return ok;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Constant-steer primitive (paths/path_constant_steer.cpp, models/kinematic_bicycle_model.cpp:5-32)
+
+struct CSteer {
+	Pose start;
+	double length, beta, cosBeta, kappa;
+	int dir;
+	double sB0, cB0; // sin/cos(beta + start.th), cached
+	bool curved; // abs(DthetaDdist) > 1e-9
+	double sT0, cT0; // sin/cos(start.th) for the straight branch
+
+	__device__ __forceinline__ void init(const ppx_csteer_edge& e)
+	{
+		start = { e.start[0], e.start[1], e.start[2] };
+		length = e.length;
+		beta = e.beta;
+		cosBeta = e.cos_beta;
+		kappa = e.dtheta_ddist;
+		dir = e.direction;
+		curved = fabs(kappa) > 1e-9;
+		if (curved)
+			sincos(beta + start.th, &sB0, &cB0);
+		else
+			sincos(start.th, &sT0, &cT0);
+	}
+
+	// PathConstantSteer::Interpolate -> KinematicBicycleModel::ConstantSteer(m_init, steering, m_length*ratio, dir)
+	__device__ __forceinline__ Pose at_dist(double dist) const
+	{
+		if (dir == 1)
+			dist = -dist;
+		dist = dist / cosBeta;
+		Pose to = start;
+		if (curved) {
+			to.th += dist * kappa;
+			double s1, c1;
+			sincos(beta + to.th, &s1, &c1);
+			to.x += 1 / kappa * (s1 - sB0);
+			to.y += 1 / kappa * (-c1 + cB0);
+		} else {
+			to.x += dist * cT0;
+			to.y += dist * sT0;
+		}
+		return to;
+	}
+	__device__ __forceinline__ Pose at(double ratio) const { return at_dist(length * ratio); }
+};
+
+__device__ __forceinline__ bool csteer_is_path_valid(const MapDev& map, const CSteer& p, float minSafeRadius, float minStep,
+	float* last, unsigned* samples)
+{
+	const double pathLength = p.length;
+	float dist = 0.0f;
+	unsigned ns = 0;
+	if (pathLength == 0.0) {
+		*last = 1.0f;
+		if (samples) *samples = 1;
+		return is_state_valid(map, p.start.x, p.start.y, p.start.th, minSafeRadius, &dist);
+	}
+	double lastValidLength = 0.0, length = 0.0;
+	bool ok = true;
+	while (length < pathLength) {
+		Pose s = p.at(length / pathLength);
+		ns++;
+		if (!is_state_valid(map, s.x, s.y, s.th, minSafeRadius, &dist)) {
+			*last = (float)(lastValidLength / pathLength);
+			ok = false;
+			break;
+		}
+		lastValidLength = length;
+		length += next_step(map, s.x, s.y, dist, minSafeRadius, minStep);
+	}
+	if (ok)
+		*last = 1.0f;
+	if (samples) *samples = ns;
+	return ok;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Straight SE(2) segment (paths/path_se2.cpp:5-22)
+__device__ __forceinline__ bool line_is_path_valid(const MapDev& map, const Pose& a, const Pose& b, float minSafeRadius,
+	float minStep, float* last)
+{
+	double dx = b.x - a.x, dy = b.y - a.y;
+	const double pathLength = sqrt(dx * dx + dy * dy);
+	float dist = 0.0f;
+	if (pathLength == 0.0) {
+		*last = 1.0f;
+		return is_state_valid(map, a.x, a.y, a.th, minSafeRadius, &dist);
+	}
+	double lastValidLength = 0.0, length = 0.0;
+	while (length < pathLength) {
+		double ratio = length / pathLength;
+		double x = (1 - ratio) * a.x + ratio * b.x;
+		double y = (1 - ratio) * a.y + ratio * b.y;
+		double th = (1 - ratio) * a.th + ratio * b.th;
+		if (!is_state_valid(map, x, y, th, minSafeRadius, &dist)) {
+			*last = (float)(lastValidLength / pathLength);
+			return false;
+		}
+		lastValidLength = length;
+		length += next_step(map, x, y, dist, minSafeRadius, minStep);
+	}
+	*last = 1.0f;
+	return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Reeds-Shepp solver (geometry/reeds_shepp.cpp)
+
+__device__ __forceinline__ bool angle_invalid(double t) { return t < 0 || t > PPX_PI; } // :13-16
+__device__ __forceinline__ double wrap_angle(double t) { return modulo(t + PPX_PI, 2 * PPX_PI) - PPX_PI; } // :18-21
+
+// Per base word: 5 x (steer|dir<<2) nibbles and 5 x length selectors (0 t, 1 u, 2 v, 3 pi/2, 7 none).
+// Built from reeds_shepp.cpp:299-... "Path" builders (:162-297).
+//                         L=0 S=1 R=2 ; F=0 B=1
+#define PPX_M(steer, dir) ((steer) | ((dir) << 2))
+#define PPX_NONE 0xA /* steer=2, dir=2(NoMotion) */
+__device__ __constant__ unsigned char c_rs_base_motion[12][5] = {
+	{ PPX_M(0, 0), PPX_M(1, 0), PPX_M(0, 0), PPX_NONE, PPX_NONE }, // LfSfLf
+	{ PPX_M(0, 0), PPX_M(1, 0), PPX_M(2, 0), PPX_NONE, PPX_NONE }, // LfSfRf
+	{ PPX_M(0, 0), PPX_M(2, 1), PPX_M(0, 0), PPX_NONE, PPX_NONE }, // LfRbLf
+	{ PPX_M(0, 0), PPX_M(2, 1), PPX_M(0, 1), PPX_NONE, PPX_NONE }, // LfRbLb
+	{ PPX_M(0, 0), PPX_M(2, 0), PPX_M(0, 1), PPX_NONE, PPX_NONE }, // LfRfLb
+	{ PPX_M(0, 0), PPX_M(2, 0), PPX_M(0, 1), PPX_M(2, 1), PPX_NONE }, // LfRufLubRb
+	{ PPX_M(0, 0), PPX_M(2, 1), PPX_M(0, 1), PPX_M(2, 0), PPX_NONE }, // LfRubLubRf
+	{ PPX_M(0, 0), PPX_M(2, 1), PPX_M(1, 1), PPX_M(0, 1), PPX_NONE }, // LfRbpi2SbLb
+	{ PPX_M(0, 0), PPX_M(2, 1), PPX_M(1, 1), PPX_M(2, 1), PPX_NONE }, // LfRbpi2SbRb
+	{ PPX_M(0, 0), PPX_M(1, 0), PPX_M(2, 0), PPX_M(0, 1), PPX_NONE }, // LfSfRfpi2Lb
+	{ PPX_M(0, 0), PPX_M(1, 0), PPX_M(0, 0), PPX_M(2, 1), PPX_NONE }, // LfSfLfpi2Rb
+	{ PPX_M(0, 0), PPX_M(2, 1), PPX_M(1, 1), PPX_M(0, 1), PPX_M(2, 0) }, // LfRbpi2SbLbpi2Rf
+};
+__device__ __constant__ unsigned char c_rs_base_len[12][5] = {
+	{ 0, 1, 2, 7, 7 }, { 0, 1, 2, 7, 7 }, { 0, 1, 2, 7, 7 }, { 0, 1, 2, 7, 7 }, { 0, 1, 2, 7, 7 },
+	{ 0, 1, 1, 2, 7 }, { 0, 1, 1, 2, 7 },
+	{ 0, 3, 1, 2, 7 }, { 0, 3, 1, 2, 7 },
+	{ 0, 1, 3, 2, 7 }, { 0, 1, 3, 2, 7 },
+	{ 0, 3, 1, 3, 2 },
+};
+
+// GetPath(word, t, u, v) (:571-606): motions of base word w/4, then Timeflip (w%4 & 1) and
+// Reflect (w%4 & 2) transforms (:495-516).  Returns m_length.
+__device__ __forceinline__ double rs_build_segment(int word, double t, double u, double v, RSSeg& seg)
+{
+	const int base = word >> 2, q = word & 3;
+	double total = 0.0;
+	uint32_t code = 0;
+	#pragma unroll
+	for (int i = 0; i < 5; i++) {
+		unsigned mcode = c_rs_base_motion[base][i];
+		unsigned sel = c_rs_base_len[base][i];
+		double len = sel == 0 ? t : sel == 1 ? u : sel == 2 ? v : sel == 3 ? PPX_PI_2 : PPX_INF;
+		if (sel != 7) {
+			unsigned steer = mcode & 3, dir = mcode >> 2;
+			if (q & 1)
+				dir ^= 1; // TimeflipTransform
+			if ((q & 2) && steer != 1)
+				steer ^= 2; // ReflectTransform (Left 0 <-> Right 2)
+			mcode = steer | (dir << 2);
+			total += fabs(len);
+		}
+		seg.len[i] = len;
+		code |= mcode << (4 * i);
+	}
+	seg.code = code;
+	return total;
+}
+
+// PathSegment::ComputeCost (:347-376)
+__device__ __forceinline__ float rs_compute_cost(const RSSeg& seg, double mLength, double r, float rev, float fwd, float sw)
+{
+	if (!seg.valid(0))
+		return __int_as_float(0x7f800000);
+	if (rev == 1.0f && sw == 0.0f)
+		return (float)(mLength * r);
+	float cost = 0;
+	int prevDirection = seg.dir(0);
+	for (int i = 0; i < 5; i++) {
+		if (!seg.valid(i))
+			break;
+		float motionCost = (float)(seg.len[i] * r);
+		int d = seg.dir(i);
+		if (d == 0)
+			motionCost *= fwd;
+		else if (d == 1)
+			motionCost *= rev;
+		if (d != prevDirection)
+			motionCost += sw;
+		prevDirection = d;
+		cost += motionCost;
+	}
+	return cost;
+}
+
+// Intermediate quantities shared by the 6 formulas of one family on one mirrored goal.
+struct RSGoalTerms {
+	double gth; // goal.theta of the mirrored goal
+	double xi, eta; // x -/+ sin(theta), y - 1 +/- cos(theta)
+	double u1sq, u1, phi; // xi^2+eta^2, sqrt, atan2(eta, xi)
+};
+
+// GetMotionLengths (:537-569) for base word `base` on the mirrored goal.  `a` holds the terms of
+// the "minus" family (x - sin, y - 1 + cos), `b` those of the "plus" family (x + sin, y - 1 - cos).
+__device__ __forceinline__ double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerms& b, double& t, double& u, double& v)
+{
+	const double INF = PPX_INF;
+	switch (base) {
+	case 0: { // LfSfLf :23-37
+		u = a.u1;
+		t = a.phi;
+		v = wrap_angle(a.gth - t);
+		if (angle_invalid(t) || angle_invalid(v))
+			return INF;
+		return t + u + v;
+	}
+	case 1: { // LfSfRf :39-59 (the `u1squared < 4` branch has no return: NaN flows on)
+		u = sqrt(b.u1sq - 4);
+		double phi = atan2(2.0, u);
+		t = wrap_angle(b.phi + phi);
+		v = wrap_angle(t - b.gth);
+		if (angle_invalid(t) || angle_invalid(v))
+			return INF;
+		return t + u + v;
+	}
+	case 2: { // LfRbLf :61-84
+		if (a.u1 > 4)
+			return INF;
+		double alpha = acos(a.u1 / 4.0);
+		t = modulo(PPX_PI_2 + alpha + a.phi, 2 * PPX_PI);
+		u = modulo(PPX_PI - 2 * alpha, 2 * PPX_PI);
+		v = modulo(a.gth - t - u, 2 * PPX_PI);
+		if (angle_invalid(t) || angle_invalid(u) || angle_invalid(v))
+			return INF;
+		return t + u + v;
+	}
+	case 3: { // LfRbLb :86-106
+		if (a.u1 > 4)
+			return INF;
+		double alpha = acos(a.u1 / 4.0);
+		t = modulo(PPX_PI_2 + alpha + a.phi, 2 * PPX_PI);
+		u = modulo(PPX_PI - 2 * alpha, 2 * PPX_PI);
+		v = modulo(t + u - a.gth, 2 * PPX_PI);
+		return t + u + v;
+	}
+	case 4: { // LfRfLb :108-129
+		if (a.u1 > 4)
+			return INF;
+		u = acos((8 - a.u1 * a.u1) / 8.0);
+		double va = sin(u);
+		double alpha = asin(2 * va / a.u1);
+		t = modulo(PPX_PI_2 - alpha + a.phi, 2 * PPX_PI);
+		v = modulo(t - u - a.gth, 2 * PPX_PI);
+		return t + u + v;
+	}
+	case 5: { // LfRufLubRb :131-160
+		if (b.u1 > 4)
+			return INF;
+		if (b.u1 > 2) {
+			double alpha = acos(b.u1 / 4 - 0.5);
+			t = modulo(PPX_PI_2 + b.phi - alpha, 2 * PPX_PI);
+			u = modulo(PPX_PI - alpha, 2 * PPX_PI);
+			v = modulo(b.gth - t + 2 * u, 2 * PPX_PI);
+		} else {
+			double alpha = acos(b.u1 / 4 + 0.5);
+			t = modulo(PPX_PI_2 + b.phi + alpha, 2 * PPX_PI);
+			u = modulo(alpha, 2 * PPX_PI);
+			v = modulo(b.gth - t + 2 * u, 2 * PPX_PI);
+		}
+		return t + u + u + v;
+	}
+	case 6: { // LfRubLubRf :162-186
+		if (b.u1 > 6)
+			return INF;
+		double va1 = 1.25 - b.u1 * b.u1 / 16; // 1.25f literal is exact
+		if (va1 < 0 || va1 > 1)
+			return INF;
+		u = acos(va1);
+		double va2 = sin(u);
+		double alpha = asin(2 * va2 / b.u1);
+		t = modulo(PPX_PI_2 + b.phi + alpha, 2 * PPX_PI);
+		v = modulo(t - b.gth, 2 * PPX_PI);
+		return t + u + u + v;
+	}
+	case 7: { // LfRbpi2SbLb :188-211
+		if (a.u1sq < 4)
+			return INF;
+		u = sqrt(a.u1sq - 4) - 2;
+		if (u < 0)
+			return INF;
+		double alpha = atan2(2.0, u + 2);
+		t = modulo(PPX_PI_2 + a.phi + alpha, 2 * PPX_PI);
+		v = modulo(t + PPX_PI_2 - a.gth, 2 * PPX_PI);
+		return t + PPX_PI_2 + u + v;
+	}
+	case 8: { // LfRbpi2SbRb :213-232
+		if (b.u1 < 2)
+			return INF;
+		t = modulo(PPX_PI_2 + b.phi, 2 * PPX_PI);
+		u = b.u1 - 2;
+		v = modulo(b.gth - t - PPX_PI_2, 2 * PPX_PI);
+		return t + PPX_PI_2 + u + v;
+	}
+	case 9: { // LfSfRfpi2Lb :234-257
+		if (a.u1sq < 4)
+			return INF;
+		u = sqrt(a.u1sq - 4) - 2;
+		if (u < 0)
+			return INF;
+		double alpha = atan2(u + 2, 2.0);
+		t = modulo(PPX_PI_2 + a.phi - alpha, 2 * PPX_PI);
+		v = modulo(t - PPX_PI_2 - a.gth, 2 * PPX_PI);
+		return t + u + PPX_PI_2 + v;
+	}
+	case 10: { // LfSfLfpi2Rb :259-278
+		if (b.u1 < 2)
+			return INF;
+		t = modulo(b.phi, 2 * PPX_PI);
+		u = b.u1 - 2;
+		v = modulo(-t - PPX_PI_2 + b.gth, 2 * PPX_PI);
+		return t + u + PPX_PI_2 + v;
+	}
+	default: { // LfRbpi2SbLbpi2Rf :280-303
+		if (b.u1sq < 16)
+			return INF;
+		u = sqrt(b.u1sq - 4) - 4;
+		if (u < 0)
+			return INF;
+		double alpha = atan2(2.0, u + 4);
+		t = modulo(PPX_PI_2 + b.phi + alpha, 2 * PPX_PI);
+		v = modulo(t - b.gth, 2 * PPX_PI);
+		return t + u + v + PPX_PI;
+	}
+	}
+}
+
+struct RSSolution {
+	int word; // PathWords, -1 = NoPath
+	RSSeg seg;
+	double mLength; // PathSegment::m_length (normalised)
+	float cost;
+};
+
+// Solver::GetOptimalPath (:654-683) when shortest == 0, Solver::GetShortestPath (:608-652) else.
+__device__ __forceinline__ void rs_solve(const Pose& start, const Pose& goal, double r, float rev, float fwd, float sw,
+	int shortest, RSSolution& out)
+{
+	// GetGoalArray (:518-535): newGoal = goal - start (2dplane.h:64-78), scaled by 1/r
+	double dx = goal.x - start.x, dy = goal.y - start.y;
+	double sN, cN;
+	sincos(-start.th, &sN, &cN);
+	double gx = cN * dx + (-sN) * dy;
+	double gy = sN * dx + cN * dy;
+	double gth = wrap_theta(wrap_theta(goal.th - start.th));
+	gx = gx / r;
+	gy = gy / r;
+	double sG, cG;
+	sincos(gth, &sG, &cG);
+
+	float bestCost = __int_as_float(0x7f800000);
+	double bestLen = PPX_INF;
+	int bestWord = -1;
+	double bt = 0, bu = 0, bv = 0;
+
+	#pragma unroll 1
+	for (int q = 0; q < 4; q++) {
+		// goals[q] = Pose2d(+-x, +-y, +-theta); sin(-theta) = -sin(theta), cos(-theta) = cos(theta)
+		double x = (q & 1) ? -gx : gx;
+		double y = (q & 2) ? -gy : gy;
+		bool flipTh = (q == 1 || q == 2);
+		double th = wrap_theta(flipTh ? -gth : gth);
+		double s = flipTh ? -sG : sG;
+		RSGoalTerms a, b;
+		a.gth = b.gth = th;
+		a.xi = x - s;
+		a.eta = y - 1 + cG;
+		b.xi = x + s;
+		b.eta = y - 1 - cG;
+		a.u1sq = a.xi * a.xi + a.eta * a.eta;
+		b.u1sq = b.xi * b.xi + b.eta * b.eta;
+		a.u1 = sqrt(a.u1sq);
+		b.u1 = sqrt(b.u1sq);
+		a.phi = atan2(a.eta, a.xi);
+		b.phi = atan2(b.eta, b.xi);
+		#pragma unroll 1
+		for (int base = 0; base < 12; base++) {
+			double t = 0, u = 0, v = 0;
+			double length = rs_motion_lengths(base, a, b, t, u, v);
+			int word = base * 4 + q;
+			if (shortest) {
+				// strict <, ties resolved by enum order: emulate by comparing (length, word)
+				if (length < bestLen || (length == bestLen && word < bestWord)) {
+					bestLen = length;
+					bestWord = word;
+					bt = t; bu = u; bv = v;
+				}
+			} else {
+				if (length == PPX_INF)
+					continue;
+				RSSeg seg;
+				double mLength = rs_build_segment(word, t, u, v, seg);
+				float cost = rs_compute_cost(seg, mLength, r, rev, fwd, sw);
+				if (cost < bestCost || (cost == bestCost && word < bestWord)) {
+					bestCost = cost;
+					bestWord = word;
+					bt = t; bu = u; bv = v;
+				}
+			}
+		}
+	}
+	out.word = bestWord;
+	if (bestWord < 0) {
+		// PathSegment(): all motions invalid, m_length 0
+		for (int i = 0; i < 5; i++)
+			out.seg.len[i] = PPX_INF;
+		out.seg.code = 0xAAAAA;
+		out.mLength = 0.0;
+		out.cost = __int_as_float(0x7f800000);
+		return;
+	}
+	out.mLength = rs_build_segment(bestWord, bt, bu, bv, out.seg);
+	out.cost = rs_compute_cost(out.seg, out.mLength, r, rev, fwd, sw);
+}
+
+}

@@ -1,0 +1,417 @@
+// libppx.so: batched StateValidatorOccupancyMap::IsStateValid / IsPathValid (A7) over
+// Reeds-Shepp, constant-steer and straight edges, and the batched Reeds-Shepp solver (A3).
+//
+// Mapping: one edge per thread, persistent grid sized to the SM count.  The reference's
+// adaptive sphere-tracing makes sample k+1 depend on the clearance read at sample k, so the
+// samples of one edge are inherently sequential (3-5 dependent L2 round trips per edge); the
+// parallelism is across edges, and the latency is hidden by resident warps.  Edge records are
+// staged through shared memory with one bulk (TMA) copy per CTA tile so that the 72-byte AoS
+// records are read from HBM fully coalesced.
+#include <algorithm>
+#include "ppx_ctx.h"
+
+using namespace ppx;
+
+namespace {
+
+constexpr int kThreads = 128;
+
+__device__ __forceinline__ void load_rs_edge(const ppx_rs_edge* __restrict__ e, Pose& start, RSSeg& seg)
+{
+	start.x = e->start[0];
+	start.y = e->start[1];
+	start.th = e->start[2];
+	#pragma unroll
+	for (int i = 0; i < 5; i++)
+		seg.len[i] = e->len[i];
+	seg.code = (uint32_t)e->code;
+}
+
+__global__ void __launch_bounds__(kThreads) k_is_state_valid(MapDev map, int64_t n, const double* __restrict__ poses,
+	float minSafeRadius, uint8_t* __restrict__ valid)
+{
+	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride) {
+		float d;
+		valid[i] = is_state_valid(map, poses[3 * i], poses[3 * i + 1], poses[3 * i + 2], minSafeRadius, &d) ? 1 : 0;
+	}
+}
+
+__global__ void __launch_bounds__(kThreads) k_check_rs(MapDev map, int64_t n, const ppx_rs_edge* __restrict__ edges, double r,
+	float minSafeRadius, float minStep, uint8_t* __restrict__ valid, float* __restrict__ last, uint32_t* __restrict__ samples)
+{
+	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride) {
+		Pose start;
+		RSSeg seg;
+		load_rs_edge(edges + i, start, seg);
+		float l;
+		unsigned ns;
+		bool ok = rs_is_path_valid(map, start, seg, r, minSafeRadius, minStep, &l, &ns);
+		valid[i] = ok ? 1 : 0;
+		last[i] = l;
+		if (samples)
+			samples[i] = ns;
+	}
+}
+
+__global__ void __launch_bounds__(kThreads) k_check_csteer(MapDev map, int64_t n, const ppx_csteer_edge* __restrict__ edges,
+	float minSafeRadius, float minStep, uint8_t* __restrict__ valid, float* __restrict__ last, double* __restrict__ finalPose)
+{
+	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride) {
+		CSteer p;
+		p.init(edges[i]);
+		float l;
+		bool ok = csteer_is_path_valid(map, p, minSafeRadius, minStep, &l, nullptr);
+		valid[i] = ok ? 1 : 0;
+		last[i] = l;
+		if (finalPose) {
+			// PathConstantSteer ctor: m_final = Interpolate(1.0); Truncate(ratio): m_final = Interpolate(ratio)
+			Pose f = p.at(ok ? 1.0 : (double)l);
+			finalPose[3 * i] = f.x;
+			finalPose[3 * i + 1] = f.y;
+			finalPose[3 * i + 2] = f.th;
+		}
+	}
+}
+
+__global__ void __launch_bounds__(kThreads) k_check_line(MapDev map, int64_t n, const ppx_line_edge* __restrict__ edges,
+	float minSafeRadius, float minStep, uint8_t* __restrict__ valid, float* __restrict__ last)
+{
+	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride) {
+		Pose a = { edges[i].from[0], edges[i].from[1], edges[i].from[2] };
+		Pose b = { edges[i].to[0], edges[i].to[1], edges[i].to[2] };
+		float l;
+		bool ok = line_is_path_valid(map, a, b, minSafeRadius, minStep, &l);
+		valid[i] = ok ? 1 : 0;
+		last[i] = l;
+	}
+}
+
+__device__ __forceinline__ void store_rs_edge(ppx_rs_edge* e, const Pose& start, const RSSeg& seg)
+{
+	e->start[0] = start.x;
+	e->start[1] = start.y;
+	e->start[2] = start.th;
+	#pragma unroll
+	for (int i = 0; i < 5; i++)
+		e->len[i] = seg.len[i];
+	e->code = seg.code;
+}
+
+// check != 0: fused PathConnectionReedsShepp::Connect + IsPathValid
+__global__ void __launch_bounds__(kThreads) k_rs_solve(MapDev map, int64_t n, const double* __restrict__ starts,
+	const double* __restrict__ goals, ppx_rs_cost_params cp, int check, float minSafeRadius, float minStep,
+	ppx_rs_edge* __restrict__ edges, int32_t* __restrict__ word, double* __restrict__ length, float* __restrict__ cost,
+	uint8_t* __restrict__ valid, float* __restrict__ last)
+{
+	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride) {
+		Pose s = { starts[3 * i], starts[3 * i + 1], starts[3 * i + 2] };
+		Pose g = { goals[3 * i], goals[3 * i + 1], goals[3 * i + 2] };
+		RSSolution sol;
+		rs_solve(s, g, cp.min_turning_radius, cp.reverse_cost_multiplier, cp.forward_cost_multiplier,
+			cp.direction_switching_cost, cp.shortest, sol);
+		if (edges)
+			store_rs_edge(edges + i, s, sol.seg);
+		if (word)
+			word[i] = sol.word;
+		if (length)
+			length[i] = sol.mLength * cp.min_turning_radius;
+		if (cost)
+			cost[i] = sol.cost;
+		if (check) {
+			float l;
+			bool ok = rs_is_path_valid(map, s, sol.seg, cp.min_turning_radius, minSafeRadius, minStep, &l, nullptr);
+			valid[i] = ok ? 1 : 0;
+			last[i] = l;
+		}
+	}
+}
+
+__global__ void __launch_bounds__(kThreads) k_rs_interpolate(int64_t n, const ppx_rs_edge* __restrict__ edges, double r,
+	int nratios, const double* __restrict__ ratios, double* __restrict__ poses)
+{
+	int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	int64_t total = n * nratios;
+	int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; idx < total; idx += stride) {
+		int64_t i = idx / nratios;
+		Pose start;
+		RSSeg seg;
+		load_rs_edge(edges + i, start, seg);
+		double totalLength = rs_total_length(seg) * r;
+		Pose p = start;
+		if (totalLength != 0) { // path_reeds_shepp.cpp:17-18
+			RSWalker w;
+			w.init(start);
+			p = w.at(seg, r, ratios[idx] * totalLength);
+		}
+		poses[3 * idx] = p.x;
+		poses[3 * idx + 1] = p.y;
+		poses[3 * idx + 2] = p.th;
+	}
+}
+
+int grid_for(const ppx_ctx* ctx, int64_t n, int threads, int blocksPerSm)
+{
+	int64_t need = (n + threads - 1) / threads;
+	int64_t cap = (int64_t)ctx->num_sms * blocksPerSm;
+	return (int)std::max<int64_t>(1, std::min(need, cap));
+}
+
+int require_map(ppx_ctx* ctx)
+{
+	if (!ctx)
+		return PPX_ERR_INVALID;
+	if (!ctx->has_map)
+		return ppx_fail(ctx, PPX_ERR_STATE, "no map uploaded (ppx_map_upload)");
+	return PPX_OK;
+}
+
+}
+
+extern "C" {
+
+int ppx_is_state_valid(ppx_ctx* ctx, int64_t n, const double* poses, const ppx_validator_params* vp, uint8_t* valid)
+{
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (poses && valid)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	double* d_poses;
+	uint8_t* d_valid;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * 3 * sizeof(double), (void**)&d_poses));
+	PPX_CHECK(ppx_scratch(ctx, 1, n, (void**)&d_valid));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_poses, poses, n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	k_is_state_valid<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_poses,
+		vp->min_safe_radius, d_valid);
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, double min_turning_radius,
+	const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, uint32_t* d_samples)
+{
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (d_edges && d_valid && d_last)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	k_check_rs<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_edges, min_turning_radius,
+		vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples);
+	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
+int ppx_check_edges_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
+	const ppx_validator_params* vp, uint8_t* valid, float* last, uint32_t* samples)
+{
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (edges && valid && last)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	ppx_rs_edge* d_edges;
+	uint8_t* d_valid;
+	float* d_last;
+	uint32_t* d_samples = nullptr;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * sizeof(ppx_rs_edge), (void**)&d_edges));
+	PPX_CHECK(ppx_scratch(ctx, 1, n, (void**)&d_valid));
+	PPX_CHECK(ppx_scratch(ctx, 2, n * sizeof(float), (void**)&d_last));
+	if (samples)
+		PPX_CHECK(ppx_scratch(ctx, 3, n * sizeof(uint32_t), (void**)&d_samples));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_edges, edges, n * sizeof(ppx_rs_edge), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CHECK(ppx_check_edges_rs_dev(ctx, n, d_edges, min_turning_radius, vp, d_valid, d_last, d_samples));
+	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(last, d_last, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	if (samples)
+		PPX_CUDA(ctx, cudaMemcpyAsync(samples, d_samples, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_check_edges_csteer(ppx_ctx* ctx, int64_t n, const ppx_csteer_edge* edges, const ppx_validator_params* vp,
+	uint8_t* valid, float* last, double* final_pose)
+{
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (edges && valid && last)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	ppx_csteer_edge* d_edges;
+	uint8_t* d_valid;
+	float* d_last;
+	double* d_final = nullptr;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * sizeof(ppx_csteer_edge), (void**)&d_edges));
+	PPX_CHECK(ppx_scratch(ctx, 1, n, (void**)&d_valid));
+	PPX_CHECK(ppx_scratch(ctx, 2, n * sizeof(float), (void**)&d_last));
+	if (final_pose)
+		PPX_CHECK(ppx_scratch(ctx, 3, n * 3 * sizeof(double), (void**)&d_final));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_edges, edges, n * sizeof(ppx_csteer_edge), cudaMemcpyHostToDevice, ctx->stream));
+	k_check_csteer<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_edges,
+		vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_final);
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(last, d_last, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	if (final_pose)
+		PPX_CUDA(ctx, cudaMemcpyAsync(final_pose, d_final, n * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_check_edges_line(ppx_ctx* ctx, int64_t n, const ppx_line_edge* edges, const ppx_validator_params* vp,
+	uint8_t* valid, float* last)
+{
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (edges && valid && last)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	ppx_line_edge* d_edges;
+	uint8_t* d_valid;
+	float* d_last;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * sizeof(ppx_line_edge), (void**)&d_edges));
+	PPX_CHECK(ppx_scratch(ctx, 1, n, (void**)&d_valid));
+	PPX_CHECK(ppx_scratch(ctx, 2, n * sizeof(float), (void**)&d_last));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_edges, edges, n * sizeof(ppx_line_edge), cudaMemcpyHostToDevice, ctx->stream));
+	k_check_line<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_edges,
+		vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last);
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(last, d_last, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_rs_solve_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, const double* d_goals,
+	const ppx_rs_cost_params* cp, ppx_rs_edge* d_edges, int32_t* d_word, double* d_length, float* d_cost)
+{
+	if (!ctx)
+		return PPX_ERR_INVALID;
+	PPX_REQUIRE(ctx, n >= 0 && cp && (n == 0 || (d_starts && d_goals)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	MapDev none {};
+	k_rs_solve<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(none, n, d_starts, d_goals, *cp, 0, 0.0f, 0.0f,
+		d_edges, d_word, d_length, d_cost, nullptr, nullptr);
+	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
+int ppx_connect_check_rs_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, const double* d_goals,
+	const ppx_rs_cost_params* cp, const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, int32_t* d_word,
+	double* d_length, float* d_cost)
+{
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && cp && vp && (n == 0 || (d_starts && d_goals && d_valid && d_last)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	k_rs_solve<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_starts, d_goals, *cp, 1,
+		vp->min_safe_radius, vp->min_path_interpolation_distance, nullptr, d_word, d_length, d_cost, d_valid, d_last);
+	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
+static int solve_host(ppx_ctx* ctx, int64_t n, const double* starts, const double* goals, const ppx_rs_cost_params* cp,
+	const ppx_validator_params* vp, ppx_rs_edge* edges, int32_t* word, double* length, float* cost, uint8_t* valid,
+	float* last)
+{
+	double *d_starts, *d_goals, *d_length = nullptr;
+	ppx_rs_edge* d_edges = nullptr;
+	int32_t* d_word = nullptr;
+	float *d_cost = nullptr, *d_last = nullptr;
+	uint8_t* d_valid = nullptr;
+	// one scratch slot, carved
+	size_t off = 0;
+	auto carve = [&](size_t bytes) {
+		size_t o = off;
+		off += (bytes + 255) & ~(size_t)255;
+		return o;
+	};
+	size_t o_starts = carve(n * 3 * sizeof(double)), o_goals = carve(n * 3 * sizeof(double));
+	size_t o_edges = carve(edges ? n * sizeof(ppx_rs_edge) : 0), o_word = carve(word ? n * 4 : 0);
+	size_t o_length = carve(length ? n * 8 : 0), o_cost = carve(cost ? n * 4 : 0);
+	size_t o_valid = carve(vp ? n : 0), o_last = carve(vp ? n * 4 : 0);
+	char* base;
+	PPX_CHECK(ppx_scratch(ctx, 0, off, (void**)&base));
+	d_starts = (double*)(base + o_starts);
+	d_goals = (double*)(base + o_goals);
+	if (edges) d_edges = (ppx_rs_edge*)(base + o_edges);
+	if (word) d_word = (int32_t*)(base + o_word);
+	if (length) d_length = (double*)(base + o_length);
+	if (cost) d_cost = (float*)(base + o_cost);
+	if (vp) {
+		d_valid = (uint8_t*)(base + o_valid);
+		d_last = (float*)(base + o_last);
+	}
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_starts, starts, n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_goals, goals, n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	if (vp)
+		PPX_CHECK(ppx_connect_check_rs_dev(ctx, n, d_starts, d_goals, cp, vp, d_valid, d_last, d_word, d_length, d_cost));
+	else
+		PPX_CHECK(ppx_rs_solve_dev(ctx, n, d_starts, d_goals, cp, d_edges, d_word, d_length, d_cost));
+	if (edges) PPX_CUDA(ctx, cudaMemcpyAsync(edges, d_edges, n * sizeof(ppx_rs_edge), cudaMemcpyDeviceToHost, ctx->stream));
+	if (word) PPX_CUDA(ctx, cudaMemcpyAsync(word, d_word, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (length) PPX_CUDA(ctx, cudaMemcpyAsync(length, d_length, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	if (cost) PPX_CUDA(ctx, cudaMemcpyAsync(cost, d_cost, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (vp) {
+		PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
+		PPX_CUDA(ctx, cudaMemcpyAsync(last, d_last, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	}
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_rs_solve(ppx_ctx* ctx, int64_t n, const double* starts, const double* goals, const ppx_rs_cost_params* cp,
+	ppx_rs_edge* edges, int32_t* word, double* length, float* cost)
+{
+	if (!ctx)
+		return PPX_ERR_INVALID;
+	PPX_REQUIRE(ctx, n >= 0 && cp && (n == 0 || (starts && goals)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	return solve_host(ctx, n, starts, goals, cp, nullptr, edges, word, length, cost, nullptr, nullptr);
+}
+
+int ppx_connect_check_rs(ppx_ctx* ctx, int64_t n, const double* starts, const double* goals,
+	const ppx_rs_cost_params* cp, const ppx_validator_params* vp, uint8_t* valid, float* last, int32_t* word,
+	double* length, float* cost)
+{
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && cp && vp && (n == 0 || (starts && goals && valid && last)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	return solve_host(ctx, n, starts, goals, cp, vp, nullptr, word, length, cost, valid, last);
+}
+
+int ppx_rs_interpolate(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius, int32_t nratios,
+	const double* ratios, double* poses)
+{
+	if (!ctx)
+		return PPX_ERR_INVALID;
+	PPX_REQUIRE(ctx, n >= 0 && nratios >= 0 && (n * nratios == 0 || (edges && ratios && poses)), "bad arguments");
+	if (n * nratios == 0)
+		return PPX_OK;
+	ppx_rs_edge* d_edges;
+	double *d_ratios, *d_poses;
+	int64_t total = n * nratios;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * sizeof(ppx_rs_edge), (void**)&d_edges));
+	PPX_CHECK(ppx_scratch(ctx, 1, total * sizeof(double), (void**)&d_ratios));
+	PPX_CHECK(ppx_scratch(ctx, 2, total * 3 * sizeof(double), (void**)&d_poses));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_edges, edges, n * sizeof(ppx_rs_edge), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_ratios, ratios, total * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	k_rs_interpolate<<<grid_for(ctx, total, kThreads, 16), kThreads, 0, ctx->stream>>>(n, d_edges, min_turning_radius, nratios,
+		d_ratios, d_poses);
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaMemcpyAsync(poses, d_poses, total * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,68 @@
+"""ctypes binding of libppx.so -- one declaration per entry point of include/ppx.h."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libppx.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        "(nvcc, sm_100a).  pathplanning_b200 has no CPU fallback.")
+
+ppx = C.CDLL(LIB_PATH)
+
+
+class MapDescC(C.Structure):
+    _fields_ = [("rows", C.c_int32), ("cols", C.c_int32), ("resolution", C.c_float), ("_pad", C.c_float),
+                ("world_origin", C.c_double * 2), ("local_origin", C.c_double * 2),
+                ("lb", C.c_double * 3), ("ub", C.c_double * 3)]
+
+
+class ValidatorParamsC(C.Structure):
+    _fields_ = [("min_safe_radius", C.c_float), ("min_path_interpolation_distance", C.c_float)]
+
+
+class RSCostParamsC(C.Structure):
+    _fields_ = [("min_turning_radius", C.c_double), ("reverse_cost_multiplier", C.c_float),
+                ("forward_cost_multiplier", C.c_float), ("direction_switching_cost", C.c_float),
+                ("shortest", C.c_int32)]
+
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_SIGS = {
+    "ppx_version": (C.c_int, []),
+    "ppx_ctx_create": (C.c_int, [C.c_int, C.POINTER(_p)]),
+    "ppx_ctx_destroy": (C.c_int, [_p]),
+    "ppx_ctx_set_stream": (C.c_int, [_p, _p]),
+    "ppx_ctx_synchronize": (C.c_int, [_p]),
+    "ppx_last_error": (C.c_char_p, [_p]),
+    "ppx_ctx_launch_count": (C.c_int64, [_p]),
+    "ppx_dev_alloc": (C.c_int, [_p, C.c_uint64, C.POINTER(_p)]),
+    "ppx_dev_free": (C.c_int, [_p, _p]),
+    "ppx_host_alloc": (C.c_int, [_p, C.c_uint64, C.POINTER(_p)]),
+    "ppx_host_free": (C.c_int, [_p, _p]),
+    "ppx_memcpy_h2d": (C.c_int, [_p, _p, _p, C.c_uint64]),
+    "ppx_memcpy_d2h": (C.c_int, [_p, _p, _p, C.c_uint64]),
+    "ppx_map_upload": (C.c_int, [_p, C.POINTER(MapDescC), _p, _p, _p]),
+    "ppx_is_state_valid": (C.c_int, [_p, _i64, _p, C.POINTER(ValidatorParamsC), _p]),
+    "ppx_check_edges_rs": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p]),
+    "ppx_check_edges_rs_dev": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p]),
+    "ppx_check_edges_csteer": (C.c_int, [_p, _i64, _p, C.POINTER(ValidatorParamsC), _p, _p, _p]),
+    "ppx_check_edges_line": (C.c_int, [_p, _i64, _p, C.POINTER(ValidatorParamsC), _p, _p]),
+    "ppx_rs_solve": (C.c_int, [_p, _i64, _p, _p, C.POINTER(RSCostParamsC), _p, _p, _p, _p]),
+    "ppx_rs_solve_dev": (C.c_int, [_p, _i64, _p, _p, C.POINTER(RSCostParamsC), _p, _p, _p, _p]),
+    "ppx_connect_check_rs": (C.c_int, [_p, _i64, _p, _p, C.POINTER(RSCostParamsC), C.POINTER(ValidatorParamsC),
+                                       _p, _p, _p, _p, _p]),
+    "ppx_connect_check_rs_dev": (C.c_int, [_p, _i64, _p, _p, C.POINTER(RSCostParamsC), C.POINTER(ValidatorParamsC),
+                                           _p, _p, _p, _p, _p]),
+    "ppx_rs_interpolate": (C.c_int, [_p, _i64, _p, C.c_double, C.c_int32, _p, _p]),
+}
+
+for _name, (_res, _args) in _SIGS.items():
+    _fn = getattr(ppx, _name)  # AttributeError here = header and library out of sync
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+EXPORTED = tuple(_SIGS)

@@ -1,0 +1,159 @@
+#!/usr/bin/env python
+"""Generates the golden fixtures in this directory from the reference itself.
+
+Runs only in the build container: it parses the reference's own known-answer test
+(/root/reference/planner/tests/test_reeds_shepp.cpp) and calls the compiled, unmodified
+reference (oracle/_ref/libpp_ref.so, built by oracle/Makefile).  The fixtures are committed so
+that the CPU and GPU test suites never need /root/reference at run time.
+
+    python tests/golden/make_golden.py
+"""
+import json
+import os
+import re
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import refapi  # noqa: E402
+from pathplanning_b200 import synth  # noqa: E402
+
+REF_TEST = "/root/reference/planner/tests/test_reeds_shepp.cpp"
+REF_HEADER = "/root/reference/planner/src/geometry/reeds_shepp.h"
+
+
+def path_word_names():
+    src = open(REF_HEADER).read()
+    body = src[src.index("enum class PathWords"):]
+    body = body[body.index("{") + 1:body.index("NumPathWords")]
+    body = re.sub(r"//.*", "", body)
+    names = [t.strip().split("=")[0].strip() for t in body.split(",") if t.strip()]
+    assert names[0] == "NoPath"
+    return names[1:]
+
+
+def parse_kats():
+    names = path_word_names()
+    assert len(names) == 48
+    src = open(REF_TEST).read()
+    src = src[src.index("int main()"):]
+    cases = []
+    start = goal = None
+    for line in src.splitlines():
+        m = re.search(r"start = \{([^}]*)\}", line)
+        if m:
+            start = [float(eval(x.replace("M_PI", "3.14159265358979323846"))) for x in m.group(1).split(",")]
+        m = re.search(r"goal = \{([^}]*)\}", line)
+        if m:
+            goal = [float(eval(x.replace("M_PI", "3.14159265358979323846"))) for x in m.group(1).split(",")]
+        m = re.search(r"Planner::Test\(start, goal, \{(.*)\}\);", line)
+        if m:
+            toks = [t.strip() for t in m.group(1).split(",") if t.strip()]
+            words = []
+            for t in toks:
+                if t == "optimalWord":
+                    words.append(current)
+                else:
+                    words.append(names.index(t.split("::")[-1]))
+            cases.append(dict(start=start, goal=goal, words=words))
+        m = re.search(r"optimalWord = Planner::ReedsShepp::PathWords::(\w+);", line)
+        if m:
+            current = names.index(m.group(1))
+    return names, cases
+
+
+def main():
+    bad, wrap = refapi.selfcheck()
+    assert bad == 0, "reference build shows trap H1"
+    names, cases = parse_kats()
+    assert len(cases) == 48, len(cases)
+    # reference outputs for the KATs (unit radius, unit multipliers, like the reference test)
+    for c in cases:
+        sh = refapi.rs_shortest(c["start"], c["goal"], 1.0)
+        assert sh["word"] in c["words"], (c, sh["word"])
+        c["ref_shortest_word"] = int(sh["word"])
+        c["ref_final"] = sh["final"].tolist()
+        c["ref_length"] = sh["length"]
+        op = refapi.rs_optimal_batch([c["start"]], [c["goal"]], 1.0)
+        assert int(op["word"][0]) in c["words"]
+        c["ref_optimal_word"] = int(op["word"][0])
+        c["ref_cost"] = float(op["cost"][0])
+    json.dump(dict(source="planner/tests/test_reeds_shepp.cpp:38-300", word_names=names, heading_wrap_h2=wrap, cases=cases),
+              open(os.path.join(HERE, "rs_kat.json"), "w"), indent=1)
+
+    # random Reeds-Shepp solves (r=2, default multipliers and a non-default set)
+    rng = np.random.default_rng(20261104)
+    n = 4000
+    starts = np.stack([rng.uniform(-20, 20, n), rng.uniform(-20, 20, n), rng.uniform(-np.pi, np.pi, n)], 1)
+    d = rng.uniform(0.05, 14, n)
+    a = rng.uniform(-np.pi, np.pi, n)
+    goals = np.stack([starts[:, 0] + d * np.cos(a), starts[:, 1] + d * np.sin(a), rng.uniform(-np.pi, np.pi, n)], 1)
+    out = {}
+    for tag, (rmin, rev, fwd, sw) in dict(default=(2.0, 1.0, 1.0, 0.0), weighted=(1.5, 2.0, 1.1, 0.7)).items():
+        r = refapi.rs_optimal_batch(starts, goals, rmin, rev, fwd, sw)
+        out.update({f"{tag}_params": np.array([rmin, rev, fwd, sw]), f"{tag}_word": r["word"].astype(np.int8),
+                    f"{tag}_steer": r["steer"].astype(np.int8), f"{tag}_dir": r["dir"].astype(np.int8),
+                    f"{tag}_len": r["len"], f"{tag}_length": r["length"], f"{tag}_cost": r["cost"]})
+    np.savez_compressed(os.path.join(HERE, "rs_random.npz"), starts=starts, goals=goals, **out)
+
+    # collision-checked edges on the C2 parking lot (400x400 @ 0.1 m)
+    cfg = synth.C2
+    rects = synth.config_rects(cfg)
+    w = refapi.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    for r in rects:
+        w.add_rectangle(*r)
+    w.update()
+    occ, sq = w.grids()
+    pathcost, vorosq = w.gvd_update()
+    info = w.info()
+    n = 20000
+    rng = np.random.default_rng(42)
+    starts = np.stack([rng.uniform(-21, 21, n), rng.uniform(-21, 21, n), rng.uniform(-np.pi, np.pi, n)], 1)
+    d = rng.uniform(0.0, 12, n)
+    d[:50] = 0.0  # zero-length paths (start == goal)
+    a = rng.uniform(-np.pi, np.pi, n)
+    goals = np.stack([starts[:, 0] + d * np.cos(a), starts[:, 1] + d * np.sin(a), rng.uniform(-np.pi, np.pi, n)], 1)
+    goals[:50, 2] = starts[:50, 2]
+    edges = {}
+    for tag, (radius, step) in dict(r10=(1.0, 0.1), r03=(0.3, 0.05)).items():
+        w.set_validator_params(radius, step)
+        r = w.check_rs_edges(starts, goals, 2.0)
+        edges.update({f"{tag}_params": np.array([radius, step], np.float32), f"{tag}_valid": r["valid"],
+                      f"{tag}_last": r["last"], f"{tag}_samples": r["samples"].astype(np.int16)})
+        if tag == "r10":
+            edges.update(word=r["word"].astype(np.int8), steer=r["steer"].astype(np.int8), dir=r["dir"].astype(np.int8),
+                         len=r["len"], length=r["length"], cost=r["cost"])
+    # constant-steer primitives and straight segments on the same map
+    m = 6000
+    cs_start = np.stack([rng.uniform(-20, 20, m), rng.uniform(-20, 20, m), rng.uniform(-np.pi, np.pi, m)], 1)
+    deltas = np.array([0.0, 0.45, -0.45, 0.9151, -0.9151])
+    cs_steer = deltas[rng.integers(0, 5, m)]
+    cs_len = np.where(rng.random(m) < 0.5, 1.5, rng.uniform(0.0, 6.0, m))
+    cs_dir = rng.integers(0, 2, m).astype(np.int32)
+    w.set_validator_params(1.0, 0.1)
+    cs = w.check_csteer(cs_start, cs_steer, cs_len, cs_dir, 2.6)
+    ln_a = np.stack([rng.uniform(-20, 20, m), rng.uniform(-20, 20, m), rng.uniform(-np.pi, np.pi, m)], 1)
+    ln_b = np.stack([rng.uniform(-20, 20, m), rng.uniform(-20, 20, m), rng.uniform(-np.pi, np.pi, m)], 1)
+    ln_b[:, :2] = ln_a[:, :2] + (ln_b[:, :2] - ln_a[:, :2]) * rng.uniform(0, 0.3, (m, 1))
+    ln = w.check_line_edges(ln_a, ln_b)
+    # IsStateValid on a pose cloud straddling the map border
+    pts = np.stack([rng.uniform(-20.5, 20.5, m), rng.uniform(-20.5, 20.5, m), rng.uniform(-4, 4, m)], 1)
+    pts[:8] = [[-20, -20, 0], [20, 20, 0], [19.999, 19.999, 0], [-20.05, 0, 0], [0, -20.05, 0], [20.0, 0, 0], [0, 20.0, 0], [0, 0, 3.2]]
+    sv = w.is_state_valid(pts)
+    np.savez_compressed(
+        os.path.join(HERE, "edges_c2.npz"), rects=np.array(rects), lb=np.array(cfg["lb"]), ub=np.array(cfg["ub"]),
+        resolution=np.float32(cfg["resolution"]), world_origin=np.array(info["world_origin"]),
+        occupancy=occ.astype(np.int16), sqdist=sq, pathcost=pathcost, vorosq=vorosq,
+        starts=starts, goals=goals, **edges,
+        cs_start=cs_start, cs_steer=cs_steer, cs_len=cs_len, cs_dir=cs_dir, cs_valid=cs["valid"], cs_last=cs["last"],
+        cs_final=cs["final"], ln_a=ln_a, ln_b=ln_b, ln_valid=ln["valid"], ln_last=ln["last"], sv_pts=pts, sv_valid=sv)
+    for f in sorted(os.listdir(HERE)):
+        print(f, os.path.getsize(os.path.join(HERE, f)))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,239 @@
+"""ctypes wrapper of the compiled reference harness (oracle/ref_harness.cpp ->
+oracle/_ref/libpp_ref.so).  TEST INFRASTRUCTURE: imported only by tests/, smoke() and bench.py's
+cpu_baseline / --impl reference legs."""
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libpp_ref.so")
+_lib = None
+
+
+def available():
+    return os.path.exists(REF_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(REF_PATH)
+        _lib.ref_world_create.restype = C.c_void_p
+        _lib.ref_hybrid_create.restype = C.c_void_p
+        for name in ("ref_check_rs_edges", "ref_check_rs_segments", "ref_wavefront", "ref_nonholo_build"):
+            getattr(_lib, name).restype = C.c_double
+        _lib.ref_hybrid_expansions.restype = C.c_long
+        _lib.ref_hybrid_solution.restype = C.c_long
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _d3(v):
+    return (C.c_double * 3)(*[float(x) for x in v])
+
+
+def selfcheck():
+    w = np.zeros(75, dtype=np.int32)
+    bad = lib().ref_selfcheck(_p(w))
+    return bad, dict(zip(range(-37, 38), w.tolist()))
+
+
+# ---- Reeds-Shepp ------------------------------------------------------------------------------
+def rs_optimal_batch(starts, goals, rmin=1.0, rev=1.0, fwd=1.0, sw=0.0):
+    starts = np.ascontiguousarray(starts, dtype=np.float64)
+    goals = np.ascontiguousarray(goals, dtype=np.float64)
+    n = len(starts)
+    words = np.empty(n, np.int32)
+    steer = np.empty((n, 5), np.int32)
+    direction = np.empty((n, 5), np.int32)
+    length = np.empty((n, 5), np.float64)
+    total = np.empty(n, np.float64)
+    cost = np.empty(n, np.float32)
+    lib().ref_rs_optimal_batch(C.c_long(n), _p(starts), _p(goals), C.c_double(rmin), C.c_float(rev), C.c_float(fwd),
+                               C.c_float(sw), _p(words), _p(steer), _p(direction), _p(length), _p(total), _p(cost))
+    return dict(word=words, steer=steer, dir=direction, len=length, length=total, cost=cost)
+
+
+def rs_shortest(start, goal, rmin=1.0):
+    steer = np.empty(5, np.int32)
+    direction = np.empty(5, np.int32)
+    length = np.empty(5, np.float64)
+    total = C.c_double()
+    final = np.empty(3, np.float64)
+    w = lib().ref_rs_shortest(_d3(start), _d3(goal), C.c_double(rmin), _p(steer), _p(direction), _p(length),
+                              C.byref(total), _p(final))
+    return dict(word=w, steer=steer, dir=direction, len=length, length=total.value, final=final)
+
+
+def rs_interpolate(start, steer, direction, length, rmin, ratios, truncate=-1.0):
+    ratios = np.ascontiguousarray(ratios, dtype=np.float64)
+    steer = np.ascontiguousarray(steer, dtype=np.int32)
+    direction = np.ascontiguousarray(direction, dtype=np.int32)
+    length = np.ascontiguousarray(length, dtype=np.float64)
+    poses = np.empty((len(ratios), 3), np.float64)
+    out_len = C.c_double()
+    final = np.empty(3, np.float64)
+    lib().ref_rs_interpolate(_d3(start), _p(steer), _p(direction), _p(length), C.c_double(rmin), C.c_double(truncate),
+                             C.c_int(len(ratios)), _p(ratios), _p(poses), C.byref(out_len), _p(final))
+    return poses, out_len.value, final
+
+
+def csteer_interpolate(start, steering, length, direction, wheelbase, ratios):
+    ratios = np.ascontiguousarray(ratios, dtype=np.float64)
+    poses = np.empty((len(ratios), 3), np.float64)
+    lib().ref_csteer_interpolate(_d3(start), C.c_double(steering), C.c_double(length), C.c_int(direction),
+                                 C.c_double(wheelbase), C.c_int(len(ratios)), _p(ratios), _p(poses))
+    return poses
+
+
+def random_uniform(seed, n, lb=0.0, ub=1.0):
+    out = np.empty(n, np.float64)
+    lib().ref_random_uniform(C.c_uint64(seed), C.c_long(n), C.c_double(lb), C.c_double(ub), _p(out))
+    return out
+
+
+# ---- World ------------------------------------------------------------------------------------
+class World:
+    """StateSpaceSE2 + ObstacleListOccupancyMap + StateValidatorOccupancyMap of the reference."""
+
+    def __init__(self, lb, ub, resolution):
+        self.lb, self.ub, self.resolution = tuple(lb), tuple(ub), float(resolution)
+        self.h = C.c_void_p(lib().ref_world_create(_d3(lb), _d3(ub), C.c_float(resolution)))
+        self.min_safe_radius = 1.0
+        self.min_step = 0.1
+
+    def close(self):
+        if self.h:
+            lib().ref_world_destroy(self.h)
+            self.h = None
+
+    def add_rectangle(self, dx, dy, x, y, theta):
+        return lib().ref_world_add_rectangle(self.h, C.c_double(dx), C.c_double(dy), C.c_double(x), C.c_double(y),
+                                             C.c_double(theta))
+
+    def set_cells(self, rows, cols, obstacle_id=0):
+        rows = np.ascontiguousarray(rows, np.int32)
+        cols = np.ascontiguousarray(cols, np.int32)
+        lib().ref_world_set_cells(self.h, C.c_long(len(rows)), _p(rows), _p(cols), C.c_int(obstacle_id))
+
+    def update(self):
+        lib().ref_world_update(self.h)
+
+    def info(self):
+        rows, cols, res = C.c_int(), C.c_int(), C.c_float()
+        org = (C.c_double * 4)()
+        lib().ref_world_info(self.h, C.byref(rows), C.byref(cols), org, C.byref(res))
+        return dict(rows=rows.value, cols=cols.value, world_origin=(org[0], org[1]), local_origin=(org[2], org[3]),
+                    resolution=res.value)
+
+    def grids(self):
+        i = self.info()
+        occ = np.empty((i["rows"], i["cols"]), np.int32)
+        sq = np.empty((i["rows"], i["cols"]), np.int32)
+        lib().ref_world_copy_grids(self.h, _p(occ), _p(sq))
+        return occ, sq
+
+    def gvd_update(self):
+        i = self.info()
+        pc = np.empty((i["rows"], i["cols"]), np.float32)
+        vd = np.empty((i["rows"], i["cols"]), np.int32)
+        lib().ref_world_gvd_update(self.h, _p(pc), _p(vd))
+        return pc, vd
+
+    def set_validator_params(self, min_safe_radius, min_step):
+        self.min_safe_radius, self.min_step = float(min_safe_radius), float(min_step)
+        lib().ref_world_set_validator_params(self.h, C.c_float(min_safe_radius), C.c_float(min_step))
+
+    def map_desc(self):
+        """ppx MapDesc equivalent of this world (what the C++ host mirror passes to ppx_map_upload)."""
+        from pathplanning_b200 import MapDesc
+        i = self.info()
+        return MapDesc(rows=i["rows"], cols=i["cols"], resolution=i["resolution"], world_origin=i["world_origin"],
+                       local_origin=i["local_origin"], lb=self.lb, ub=self.ub)
+
+    def is_state_valid(self, poses):
+        poses = np.ascontiguousarray(poses, np.float64)
+        out = np.empty(len(poses), np.uint8)
+        lib().ref_is_state_valid_batch(self.h, C.c_long(len(poses)), _p(poses), _p(out))
+        return out.astype(bool)
+
+    def check_rs_edges(self, starts, goals, rmin=1.0, rev=1.0, fwd=1.0, sw=0.0, full=True):
+        """Solve + build + IsPathValid.  Returns dict incl. wall seconds."""
+        starts = np.ascontiguousarray(starts, np.float64)
+        goals = np.ascontiguousarray(goals, np.float64)
+        n = len(starts)
+        valid = np.empty(n, np.uint8)
+        last = np.empty(n, np.float32)
+        if full:
+            samples = np.empty(n, np.int32)
+            words = np.empty(n, np.int32)
+            steer = np.empty((n, 5), np.int32)
+            direction = np.empty((n, 5), np.int32)
+            length = np.empty((n, 5), np.float64)
+            total = np.empty(n, np.float64)
+            cost = np.empty(n, np.float32)
+        else:
+            samples = words = steer = direction = length = total = cost = None
+        sec = lib().ref_check_rs_edges(self.h, C.c_long(n), _p(starts), _p(goals), C.c_double(rmin), C.c_float(rev),
+                                       C.c_float(fwd), C.c_float(sw), _p(valid), _p(last), _p(samples), _p(words),
+                                       _p(steer), _p(direction), _p(length), _p(total), _p(cost))
+        return dict(valid=valid.astype(bool), last=last, samples=samples, word=words, steer=steer, dir=direction,
+                    len=length, length=total, cost=cost, seconds=sec)
+
+    def check_rs_segments(self, starts, steer, direction, length, rmin=1.0):
+        starts = np.ascontiguousarray(starts, np.float64)
+        steer = np.ascontiguousarray(steer, np.int32)
+        direction = np.ascontiguousarray(direction, np.int32)
+        length = np.ascontiguousarray(length, np.float64)
+        n = len(starts)
+        valid = np.empty(n, np.uint8)
+        last = np.empty(n, np.float32)
+        samples = np.empty(n, np.int32)
+        sec = lib().ref_check_rs_segments(self.h, C.c_long(n), _p(starts), _p(steer), _p(direction), _p(length),
+                                          C.c_double(rmin), _p(valid), _p(last), _p(samples))
+        return dict(valid=valid.astype(bool), last=last, samples=samples, seconds=sec)
+
+    def check_csteer(self, starts, steering, length, direction, wheelbase=2.6):
+        starts = np.ascontiguousarray(starts, np.float64)
+        steering = np.ascontiguousarray(steering, np.float64)
+        length = np.ascontiguousarray(length, np.float64)
+        direction = np.ascontiguousarray(direction, np.int32)
+        n = len(starts)
+        valid = np.empty(n, np.uint8)
+        last = np.empty(n, np.float32)
+        final = np.empty((n, 3), np.float64)
+        flen = np.empty(n, np.float64)
+        lib().ref_check_csteer(self.h, C.c_long(n), _p(starts), _p(steering), _p(length), _p(direction),
+                               C.c_double(wheelbase), _p(valid), _p(last), _p(final), _p(flen))
+        return dict(valid=valid.astype(bool), last=last, final=final, final_len=flen)
+
+    def check_line_edges(self, a, b):
+        a = np.ascontiguousarray(a, np.float64)
+        b = np.ascontiguousarray(b, np.float64)
+        n = len(a)
+        valid = np.empty(n, np.uint8)
+        last = np.empty(n, np.float32)
+        lib().ref_check_line_edges(self.h, C.c_long(n), _p(a), _p(b), _p(valid), _p(last))
+        return dict(valid=valid.astype(bool), last=last)
+
+    def wavefront(self, goal, rev=1.0, fwd=1.0):
+        i = self.info()
+        cost = np.empty((i["rows"], i["cols"]), np.float32)
+        explored = np.empty((i["rows"], i["cols"]), np.uint8)
+        sec = lib().ref_wavefront(self.h, _d3(goal), C.c_double(rev), C.c_double(fwd), _p(cost), _p(explored))
+        return cost, explored.astype(bool), sec
+
+
+def nonholo_build(lb, ub, spatial_res=1.0, ang_res=0.0872, rmin=2.0, rev=1.0, fwd=1.0, sw=0.0):
+    dims = np.zeros(3, np.int32)
+    off = np.zeros(2, np.float64)
+    lib().ref_nonholo_build(_d3(lb), _d3(ub), C.c_double(spatial_res), C.c_double(ang_res), C.c_double(rmin),
+                            C.c_double(rev), C.c_double(fwd), C.c_double(sw), _p(dims), _p(off), None)
+    vals = np.empty(tuple(dims.tolist()), np.float64)
+    sec = lib().ref_nonholo_build(_d3(lb), _d3(ub), C.c_double(spatial_res), C.c_double(ang_res), C.c_double(rmin),
+                                  C.c_double(rev), C.c_double(fwd), C.c_double(sw), _p(dims), _p(off), _p(vals))
+    return vals, off, sec

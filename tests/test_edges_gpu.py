@@ -1,0 +1,143 @@
+"""GPU parity tests of the collision-checked edge path (A3, A4, A7) through the C ABI.
+
+Bars (BASELINE.json north_star): collision verdicts and chosen path words bit-exact; `last`
+ratios, Reeds-Shepp lengths and costs within 1e-6 relative (double transcendental functions on
+the device are not the host libm, SURVEY.md section 7 hard part 4).
+"""
+import numpy as np
+import pytest
+
+import pathplanning_b200 as pp
+from common import load_kat, load_npz, c2_world_desc, assert_close_rel
+
+pytestmark = pytest.mark.gpu
+REL = 1e-6
+
+
+def _edges_from(g, prefix=""):
+    return pp.make_rs_edges(g[prefix + "starts"] if prefix else g["starts"], g["steer"], g["dir"], g["len"])
+
+
+def test_rs_kat_words(ctx):
+    """The reference's own 48 known-answer cases (planner/tests/test_reeds_shepp.cpp:38-300)."""
+    kat = load_kat()
+    starts = np.array([c["start"] for c in kat["cases"]])
+    goals = np.array([c["goal"] for c in kat["cases"]])
+    for shortest in (0, 1):
+        r = ctx.rs_solve(starts, goals, pp.RSCostParams(1.0, 1.0, 1.0, 0.0, shortest))
+        for i, c in enumerate(kat["cases"]):
+            assert int(r["word"][i]) in c["words"], (i, kat["word_names"][int(r["word"][i])], c)
+        key = "ref_shortest_word" if shortest else "ref_optimal_word"
+        assert [int(w) for w in r["word"]] == [c[key] for c in kat["cases"]]
+        assert_close_rel(r["length"], [c["ref_length"] for c in kat["cases"]], REL, "KAT length")
+        # closure: the path built from the solution ends on the goal (test_reeds_shepp.cpp:17-22)
+        end = ctx.rs_interpolate(r["edges"], 1.0, np.array([1.0]))[:, 0, :]
+        assert np.abs(end[:, :2] - goals[:, :2]).max() < 1e-6
+        assert np.abs(end[:, 2] - goals[:, 2]).max() < 1e-6 * np.pi / 180
+
+
+@pytest.mark.parametrize("tag", ["default", "weighted"])
+def test_rs_random_golden(ctx, tag):
+    g = load_npz("rs_random.npz")
+    rmin, rev, fwd, sw = g[f"{tag}_params"]
+    r = ctx.rs_solve(g["starts"], g["goals"], pp.RSCostParams(rmin, rev, fwd, sw))
+    word = g[f"{tag}_word"].astype(np.int32)
+    assert np.array_equal(r["word"], word), f"{(r['word'] != word).sum()} words differ"
+    e = r["edges"]
+    code = np.zeros(len(word), np.uint64)
+    for i in range(5):
+        code |= ((g[f"{tag}_steer"][:, i].astype(np.uint64) & 3) | ((g[f"{tag}_dir"][:, i].astype(np.uint64) & 3) << 2)) << np.uint64(4 * i)
+    valid_motion = g[f"{tag}_dir"] != 2
+    mask = np.zeros(len(word), np.uint64)
+    for i in range(5):
+        mask |= np.where(valid_motion[:, i], np.uint64(0xF), np.uint64(0)) << np.uint64(4 * i)
+    assert np.array_equal(e["code"] & mask, code & mask)
+    assert_close_rel(np.where(valid_motion, e["len"], 0.0), np.where(valid_motion, g[f"{tag}_len"], 0.0), 1e-6, "motion lengths")
+    assert_close_rel(r["length"], g[f"{tag}_length"], REL, "length")
+    assert_close_rel(r["cost"], g[f"{tag}_cost"], REL, "cost")
+
+
+@pytest.fixture(scope="module")
+def c2(ctx):
+    g = load_npz("edges_c2.npz")
+    desc, occ, sq, pc = c2_world_desc(g)
+    ctx.upload_map(desc, sq, occ, pc)
+    return g
+
+
+def test_is_state_valid_golden(ctx, c2):
+    got = ctx.is_state_valid(c2["sv_pts"], pp.ValidatorParams(1.0, 0.1))
+    assert np.array_equal(got, c2["sv_valid"])
+
+
+@pytest.mark.parametrize("tag", ["r10", "r03"])
+def test_check_rs_edges_golden(ctx, c2, tag):
+    """Check-only: the reference's pre-solved segments go in, verdict / last / sample count out."""
+    radius, step = c2[f"{tag}_params"]
+    edges = pp.make_rs_edges(c2["starts"], c2["steer"], c2["dir"], c2["len"])
+    valid, last, samples = ctx.check_edges_rs(edges, 2.0, pp.ValidatorParams(float(radius), float(step)), want_samples=True)
+    assert np.array_equal(valid, c2[f"{tag}_valid"]), f"{(valid != c2[f'{tag}_valid']).sum()} verdicts differ"
+    assert np.array_equal(samples.astype(np.int64), c2[f"{tag}_samples"].astype(np.int64))
+    assert_close_rel(last, c2[f"{tag}_last"], REL, "last")
+    assert 0.05 < valid.mean() < 0.95  # the fixture exercises both outcomes
+
+
+def test_connect_check_rs_golden(ctx, c2):
+    """Fused solve + check from raw start/goal pairs."""
+    r = ctx.connect_check_rs(c2["starts"], c2["goals"], pp.RSCostParams(2.0), pp.ValidatorParams(1.0, 0.1))
+    assert np.array_equal(r["word"], c2["word"].astype(np.int32))
+    assert np.array_equal(r["valid"], c2["r10_valid"])
+    assert_close_rel(r["last"], c2["r10_last"], REL, "last")
+    assert_close_rel(r["length"], c2["length"], REL, "length")
+    assert_close_rel(r["cost"], c2["cost"], REL, "cost")
+
+
+def test_check_csteer_golden(ctx, c2):
+    e = pp.make_csteer_edges(c2["cs_start"], c2["cs_steer"], c2["cs_len"], c2["cs_dir"], wheelbase=2.6)
+    valid, last, final = ctx.check_edges_csteer(e, pp.ValidatorParams(1.0, 0.1), want_final=True)
+    assert np.array_equal(valid, c2["cs_valid"])
+    assert_close_rel(last, c2["cs_last"], REL, "last")
+    assert np.abs(final - c2["cs_final"]).max() < 1e-9
+
+
+def test_check_line_golden(ctx, c2):
+    e = np.zeros(len(c2["ln_a"]), dtype=pp.LINE_EDGE)
+    e["from"], e["to"] = c2["ln_a"], c2["ln_b"]
+    valid, last = ctx.check_edges_line(e, pp.ValidatorParams(1.0, 0.1))
+    assert np.array_equal(valid, c2["ln_valid"])
+    assert_close_rel(last, c2["ln_last"], REL, "last")
+
+
+def test_empty_and_degenerate(ctx, c2):
+    vp = pp.ValidatorParams(1.0, 0.1)
+    v, l = ctx.check_edges_rs(np.zeros(0, dtype=pp.RS_EDGE), 2.0, vp)
+    assert len(v) == 0 and len(l) == 0
+    # a segment with no motion: zero-length path => validity of the initial state, last = 1
+    e = pp.make_rs_edges(np.array([[0.0, 0.0, 0.0], [-15.9, -12.1, 0.0]]), np.zeros((2, 5), int), np.full((2, 5), 2), np.full((2, 5), np.inf))
+    v, l = ctx.check_edges_rs(e, 2.0, vp)
+    assert np.array_equal(v, ctx.is_state_valid(e["start"], vp)) and np.all(l == 1.0)
+
+
+def test_live_reference_large(ctx, ref):
+    """100k fresh edges on the C2 map against the compiled reference running here."""
+    g = load_npz("edges_c2.npz")
+    w = ref.World(g["lb"], g["ub"], float(g["resolution"]))
+    for r in g["rects"]:
+        w.add_rectangle(*r)
+    w.update()
+    occ, sq = w.grids()
+    ctx.upload_map(w.map_desc(), sq, occ, None)
+    rng = np.random.default_rng(99)
+    n = 100000
+    starts = np.stack([rng.uniform(-20, 20, n), rng.uniform(-20, 20, n), rng.uniform(-np.pi, np.pi, n)], 1)
+    d, a = rng.uniform(0.1, 15, n), rng.uniform(-np.pi, np.pi, n)
+    goals = np.stack([starts[:, 0] + d * np.cos(a), starts[:, 1] + d * np.sin(a), rng.uniform(-np.pi, np.pi, n)], 1)
+    rr = w.check_rs_edges(starts, goals, 2.0)
+    got = ctx.connect_check_rs(starts, goals, pp.RSCostParams(2.0), pp.ValidatorParams(1.0, 0.1))
+    assert np.array_equal(got["word"], rr["word"])
+    assert np.array_equal(got["valid"], rr["valid"])
+    assert_close_rel(got["last"], rr["last"], REL, "last")
+    edges = pp.make_rs_edges(starts, rr["steer"], rr["dir"], rr["len"])
+    v, l, s = ctx.check_edges_rs(edges, 2.0, pp.ValidatorParams(1.0, 0.1), want_samples=True)
+    assert np.array_equal(v, rr["valid"]) and np.array_equal(s.astype(np.int64), rr["samples"].astype(np.int64))
+    w.close()
