@@ -202,7 +202,12 @@ def ours_main(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = pp.Context(local_rank)
-    stream = torch.cuda.current_stream()
+    # A dedicated (non-null) stream shared by torch and the context: ppx_ctx_set_stream(NULL) means
+    # "the context's own stream", so torch's legacy default stream (handle 0) must not be passed --
+    # the events below would then bracket nothing (that was the bug of the first r1 run).
+    stream = torch.cuda.Stream(device=torch.device("cuda", local_rank))
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     ctx.set_stream(stream.cuda_stream)
 
     # world model: replicated on every rank (setup, untimed)
@@ -270,14 +275,19 @@ def ours_main(args):
     launches0 = ctx.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler.active.set()
+    wall0 = time.perf_counter()
     ev0.record(stream)
     for i in range(args.steps):
         step(i % N_BATCHES)
     ev1.record(stream)
     barrier()
+    wall_ms = (time.perf_counter() - wall0) * 1e3
     sampler.active.clear()
     launches = ctx.launch_count - launches0
     ms = ev0.elapsed_time(ev1)
+    # the events must bracket the kernels: device time and host wall time of the same region agree
+    if not (0.5 * wall_ms <= ms <= 1.05 * wall_ms + 0.5):
+        raise RuntimeError(f"timing self-check failed: events {ms:.3f} ms vs wall {wall_ms:.3f} ms")
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

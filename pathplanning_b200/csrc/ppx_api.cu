@@ -69,6 +69,7 @@ int ppx_ctx_create(int device, ppx_ctx** out)
 	PPX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
 	ctx->stream = ctx->own_stream;
 	PPX_CUDA(ctx, cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device));
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_queue, 64));
 	*out = ctx;
 	return PPX_OK;
 }
@@ -83,6 +84,7 @@ int ppx_ctx_destroy(ppx_ctx* ctx)
 	cudaFree(ctx->d_occupancy);
 	cudaFree(ctx->d_pathcost);
 	cudaFree(ctx->d_clearance);
+	cudaFree(ctx->d_queue);
 	cudaFree(ctx->d_nonholo);
 	cudaFree(ctx->d_wf_cost);
 	cudaFree(ctx->d_wf_explored);

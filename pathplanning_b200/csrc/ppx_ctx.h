@@ -31,6 +31,7 @@ struct ppx_ctx {
 		size_t bytes = 0;
 	};
 	Scratch scratch[8];
+	unsigned long long* d_queue = nullptr; // work-queue cursor of the lane-refill kernels
 
 	// non-holonomic table (A9)
 	bool has_nonholo = false;

@@ -3,8 +3,7 @@
 // and its float/double mixing, because collision verdicts and `last` ratios are compared
 // bit-for-bit with the reference.  Compiled with -fmad=false (no FMA contraction).
 #pragma once
-#include <cstdint>
-#include <cuda_runtime.h>
+#include "ppx_hd.h"
 #include "ppx.h"
 
 #define PPX_PI 3.14159265358979323846
@@ -33,7 +32,7 @@ struct Pose {
 
 // Pose2<double>::WrapTheta, geometry/2dplane.h:36-45.  Non-finite / astronomically large
 // headings would spin forever in the reference; the kernel returns them unchanged instead.
-__device__ __forceinline__ double wrap_theta(double t)
+PPX_HD double wrap_theta(double t)
 {
 	if (!(fabs(t) < 1e15))
 		return t;
@@ -46,7 +45,7 @@ __device__ __forceinline__ double wrap_theta(double t)
 
 // static_cast<int>(double) as x86-64 cvttsd2si does it (out of range / NaN -> INT_MIN),
 // occupancy_map.h:108-109.
-__device__ __forceinline__ int trunc_i32(double v)
+PPX_HD int trunc_i32(double v)
 {
 	if (!(v > -2147483649.0 && v < 2147483648.0))
 		return INT_MIN;
@@ -54,12 +53,12 @@ __device__ __forceinline__ int trunc_i32(double v)
 }
 
 // std::min(a,b) / std::max(a,b) with the library's comparison direction (matters for NaN).
-__device__ __forceinline__ double std_min(double a, double b) { return (b < a) ? b : a; }
-__device__ __forceinline__ float std_minf(float a, float b) { return (b < a) ? b : a; }
-__device__ __forceinline__ float std_maxf(float a, float b) { return (a < b) ? b : a; }
+PPX_HD double std_min(double a, double b) { return (b < a) ? b : a; }
+PPX_HD float std_minf(float a, float b) { return (b < a) ? b : a; }
+PPX_HD float std_maxf(float a, float b) { return (a < b) ? b : a; }
 
 // Maths::Modulo, utils/maths.h:9-16
-__device__ __forceinline__ double modulo(double in, double mod)
+PPX_HD double modulo(double in, double mod)
 {
 	double out = fmod(in, mod);
 	if (out < 0)
@@ -69,7 +68,7 @@ __device__ __forceinline__ double modulo(double in, double mod)
 
 // StateValidatorOccupancyMap::IsStateValid, state_validator_occupancy_map.cpp:15-26.
 // Returns validity; *dist receives the clearance of the pose's cell when it is inside the map.
-__device__ __forceinline__ bool is_state_valid(const MapDev& m, double x, double y, double th, float minSafeRadius, float* dist)
+PPX_HD bool is_state_valid(const MapDev& m, double x, double y, double th, float minSafeRadius, float* dist)
 {
 	// Pose2d localState(WorldPositionToLocalPosition(position), theta): the ctor wraps theta
 	double lx = x - m.lox;
@@ -83,13 +82,13 @@ __device__ __forceinline__ bool is_state_valid(const MapDev& m, double x, double
 	bool inBounds = !(lx < m.lbx || lx > m.ubx) && !(ly < m.lby || ly > m.uby) && !(lth < m.lbt || lth > m.ubt);
 	if (!inBounds || !inside)
 		return false;
-	float d = __ldg(m.clearance + (size_t)row * m.cols + col);
+	float d = PPX_LDG(m.clearance + (size_t)row * m.cols + col);
 	*dist = d;
 	return d >= minSafeRadius;
 }
 
 // The step of IsPathValid after a valid sample, state_validator_occupancy_map.cpp:54-65.
-__device__ __forceinline__ double next_step(const MapDev& m, double x, double y, float distance, float minSafeRadius, float minStep)
+PPX_HD double next_step(const MapDev& m, double x, double y, float distance, float minSafeRadius, float minStep)
 {
 	// std::min({a,b,c,d}) keeps the first element unless a later one compares less
 	double b0 = x - m.lbx;
@@ -112,14 +111,14 @@ __device__ __forceinline__ double next_step(const MapDev& m, double x, double y,
 struct RSSeg {
 	double len[5];
 	uint32_t code; // 4 bits per motion: steer | dir<<2
-	__device__ __forceinline__ int steer(int i) const { return (code >> (4 * i)) & 3; }
-	__device__ __forceinline__ int dir(int i) const { return (code >> (4 * i + 2)) & 3; }
+	PPX_HD int steer(int i) const { return (code >> (4 * i)) & 3; }
+	PPX_HD int dir(int i) const { return (code >> (4 * i + 2)) & 3; }
 	// Motion::IsValid, reeds_shepp.cpp:305-308
-	__device__ __forceinline__ bool valid(int i) const { return i < 5 && len[i] != PPX_INF && dir(i) != 2; }
+	PPX_HD bool valid(int i) const { return i < 5 && len[i] != PPX_INF && dir(i) != 2; }
 };
 
 // PathSegment::m_length as AddMotion accumulates it (reeds_shepp.cpp:319-335)
-__device__ __forceinline__ double rs_total_length(const RSSeg& s)
+PPX_HD double rs_total_length(const RSSeg& s)
 {
 	double total = 0.0;
 	for (int i = 0; i < 5; i++) {
@@ -131,7 +130,7 @@ __device__ __forceinline__ double rs_total_length(const RSSeg& s)
 }
 
 // Pose2 operator+ (2dplane.h:49-62) with the rotation of the left pose cached (sL, cL).
-__device__ __forceinline__ Pose pose_compose(const Pose& l, double sL, double cL, double rx, double ry, double rth)
+PPX_HD Pose pose_compose(const Pose& l, double sL, double cL, double rx, double ry, double rth)
 {
 	Pose out;
 	out.x = (cL * rx + (-sL) * ry) + l.x;
@@ -142,7 +141,7 @@ __device__ __forceinline__ Pose pose_compose(const Pose& l, double sL, double cL
 
 // PathReedsShepp::Straight / Turn (path_reeds_shepp.cpp:121-151) applied to a knot pose whose
 // sin/cos are cached.  `amount` = motion.length * motionRatio.
-__device__ __forceinline__ Pose rs_advance(const Pose& k, double sK, double cK, int steer, int dir, double amount, double r)
+PPX_HD Pose rs_advance(const Pose& k, double sK, double cK, int steer, int dir, double amount, double r)
 {
 	if (steer == 1) { // Straight
 		double length = amount;
@@ -182,7 +181,7 @@ struct RSWalker {
 	double lenAcc; // `length` accumulated over completed motions
 	int m;
 
-	__device__ __forceinline__ void init(const Pose& start)
+	PPX_HD void init(const Pose& start)
 	{
 		k = start;
 		sincos(k.th, &sK, &cK);
@@ -191,7 +190,7 @@ struct RSWalker {
 	}
 
 	// Pose at `target` = ratio * totalLength (targets must be non-decreasing across calls).
-	__device__ __forceinline__ Pose at(const RSSeg& s, double r, double target)
+	PPX_HD Pose at(const RSSeg& s, double r, double target)
 	{
 		while (true) {
 			if (!s.valid(m))
@@ -217,7 +216,7 @@ struct RSWalker {
 
 // StateValidatorOccupancyMap::IsPathValid on a PathReedsShepp,
 // state_validator_occupancy_map.cpp:28-71.
-__device__ __forceinline__ bool rs_is_path_valid(const MapDev& map, const Pose& start, const RSSeg& seg, double r,
+PPX_HD bool rs_is_path_valid(const MapDev& map, const Pose& start, const RSSeg& seg, double r,
 	float minSafeRadius, float minStep, float* last, unsigned* samples)
 {
 	const double pathLength = rs_total_length(seg) * r; // PathSegment::GetLength(r)
@@ -253,6 +252,163 @@ __device__ __forceinline__ bool rs_is_path_valid(const MapDev& map, const Pose& 
 }
 
 // ---------------------------------------------------------------------------------------------
+// Lane state machine of the re-converging Reeds-Shepp edge checker ("lane refill").
+//
+// IsPathValid on an RS path is a chain of data-dependent samples, each of which walks a
+// data-dependent number of motions.  Run as one thread per edge that costs 26 of 32 lanes
+// (ncu r1a: 6.1 active threads per instruction).  Here the same arithmetic is cut into uniform
+// MICRO-STEPS -- each is "apply (part of) one motion to the current knot", needs exactly one
+// sincos, and ends either in a knot commit (the motion ended before the target) or in a sample
+// (IsStateValid + next step).  A warp keeps 32 such lanes busy and refills finished lanes from
+// its edge queue, so every lane executes the same instruction stream all the time.
+//   pre()  -> argument of the one sincos of this micro-step
+//   post() -> consumes sin/cos, returns true when the edge is finished (verdict/last/ns set)
+// The sin/cos of a committed knot's heading follow from the angle-addition identities applied to
+// the cached sin/cos of the previous knot and the turn's half-angle sin/cos that the chord formula
+// already needs, instead of a second sincos of the new heading.
+template <class LenStore>
+struct RSLane {
+	double pathLength;
+	uint32_t code;
+	Pose k;
+	double sK, cK, lenAcc;
+	int m; // -1: the micro-step that evaluates sincos(start.theta)
+	double length, lastValidLength;
+	unsigned ns;
+	bool verdict;
+	float last;
+	// scratch pre() -> post()
+	double amount, motionLength, target;
+	int kind; // 0 init, 1 motion, 2 sample at the knot (ran past the last valid motion)
+
+	PPX_HD int steer(int i) const { return (code >> (4 * i)) & 3; }
+	PPX_HD int dir(int i) const { return (code >> (4 * i + 2)) & 3; }
+	PPX_HD bool valid(const LenStore& L, int i) const { return i < 5 && dir(i) != 2 && L.get(i) != PPX_INF; }
+
+	// `L` must already hold the 5 normalised motion lengths of the edge.
+	PPX_HD void begin(const LenStore& L, const Pose& start, uint32_t code_, double r)
+	{
+		code = code_;
+		k = start;
+		double total = 0.0; // PathSegment::m_length as AddMotion accumulates it
+		for (int i = 0; i < 5; i++) {
+			if (!valid(L, i))
+				break;
+			total += fabs(L.get(i));
+		}
+		pathLength = total * r;
+		lenAcc = 0.0;
+		m = -1;
+		length = 0.0;
+		lastValidLength = 0.0;
+		ns = 0;
+	}
+
+	PPX_HD double pre(const LenStore& L, double r)
+	{
+		if (m < 0) {
+			kind = 0;
+			return k.th;
+		}
+		target = (length / pathLength) * pathLength; // Interpolate(length / pathLength): ratio * totalLength
+		while (valid(L, m) && L.get(m) * r == 0)
+			m++; // `continue` on zero-length motions, path_reeds_shepp.cpp:27-28
+		if (!valid(L, m)) {
+			kind = 2;
+			return 0.0;
+		}
+		kind = 1;
+		double len = L.get(m);
+		motionLength = len * r;
+		double motionRatio = (target - lenAcc) / motionLength;
+		motionRatio = std_min(motionRatio, 1.0);
+		amount = len * motionRatio;
+		if (steer(m) == 1)
+			return 0.0;
+		double turnAngle = amount;
+		if (dir(m) == 1)
+			turnAngle = -turnAngle;
+		return turnAngle / 2;
+	}
+
+	PPX_HD bool sample(const MapDev& map, const Pose& p, float minSafeRadius, float minStep)
+	{
+		float dist = 0.0f;
+		ns++;
+		if (!is_state_valid(map, p.x, p.y, p.th, minSafeRadius, &dist)) {
+			verdict = false;
+			last = (float)(lastValidLength / pathLength);
+			return true;
+		}
+		lastValidLength = length;
+		length += next_step(map, p.x, p.y, dist, minSafeRadius, minStep);
+		if (length < pathLength)
+			return false;
+		verdict = true;
+		last = 1.0f;
+		return true;
+	}
+
+	PPX_HD bool post(const MapDev& map, double s, double c, double r, float minSafeRadius, float minStep)
+	{
+		if (kind == 0) {
+			sK = s;
+			cK = c;
+			m = 0;
+			if (pathLength == 0.0) { // state_validator_occupancy_map.cpp:34-38
+				float dist;
+				ns = 1;
+				last = 1.0f;
+				verdict = is_state_valid(map, k.x, k.y, k.th, minSafeRadius, &dist);
+				return true;
+			}
+			return false;
+		}
+		if (kind == 2)
+			return sample(map, k, minSafeRadius, minStep);
+		const int st = steer(m), dr = dir(m);
+		Pose p;
+		double sT = 0.0, cT = 1.0;
+		if (st == 1) { // PathReedsShepp::Straight, path_reeds_shepp.cpp:121-133
+			double len = amount;
+			if (dr == 1)
+				len = -len;
+			len *= r;
+			p.x = k.x + len * cK;
+			p.y = k.y + len * sK;
+			p.th = wrap_theta(k.th);
+		} else { // PathReedsShepp::Turn, :135-151
+			double turnAngle = amount;
+			if (dr == 1)
+				turnAngle = -turnAngle;
+			double chord = 2 * s * r;
+			double x = chord * c;
+			double y = chord * s;
+			sT = 2 * s * c;
+			cT = c * c - s * s;
+			if (st == 2) {
+				y *= -1;
+				turnAngle *= -1;
+				sT = -sT;
+			}
+			p = pose_compose(k, sK, cK, x, y, wrap_theta(turnAngle));
+		}
+		double lenEnd = lenAcc + motionLength;
+		if (lenEnd >= target)
+			return sample(map, p, minSafeRadius, minStep);
+		// the motion ends before the target: commit its end pose as the next knot
+		k = p;
+		double sN = sK * cT + cK * sT;
+		double cN = cK * cT - sK * sT;
+		sK = sN;
+		cK = cN;
+		lenAcc = lenEnd;
+		m++;
+		return false;
+	}
+};
+
+// ---------------------------------------------------------------------------------------------
 // Constant-steer primitive (paths/path_constant_steer.cpp, models/kinematic_bicycle_model.cpp:5-32)
 
 struct CSteer {
@@ -263,7 +419,7 @@ struct CSteer {
 	bool curved; // abs(DthetaDdist) > 1e-9
 	double sT0, cT0; // sin/cos(start.th) for the straight branch
 
-	__device__ __forceinline__ void init(const ppx_csteer_edge& e)
+	PPX_HD void init(const ppx_csteer_edge& e)
 	{
 		start = { e.start[0], e.start[1], e.start[2] };
 		length = e.length;
@@ -279,7 +435,7 @@ struct CSteer {
 	}
 
 	// PathConstantSteer::Interpolate -> KinematicBicycleModel::ConstantSteer(m_init, steering, m_length*ratio, dir)
-	__device__ __forceinline__ Pose at_dist(double dist) const
+	PPX_HD Pose at_dist(double dist) const
 	{
 		if (dir == 1)
 			dist = -dist;
@@ -297,10 +453,10 @@ struct CSteer {
 		}
 		return to;
 	}
-	__device__ __forceinline__ Pose at(double ratio) const { return at_dist(length * ratio); }
+	PPX_HD Pose at(double ratio) const { return at_dist(length * ratio); }
 };
 
-__device__ __forceinline__ bool csteer_is_path_valid(const MapDev& map, const CSteer& p, float minSafeRadius, float minStep,
+PPX_HD bool csteer_is_path_valid(const MapDev& map, const CSteer& p, float minSafeRadius, float minStep,
 	float* last, unsigned* samples)
 {
 	const double pathLength = p.length;
@@ -332,7 +488,7 @@ __device__ __forceinline__ bool csteer_is_path_valid(const MapDev& map, const CS
 
 // ---------------------------------------------------------------------------------------------
 // Straight SE(2) segment (paths/path_se2.cpp:5-22)
-__device__ __forceinline__ bool line_is_path_valid(const MapDev& map, const Pose& a, const Pose& b, float minSafeRadius,
+PPX_HD bool line_is_path_valid(const MapDev& map, const Pose& a, const Pose& b, float minSafeRadius,
 	float minStep, float* last)
 {
 	double dx = b.x - a.x, dy = b.y - a.y;
@@ -362,15 +518,15 @@ __device__ __forceinline__ bool line_is_path_valid(const MapDev& map, const Pose
 // ---------------------------------------------------------------------------------------------
 // Reeds-Shepp solver (geometry/reeds_shepp.cpp)
 
-__device__ __forceinline__ bool angle_invalid(double t) { return t < 0 || t > PPX_PI; } // :13-16
-__device__ __forceinline__ double wrap_angle(double t) { return modulo(t + PPX_PI, 2 * PPX_PI) - PPX_PI; } // :18-21
+PPX_HD bool angle_invalid(double t) { return t < 0 || t > PPX_PI; } // :13-16
+PPX_HD double wrap_angle(double t) { return modulo(t + PPX_PI, 2 * PPX_PI) - PPX_PI; } // :18-21
 
 // Per base word: 5 x (steer|dir<<2) nibbles and 5 x length selectors (0 t, 1 u, 2 v, 3 pi/2, 7 none).
 // Built from reeds_shepp.cpp:299-... "Path" builders (:162-297).
 //                         L=0 S=1 R=2 ; F=0 B=1
 #define PPX_M(steer, dir) ((steer) | ((dir) << 2))
 #define PPX_NONE 0xA /* steer=2, dir=2(NoMotion) */
-__device__ __constant__ unsigned char c_rs_base_motion[12][5] = {
+PPX_CONST unsigned char c_rs_base_motion[12][5] = {
 	{ PPX_M(0, 0), PPX_M(1, 0), PPX_M(0, 0), PPX_NONE, PPX_NONE }, // LfSfLf
 	{ PPX_M(0, 0), PPX_M(1, 0), PPX_M(2, 0), PPX_NONE, PPX_NONE }, // LfSfRf
 	{ PPX_M(0, 0), PPX_M(2, 1), PPX_M(0, 0), PPX_NONE, PPX_NONE }, // LfRbLf
@@ -384,7 +540,7 @@ __device__ __constant__ unsigned char c_rs_base_motion[12][5] = {
 	{ PPX_M(0, 0), PPX_M(1, 0), PPX_M(0, 0), PPX_M(2, 1), PPX_NONE }, // LfSfLfpi2Rb
 	{ PPX_M(0, 0), PPX_M(2, 1), PPX_M(1, 1), PPX_M(0, 1), PPX_M(2, 0) }, // LfRbpi2SbLbpi2Rf
 };
-__device__ __constant__ unsigned char c_rs_base_len[12][5] = {
+PPX_CONST unsigned char c_rs_base_len[12][5] = {
 	{ 0, 1, 2, 7, 7 }, { 0, 1, 2, 7, 7 }, { 0, 1, 2, 7, 7 }, { 0, 1, 2, 7, 7 }, { 0, 1, 2, 7, 7 },
 	{ 0, 1, 1, 2, 7 }, { 0, 1, 1, 2, 7 },
 	{ 0, 3, 1, 2, 7 }, { 0, 3, 1, 2, 7 },
@@ -394,7 +550,7 @@ __device__ __constant__ unsigned char c_rs_base_len[12][5] = {
 
 // GetPath(word, t, u, v) (:571-606): motions of base word w/4, then Timeflip (w%4 & 1) and
 // Reflect (w%4 & 2) transforms (:495-516).  Returns m_length.
-__device__ __forceinline__ double rs_build_segment(int word, double t, double u, double v, RSSeg& seg)
+PPX_HD double rs_build_segment(int word, double t, double u, double v, RSSeg& seg)
 {
 	const int base = word >> 2, q = word & 3;
 	double total = 0.0;
@@ -421,7 +577,7 @@ __device__ __forceinline__ double rs_build_segment(int word, double t, double u,
 }
 
 // PathSegment::ComputeCost (:347-376)
-__device__ __forceinline__ float rs_compute_cost(const RSSeg& seg, double mLength, double r, float rev, float fwd, float sw)
+PPX_HD float rs_compute_cost(const RSSeg& seg, double mLength, double r, float rev, float fwd, float sw)
 {
 	if (!seg.valid(0))
 		return __int_as_float(0x7f800000);
@@ -455,7 +611,7 @@ struct RSGoalTerms {
 
 // GetMotionLengths (:537-569) for base word `base` on the mirrored goal.  `a` holds the terms of
 // the "minus" family (x - sin, y - 1 + cos), `b` those of the "plus" family (x + sin, y - 1 - cos).
-__device__ __forceinline__ double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerms& b, double& t, double& u, double& v)
+PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerms& b, double& t, double& u, double& v)
 {
 	const double INF = PPX_INF;
 	switch (base) {
@@ -595,7 +751,7 @@ struct RSSolution {
 };
 
 // Solver::GetOptimalPath (:654-683) when shortest == 0, Solver::GetShortestPath (:608-652) else.
-__device__ __forceinline__ void rs_solve(const Pose& start, const Pose& goal, double r, float rev, float fwd, float sw,
+PPX_HD void rs_solve(const Pose& start, const Pose& goal, double r, float rev, float fwd, float sw,
 	int shortest, RSSolution& out)
 {
 	// GetGoalArray (:518-535): newGoal = goal - start (2dplane.h:64-78), scaled by 1/r

@@ -38,22 +38,80 @@ __global__ void __launch_bounds__(kThreads) k_is_state_valid(MapDev map, int64_t
 	}
 }
 
-__global__ void __launch_bounds__(kThreads) k_check_rs(MapDev map, int64_t n, const ppx_rs_edge* __restrict__ edges, double r,
-	float minSafeRadius, float minStep, uint8_t* __restrict__ valid, float* __restrict__ last, uint32_t* __restrict__ samples)
+// Per-thread column of the CTA's shared-memory copy of the motion lengths: the lane machine
+// indexes them with a data-dependent motion number, which in registers would spill to local memory.
+struct SmemLen {
+	const double* col; // &s_len[0][threadIdx.x]
+	__device__ __forceinline__ double get(int i) const { return col[i * kThreads]; }
+};
+
+// A7 on Reeds-Shepp edges, re-converging form: every lane runs the RSLane micro-step machine
+// (ppx_device.cuh) on its own edge; finished lanes are refilled by warp vote from the warp's chunk
+// of the edge queue (chunks of kGrab edges are taken from one global counter), so the 32 lanes of
+// a warp stay on one instruction stream although edges need between 1 and ~200 samples.
+constexpr int kGrab = 128;
+constexpr int kCheckCtasPerSm = 8;
+
+__global__ void __launch_bounds__(kThreads, kCheckCtasPerSm) k_check_rs(MapDev map, int64_t n, const ppx_rs_edge* __restrict__ edges, double r,
+	float minSafeRadius, float minStep, uint8_t* __restrict__ valid, float* __restrict__ last, uint32_t* __restrict__ samples,
+	unsigned long long* __restrict__ queue)
 {
-	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-	int64_t stride = (int64_t)gridDim.x * blockDim.x;
-	for (; i < n; i += stride) {
-		Pose start;
-		RSSeg seg;
-		load_rs_edge(edges + i, start, seg);
-		float l;
-		unsigned ns;
-		bool ok = rs_is_path_valid(map, start, seg, r, minSafeRadius, minStep, &l, &ns);
-		valid[i] = ok ? 1 : 0;
-		last[i] = l;
-		if (samples)
-			samples[i] = ns;
+	__shared__ double s_len[5][kThreads];
+	const unsigned lane_id = threadIdx.x & 31;
+	const unsigned lt_mask = (1u << lane_id) - 1;
+	double* mycol = &s_len[0][threadIdx.x];
+	SmemLen L { mycol };
+	RSLane<SmemLen> lane;
+	bool active = false;
+	int64_t idx = 0;
+	int64_t cursor = 0, limit = 0; // warp-uniform
+	bool exhausted = false; // warp-uniform
+
+	while (true) {
+		unsigned idle = __ballot_sync(0xffffffffu, !active);
+		if (idle) {
+			if (cursor >= limit && !exhausted) {
+				unsigned long long base = 0;
+				if (lane_id == 0)
+					base = atomicAdd(queue, (unsigned long long)kGrab);
+				base = __shfl_sync(0xffffffffu, base, 0);
+				cursor = (int64_t)base;
+				limit = cursor + kGrab < n ? cursor + kGrab : n;
+				if (cursor >= n) {
+					exhausted = true;
+					limit = cursor;
+				}
+			}
+			int64_t avail = limit - cursor;
+			int rank = __popc(idle & lt_mask);
+			if (!active && rank < avail) {
+				idx = cursor + rank;
+				const ppx_rs_edge* e = edges + idx;
+				Pose start = { e->start[0], e->start[1], e->start[2] };
+				#pragma unroll
+				for (int i = 0; i < 5; i++)
+					mycol[i * kThreads] = e->len[i];
+				lane.begin(L, start, (uint32_t)e->code, r);
+				active = true;
+			}
+			int need = __popc(idle);
+			cursor += need < avail ? need : avail;
+			if (!__any_sync(0xffffffffu, active)) {
+				if (exhausted)
+					break;
+				continue;
+			}
+		}
+		double arg = active ? lane.pre(L, r) : 0.0;
+		double s, c;
+		sincos(arg, &s, &c);
+		if (active && lane.post(map, s, c, r, minSafeRadius, minStep)) {
+			valid[idx] = lane.verdict ? 1 : 0;
+			last[idx] = lane.last;
+			if (samples)
+				samples[idx] = lane.ns;
+			active = false;
+		}
 	}
 }
 
@@ -206,8 +264,9 @@ int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (d_edges && d_valid && d_last)), "bad arguments");
 	if (n == 0)
 		return PPX_OK;
-	k_check_rs<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_edges, min_turning_radius,
-		vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples);
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
+	k_check_rs<<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_edges,
+		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue);
 	PPX_LAUNCHED(ctx);
 	return PPX_OK;
 }
