@@ -195,6 +195,19 @@ int ppx_connect_check_rs_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, co
 int ppx_rs_interpolate(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius, int32_t nratios,
 	const double* ratios, double* poses);
 
+/* ------------------------------------------------------------------------------------------ */
+/* A8: ObstaclesHeuristic::Update, batched over goals  (algo/heuristics.cpp:106-153)           */
+/*
+ * For each goal pose (3 doubles, only x,y are used) runs the holonomic-with-obstacles wavefront
+ * over the uploaded occupancy grid with the reference's exact semantics (first reach wins, pops
+ * in ascending float cost with LIFO ties, utils/frontier.h:39-48,83-91).
+ *   cost      n * rows * cols floats: ObstaclesHeuristic::m_cost (+inf where never reached)
+ *   explored  optional n * rows * cols bytes: ObstaclesHeuristic::m_explored
+ * A goal outside the map leaves its grid all +inf (heuristics.cpp:115-117).
+ */
+int ppx_wavefront(ppx_ctx* ctx, int64_t n, const double* goals, float* cost, uint8_t* explored);
+int ppx_wavefront_dev(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored);
+
 #ifdef __cplusplus
 }
 #endif

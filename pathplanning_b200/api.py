@@ -242,3 +242,14 @@ class Context:
         poses = np.empty((n, nr, 3), dtype=np.float64)
         self._check(ppx.ppx_rs_interpolate(self._h, n, _ptr(edges), float(min_turning_radius), nr, _ptr(ratios), _ptr(poses)))
         return poses
+
+    # ---- A8 -----------------------------------------------------------------------------------
+    def wavefront(self, goals, want_explored=True):
+        """ObstaclesHeuristic::Update for each goal -> (cost (n,rows,cols) f32, explored (n,rows,cols) bool)."""
+        goals = _f64(goals)
+        n = len(goals)
+        rows, cols = self.map.rows, self.map.cols
+        cost = np.empty((n, rows, cols), dtype=np.float32)
+        explored = np.empty((n, rows, cols), dtype=np.uint8) if want_explored else None
+        self._check(ppx.ppx_wavefront(self._h, n, _ptr(goals), _ptr(cost), _ptr(explored)))
+        return (cost, explored.astype(bool)) if want_explored else cost

@@ -1,4 +1,5 @@
 // libppx.so: context, memory helpers and world-model upload.
+#include <algorithm>
 #include <cstdarg>
 #include <cstring>
 #include "ppx_ctx.h"
@@ -46,6 +47,15 @@ __global__ void k_clearance(const int* __restrict__ sqdist, float* __restrict__ 
 	for (; i < n; i += stride)
 		clearance[i] = (float)(sqrt((double)sqdist[i]) * (double)res);
 }
+
+// ObstacleListOccupancyMap::IsOccupied, obstacle_list_occupancy_map.cpp:63-69
+__global__ void k_occupied(const int* __restrict__ occupancy, uint8_t* __restrict__ occ8, size_t n)
+{
+	size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+	size_t stride = (size_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride)
+		occ8[i] = occupancy[i] >= 0 ? 1 : 0;
+}
 }
 
 extern "C" {
@@ -84,6 +94,7 @@ int ppx_ctx_destroy(ppx_ctx* ctx)
 	cudaFree(ctx->d_occupancy);
 	cudaFree(ctx->d_pathcost);
 	cudaFree(ctx->d_clearance);
+	cudaFree(ctx->d_occ8);
 	cudaFree(ctx->d_queue);
 	cudaFree(ctx->d_nonholo);
 	cudaFree(ctx->d_wf_cost);
@@ -182,12 +193,16 @@ int ppx_map_upload(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* sqdist
 		cudaFree(ctx->d_occupancy);
 		cudaFree(ctx->d_pathcost);
 		cudaFree(ctx->d_clearance);
+		cudaFree(ctx->d_occ8);
+		ctx->d_occ8 = nullptr;
 		ctx->d_sqdist = ctx->d_occupancy = nullptr;
 		ctx->d_pathcost = ctx->d_clearance = nullptr;
 		PPX_CUDA(ctx, cudaMalloc(&ctx->d_sqdist, cells * sizeof(int32_t)));
 		PPX_CUDA(ctx, cudaMalloc(&ctx->d_occupancy, cells * sizeof(int32_t)));
 		PPX_CUDA(ctx, cudaMalloc(&ctx->d_pathcost, cells * sizeof(float)));
 		PPX_CUDA(ctx, cudaMalloc(&ctx->d_clearance, cells * sizeof(float)));
+		PPX_CUDA(ctx, cudaMalloc(&ctx->d_occ8, cells));
+		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_occ8, 0, cells, ctx->stream));
 		// defaults of an empty map: INT_MAX distance (gvd.cpp:22), free cells (-1), zero potential
 		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_occupancy, 0xff, cells * sizeof(int32_t), ctx->stream));
 		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_pathcost, 0, cells * sizeof(float), ctx->stream));
@@ -204,8 +219,13 @@ int ppx_map_upload(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* sqdist
 		k_clearance<<<blocks, threads, 0, ctx->stream>>>(ctx->d_sqdist, ctx->d_clearance, cells, desc->resolution);
 		PPX_LAUNCHED(ctx);
 	}
-	if (occupancy)
+	if (occupancy) {
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_occupancy, occupancy, cells * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+		int threads = 256;
+		int blocks = (int)std::min<size_t>((cells + threads - 1) / threads, (size_t)ctx->num_sms * 8);
+		k_occupied<<<blocks, threads, 0, ctx->stream>>>(ctx->d_occupancy, ctx->d_occ8, cells);
+		PPX_LAUNCHED(ctx);
+	}
 	if (pathcost)
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_pathcost, pathcost, cells * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
 	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

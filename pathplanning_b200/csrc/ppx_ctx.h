@@ -23,6 +23,7 @@ struct ppx_ctx {
 	int32_t* d_occupancy = nullptr;
 	float* d_pathcost = nullptr;
 	float* d_clearance = nullptr;
+	uint8_t* d_occ8 = nullptr; // occupancy >= 0 (IsOccupied), one byte per cell
 	size_t cells = 0;
 
 	// grow-only device scratch for the host-buffer entry points
@@ -42,6 +43,7 @@ struct ppx_ctx {
 	float* d_wf_cost = nullptr;
 	uint8_t* d_wf_explored = nullptr;
 	double* d_wf_goals = nullptr;
+	int* d_wf_status = nullptr; // device status word of the last wavefront launch (points into scratch)
 
 	ppx::MapDev map_dev() const
 	{

@@ -1,0 +1,421 @@
+// libppx.so: ObstaclesHeuristic::Update (A8), the holonomic-with-obstacles cost-to-go wavefront,
+// batched over goals, bit-exact with the reference's order-dependent semantics.
+//
+// Reference semantics (algo/heuristics.cpp:106-153, utils/frontier.h:39-48,83-91):
+//   * cells pop in ascending float cost, LIFO among equal costs (sorted vector, insertion after the
+//     run of equal values, pop from the back);
+//   * a popped cell pushes every free, never-reached neighbour (enumeration order of
+//     utils/grid.cpp:29-47, corner rule heuristics.cpp:130-132) with cost = w + cost[parent] in
+//     float32, w in {1.0f, sqrtf(2)};
+//   * the decrease-key branch (:142-150) compares two copies of the same value and never fires:
+//     the FIRST popped neighbour fixes a cell's cost for good.  It is not Dijkstra.
+//
+// Parallel formulation ("bucketed frontier"):  every push costs at least parent + 1, and
+// fl(c + 1) >= floor(c) + 1, so while the cells with floor(cost) == b are being popped nothing is
+// inserted into bucket b any more: the bucket is FROZEN, and its pop order is a pure function of
+// its content -- ascending (cost, -insertion sequence).  So one frontier bucket is processed per
+// step by a whole CTA:
+//   1. sort the bucket by (cost bits, ~seq)  -> pop rank of every parent;
+//   2. every (parent rank, neighbour j) pair claims its neighbour cell with
+//      atomicMax(tag[cell], 0x7fffffff - (rank*8+j)): the maximum is the pair that the sequential
+//      reference reaches first ("first reach wins"); cells reached earlier hold 0x80000000|seq,
+//      which beats every claim;
+//   3. winners write cost = w + cost[parent], get insertion sequence numbers in (rank, j) order by a
+//      block prefix sum (the order the reference pushes them), and are appended to bucket
+//      floor(cost) in {b+1, b+2} of a 4-slot ring.
+// The frontier is always compact (bucket lists, never a sweep over the grid); one CTA per goal,
+// as many goals in flight as CTAs fit on the 148 SMs.
+#include <algorithm>
+#include "ppx_ctx.h"
+
+using namespace ppx;
+
+namespace {
+
+constexpr int kRing = 4;
+constexpr uint32_t kUnreached = 0u;
+constexpr uint32_t kSeqFlag = 0x80000000u;
+
+struct WfWork {
+	uint32_t* tag; // [ctas][cells]   0 unreached; claim (< 2^31) during a step; kSeqFlag|seq once reached
+	unsigned long long* keys; // [ctas][kRing][cap]  (cost bits << 32) | ~seq
+	uint32_t* cells; // [ctas][kRing][cap]  row << 16 | col
+	uint32_t cap; // power of two
+};
+
+__device__ __forceinline__ unsigned long long make_key(float cost, uint32_t seq)
+{
+	return ((unsigned long long)__float_as_uint(cost) << 32) | (unsigned long long)(0xffffffffu - seq);
+}
+
+// Claim of neighbour j by the parent with pop rank `rank`: larger = earlier in the reference's order.
+__device__ __forceinline__ uint32_t claim_key(uint32_t rank, int j) { return 0x7fffffffu - (rank * 8u + (uint32_t)j); }
+
+// neighbour enumeration order of GridCellPosition::GetNeighbors, utils/grid.cpp:29-47
+__constant__ int c_dr[8] = { 0, -1, 1, 0, -1, 1, -1, 1 };
+__constant__ int c_dc[8] = { -1, -1, -1, 1, 1, 1, 0, 0 };
+
+// In-place bitonic sort of n (power of two) (key, cell) pairs by the whole CTA.
+__device__ void cta_bitonic_sort(unsigned long long* keys, uint32_t* cells, uint32_t n)
+{
+	for (uint32_t k = 2; k <= n; k <<= 1) {
+		for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+			for (uint32_t p = threadIdx.x; p < (n >> 1); p += blockDim.x) {
+				uint32_t i = ((p & ~(j - 1)) << 1) | (p & (j - 1));
+				uint32_t q = i | j;
+				unsigned long long a = keys[i], b = keys[q];
+				bool up = (i & k) == 0;
+				if ((a > b) == up) {
+					keys[i] = b;
+					keys[q] = a;
+					uint32_t t = cells[i];
+					cells[i] = cells[q];
+					cells[q] = t;
+				}
+			}
+			__syncthreads();
+		}
+	}
+}
+
+// Rank by counting for small buckets: rank_i = #{k : key_k < key_i} (keys are unique).
+__device__ void cta_rank_sort(const unsigned long long* inKeys, const uint32_t* inCells, uint32_t L,
+	unsigned long long* outKeys, uint32_t* outCells)
+{
+	for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
+		unsigned long long mine = inKeys[i];
+		uint32_t rank = 0;
+		for (uint32_t k = 0; k < L; k++)
+			rank += inKeys[k] < mine ? 1u : 0u;
+		outKeys[rank] = mine;
+		outCells[rank] = inCells[i];
+	}
+	__syncthreads();
+}
+
+// Exclusive prefix sum of one value per thread over the CTA; returns the exclusive prefix and the
+// CTA total through *total.  s_warp must hold 32 entries.
+__device__ uint32_t cta_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t* total)
+{
+	const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	const unsigned nwarps = (blockDim.x + 31) >> 5;
+	uint32_t incl = v;
+	#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+		if (lane >= (unsigned)o)
+			incl += t;
+	}
+	if (lane == 31)
+		s_warp[warp] = incl;
+	__syncthreads();
+	if (warp == 0) {
+		uint32_t w = lane < nwarps ? s_warp[lane] : 0;
+		uint32_t wi = w;
+		#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+			if (lane >= (unsigned)o)
+				wi += t;
+		}
+		s_warp[lane] = wi - w; // exclusive prefix of the warp sums
+		if (lane == 31)
+			*total = wi;
+	}
+	__syncthreads();
+	uint32_t out = s_warp[warp] + incl - v;
+	__syncthreads(); // s_warp may be reused by the caller right away
+	return out;
+}
+
+// One goal per CTA at a time; CTAs take goals from a global cursor.
+__global__ void k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_t nGoals, const double* __restrict__ goals,
+	float* __restrict__ costOut, uint8_t* __restrict__ exploredOut, WfWork work, uint32_t sortCap,
+	unsigned long long* __restrict__ queue, int* __restrict__ status)
+{
+	extern __shared__ unsigned long long s_dyn[];
+	unsigned long long* s_keys = s_dyn; // [sortCap]
+	unsigned long long* s_keys2 = s_dyn + sortCap; // [sortCap/4] scratch for the rank sort input
+	uint32_t* s_cells = (uint32_t*)(s_dyn + sortCap + sortCap / 4); // [sortCap]
+	uint32_t* s_cells2 = s_cells + sortCap; // [sortCap/4]
+	__shared__ uint32_t s_cnt[kRing];
+	__shared__ uint32_t s_warp[32];
+	__shared__ uint32_t s_total;
+	__shared__ long long s_goal;
+	__shared__ int s_err;
+
+	const int rows = map.rows, cols = map.cols;
+	const size_t ncells = (size_t)rows * cols;
+	uint32_t* tag = work.tag + (size_t)blockIdx.x * ncells;
+	unsigned long long* ringKeys = work.keys + (size_t)blockIdx.x * kRing * work.cap;
+	uint32_t* ringCells = work.cells + (size_t)blockIdx.x * kRing * work.cap;
+	const float sqrt2 = sqrtf(2.0f); // std::sqrt(2.0f), heuristics.cpp:134
+
+	while (true) {
+		if (threadIdx.x == 0)
+			s_goal = (long long)atomicAdd(queue, 1ull);
+		__syncthreads();
+		const long long g = s_goal;
+		if (g >= nGoals)
+			return;
+		float* cost = costOut + (size_t)g * ncells;
+
+		// heuristics.cpp:108-113: every cell infinity / not explored
+		for (size_t i = threadIdx.x; i < ncells; i += blockDim.x) {
+			cost[i] = __int_as_float(0x7f800000);
+			tag[i] = kUnreached;
+		}
+		if (threadIdx.x < kRing)
+			s_cnt[threadIdx.x] = 0;
+		if (threadIdx.x == 0)
+			s_err = 0;
+		// goal cell, bounded WorldPositionToGridCell (occupancy_map.h:106-117,180-183)
+		const int r0 = trunc_i32((goals[3 * g] - map.ox) / map.resd);
+		const int c0 = trunc_i32((goals[3 * g + 1] - map.oy) / map.resd);
+		const bool startValid = r0 >= 0 && r0 < rows && c0 >= 0 && c0 < cols;
+		__syncthreads();
+		uint32_t pending = 0, counter = 1;
+		int b = 0;
+		const int maxBucket = (int)min((size_t)0x7ffffff0, 2 * ncells + 8);
+		if (startValid) {
+			if (threadIdx.x == 0) {
+				cost[(size_t)r0 * cols + c0] = 0.0f;
+				tag[(size_t)r0 * cols + c0] = kSeqFlag | 0u;
+				ringKeys[0] = make_key(0.0f, 0);
+				ringCells[0] = ((uint32_t)r0 << 16) | (uint32_t)c0;
+				s_cnt[0] = 1;
+			}
+			pending = 1;
+		}
+		__syncthreads();
+
+		while (pending > 0) {
+			const int slot = b & (kRing - 1);
+			const uint32_t L = s_cnt[slot];
+			if (L == 0) {
+				// cannot happen while the bookkeeping is right (every pending cell sits in bucket b+1 or b+2);
+				// the guard turns a would-be endless scan into an error status
+				if (++b > maxBucket) {
+					if (threadIdx.x == 0) {
+						atomicExch(status, 2);
+						printf("ppx wavefront: goal %lld lost %u pending cells at bucket %d (seq %u)\n", g, pending, b, counter);
+					}
+					break;
+				}
+				continue;
+			}
+			unsigned long long* gk = ringKeys + (size_t)slot * work.cap;
+			uint32_t* gc = ringCells + (size_t)slot * work.cap;
+			// ---- 1. pop order of the frozen bucket -------------------------------------------------
+			const unsigned long long* sk;
+			const uint32_t* sc;
+			if (L <= sortCap / 4 && L <= 2 * blockDim.x) {
+				for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
+					s_keys2[i] = gk[i];
+					s_cells2[i] = gc[i];
+				}
+				__syncthreads();
+				cta_rank_sort(s_keys2, s_cells2, L, s_keys, s_cells);
+				sk = s_keys;
+				sc = s_cells;
+			} else {
+				uint32_t n = 2;
+				while (n < L)
+					n <<= 1;
+				if (n <= sortCap) {
+					for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+						s_keys[i] = i < L ? gk[i] : ~0ull;
+						s_cells[i] = i < L ? gc[i] : 0u;
+					}
+					__syncthreads();
+					cta_bitonic_sort(s_keys, s_cells, n);
+					sk = s_keys;
+					sc = s_cells;
+				} else { // oversized bucket: sort it where it lies (n <= cap is guaranteed by the append check)
+					for (uint32_t i = L + threadIdx.x; i < n; i += blockDim.x) {
+						gk[i] = ~0ull;
+						gc[i] = 0u;
+					}
+					__syncthreads();
+					cta_bitonic_sort(gk, gc, n);
+					sk = gk;
+					sc = gc;
+				}
+			}
+			// ---- 2. claims: contiguous block of parents per thread -----------------------------------
+			const uint32_t per = (L + blockDim.x - 1) / blockDim.x;
+			const uint32_t first = threadIdx.x * per;
+			const uint32_t lastp = first + per < L ? first + per : L;
+			for (uint32_t rank = first; rank < lastp; rank++) {
+				const uint32_t cell = sc[rank];
+				const int r = (int)(cell >> 16), c = (int)(cell & 0xffffu);
+				#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					const int rr = r + c_dr[j], cc = c + c_dc[j];
+					if (rr < 0 || rr >= rows || cc < 0 || cc >= cols)
+						continue;
+					const size_t ni = (size_t)rr * cols + cc;
+					if (occ8[ni])
+						continue;
+					if (c_dr[j] != 0 && c_dc[j] != 0 && occ8[(size_t)rr * cols + c] && occ8[(size_t)r * cols + cc])
+						continue;
+					// reached cells hold kSeqFlag|seq >= 2^31 > any claim: the atomicMax leaves them alone
+					atomicMax(&tag[ni], claim_key(rank, j));
+				}
+			}
+			__syncthreads();
+			// ---- 3. winners ------------------------------------------------------------------------
+			uint32_t wins = 0;
+			for (uint32_t rank = first; rank < lastp; rank++) {
+				const uint32_t cell = sc[rank];
+				const int r = (int)(cell >> 16), c = (int)(cell & 0xffffu);
+				#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					const int rr = r + c_dr[j], cc = c + c_dc[j];
+					if (rr < 0 || rr >= rows || cc < 0 || cc >= cols)
+						continue;
+					wins += tag[(size_t)rr * cols + cc] == claim_key(rank, j) ? 1u : 0u;
+				}
+			}
+			uint32_t seq = counter + cta_exclusive_scan(wins, s_warp, &s_total);
+			const uint32_t total = s_total;
+			for (uint32_t rank = first; rank < lastp; rank++) {
+				const uint32_t cell = sc[rank];
+				const int r = (int)(cell >> 16), c = (int)(cell & 0xffffu);
+				const float parentCost = __uint_as_float((uint32_t)(sk[rank] >> 32));
+				#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					const int rr = r + c_dr[j], cc = c + c_dc[j];
+					if (rr < 0 || rr >= rows || cc < 0 || cc >= cols)
+						continue;
+					const size_t ni = (size_t)rr * cols + cc;
+					if (tag[ni] != claim_key(rank, j))
+						continue;
+					const float w = (c_dr[j] == 0 || c_dc[j] == 0) ? 1.0f : sqrt2;
+					const float pathCost = w + parentCost;
+					cost[ni] = pathCost;
+					tag[ni] = kSeqFlag | seq;
+					const int nb = (int)pathCost;
+					const int ns = nb & (kRing - 1);
+					const uint32_t pos = atomicAdd(&s_cnt[ns], 1u);
+					if (pos < work.cap && nb > b && nb <= b + 2) {
+						ringKeys[(size_t)ns * work.cap + pos] = make_key(pathCost, seq);
+						ringCells[(size_t)ns * work.cap + pos] = ((uint32_t)rr << 16) | (uint32_t)cc;
+					} else {
+						s_err = 1;
+					}
+					seq++;
+				}
+			}
+			__syncthreads();
+			if (threadIdx.x == 0)
+				s_cnt[slot] = 0;
+			pending = pending - L + total;
+			counter += total;
+			b++;
+			const int err = s_err;
+			__syncthreads();
+			if (err) {
+				pending = 0;
+				if (threadIdx.x == 0)
+					atomicExch(status, 1);
+			}
+		}
+		// every reached cell has been popped when the frontier drains: explored <=> cost finite
+		if (exploredOut) {
+			uint8_t* ex = exploredOut + (size_t)g * ncells;
+			for (size_t i = threadIdx.x; i < ncells; i += blockDim.x)
+				ex[i] = cost[i] != __int_as_float(0x7f800000) ? 1 : 0;
+		}
+		__syncthreads();
+	}
+}
+
+}
+
+int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored)
+{
+	const int rows = ctx->desc.rows, cols = ctx->desc.cols;
+	if (rows > 65535 || cols > 65535)
+		return ppx_fail(ctx, PPX_ERR_INVALID, "wavefront: map larger than 65535 cells per side");
+	const size_t ncells = (size_t)rows * cols;
+	// team size and sort capacity from the map perimeter (a wave front is a closed curve through the map)
+	const int perimeter = 2 * (rows + cols);
+	int threads = perimeter <= 1024 ? 128 : perimeter <= 2048 ? 256 : perimeter <= 4096 ? 512 : 1024;
+	uint32_t sortCap = (uint32_t)threads * 8;
+	size_t smem = (size_t)sortCap * 8 + sortCap / 4 * 8 + (size_t)sortCap * 4 + sortCap / 4 * 4;
+	PPX_CUDA(ctx, cudaFuncSetAttribute(k_wavefront, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+	int perSm = 1;
+	PPX_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_wavefront, threads, smem));
+	if (perSm < 1)
+		perSm = 1;
+	int ctas = (int)std::min<int64_t>(n, (int64_t)ctx->num_sms * perSm);
+	uint32_t cap = 1024;
+	while (cap < (uint32_t)(8 * (rows + cols)))
+		cap <<= 1;
+	while ((size_t)cap > 2 * ncells && cap > 1024)
+		cap >>= 1;
+	WfWork work;
+	work.cap = cap;
+	char* base;
+	size_t bytesTag = (size_t)ctas * ncells * 4, bytesKeys = (size_t)ctas * kRing * cap * 8, bytesCells = (size_t)ctas * kRing * cap * 4;
+	size_t offKeys = (bytesTag + 255) & ~(size_t)255, offCells = offKeys + bytesKeys, offStatus = offCells + ((bytesCells + 255) & ~(size_t)255);
+	PPX_CHECK(ppx_scratch(ctx, 4, offStatus + 256, (void**)&base));
+	work.tag = (uint32_t*)base;
+	work.keys = (unsigned long long*)(base + offKeys);
+	work.cells = (uint32_t*)(base + offCells);
+	int* d_status = (int*)(base + offStatus);
+	PPX_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int), ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
+	k_wavefront<<<ctas, threads, smem, ctx->stream>>>(ctx->map_dev(), ctx->d_occ8, n, d_goals, d_cost, d_explored, work, sortCap,
+		ctx->d_queue, d_status);
+	PPX_LAUNCHED(ctx);
+	ctx->d_wf_status = d_status;
+	return PPX_OK;
+}
+
+extern "C" {
+
+int ppx_wavefront_dev(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored)
+{
+	if (!ctx)
+		return PPX_ERR_INVALID;
+	if (!ctx->has_map)
+		return ppx_fail(ctx, PPX_ERR_STATE, "no map uploaded (ppx_map_upload)");
+	PPX_REQUIRE(ctx, n >= 0 && (n == 0 || (d_goals && d_cost)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	return ppx_wavefront_launch(ctx, n, d_goals, d_cost, d_explored);
+}
+
+int ppx_wavefront(ppx_ctx* ctx, int64_t n, const double* goals, float* cost, uint8_t* explored)
+{
+	if (!ctx)
+		return PPX_ERR_INVALID;
+	if (!ctx->has_map)
+		return ppx_fail(ctx, PPX_ERR_STATE, "no map uploaded (ppx_map_upload)");
+	PPX_REQUIRE(ctx, n >= 0 && (n == 0 || (goals && cost)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	const size_t ncells = ctx->cells;
+	double* d_goals;
+	float* d_cost;
+	uint8_t* d_explored = nullptr;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * 3 * sizeof(double), (void**)&d_goals));
+	PPX_CHECK(ppx_scratch(ctx, 1, n * ncells * sizeof(float), (void**)&d_cost));
+	if (explored)
+		PPX_CHECK(ppx_scratch(ctx, 2, n * ncells, (void**)&d_explored));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_goals, goals, n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CHECK(ppx_wavefront_launch(ctx, n, d_goals, d_cost, d_explored));
+	int status = 0;
+	PPX_CUDA(ctx, cudaMemcpyAsync(&status, ctx->d_wf_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(cost, d_cost, n * ncells * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	if (explored)
+		PPX_CUDA(ctx, cudaMemcpyAsync(explored, d_explored, n * ncells, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	if (status)
+		return ppx_fail(ctx, PPX_ERR_CAPACITY, "wavefront: device status %d (1: a frontier bucket overflowed its ring slot, 2: internal)", status);
+	return PPX_OK;
+}
+
+} // extern "C"

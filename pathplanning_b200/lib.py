@@ -58,6 +58,8 @@ _SIGS = {
     "ppx_connect_check_rs_dev": (C.c_int, [_p, _i64, _p, _p, C.POINTER(RSCostParamsC), C.POINTER(ValidatorParamsC),
                                            _p, _p, _p, _p, _p]),
     "ppx_rs_interpolate": (C.c_int, [_p, _i64, _p, C.c_double, C.c_int32, _p, _p]),
+    "ppx_wavefront": (C.c_int, [_p, _i64, _p, _p, _p]),
+    "ppx_wavefront_dev": (C.c_int, [_p, _i64, _p, _p, _p]),
 }
 
 for _name, (_res, _args) in _SIGS.items():

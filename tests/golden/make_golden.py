@@ -155,5 +155,44 @@ def main():
         print(f, os.path.getsize(os.path.join(HERE, f)))
 
 
+def c2_world():
+    cfg = synth.C2
+    w = refapi.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    for r in synth.config_rects(cfg):
+        w.add_rectangle(*r)
+    w.update()
+    return w
+
+
+WAVEFRONT_GOALS = [
+    (17.0, 17.5, np.pi / 2),  # the C2 query goal
+    (-16.0, -14.0, 0.0),  # centre of the first parked car: enclosed by its outline
+    (0.3, 0.2, 0.0),  # map centre
+    (-19.95, 19.95, 0.0),  # corner cell
+    (25.0, 0.0, 0.0),  # outside the map: nothing reached
+    (-16.0, -11.75, 0.0),  # on a car outline (occupied goal cell)
+]
+
+
+def main_wavefront():
+    """ObstaclesHeuristic::Update on the C2 parking lot: two full cost grids + digests of all."""
+    import hashlib
+    w = c2_world()
+    costs, digests, reached = [], [], []
+    for g in WAVEFRONT_GOALS:
+        cost, explored, _ = w.wavefront(g)
+        assert np.array_equal(explored, np.isfinite(cost))
+        costs.append(cost)
+        digests.append(hashlib.sha256(cost.tobytes()).hexdigest())
+        reached.append(int(explored.sum()))
+    np.savez_compressed(os.path.join(HERE, "wavefront_c2.npz"), goals=np.array(WAVEFRONT_GOALS), cost0=costs[0], cost1=costs[1],
+                        digests=np.array(digests), reached=np.array(reached))
+    print("wavefront reached:", reached)
+
+
 if __name__ == "__main__":
-    main()
+    which = sys.argv[1] if len(sys.argv) > 1 else "all"
+    if which in ("all", "base"):
+        main()
+    if which in ("all", "wavefront"):
+        main_wavefront()
