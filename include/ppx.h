@@ -208,6 +208,125 @@ int ppx_rs_interpolate(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double
 int ppx_wavefront(ppx_ctx* ctx, int64_t n, const double* goals, float* cost, uint8_t* explored);
 int ppx_wavefront_dev(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored);
 
+/* ------------------------------------------------------------------------------------------ */
+/* A1-A6, A9: Hybrid A* successor generation, heuristics and the batched on-device graph search  */
+/*
+ * HybridAStar::SearchParameters (algo/hybrid_a_star.h:29-50).  The 8-argument constructor of the
+ * reference cannot set wheelbase (it stays 2.6); the field is here so the host mirror passes
+ * whatever its SearchParameters holds.
+ */
+typedef struct ppx_hybrid_params {
+	double wheelbase;
+	double min_turning_radius;
+	double direction_switching_cost;
+	double reverse_cost_multiplier;
+	double forward_cost_multiplier;
+	double voronoi_cost_multiplier;
+	uint32_t num_generated_motion;
+	uint32_t _pad;
+	double spatial_resolution;
+	double angular_resolution;
+} ppx_hybrid_params;
+
+typedef struct ppx_hybrid ppx_hybrid;
+
+/*
+ * HybridAStar::Initialize (algo/hybrid_a_star.cpp:206-235) for the map currently uploaded to ctx:
+ * derives the steering set (hybrid_a_star.cpp:13-29), builds the NonHolonomicHeuristic table on the
+ * device (algo/heuristics.cpp:36-76, one Reeds-Shepp solve per entry) and keeps the validator
+ * parameters.  The planner reads the context's map at search time, so ppx_map_upload may refresh the
+ * grids between searches (same size and bounds).
+ */
+int ppx_hybrid_create(ppx_ctx* ctx, const ppx_hybrid_params* params, const ppx_validator_params* vp, ppx_hybrid** out);
+int ppx_hybrid_destroy(ppx_hybrid* h);
+/* NonHolonomicHeuristic: dims = {numSpatialX, numSpatialY, numAngular}, offsets = {offsetX, offsetY},
+ * values (may be NULL) = m_values[i][j][k] row-major. */
+int ppx_hybrid_table(ppx_hybrid* h, int32_t* dims, double* offsets, double* values);
+/*
+ * AStarCombinedHeuristic / NonHolonomicHeuristic / ObstaclesHeuristic ::GetHeuristicValue
+ * (algo/a_star.h:102-109, algo/heuristics.cpp:78-95,155-165) for n poses and one goal; runs the
+ * wavefront of that goal first (ObstaclesHeuristic::Update).  Any output may be NULL.
+ * Reads of the table with a negative heading index (out of bounds in the reference)
+ * are defined as index + numAngular.
+ */
+int ppx_hybrid_heuristic(ppx_hybrid* h, const double* goal, int64_t n, const double* poses, double* combined,
+	double* nonholo, double* obstacles);
+
+#define PPX_MAX_CHILDREN 19
+typedef struct ppx_hybrid_child {
+	double pose[3]; /* State::continuousPose */
+	double cost; /* transition cost */
+	double heuristic; /* combined heuristic of the child */
+	double length; /* action path length (after truncation) */
+	int32_t key[3]; /* State::discretePose (x, y, theta bin) */
+	int32_t direction; /* State::direction */
+	int32_t kind; /* 0 constant steer, 1 Reeds-Shepp */
+	float last; /* lastValidRatio of the primitive (1 when fully valid) */
+} ppx_hybrid_child;
+
+/*
+ * StatePropagator::GetNeighborStates (algo/hybrid_a_star.cpp:59-91) for n arbitrary parents and one
+ * goal: children[i*PPX_MAX_CHILDREN + c], c < n_children[i], in the reference's order.  seeds[i] seeds
+ * the std::mt19937_64 that decides the Reeds-Shepp shot of parent i (hybrid_a_star.cpp:82, trap H4).
+ */
+int ppx_hybrid_expand(ppx_hybrid* h, const double* goal, int64_t n, const double* parents, const uint64_t* seeds,
+	int32_t* n_children, ppx_hybrid_child* children, double* parent_heuristic);
+
+#define PPX_ERR_LIMIT (-6) /* search stopped at ppx_hybrid_limits.max_expansions */
+
+typedef struct ppx_hybrid_limits {
+	int32_t max_nodes; /* node pool per query; 0 = 2 x number of discrete states inside the bounds */
+	int32_t max_expansions; /* 0 = unlimited (the reference has no limit) */
+	int32_t max_path; /* capacity of the per-query path output (states) */
+	int32_t max_log; /* capacity of the per-query expansion log (entries); 0 = no log */
+} ppx_hybrid_limits;
+
+typedef struct ppx_hybrid_result {
+	int32_t status; /* 0 Success, -1 Failure (frontier exhausted) like Planner::Status; PPX_ERR_CAPACITY; PPX_ERR_LIMIT */
+	int32_t n_expanded; /* nodes popped and expanded */
+	int32_t n_nodes; /* nodes created (pushed to the frontier) */
+	int32_t n_children; /* children generated */
+	int32_t n_rs_attempts; /* Reeds-Shepp shots attempted */
+	int32_t path_len; /* states on the solution chain root..goal (0 without solution) */
+	double cost; /* GraphSearch::GetOptimalCost (+inf without solution) */
+	uint64_t expanded_hash; /* order-sensitive FNV hash of the expanded discrete states */
+} ppx_hybrid_result;
+
+/* One state of the solution chain (AStar::GetPath / GetActions): the action that reaches it is
+ * reconstructed by the host mirror as PathConstantSteer(parent pose, delta[slot/2], dir) truncated to
+ * `last`, or as the Reeds-Shepp connection parent -> goal. */
+typedef struct ppx_hybrid_path_state {
+	double pose[3];
+	double length;
+	float last;
+	int8_t kind; /* -1 root, 0 constant steer, 1 Reeds-Shepp */
+	int8_t direction;
+	int8_t slot; /* child slot in GetNeighborStates order */
+	int8_t _pad;
+} ppx_hybrid_path_state;
+
+typedef struct ppx_hybrid_log_entry {
+	int32_t key[3];
+	int32_t direction;
+	double pose[3];
+} ppx_hybrid_log_entry;
+
+/*
+ * The graph-search part of HybridAStar::SearchPath (algo/hybrid_a_star.cpp:248-257) for nq
+ * independent queries: ObstaclesHeuristic::Update(goal) (one wavefront per distinct goal cell), then
+ * AStar::SearchPath (algo/a_star.h:326-346) with the Frontier's tie order, entirely on the device,
+ * one warp per query.  seeds[q] seeds query q's private std::mt19937_64 (trap H4).
+ *   results  nq records
+ *   paths    optional, nq * limits->max_path states
+ *   log      optional, nq * limits->max_log entries: the expanded nodes in expansion order
+ */
+int ppx_hybrid_search(ppx_hybrid* h, int64_t nq, const double* starts, const double* goals, const uint64_t* seeds,
+	const ppx_hybrid_limits* limits, ppx_hybrid_result* results, ppx_hybrid_path_state* paths, ppx_hybrid_log_entry* log);
+/* Device-resident variant: no host copies, no synchronisation, one wavefront per query. */
+int ppx_hybrid_search_dev(ppx_hybrid* h, int64_t nq, const double* d_starts, const double* d_goals,
+	const uint64_t* d_seeds, const ppx_hybrid_limits* limits, ppx_hybrid_result* d_results,
+	ppx_hybrid_path_state* d_paths, ppx_hybrid_log_entry* d_log);
+
 #ifdef __cplusplus
 }
 #endif

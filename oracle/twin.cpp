@@ -13,6 +13,7 @@
 #include <vector>
 #include <cstdio>
 #include "ppx_device.cuh"
+#include "ppx_hybrid_host.h"
 
 using namespace ppx;
 
@@ -107,6 +108,205 @@ void twin_check_rs(void* h, long n, const ppx_rs_edge* edges, double r, float ra
 			if (microsteps) microsteps[i] = steps;
 		}
 	}
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Hybrid A*: the successor / heuristic / bookkeeping code of ppx_hybrid.cuh run sequentially.  The
+// non-holonomic table and the wavefront grid are INPUTS here (taken from the reference by the test),
+// so this checks exactly the logic the search kernel runs per warp.
+namespace {
+struct TwinHybrid {
+	TwinWorld* world;
+	ppx_hybrid_params params;
+	HybridDev dev;
+	std::vector<double> table;
+	int x0, y0, tx, ty;
+};
+}
+
+void* twin_hybrid_create(void* hw, const ppx_hybrid_params* params, const ppx_validator_params* vp, const double* table)
+{
+	auto* w = (TwinWorld*)hw;
+	auto* h = new TwinHybrid();
+	h->world = w;
+	h->params = *params;
+	if (hybrid_derive(*params, *vp, w->desc, h->dev) != PPX_OK) {
+		delete h;
+		return nullptr;
+	}
+	size_t total = (size_t)h->dev.nhX * h->dev.nhY * h->dev.nhA;
+	if (table) {
+		h->table.assign(table, table + total);
+	} else { // NonHolonomicHeuristic::Build with the twin's own solver
+		h->table.resize(total);
+		const HybridDev& P = h->dev;
+		for (size_t idx = 0; idx < total; idx++) {
+			int k = (int)(idx % P.nhA), j = (int)((idx / P.nhA) % P.nhY), i = (int)(idx / ((size_t)P.nhA * P.nhY));
+			Pose pose = { i * P.spatialRes - P.nhOffX, j * P.spatialRes - P.nhOffY, wrap_theta(k * P.angRes) };
+			Pose goal = { 0.0, 0.0, 0.0 };
+			RSSolution sol;
+			rs_solve(pose, goal, P.rmin, P.revF, P.fwdF, P.swF, 0, sol);
+			h->table[idx] = (double)sol.cost;
+		}
+	}
+	h->dev.nh = h->table.data();
+	hybrid_key_table(*params, w->desc, h->x0, h->y0, h->tx, h->ty);
+	return h;
+}
+
+void twin_hybrid_destroy(void* hh) { delete (TwinHybrid*)hh; }
+
+void twin_hybrid_info(void* hh, int* dims, double* offsets, double* deltasOut, double* table)
+{
+	auto* h = (TwinHybrid*)hh;
+	dims[0] = h->dev.nhX; dims[1] = h->dev.nhY; dims[2] = h->dev.nhA; dims[3] = h->dev.numDeltas;
+	offsets[0] = h->dev.nhOffX; offsets[1] = h->dev.nhOffY;
+	if (deltasOut)
+		for (int i = 0; i < h->dev.numDeltas; i++)
+			deltasOut[i] = h->dev.kappa[i];
+	if (table)
+		memcpy(table, h->table.data(), h->table.size() * sizeof(double));
+}
+
+void twin_hybrid_heuristic(void* hh, const float* wfCost, const double* goal, long n, const double* poses, double* combined,
+	double* nonholo, double* obstacles)
+{
+	auto* h = (TwinHybrid*)hh;
+	MapDev map = h->world->dev();
+	Pose g = { goal[0], goal[1], goal[2] };
+	for (long i = 0; i < n; i++) {
+		Pose s = { poses[3 * i], poses[3 * i + 1], poses[3 * i + 2] };
+		if (combined) combined[i] = combined_heuristic(h->dev, map, wfCost, g, s);
+		if (nonholo) nonholo[i] = nonholo_heuristic(h->dev, g, s);
+		if (obstacles) obstacles[i] = obstacle_heuristic(h->dev, map, wfCost, g, s);
+	}
+}
+
+void twin_hybrid_expand(void* hh, const float* wfCost, const double* goal, long n, const double* parents, const uint64_t* seeds,
+	int32_t* nChildren, ppx_hybrid_child* children, double* parentHeuristic)
+{
+	auto* h = (TwinHybrid*)hh;
+	const HybridDev& P = h->dev;
+	MapDev map = h->world->dev();
+	Pose g = { goal[0], goal[1], goal[2] };
+	std::vector<unsigned long long> mt(312);
+	for (long i = 0; i < n; i++) {
+		Pose parent = { parents[3 * i], parents[3 * i + 1], parents[3 * i + 2] };
+		Key3 pk = discretize_pose(P, parent);
+		double hCost = combined_heuristic(P, map, wfCost, g, parent);
+		if (parentHeuristic) parentHeuristic[i] = hCost;
+		int idx = 0;
+		Mt64 rng { mt.data(), &idx };
+		rng.seed(seeds[i]);
+		int nslots = 2 * P.numDeltas + (rs_shot_wanted(rng, hCost) ? 1 : 0);
+		int count = 0;
+		for (int s = 0; s < nslots; s++) {
+			Child c;
+			make_child(P, map, parent, pk, g, s, c);
+			if (!c.ok)
+				continue;
+			ppx_hybrid_child& o = children[i * PPX_MAX_CHILDREN + count++];
+			o.pose[0] = c.pose.x; o.pose[1] = c.pose.y; o.pose[2] = c.pose.th;
+			o.cost = c.cost;
+			o.heuristic = combined_heuristic(P, map, wfCost, g, c.pose);
+			o.length = c.length;
+			o.key[0] = c.key.x; o.key[1] = c.key.y; o.key[2] = c.key.k;
+			o.direction = c.dir;
+			o.kind = c.kind;
+			o.last = c.last;
+		}
+		nChildren[i] = count;
+	}
+}
+
+// The loop of k_hybrid_search for one query, sequentially.
+void twin_hybrid_search(void* hh, const float* wfCost, const double* start, const double* goal, uint64_t seed,
+	const ppx_hybrid_limits* limits, ppx_hybrid_result* result, ppx_hybrid_path_state* path, ppx_hybrid_log_entry* log)
+{
+	auto* h = (TwinHybrid*)hh;
+	const HybridDev& P = h->dev;
+	MapDev map = h->world->dev();
+	const int tableSize = h->tx * h->ty * 7;
+	const int maxNodes = limits->max_nodes > 0 ? limits->max_nodes : 2 * tableSize;
+	std::vector<double> pose(3 * (size_t)maxNodes), g(maxNodes), f(maxNodes), length(maxNodes), heapF(maxNodes);
+	std::vector<int> parent(maxNodes), keyIdx(maxNodes);
+	std::vector<uint32_t> meta(maxNodes), heapSeq(maxNodes), heapNode(maxNodes), table(tableSize, 0u);
+	std::vector<float> lastv(maxNodes);
+	std::vector<unsigned long long> mt(312);
+	SearchWs W;
+	W.pose = pose.data(); W.g = g.data(); W.f = f.data(); W.parent = parent.data(); W.keyIdx = keyIdx.data();
+	W.meta = meta.data(); W.last = lastv.data(); W.length = length.data(); W.heapF = heapF.data();
+	W.heapSeq = heapSeq.data(); W.heapNode = heapNode.data(); W.table = table.data(); W.mt = mt.data();
+	W.maxNodes = maxNodes; W.tx = h->tx; W.ty = h->ty; W.x0 = h->x0; W.y0 = h->y0;
+	SearchState S;
+	Mt64 rng { W.mt, &S.mtIdx };
+	rng.seed(seed);
+	Pose st = { start[0], start[1], start[2] }, gl = { goal[0], goal[1], goal[2] };
+	search_init(P, W, S, st);
+	while (S.status == PPX_SEARCH_RUNNING) {
+		if (limits->max_expansions > 0 && S.nExpanded >= limits->max_expansions) {
+			S.status = PPX_ERR_LIMIT;
+			break;
+		}
+		int n = search_pop(W, S, gl);
+		if (n < 0)
+			break;
+		Pose par = { W.pose[3 * n], W.pose[3 * n + 1], W.pose[3 * n + 2] };
+		Key3 pk = discretize_pose(P, par);
+		double hCost = combined_heuristic(P, map, wfCost, gl, par);
+		if (log && S.nExpanded <= limits->max_log) {
+			ppx_hybrid_log_entry& e = log[S.nExpanded - 1];
+			e.key[0] = pk.x; e.key[1] = pk.y; e.key[2] = pk.k;
+			e.direction = (int)(W.meta[n] & 3u);
+			e.pose[0] = par.x; e.pose[1] = par.y; e.pose[2] = par.th;
+		}
+		int want = rs_shot_wanted(rng, hCost) ? 1 : 0;
+		S.nRsAttempts += want;
+		int nslots = 2 * P.numDeltas + want;
+		double parentG = W.g[n];
+		for (int s = 0; s < nslots && S.status == PPX_SEARCH_RUNNING; s++) {
+			Child c;
+			make_child(P, map, par, pk, gl, s, c);
+			if (!c.ok)
+				continue;
+			double hc = combined_heuristic(P, map, wfCost, gl, c.pose);
+			consume_child(W, S, n, parentG, c, hc, s);
+		}
+	}
+	ppx_hybrid_result r;
+	r.status = S.status == PPX_SEARCH_RUNNING ? -1 : S.status;
+	r.n_expanded = S.nExpanded; r.n_nodes = S.numNodes; r.n_children = S.nChildren; r.n_rs_attempts = S.nRsAttempts;
+	r.path_len = 0; r.cost = PPX_INF; r.expanded_hash = S.hash;
+	if (S.status == PPX_OK && S.solution >= 0) {
+		r.cost = W.g[S.solution];
+		int depth = 0;
+		for (int m = S.solution; m >= 0; m = W.parent[m]) depth++;
+		r.path_len = depth;
+		if (path && limits->max_path > 0) {
+			int pos = depth - 1;
+			for (int m = S.solution; m >= 0; m = W.parent[m], pos--) {
+				if (pos >= limits->max_path) continue;
+				ppx_hybrid_path_state& o = path[pos];
+				o.pose[0] = W.pose[3 * m]; o.pose[1] = W.pose[3 * m + 1]; o.pose[2] = W.pose[3 * m + 2];
+				o.length = W.length[m]; o.last = W.last[m];
+				uint32_t mm = W.meta[m];
+				o.kind = W.parent[m] < 0 ? (int8_t)-1 : (int8_t)((mm >> 2) & 1u);
+				o.direction = (int8_t)(mm & 3u); o.slot = (int8_t)((mm >> 3) & 31u); o._pad = 0;
+			}
+		}
+	}
+	*result = r;
+}
+
+void twin_mt64_uniform(uint64_t seed, long n, double* out)
+{
+	std::vector<unsigned long long> mt(312);
+	int idx = 0;
+	Mt64 rng { mt.data(), &idx };
+	rng.seed(seed);
+	for (long i = 0; i < n; i++)
+		out[i] = rng.uniform01();
 }
 
 } // extern "C"

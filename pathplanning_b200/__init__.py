@@ -10,5 +10,5 @@ importing :mod:`pathplanning_b200.lib` raises if the library is missing, and cre
 from . import lib  # noqa: F401  (raises ImportError loudly when libppx.so is not built)
 from .api import (  # noqa: F401
     Context, MapDesc, ValidatorParams, RSCostParams, PPXError,
-    RS_EDGE, CSTEER_EDGE, LINE_EDGE, make_rs_edges, make_csteer_edges,
+    RS_EDGE, CSTEER_EDGE, LINE_EDGE, make_rs_edges, make_csteer_edges, HybridParams, HybridAStar,
 )

@@ -11,13 +11,23 @@ from dataclasses import dataclass, field
 
 import numpy as np
 
-from .lib import ppx, MapDescC, ValidatorParamsC, RSCostParamsC
+from .lib import ppx, MapDescC, ValidatorParamsC, RSCostParamsC, HybridParamsC, HybridLimitsC
 
 RS_EDGE = np.dtype([("start", "<f8", (3,)), ("len", "<f8", (5,)), ("code", "<u8")], align=True)
 CSTEER_EDGE = np.dtype([("start", "<f8", (3,)), ("length", "<f8"), ("beta", "<f8"), ("cos_beta", "<f8"),
                         ("dtheta_ddist", "<f8"), ("direction", "<i4"), ("_pad", "<i4")], align=True)
 LINE_EDGE = np.dtype([("from", "<f8", (3,)), ("to", "<f8", (3,))], align=True)
 assert RS_EDGE.itemsize == 72 and CSTEER_EDGE.itemsize == 64 and LINE_EDGE.itemsize == 48
+HYBRID_CHILD = np.dtype([("pose", "<f8", (3,)), ("cost", "<f8"), ("heuristic", "<f8"), ("length", "<f8"),
+                         ("key", "<i4", (3,)), ("direction", "<i4"), ("kind", "<i4"), ("last", "<f4")], align=True)
+HYBRID_RESULT = np.dtype([("status", "<i4"), ("n_expanded", "<i4"), ("n_nodes", "<i4"), ("n_children", "<i4"),
+                          ("n_rs_attempts", "<i4"), ("path_len", "<i4"), ("cost", "<f8"), ("expanded_hash", "<u8")], align=True)
+HYBRID_PATH_STATE = np.dtype([("pose", "<f8", (3,)), ("length", "<f8"), ("last", "<f4"), ("kind", "i1"), ("direction", "i1"),
+                              ("slot", "i1"), ("_pad", "i1")], align=True)
+HYBRID_LOG_ENTRY = np.dtype([("key", "<i4", (3,)), ("direction", "<i4"), ("pose", "<f8", (3,))], align=True)
+assert HYBRID_CHILD.itemsize == 72 and HYBRID_RESULT.itemsize == 40 and HYBRID_PATH_STATE.itemsize == 40
+assert HYBRID_LOG_ENTRY.itemsize == 40
+MAX_CHILDREN = 19
 
 
 class PPXError(RuntimeError):
@@ -253,3 +263,84 @@ class Context:
         explored = np.empty((n, rows, cols), dtype=np.uint8) if want_explored else None
         self._check(ppx.ppx_wavefront(self._h, n, _ptr(goals), _ptr(cost), _ptr(explored)))
         return (cost, explored.astype(bool)) if want_explored else cost
+
+
+@dataclass
+class HybridParams:
+    """HybridAStar::SearchParameters (algo/hybrid_a_star.h:29-50)."""
+    wheelbase: float = 2.6
+    min_turning_radius: float = 2.0
+    direction_switching_cost: float = 0.0
+    reverse_cost_multiplier: float = 1.0
+    forward_cost_multiplier: float = 1.0
+    voronoi_cost_multiplier: float = 1.0
+    num_generated_motion: int = 5
+    spatial_resolution: float = 1.0
+    angular_resolution: float = 0.0872
+
+    def to_c(self):
+        return HybridParamsC(self.wheelbase, self.min_turning_radius, self.direction_switching_cost,
+                             self.reverse_cost_multiplier, self.forward_cost_multiplier, self.voronoi_cost_multiplier,
+                             self.num_generated_motion, 0, self.spatial_resolution, self.angular_resolution)
+
+
+class HybridAStar:
+    """ppx_hybrid: HybridAStar::Initialize + the batched graph search (algo/hybrid_a_star.cpp:206-257)."""
+
+    def __init__(self, ctx: Context, params: HybridParams = None, vp: ValidatorParams = None):
+        self.ctx = ctx
+        self.params = params or HybridParams()
+        self.vp = vp or ValidatorParams()
+        h = C.c_void_p()
+        p, v = self.params.to_c(), self.vp.to_c()
+        ctx._check(ppx.ppx_hybrid_create(ctx.handle, C.byref(p), C.byref(v), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            ppx.ppx_hybrid_destroy(self._h)
+            self._h = None
+
+    @property
+    def handle(self):
+        return self._h
+
+    def table(self):
+        dims = np.zeros(3, np.int32)
+        off = np.zeros(2, np.float64)
+        self.ctx._check(ppx.ppx_hybrid_table(self._h, _ptr(dims), _ptr(off), None))
+        vals = np.empty(tuple(dims.tolist()), np.float64)
+        self.ctx._check(ppx.ppx_hybrid_table(self._h, _ptr(dims), _ptr(off), _ptr(vals)))
+        return vals, off
+
+    def heuristic(self, goal, poses):
+        poses = _f64(poses)
+        goal = np.ascontiguousarray(goal, np.float64)
+        n = len(poses)
+        v, nh, ob = np.empty(n), np.empty(n), np.empty(n)
+        self.ctx._check(ppx.ppx_hybrid_heuristic(self._h, _ptr(goal), n, _ptr(poses), _ptr(v), _ptr(nh), _ptr(ob)))
+        return v, nh, ob
+
+    def expand(self, goal, parents, seeds):
+        parents = _f64(parents)
+        seeds = np.ascontiguousarray(seeds, np.uint64)
+        goal = np.ascontiguousarray(goal, np.float64)
+        n = len(parents)
+        count = np.zeros(n, np.int32)
+        children = np.zeros((n, MAX_CHILDREN), HYBRID_CHILD)
+        ph = np.empty(n)
+        self.ctx._check(ppx.ppx_hybrid_expand(self._h, _ptr(goal), n, _ptr(parents), _ptr(seeds), _ptr(count), _ptr(children), _ptr(ph)))
+        return count, children, ph
+
+    def search(self, starts, goals, seeds, max_path=0, max_log=0, max_expansions=0, max_nodes=0):
+        """-> dict(results (nq,) HYBRID_RESULT, paths (nq,max_path) or None, log (nq,max_log) or None)"""
+        starts, goals = _f64(starts), _f64(goals)
+        seeds = np.ascontiguousarray(seeds, np.uint64)
+        nq = len(starts)
+        lim = HybridLimitsC(max_nodes, max_expansions, max_path, max_log)
+        res = np.zeros(nq, HYBRID_RESULT)
+        paths = np.zeros((nq, max_path), HYBRID_PATH_STATE) if max_path else None
+        log = np.zeros((nq, max_log), HYBRID_LOG_ENTRY) if max_log else None
+        self.ctx._check(ppx.ppx_hybrid_search(self._h, nq, _ptr(starts), _ptr(goals), _ptr(seeds), C.byref(lim), _ptr(res),
+                                              _ptr(paths), _ptr(log)))
+        return dict(results=res, paths=paths, log=log)

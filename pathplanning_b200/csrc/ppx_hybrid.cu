@@ -1,0 +1,610 @@
+// libppx.so: Hybrid A* on the device -- NonHolonomicHeuristic table build (A9), batched successor
+// generation (A1/A2/A5/A6), heuristic lookups (A8/A9) and the batched graph search, one warp per
+// query (algo/hybrid_a_star.cpp:59-173,206-257, algo/a_star.h:326-434).
+//
+// Search kernel mapping: a query is a chain of dependent expansions (pop -> <=11 children ->
+// frontier updates), so the parallelism inside a query is the children of one node: lane c of the
+// query's warp generates child c (constant-steer rollout + adaptive collision check + Voronoi term
+// + heuristics, or the Reeds-Shepp shot), then lane 0 commits the children IN THE REFERENCE'S ORDER
+// to the frontier heap / key table, which is what makes expansion order -- and hence the expanded
+// set -- reproducible.  Throughput comes from thousands of independent queries in flight (one warp
+// each, persistent grid fed from one atomic cursor).
+#include <algorithm>
+#include <unordered_map>
+#include <vector>
+#include "ppx_ctx.h"
+#include "ppx_hybrid_host.h"
+
+using namespace ppx;
+
+int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored);
+
+struct ppx_hybrid {
+	ppx_ctx* ctx = nullptr;
+	ppx_hybrid_params params {};
+	ppx_validator_params vp {};
+	HybridDev dev {};
+	double* d_table = nullptr;
+	int x0 = 0, y0 = 0, tx = 0, ty = 0;
+	// grow-only device buffers
+	void* d_slabs = nullptr;
+	size_t slabBytes = 0;
+	float* d_wf = nullptr;
+	size_t wfBytes = 0;
+	void* d_io = nullptr;
+	size_t ioBytes = 0;
+};
+
+namespace {
+
+constexpr int kSearchWarps = 4; // warps (queries) per CTA
+
+// NonHolonomicHeuristic::Build, heuristics.cpp:62-73: one Reeds-Shepp solve per table entry
+__global__ void __launch_bounds__(128) k_nonholo_build(HybridDev P, double* __restrict__ values)
+{
+	const size_t total = (size_t)P.nhX * P.nhY * P.nhA;
+	size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+	const size_t stride = (size_t)gridDim.x * blockDim.x;
+	for (; idx < total; idx += stride) {
+		int k = (int)(idx % P.nhA);
+		int j = (int)((idx / P.nhA) % P.nhY);
+		int i = (int)(idx / ((size_t)P.nhA * P.nhY));
+		// Pose2d pose(i * spatialResolution - offsetX, j * spatialResolution - offsetY, k * angularResolution): ctor wraps
+		Pose pose = { i * P.spatialRes - P.nhOffX, j * P.spatialRes - P.nhOffY, wrap_theta(k * P.angRes) };
+		Pose goal = { 0.0, 0.0, 0.0 };
+		RSSolution sol;
+		rs_solve(pose, goal, P.rmin, P.revF, P.fwdF, P.swF, 0, sol);
+		values[idx] = (double)sol.cost;
+	}
+}
+
+__global__ void __launch_bounds__(128) k_hybrid_heuristic(HybridDev P, MapDev map, const float* __restrict__ wfCost, Pose goal,
+	int64_t n, const double* __restrict__ poses, double* __restrict__ combined, double* __restrict__ nonholo,
+	double* __restrict__ obstacles)
+{
+	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride) {
+		Pose s = { poses[3 * i], poses[3 * i + 1], poses[3 * i + 2] };
+		double h0 = nonholo_heuristic(P, goal, s);
+		double h1 = obstacle_heuristic(P, map, wfCost, goal, s);
+		if (nonholo)
+			nonholo[i] = h0;
+		if (obstacles)
+			obstacles[i] = h1;
+		if (combined)
+			combined[i] = combined_heuristic(P, map, wfCost, goal, s);
+	}
+}
+
+// GetNeighborStates for arbitrary parents: one warp per parent, lane c = child slot c.
+__global__ void __launch_bounds__(128) k_hybrid_expand(HybridDev P, MapDev map, const float* __restrict__ wfCost, Pose goal,
+	int64_t n, const double* __restrict__ parents, const unsigned long long* __restrict__ seeds,
+	int32_t* __restrict__ nChildren, ppx_hybrid_child* __restrict__ children, double* __restrict__ parentHeuristic,
+	unsigned long long* __restrict__ mtScratch)
+{
+	const unsigned lane = threadIdx.x & 31;
+	const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+	const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+	for (int64_t i = warp; i < n; i += nwarps) {
+		Pose parent = { parents[3 * i], parents[3 * i + 1], parents[3 * i + 2] };
+		Key3 pk = discretize_pose(P, parent);
+		double hCost = combined_heuristic(P, map, wfCost, goal, parent);
+		int want = 0;
+		if (lane == 0) {
+			int idx = 0;
+			Mt64 rng { mtScratch + (size_t)warp * 312, &idx };
+			rng.seed(seeds[i]);
+			want = rs_shot_wanted(rng, hCost) ? 1 : 0;
+			if (parentHeuristic)
+				parentHeuristic[i] = hCost;
+		}
+		want = __shfl_sync(0xffffffffu, want, 0);
+		const int nslots = 2 * P.numDeltas + want;
+		Child c;
+		c.ok = false;
+		double h = 0.0;
+		if ((int)lane < nslots) {
+			make_child(P, map, parent, pk, goal, (int)lane, c);
+			if (c.ok)
+				h = combined_heuristic(P, map, wfCost, goal, c.pose);
+		}
+		unsigned okMask = __ballot_sync(0xffffffffu, c.ok);
+		if (c.ok) {
+			int pos = __popc(okMask & ((1u << lane) - 1));
+			ppx_hybrid_child& o = children[i * PPX_MAX_CHILDREN + pos];
+			o.pose[0] = c.pose.x;
+			o.pose[1] = c.pose.y;
+			o.pose[2] = c.pose.th;
+			o.cost = c.cost;
+			o.heuristic = h;
+			o.length = c.length;
+			o.key[0] = c.key.x;
+			o.key[1] = c.key.y;
+			o.key[2] = c.key.k;
+			o.direction = c.dir;
+			o.kind = c.kind;
+			o.last = c.last;
+		}
+		if (lane == 0)
+			nChildren[i] = __popc(okMask);
+		__syncwarp();
+	}
+}
+
+}
+
+namespace {
+
+struct WsLayout {
+	size_t bytes; // per warp
+	int maxNodes, tableSize;
+	int x0, y0, tx, ty;
+};
+
+__host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
+
+__host__ __device__ inline size_t ws_bytes(int maxNodes, int tableSize)
+{
+	size_t n = (size_t)maxNodes;
+	return align16(n * 24) + 4 * align16(n * 8) + 6 * align16(n * 4) + align16((size_t)tableSize * 4) + align16(312 * 8);
+}
+
+__device__ inline SearchWs ws_carve(char* base, const WsLayout& L)
+{
+	SearchWs W;
+	size_t n = (size_t)L.maxNodes;
+	char* p = base;
+	W.pose = (double*)p; p += align16(n * 24);
+	W.g = (double*)p; p += align16(n * 8);
+	W.f = (double*)p; p += align16(n * 8);
+	W.length = (double*)p; p += align16(n * 8);
+	W.heapF = (double*)p; p += align16(n * 8);
+	W.mt = (unsigned long long*)p; p += align16(312 * 8);
+	W.parent = (int*)p; p += align16(n * 4);
+	W.keyIdx = (int*)p; p += align16(n * 4);
+	W.meta = (uint32_t*)p; p += align16(n * 4);
+	W.last = (float*)p; p += align16(n * 4);
+	W.heapSeq = (uint32_t*)p; p += align16(n * 4);
+	W.heapNode = (uint32_t*)p; p += align16(n * 4);
+	W.table = (uint32_t*)p;
+	W.maxNodes = L.maxNodes;
+	W.x0 = L.x0; W.y0 = L.y0; W.tx = L.tx; W.ty = L.ty;
+	return W;
+}
+
+// The graph search of one query per warp.
+__global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(HybridDev P, MapDev map, int64_t nq,
+	const double* __restrict__ starts, const double* __restrict__ goals, const unsigned long long* __restrict__ seeds,
+	const int* __restrict__ wfSlot, const float* __restrict__ wfCost, WsLayout L, char* __restrict__ slabs,
+	ppx_hybrid_limits limits, ppx_hybrid_result* __restrict__ results, ppx_hybrid_path_state* __restrict__ paths,
+	ppx_hybrid_log_entry* __restrict__ logs, unsigned long long* __restrict__ queue)
+{
+	__shared__ Child s_child[kSearchWarps][kMaxChildren];
+	__shared__ double s_h[kSearchWarps][kMaxChildren];
+	const unsigned lane = threadIdx.x & 31;
+	const int wib = threadIdx.x >> 5;
+	const size_t gwarp = (size_t)blockIdx.x * kSearchWarps + wib;
+	const SearchWs W = ws_carve(slabs + gwarp * L.bytes, L);
+	const size_t cells = (size_t)map.rows * map.cols;
+	Child* myChildren = s_child[wib];
+	double* myH = s_h[wib];
+
+	while (true) {
+		long long q = 0;
+		if (lane == 0)
+			q = (long long)atomicAdd(queue, 1ull);
+		q = __shfl_sync(0xffffffffu, q, 0);
+		if (q >= nq)
+			break;
+		for (int i = (int)lane; i < L.tableSize; i += 32)
+			W.table[i] = 0u;
+		__syncwarp();
+		const Pose start = { starts[3 * q], starts[3 * q + 1], starts[3 * q + 2] };
+		const Pose goal = { goals[3 * q], goals[3 * q + 1], goals[3 * q + 2] };
+		const float* wf = wfCost + (size_t)(wfSlot ? wfSlot[q] : q) * cells;
+		SearchState S;
+		Mt64 rng { W.mt, &S.mtIdx };
+		if (lane == 0) {
+			rng.seed(seeds ? seeds[q] : 0ull);
+			search_init(P, W, S, start);
+		}
+		__syncwarp();
+		int status = __shfl_sync(0xffffffffu, S.status, 0);
+		ppx_hybrid_log_entry* log = (logs && limits.max_log > 0) ? logs + (size_t)q * limits.max_log : nullptr;
+
+		while (status == PPX_SEARCH_RUNNING) {
+			int n = -1;
+			if (lane == 0) {
+				if (limits.max_expansions > 0 && S.nExpanded >= limits.max_expansions)
+					S.status = PPX_ERR_LIMIT;
+				else
+					n = search_pop(W, S, goal);
+			}
+			n = __shfl_sync(0xffffffffu, n, 0);
+			if (n < 0)
+				break;
+			// node n was written by lane 0 in an earlier iteration (ordered by the __syncwarp below)
+			const Pose parent = { W.pose[3 * n], W.pose[3 * n + 1], W.pose[3 * n + 2] };
+			const Key3 pk = discretize_pose(P, parent);
+			const double hCost = combined_heuristic(P, map, wf, goal, parent);
+			int want = 0;
+			if (lane == 0) {
+				if (log && S.nExpanded <= limits.max_log) {
+					ppx_hybrid_log_entry& e = log[S.nExpanded - 1];
+					e.key[0] = pk.x;
+					e.key[1] = pk.y;
+					e.key[2] = pk.k;
+					e.direction = (int)(W.meta[n] & 3u);
+					e.pose[0] = parent.x;
+					e.pose[1] = parent.y;
+					e.pose[2] = parent.th;
+				}
+				want = rs_shot_wanted(rng, hCost) ? 1 : 0;
+				S.nRsAttempts += want;
+			}
+			want = __shfl_sync(0xffffffffu, want, 0);
+			const int nslots = 2 * P.numDeltas + want;
+			if ((int)lane < nslots) {
+				Child c;
+				make_child(P, map, parent, pk, goal, (int)lane, c);
+				double h = 0.0;
+				if (c.ok)
+					h = combined_heuristic(P, map, wf, goal, c.pose);
+				myChildren[lane] = c;
+				myH[lane] = h;
+			}
+			__syncwarp();
+			if (lane == 0) {
+				const double parentG = W.g[n];
+				for (int s = 0; s < nslots && S.status == PPX_SEARCH_RUNNING; s++)
+					if (myChildren[s].ok)
+						consume_child(W, S, n, parentG, myChildren[s], myH[s], s);
+			}
+			__syncwarp();
+			status = __shfl_sync(0xffffffffu, S.status, 0);
+		}
+
+		if (lane == 0) {
+			ppx_hybrid_result r;
+			r.status = S.status == PPX_SEARCH_RUNNING ? -1 : S.status;
+			r.n_expanded = S.nExpanded;
+			r.n_nodes = S.numNodes;
+			r.n_children = S.nChildren;
+			r.n_rs_attempts = S.nRsAttempts;
+			r.path_len = 0;
+			r.cost = PPX_INF;
+			r.expanded_hash = S.hash;
+			if (S.status == PPX_OK && S.solution >= 0) {
+				r.cost = W.g[S.solution]; // GetOptimalCost, a_star.h:300-305
+				int depth = 0;
+				for (int m = S.solution; m >= 0; m = W.parent[m])
+					depth++;
+				r.path_len = depth;
+				if (paths && limits.max_path > 0) {
+					ppx_hybrid_path_state* out = paths + (size_t)q * limits.max_path;
+					int pos = depth - 1;
+					for (int m = S.solution; m >= 0; m = W.parent[m], pos--) {
+						if (pos >= limits.max_path)
+							continue;
+						ppx_hybrid_path_state& o = out[pos];
+						o.pose[0] = W.pose[3 * m];
+						o.pose[1] = W.pose[3 * m + 1];
+						o.pose[2] = W.pose[3 * m + 2];
+						o.length = W.length[m];
+						o.last = W.last[m];
+						uint32_t meta = W.meta[m];
+						o.kind = W.parent[m] < 0 ? (int8_t)-1 : (int8_t)((meta >> 2) & 1u);
+						o.direction = (int8_t)(meta & 3u);
+						o.slot = (int8_t)((meta >> 3) & 31u);
+						o._pad = 0;
+					}
+				}
+			}
+			results[q] = r;
+		}
+		__syncwarp();
+	}
+}
+
+}
+
+namespace {
+
+int grow(ppx_ctx* ctx, void** ptr, size_t* have, size_t want)
+{
+	if (*have >= want)
+		return PPX_OK;
+	if (*ptr) {
+		PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+		PPX_CUDA(ctx, cudaFree(*ptr));
+		*ptr = nullptr;
+		*have = 0;
+	}
+	size_t bytes = want + want / 8 + 256;
+	PPX_CUDA(ctx, cudaMalloc(ptr, bytes));
+	*have = bytes;
+	return PPX_OK;
+}
+
+int check_handle(ppx_hybrid* h)
+{
+	if (!h || !h->ctx)
+		return PPX_ERR_INVALID;
+	if (!h->ctx->has_map)
+		return ppx_fail(h->ctx, PPX_ERR_STATE, "no map uploaded (ppx_map_upload)");
+	return PPX_OK;
+}
+
+// One wavefront for `goal` into h->d_wf (slot 0).
+int single_wavefront(ppx_hybrid* h, const double* goal)
+{
+	ppx_ctx* ctx = h->ctx;
+	PPX_CHECK(grow(ctx, (void**)&h->d_wf, &h->wfBytes, ctx->cells * sizeof(float)));
+	double* d_goal;
+	PPX_CHECK(ppx_scratch(ctx, 5, 3 * sizeof(double), (void**)&d_goal));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_goal, goal, 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	return ppx_wavefront_launch(ctx, 1, d_goal, h->d_wf, nullptr);
+}
+
+// Sizes the per-warp slabs and launches the search kernel over device-resident queries.
+int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const double* d_goals, const uint64_t* d_seeds,
+	const int* d_wfSlot, const float* d_wf, const ppx_hybrid_limits& limits, ppx_hybrid_result* d_results,
+	ppx_hybrid_path_state* d_paths, ppx_hybrid_log_entry* d_log)
+{
+	ppx_ctx* ctx = h->ctx;
+	WsLayout L;
+	L.x0 = h->x0; L.y0 = h->y0; L.tx = h->tx; L.ty = h->ty;
+	L.tableSize = h->tx * h->ty * 7;
+	L.maxNodes = limits.max_nodes > 0 ? limits.max_nodes : 2 * L.tableSize;
+	L.bytes = (ws_bytes(L.maxNodes, L.tableSize) + 255) & ~(size_t)255;
+	// as many queries in flight as fit: 16 warps per SM, at most 12 GB of slabs
+	int64_t warps = std::min<int64_t>(nq, (int64_t)ctx->num_sms * 16);
+	const size_t budget = (size_t)12 << 30;
+	warps = std::max<int64_t>(1, std::min<int64_t>(warps, (int64_t)(budget / L.bytes)));
+	int ctas = (int)((warps + kSearchWarps - 1) / kSearchWarps);
+	PPX_CHECK(grow(ctx, &h->d_slabs, &h->slabBytes, (size_t)ctas * kSearchWarps * L.bytes));
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
+	k_hybrid_search<<<ctas, kSearchWarps * 32, 0, ctx->stream>>>(h->dev, ctx->map_dev(), nq, d_starts, d_goals,
+		(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, (char*)h->d_slabs, limits, d_results, d_paths, d_log, ctx->d_queue);
+	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
+}
+
+extern "C" {
+
+int ppx_hybrid_create(ppx_ctx* ctx, const ppx_hybrid_params* params, const ppx_validator_params* vp, ppx_hybrid** out)
+{
+	if (!ctx || !out)
+		return PPX_ERR_INVALID;
+	*out = nullptr;
+	PPX_REQUIRE(ctx, params && vp, "bad arguments");
+	if (!ctx->has_map)
+		return ppx_fail(ctx, PPX_ERR_STATE, "no map uploaded (ppx_map_upload)");
+	PPX_REQUIRE(ctx, params->spatial_resolution > 0 && params->angular_resolution > 0 && params->min_turning_radius > 0,
+		"resolutions and turning radius must be positive");
+	auto* h = new ppx_hybrid();
+	h->ctx = ctx;
+	h->params = *params;
+	h->vp = *vp;
+	if (hybrid_derive(*params, *vp, ctx->desc, h->dev) != PPX_OK) {
+		delete h;
+		return ppx_fail(ctx, PPX_ERR_INVALID, "num_generated_motion too large (max %d steering angles)", kMaxDeltas);
+	}
+	hybrid_key_table(*params, ctx->desc, h->x0, h->y0, h->tx, h->ty);
+	const size_t total = (size_t)h->dev.nhX * h->dev.nhY * h->dev.nhA;
+	cudaError_t e = cudaMalloc(&h->d_table, total * sizeof(double));
+	if (e != cudaSuccess) {
+		delete h;
+		return ppx_fail(ctx, PPX_ERR_CUDA, "cudaMalloc(heuristic table): %s", cudaGetErrorString(e));
+	}
+	h->dev.nh = h->d_table;
+	int blocks = (int)std::min<size_t>((total + 127) / 128, (size_t)ctx->num_sms * 16);
+	k_nonholo_build<<<blocks, 128, 0, ctx->stream>>>(h->dev, h->d_table);
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	*out = h;
+	return PPX_OK;
+}
+
+int ppx_hybrid_destroy(ppx_hybrid* h)
+{
+	if (!h)
+		return PPX_ERR_INVALID;
+	cudaStreamSynchronize(h->ctx->stream);
+	cudaFree(h->d_table);
+	cudaFree(h->d_slabs);
+	cudaFree(h->d_wf);
+	cudaFree(h->d_io);
+	delete h;
+	return PPX_OK;
+}
+
+int ppx_hybrid_table(ppx_hybrid* h, int32_t* dims, double* offsets, double* values)
+{
+	if (!h)
+		return PPX_ERR_INVALID;
+	if (dims) {
+		dims[0] = h->dev.nhX;
+		dims[1] = h->dev.nhY;
+		dims[2] = h->dev.nhA;
+	}
+	if (offsets) {
+		offsets[0] = h->dev.nhOffX;
+		offsets[1] = h->dev.nhOffY;
+	}
+	if (values) {
+		const size_t total = (size_t)h->dev.nhX * h->dev.nhY * h->dev.nhA;
+		PPX_CUDA(h->ctx, cudaMemcpyAsync(values, h->d_table, total * sizeof(double), cudaMemcpyDeviceToHost, h->ctx->stream));
+		PPX_CUDA(h->ctx, cudaStreamSynchronize(h->ctx->stream));
+	}
+	return PPX_OK;
+}
+
+int ppx_hybrid_heuristic(ppx_hybrid* h, const double* goal, int64_t n, const double* poses, double* combined,
+	double* nonholo, double* obstacles)
+{
+	PPX_CHECK(check_handle(h));
+	ppx_ctx* ctx = h->ctx;
+	PPX_REQUIRE(ctx, goal && n >= 0 && (n == 0 || poses), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	PPX_CHECK(single_wavefront(h, goal));
+	double* d_poses;
+	double* d_out;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * 3 * sizeof(double), (void**)&d_poses));
+	PPX_CHECK(ppx_scratch(ctx, 1, n * 3 * sizeof(double), (void**)&d_out));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_poses, poses, n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	// Pose2d goal as HybridAStar::SetGoalState stores it (ctor wrap is the caller's, like everywhere in this ABI)
+	Pose g = { goal[0], goal[1], goal[2] };
+	int blocks = (int)std::min<int64_t>((n + 127) / 128, (int64_t)ctx->num_sms * 16);
+	k_hybrid_heuristic<<<blocks, 128, 0, ctx->stream>>>(h->dev, ctx->map_dev(), h->d_wf, g, n, d_poses, d_out, d_out + n, d_out + 2 * n);
+	PPX_LAUNCHED(ctx);
+	if (combined)
+		PPX_CUDA(ctx, cudaMemcpyAsync(combined, d_out, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	if (nonholo)
+		PPX_CUDA(ctx, cudaMemcpyAsync(nonholo, d_out + n, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	if (obstacles)
+		PPX_CUDA(ctx, cudaMemcpyAsync(obstacles, d_out + 2 * n, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_hybrid_expand(ppx_hybrid* h, const double* goal, int64_t n, const double* parents, const uint64_t* seeds,
+	int32_t* n_children, ppx_hybrid_child* children, double* parent_heuristic)
+{
+	PPX_CHECK(check_handle(h));
+	ppx_ctx* ctx = h->ctx;
+	PPX_REQUIRE(ctx, goal && n >= 0 && (n == 0 || (parents && seeds && n_children && children)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	PPX_CHECK(single_wavefront(h, goal));
+	int blocks = (int)std::min<int64_t>((n + 3) / 4, (int64_t)ctx->num_sms * 8);
+	const size_t nwarps = (size_t)blocks * 4;
+	size_t off = 0;
+	auto carve = [&](size_t bytes) {
+		size_t o = off;
+		off += (bytes + 255) & ~(size_t)255;
+		return o;
+	};
+	size_t oParents = carve(n * 3 * sizeof(double)), oSeeds = carve(n * sizeof(uint64_t)), oCount = carve(n * sizeof(int32_t));
+	size_t oChildren = carve(n * PPX_MAX_CHILDREN * sizeof(ppx_hybrid_child)), oHeur = carve(n * sizeof(double));
+	size_t oMt = carve(nwarps * 312 * sizeof(unsigned long long));
+	char* base;
+	PPX_CHECK(ppx_scratch(ctx, 0, off, (void**)&base));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oParents, parents, n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oSeeds, seeds, n * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(base + oChildren, 0, n * PPX_MAX_CHILDREN * sizeof(ppx_hybrid_child), ctx->stream));
+	Pose g = { goal[0], goal[1], goal[2] };
+	k_hybrid_expand<<<blocks, 128, 0, ctx->stream>>>(h->dev, ctx->map_dev(), h->d_wf, g, n, (const double*)(base + oParents),
+		(const unsigned long long*)(base + oSeeds), (int32_t*)(base + oCount), (ppx_hybrid_child*)(base + oChildren),
+		(double*)(base + oHeur), (unsigned long long*)(base + oMt));
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaMemcpyAsync(n_children, base + oCount, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(children, base + oChildren, n * PPX_MAX_CHILDREN * sizeof(ppx_hybrid_child), cudaMemcpyDeviceToHost, ctx->stream));
+	if (parent_heuristic)
+		PPX_CUDA(ctx, cudaMemcpyAsync(parent_heuristic, base + oHeur, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_hybrid_search_dev(ppx_hybrid* h, int64_t nq, const double* d_starts, const double* d_goals,
+	const uint64_t* d_seeds, const ppx_hybrid_limits* limits, ppx_hybrid_result* d_results,
+	ppx_hybrid_path_state* d_paths, ppx_hybrid_log_entry* d_log)
+{
+	PPX_CHECK(check_handle(h));
+	ppx_ctx* ctx = h->ctx;
+	PPX_REQUIRE(ctx, nq >= 0 && limits && (nq == 0 || (d_starts && d_goals && d_results)), "bad arguments");
+	if (nq == 0)
+		return PPX_OK;
+	// chunks of queries whose wavefront grids fit the budget (8 GB)
+	const size_t grid = ctx->cells * sizeof(float);
+	const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(((size_t)8 << 30) / grid)));
+	PPX_CHECK(grow(ctx, (void**)&h->d_wf, &h->wfBytes, (size_t)chunk * grid));
+	for (int64_t q0 = 0; q0 < nq; q0 += chunk) {
+		const int64_t m = std::min(chunk, nq - q0);
+		PPX_CHECK(ppx_wavefront_launch(ctx, m, d_goals + 3 * q0, h->d_wf, nullptr));
+		PPX_CHECK(launch_search(h, m, d_starts + 3 * q0, d_goals + 3 * q0, d_seeds ? d_seeds + q0 : nullptr, nullptr, h->d_wf, *limits,
+			d_results + q0, d_paths ? d_paths + (size_t)q0 * limits->max_path : nullptr,
+			d_log ? d_log + (size_t)q0 * limits->max_log : nullptr));
+	}
+	return PPX_OK;
+}
+
+int ppx_hybrid_search(ppx_hybrid* h, int64_t nq, const double* starts, const double* goals, const uint64_t* seeds,
+	const ppx_hybrid_limits* limits, ppx_hybrid_result* results, ppx_hybrid_path_state* paths, ppx_hybrid_log_entry* log)
+{
+	PPX_CHECK(check_handle(h));
+	ppx_ctx* ctx = h->ctx;
+	PPX_REQUIRE(ctx, nq >= 0 && limits && (nq == 0 || (starts && goals && results)), "bad arguments");
+	PPX_REQUIRE(ctx, !paths || limits->max_path > 0, "paths requested with max_path == 0");
+	PPX_REQUIRE(ctx, !log || limits->max_log > 0, "log requested with max_log == 0");
+	if (nq == 0)
+		return PPX_OK;
+	const ppx_map_desc& d = ctx->desc;
+	// ObstaclesHeuristic::Update depends on the goal CELL only: one wavefront per distinct cell
+	std::unordered_map<long long, int> slotOf;
+	std::vector<int> wfSlot(nq);
+	std::vector<double> uniqueGoals;
+	for (int64_t q = 0; q < nq; q++) {
+		double gx = (goals[3 * q] - d.world_origin[0]) / (double)d.resolution;
+		double gy = (goals[3 * q + 1] - d.world_origin[1]) / (double)d.resolution;
+		bool in = gx > -2147483649.0 && gx < 2147483648.0 && gy > -2147483649.0 && gy < 2147483648.0;
+		int r = in ? (int)gx : -1, c = in ? (int)gy : -1;
+		if (r < 0 || r >= d.rows || c < 0 || c >= d.cols)
+			r = c = -1; // every goal outside the map shares one (all-infinite) grid
+		long long key = (long long)r * 0x100000000LL + (long long)(unsigned int)c;
+		auto it = slotOf.find(key);
+		if (it == slotOf.end()) {
+			it = slotOf.emplace(key, (int)(uniqueGoals.size() / 3)).first;
+			uniqueGoals.insert(uniqueGoals.end(), goals + 3 * q, goals + 3 * q + 3);
+		}
+		wfSlot[q] = it->second;
+	}
+	const int64_t nGoals = (int64_t)uniqueGoals.size() / 3;
+	const size_t grid = ctx->cells * sizeof(float);
+	PPX_REQUIRE(ctx, (size_t)nGoals * grid <= ((size_t)64 << 30), "too many distinct goals for one call (wavefront grids > 64 GB)");
+	PPX_CHECK(grow(ctx, (void**)&h->d_wf, &h->wfBytes, (size_t)nGoals * grid));
+	size_t off = 0;
+	auto carve = [&](size_t bytes) {
+		size_t o = off;
+		off += (bytes + 255) & ~(size_t)255;
+		return o;
+	};
+	size_t oStarts = carve(nq * 24), oGoals = carve(nq * 24), oSeeds = carve(nq * 8), oSlot = carve(nq * 4);
+	size_t oUGoals = carve(nGoals * 24), oRes = carve(nq * sizeof(ppx_hybrid_result));
+	size_t oPaths = carve(paths ? (size_t)nq * limits->max_path * sizeof(ppx_hybrid_path_state) : 0);
+	size_t oLog = carve(log ? (size_t)nq * limits->max_log * sizeof(ppx_hybrid_log_entry) : 0);
+	PPX_CHECK(grow(ctx, &h->d_io, &h->ioBytes, off));
+	char* base = (char*)h->d_io;
+	std::vector<uint64_t> zeroSeeds;
+	if (!seeds) {
+		zeroSeeds.assign(nq, 0);
+		seeds = zeroSeeds.data();
+	}
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oStarts, starts, nq * 24, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oGoals, goals, nq * 24, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oSeeds, seeds, nq * 8, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oSlot, wfSlot.data(), nq * 4, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oUGoals, uniqueGoals.data(), nGoals * 24, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CHECK(ppx_wavefront_launch(ctx, nGoals, (const double*)(base + oUGoals), h->d_wf, nullptr));
+	ppx_hybrid_path_state* d_paths = paths ? (ppx_hybrid_path_state*)(base + oPaths) : nullptr;
+	ppx_hybrid_log_entry* d_log = log ? (ppx_hybrid_log_entry*)(base + oLog) : nullptr;
+	if (d_paths)
+		PPX_CUDA(ctx, cudaMemsetAsync(d_paths, 0, (size_t)nq * limits->max_path * sizeof(ppx_hybrid_path_state), ctx->stream));
+	if (d_log)
+		PPX_CUDA(ctx, cudaMemsetAsync(d_log, 0, (size_t)nq * limits->max_log * sizeof(ppx_hybrid_log_entry), ctx->stream));
+	PPX_CHECK(launch_search(h, nq, (const double*)(base + oStarts), (const double*)(base + oGoals), (const uint64_t*)(base + oSeeds),
+		(const int*)(base + oSlot), h->d_wf, *limits, (ppx_hybrid_result*)(base + oRes), d_paths, d_log));
+	PPX_CUDA(ctx, cudaMemcpyAsync(results, base + oRes, nq * sizeof(ppx_hybrid_result), cudaMemcpyDeviceToHost, ctx->stream));
+	if (paths)
+		PPX_CUDA(ctx, cudaMemcpyAsync(paths, d_paths, (size_t)nq * limits->max_path * sizeof(ppx_hybrid_path_state), cudaMemcpyDeviceToHost, ctx->stream));
+	if (log)
+		PPX_CUDA(ctx, cudaMemcpyAsync(log, d_log, (size_t)nq * limits->max_log * sizeof(ppx_hybrid_log_entry), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+} // extern "C"

@@ -29,6 +29,17 @@ class RSCostParamsC(C.Structure):
                 ("shortest", C.c_int32)]
 
 
+class HybridParamsC(C.Structure):
+    _fields_ = [("wheelbase", C.c_double), ("min_turning_radius", C.c_double), ("direction_switching_cost", C.c_double),
+                ("reverse_cost_multiplier", C.c_double), ("forward_cost_multiplier", C.c_double),
+                ("voronoi_cost_multiplier", C.c_double), ("num_generated_motion", C.c_uint32), ("_pad", C.c_uint32),
+                ("spatial_resolution", C.c_double), ("angular_resolution", C.c_double)]
+
+
+class HybridLimitsC(C.Structure):
+    _fields_ = [("max_nodes", C.c_int32), ("max_expansions", C.c_int32), ("max_path", C.c_int32), ("max_log", C.c_int32)]
+
+
 _p = C.c_void_p
 _i64 = C.c_int64
 _SIGS = {
@@ -60,6 +71,13 @@ _SIGS = {
     "ppx_rs_interpolate": (C.c_int, [_p, _i64, _p, C.c_double, C.c_int32, _p, _p]),
     "ppx_wavefront": (C.c_int, [_p, _i64, _p, _p, _p]),
     "ppx_wavefront_dev": (C.c_int, [_p, _i64, _p, _p, _p]),
+    "ppx_hybrid_create": (C.c_int, [_p, C.POINTER(HybridParamsC), C.POINTER(ValidatorParamsC), C.POINTER(_p)]),
+    "ppx_hybrid_destroy": (C.c_int, [_p]),
+    "ppx_hybrid_table": (C.c_int, [_p, _p, _p, _p]),
+    "ppx_hybrid_heuristic": (C.c_int, [_p, _p, _i64, _p, _p, _p, _p]),
+    "ppx_hybrid_expand": (C.c_int, [_p, _p, _i64, _p, _p, _p, _p, _p]),
+    "ppx_hybrid_search": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
+    "ppx_hybrid_search_dev": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
 }
 
 for _name, (_res, _args) in _SIGS.items():

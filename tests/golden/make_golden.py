@@ -190,9 +190,81 @@ def main_wavefront():
     print("wavefront reached:", reached)
 
 
+HYBRID_QUERIES_FIXED = [
+    ((-18.0, -18.0, 0.0), (17.0, 17.5, np.pi / 2), 42),  # BASELINE config C2
+    ((5.0, 2.0, 1.0), (5.0, 2.0, 1.0), 1),  # start == goal
+    ((-18.0, -18.0, 0.0), (-16.0, -14.0, 0.0), 2),  # goal enclosed by a car outline: Failure
+    ((0.0, 2.0, 0.0), (6.0, 2.5, 0.3), 3),  # short hop, solved by an early Reeds-Shepp shot
+]
+
+
+def hybrid_queries(w, n_random=12):
+    rng = np.random.default_rng(2026)
+    qs = list(HYBRID_QUERIES_FIXED)
+    while len(qs) < len(HYBRID_QUERIES_FIXED) + n_random:
+        p = np.stack([rng.uniform(-18.5, 18.5, 2), rng.uniform(-18.5, 18.5, 2), rng.uniform(-np.pi, np.pi, 2)], 1)
+        if w.is_state_valid(p).all():
+            qs.append((tuple(p[0]), tuple(p[1]), 1000 + len(qs)))
+    return qs
+
+
+def main_hybrid():
+    """Hybrid A* on the C2 parking lot: heuristic table, heuristic lookups, GetNeighborStates on random
+    parents, and whole graph searches with their expansion sequences."""
+    w = c2_world()
+    w.set_validator_params(1.0, 0.1)
+    H = refapi.Hybrid(w)
+    table, off = H.table()
+    assert np.array_equal(table, table.astype(np.float32).astype(np.float64))  # float-precision costs
+    goal = HYBRID_QUERIES_FIXED[0][1]
+    H.prepare_goal(goal)
+    rng = np.random.default_rng(77)
+    m = 3000
+    hp = np.stack([rng.uniform(-21, 21, m), rng.uniform(-21, 21, m), rng.uniform(-4, 4, m)], 1)
+    hv, hnh, hob = H.heuristic(hp)
+    par = np.stack([rng.uniform(-19.5, 19.5, 1200), rng.uniform(-19.5, 19.5, 1200), rng.uniform(-3.5, 3.5, 1200)], 1)
+    par = par[w.is_state_valid(par)][:400]
+    # a cluster near the goal so that Reeds-Shepp shots are attempted and succeed
+    near = np.stack([goal[0] + rng.uniform(-4, 2, 60), goal[1] + rng.uniform(-6, 1, 60), rng.uniform(-np.pi, np.pi, 60)], 1)
+    par = np.concatenate([par, near[w.is_state_valid(near)]])
+    seeds = (np.arange(len(par)) + 11).astype(np.uint64)
+    ex_n = np.zeros(len(par), np.int32)
+    ex = {k: np.zeros((len(par), 11) + sh, dt) for k, sh, dt in (("poses", (3,), np.float64), ("keys", (3,), np.int32),
+          ("dirs", (), np.int32), ("costs", (), np.float64), ("kinds", (), np.int32), ("heuristics", (), np.float64))}
+    ex_ph = np.zeros(len(par))
+    for i in range(len(par)):
+        e = H.expand(par[i], int(seeds[i]))
+        ex_n[i] = e["n"]
+        ex_ph[i] = e["parent_heuristic"]
+        for k in ex:
+            ex[k][i, :e["n"]] = e[k]
+    out = dict(table=table.astype(np.float32), table_off=off, heur_goal=np.array(goal), heur_poses=hp, heur_combined=hv,
+               heur_nonholo=hnh, heur_obstacles=hob, ex_parents=par, ex_seeds=seeds, ex_n=ex_n, ex_parent_heuristic=ex_ph,
+               **{"ex_" + k: v for k, v in ex.items()})
+    qs = hybrid_queries(w)
+    out["q_start"] = np.array([q[0] for q in qs])
+    out["q_goal"] = np.array([q[1] for q in qs])
+    out["q_seed"] = np.array([q[2] for q in qs], np.uint64)
+    st, cost, nexp, nchild = [], [], [], []
+    for i, (s, g, seed) in enumerate(qs):
+        r = H.search(s, g, seed)
+        st.append(r["status"]); cost.append(r["cost"]); nexp.append(r["n_expanded"]); nchild.append(r["n_children"])
+        out[f"q{i}_keys"] = r["exp_keys"].astype(np.int16)
+        out[f"q{i}_poses"] = r["exp_poses"]
+        out[f"q{i}_path"] = r["path"]
+        out[f"q{i}_kinds"] = r["kinds"].astype(np.int8)
+        out[f"q{i}_lengths"] = r["lengths"]
+        print("query", i, "status", r["status"], "cost", r["cost"], "expanded", r["n_expanded"], "children", r["n_children"])
+    out.update(q_status=np.array(st), q_cost=np.array(cost), q_expanded=np.array(nexp), q_children=np.array(nchild))
+    np.savez_compressed(os.path.join(HERE, "hybrid_c2.npz"), **out)
+    print("hybrid_c2.npz", os.path.getsize(os.path.join(HERE, "hybrid_c2.npz")))
+
+
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
     if which in ("all", "base"):
         main()
     if which in ("all", "wavefront"):
         main_wavefront()
+    if which in ("all", "hybrid"):
+        main_hybrid()

@@ -237,3 +237,89 @@ def nonholo_build(lb, ub, spatial_res=1.0, ang_res=0.0872, rmin=2.0, rev=1.0, fw
     sec = lib().ref_nonholo_build(_d3(lb), _d3(ub), C.c_double(spatial_res), C.c_double(ang_res), C.c_double(rmin),
                                   C.c_double(rev), C.c_double(fwd), C.c_double(sw), _p(dims), _p(off), _p(vals))
     return vals, off, sec
+
+
+# ---- Hybrid A* --------------------------------------------------------------------------------
+DEFAULT_HYBRID = dict(min_turning_radius=2.0, direction_switching_cost=0.0, reverse_cost_multiplier=1.0,
+                      forward_cost_multiplier=1.0, voronoi_cost_multiplier=1.0, num_generated_motion=5,
+                      spatial_resolution=1.0, angular_resolution=0.0872)
+
+
+class Hybrid:
+    """HybridAStar of the reference over a World (Initialize runs in the constructor)."""
+
+    def __init__(self, world, **kw):
+        p = dict(DEFAULT_HYBRID)
+        p.update(kw)
+        self.params = p
+        self.world = world
+        L = lib()
+        L.ref_hybrid_create.restype = C.c_void_p
+        self.h = C.c_void_p(L.ref_hybrid_create(
+            world.h, C.c_double(p["min_turning_radius"]), C.c_double(p["direction_switching_cost"]),
+            C.c_double(p["reverse_cost_multiplier"]), C.c_double(p["forward_cost_multiplier"]),
+            C.c_double(p["voronoi_cost_multiplier"]), C.c_uint(p["num_generated_motion"]),
+            C.c_double(p["spatial_resolution"]), C.c_double(p["angular_resolution"])))
+        if not self.h:
+            raise RuntimeError("ref_hybrid_create failed")
+
+    def close(self):
+        if self.h:
+            lib().ref_hybrid_destroy(self.h)
+            self.h = None
+
+    def table(self):
+        dims = np.zeros(3, np.int32)
+        off = np.zeros(2, np.float64)
+        lib().ref_hybrid_table(self.h, _p(dims), _p(off), None)
+        vals = np.empty(tuple(dims.tolist()), np.float64)
+        lib().ref_hybrid_table(self.h, _p(dims), _p(off), _p(vals))
+        return vals, off
+
+    def search(self, start, goal, seed, cap=200000):
+        """Wavefront + GVD update + graph search (hybrid_a_star.cpp:248-257)."""
+        cost = C.c_double()
+        nexp, nchild, nsamp = C.c_long(), C.c_long(), C.c_long()
+        times = (C.c_double * 3)()
+        st = lib().ref_hybrid_search(self.h, _d3(start), _d3(goal), C.c_uint64(seed), C.c_int(1), C.byref(cost),
+                                     C.byref(nexp), C.byref(nchild), C.byref(nsamp), times)
+        n = nexp.value
+        keys = np.empty((max(n, 1), 4), np.int32)
+        poses = np.empty((max(n, 1), 3), np.float64)
+        lib().ref_hybrid_expansions(self.h, C.c_long(n), _p(keys), _p(poses))
+        sp = np.empty((4096, 3), np.float64)
+        kinds = np.empty(4096, np.int32)
+        lens = np.empty(4096, np.float64)
+        m = lib().ref_hybrid_solution(self.h, C.c_long(4096), _p(sp), _p(kinds), _p(lens)) if st == 0 else 0
+        return dict(status=st, cost=cost.value, n_expanded=n, n_children=nchild.value, n_samples=nsamp.value,
+                    times=list(times), exp_keys=keys[:n], exp_poses=poses[:n], path=sp[:m].copy(), kinds=kinds[:m].copy(),
+                    lengths=lens[:m].copy())
+
+    def search_full(self, start, goal, seed):
+        sec = C.c_double()
+        plen = C.c_long()
+        st = lib().ref_hybrid_search_full(self.h, _d3(start), _d3(goal), C.c_uint64(seed), C.byref(sec), C.byref(plen))
+        return st, sec.value, plen.value
+
+    def prepare_goal(self, goal):
+        lib().ref_hybrid_prepare_goal(self.h, _d3(goal))
+
+    def expand(self, parent, seed):
+        poses = np.empty((11, 3), np.float64)
+        keys = np.empty((11, 3), np.int32)
+        dirs = np.empty(11, np.int32)
+        costs = np.empty(11, np.float64)
+        kinds = np.empty(11, np.int32)
+        heur = np.empty(11, np.float64)
+        ph = C.c_double()
+        n = lib().ref_hybrid_expand(self.h, _d3(parent), C.c_uint64(seed), _p(poses), _p(keys), _p(dirs), _p(costs),
+                                    _p(kinds), _p(heur), C.byref(ph))
+        return dict(n=n, poses=poses[:n], keys=keys[:n], dirs=dirs[:n], costs=costs[:n], kinds=kinds[:n],
+                    heuristics=heur[:n], parent_heuristic=ph.value)
+
+    def heuristic(self, poses):
+        poses = np.ascontiguousarray(poses, np.float64)
+        n = len(poses)
+        v, nh, ob = np.empty(n), np.empty(n), np.empty(n)
+        lib().ref_hybrid_heuristic(self.h, C.c_long(n), _p(poses), _p(v), _p(nh), _p(ob))
+        return v, nh, ob

@@ -1,0 +1,135 @@
+"""GPU parity tests of Hybrid A* (A1-A6, A8 lookup, A9) through the C ABI against the fixture
+generated from the compiled reference (tests/golden/hybrid_c2.npz) and the live reference.
+
+Bars (BASELINE.json north_star): discrete results -- successor keys / kinds / directions, expansion
+sequences, statuses -- bit-exact; continuous costs, heuristics and poses within 1e-6 relative (the
+device libm is not the host's, so a last-ulp difference in a pose is expected and allowed).
+"""
+import numpy as np
+import pytest
+
+import pathplanning_b200 as pp
+from common import load_npz, c2_world_desc, assert_close_rel
+
+pytestmark = pytest.mark.gpu
+REL = 1e-6
+
+
+@pytest.fixture(scope="module")
+def fx():
+    return load_npz("hybrid_c2.npz")
+
+
+@pytest.fixture(scope="module")
+def planner(ctx):
+    g = load_npz("edges_c2.npz")
+    desc, occ, sq, pc = c2_world_desc(g)
+    ctx.upload_map(desc, sq, occ, pc)
+    h = pp.HybridAStar(ctx, pp.HybridParams(), pp.ValidatorParams(1.0, 0.1))
+    yield h
+    h.close()
+
+
+def test_nonholo_table(planner, fx):
+    """NonHolonomicHeuristic::Build: 41 x 41 x 73 Reeds-Shepp costs (float precision)."""
+    table, off = planner.table()
+    assert table.shape == fx["table"].shape and np.array_equal(off, fx["table_off"])
+    ref = fx["table"].astype(np.float64)
+    assert_close_rel(table, ref, REL, "table")
+    assert (table != ref).mean() < 1e-3  # float-rounded costs: all but a handful are bit-identical
+
+
+def test_heuristics(planner, fx):
+    v, nh, ob = planner.heuristic(fx["heur_goal"], fx["heur_poses"])
+    assert_close_rel(ob, fx["heur_obstacles"], REL, "obstacle heuristic")
+    assert_close_rel(nh, fx["heur_nonholo"], REL, "non-holonomic heuristic")
+    assert_close_rel(v, fx["heur_combined"], REL, "combined heuristic")
+
+
+def test_expand(planner, fx):
+    cnt, ch, ph = planner.expand(fx["heur_goal"], fx["ex_parents"], fx["ex_seeds"])
+    assert np.array_equal(cnt, fx["ex_n"])
+    assert_close_rel(ph, fx["ex_parent_heuristic"], REL, "parent heuristic")
+    for i in range(len(cnt)):
+        n = cnt[i]
+        c = ch[i, :n]
+        assert np.array_equal(c["key"], fx["ex_keys"][i, :n]), i
+        assert np.array_equal(c["direction"], fx["ex_dirs"][i, :n]), i
+        assert np.array_equal(c["kind"], fx["ex_kinds"][i, :n]), i
+        assert np.abs(c["pose"] - fx["ex_poses"][i, :n]).max(initial=0) < 1e-9, i
+        assert_close_rel(c["cost"], fx["ex_costs"][i, :n], REL, f"cost {i}")
+        assert_close_rel(c["heuristic"], fx["ex_heuristics"][i, :n], REL, f"heuristic {i}")
+
+
+def _check_query(fx, i, res, path, log):
+    assert int(res["status"]) == fx["q_status"][i], (i, res)
+    assert int(res["n_expanded"]) == fx["q_expanded"][i], (i, res)
+    assert int(res["n_children"]) == fx["q_children"][i], (i, res)
+    keys = fx[f"q{i}_keys"].astype(np.int32)
+    n = len(keys)
+    assert np.array_equal(log["key"][:n], keys[:, :3]), i
+    assert np.array_equal(log["direction"][:n], keys[:, 3]), i
+    assert np.abs(log["pose"][:n] - fx[f"q{i}_poses"]).max(initial=0) < 1e-9, i
+    if fx["q_status"][i] == 0:
+        assert_close_rel([res["cost"]], [fx["q_cost"][i]], REL, f"cost {i}")
+        m = int(res["path_len"])
+        assert m == len(fx[f"q{i}_path"])
+        assert np.abs(path["pose"][:m] - fx[f"q{i}_path"]).max() < 1e-9
+        assert np.array_equal(path["kind"][1:m], fx[f"q{i}_kinds"][1:])
+        assert_close_rel(path["length"][1:m], fx[f"q{i}_lengths"][1:], REL, "action lengths")
+
+
+def test_search_golden_batch(planner, fx):
+    """All fixture queries in ONE batched call (one warp each), expansion logs compared entry by entry."""
+    out = planner.search(fx["q_start"], fx["q_goal"], fx["q_seed"], max_path=256, max_log=8192)
+    for i in range(len(fx["q_seed"])):
+        _check_query(fx, i, out["results"][i], out["paths"][i], out["log"][i])
+
+
+def test_search_single_equals_batch(planner, fx):
+    a = planner.search(fx["q_start"][:1], fx["q_goal"][:1], fx["q_seed"][:1], max_path=256, max_log=2048)
+    _check_query(fx, 0, a["results"][0], a["paths"][0], a["log"][0])
+
+
+def test_search_limits(planner, fx):
+    out = planner.search(fx["q_start"][:1], fx["q_goal"][:1], fx["q_seed"][:1], max_expansions=100)
+    assert int(out["results"][0]["status"]) == -6 and int(out["results"][0]["n_expanded"]) == 100
+    out = planner.search(fx["q_start"][:1], fx["q_goal"][:1], fx["q_seed"][:1], max_nodes=64)
+    assert int(out["results"][0]["status"]) == -4
+
+
+def test_search_live_reference(ctx, ref, planner):
+    """200 fresh queries against the reference running here: statuses, expansion counts and hashes of
+    the expansion sequences (compared through the logs), costs within 1e-6."""
+    g = load_npz("edges_c2.npz")
+    w = ref.World(g["lb"], g["ub"], float(g["resolution"]))
+    for r in g["rects"]:
+        w.add_rectangle(*r)
+    w.update()
+    w.set_validator_params(1.0, 0.1)
+    H = ref.Hybrid(w)
+    rng = np.random.default_rng(99)
+    starts, goals = [], []
+    while len(starts) < 200:
+        p = np.stack([rng.uniform(-18.5, 18.5, 2), rng.uniform(-18.5, 18.5, 2), rng.uniform(-np.pi, np.pi, 2)], 1)
+        if w.is_state_valid(p).all():
+            starts.append(p[0])
+            goals.append(p[1])
+    starts, goals = np.array(starts), np.array(goals)
+    seeds = np.arange(200, dtype=np.uint64) + 5000
+    out = planner.search(starts, goals, seeds, max_path=256, max_log=4096)
+    differing = []
+    for i in range(200):
+        r = H.search(starts[i], goals[i], int(seeds[i]))
+        res = out["results"][i]
+        n = r["n_expanded"]
+        same = (int(res["status"]) == r["status"] and int(res["n_expanded"]) == n and n <= 4096
+                and np.array_equal(out["log"][i]["key"][:n], r["exp_keys"][:, :3]))
+        if not same:
+            differing.append(i)
+            continue
+        if r["status"] == 0:
+            assert_close_rel([res["cost"]], [r["cost"]], REL, f"cost {i}")
+    H.close()
+    w.close()
+    assert not differing, f"queries with a different expansion sequence: {differing}"

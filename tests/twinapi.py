@@ -51,3 +51,73 @@ class World:
         lib().twin_check_rs(self.h, C.c_long(n), _p(edges), C.c_double(rmin), C.c_float(radius), C.c_float(min_step),
                             C.c_int(impl), _p(valid), _p(last), _p(samples), _p(micro))
         return dict(valid=valid.astype(bool), last=last, samples=samples, microsteps=micro)
+
+
+class Hybrid:
+    """The Hybrid A* device code (ppx_hybrid.cuh) run sequentially on the host."""
+
+    def __init__(self, world, params, vp, table=None):
+        from pathplanning_b200.lib import HybridParamsC, ValidatorParamsC
+        self.world = world
+        self.params = HybridParamsC(**params) if isinstance(params, dict) else params
+        self.vp = vp
+        L = lib()
+        L.twin_hybrid_create.restype = C.c_void_p
+        t = None if table is None else np.ascontiguousarray(table, np.float64)
+        self.h = C.c_void_p(L.twin_hybrid_create(world.h, C.byref(self.params), C.byref(vp), _p(t)))
+        assert self.h
+
+    def close(self):
+        if self.h:
+            lib().twin_hybrid_destroy(self.h)
+            self.h = None
+
+    def table(self):
+        dims = np.zeros(4, np.int32)
+        off = np.zeros(2, np.float64)
+        lib().twin_hybrid_info(self.h, _p(dims), _p(off), None, None)
+        vals = np.empty(tuple(dims[:3].tolist()), np.float64)
+        lib().twin_hybrid_info(self.h, _p(dims), _p(off), None, _p(vals))
+        return vals, off
+
+    def heuristic(self, wf, goal, poses):
+        poses = np.ascontiguousarray(poses, np.float64)
+        wf = np.ascontiguousarray(wf, np.float32)
+        goal = np.ascontiguousarray(goal, np.float64)
+        n = len(poses)
+        v, nh, ob = np.empty(n), np.empty(n), np.empty(n)
+        lib().twin_hybrid_heuristic(self.h, _p(wf), _p(goal), C.c_long(n), _p(poses), _p(v), _p(nh), _p(ob))
+        return v, nh, ob
+
+    def expand(self, wf, goal, parents, seeds):
+        from pathplanning_b200.api import HYBRID_CHILD
+        parents = np.ascontiguousarray(parents, np.float64)
+        seeds = np.ascontiguousarray(seeds, np.uint64)
+        wf = np.ascontiguousarray(wf, np.float32)
+        goal = np.ascontiguousarray(goal, np.float64)
+        n = len(parents)
+        count = np.zeros(n, np.int32)
+        children = np.zeros((n, 19), HYBRID_CHILD)
+        ph = np.empty(n)
+        lib().twin_hybrid_expand(self.h, _p(wf), _p(goal), C.c_long(n), _p(parents), _p(seeds), _p(count), _p(children), _p(ph))
+        return count, children, ph
+
+    def search(self, wf, start, goal, seed, max_path=2048, max_log=100000, max_expansions=0):
+        from pathplanning_b200.api import HYBRID_RESULT, HYBRID_PATH_STATE, HYBRID_LOG_ENTRY
+        from pathplanning_b200.lib import HybridLimitsC
+        wf = np.ascontiguousarray(wf, np.float32)
+        lim = HybridLimitsC(0, max_expansions, max_path, max_log)
+        res = np.zeros(1, HYBRID_RESULT)
+        path = np.zeros(max_path, HYBRID_PATH_STATE)
+        log = np.zeros(max_log, HYBRID_LOG_ENTRY)
+        s = np.ascontiguousarray(start, np.float64)
+        g = np.ascontiguousarray(goal, np.float64)
+        lib().twin_hybrid_search(self.h, _p(wf), _p(s), _p(g), C.c_uint64(seed), C.byref(lim), _p(res), _p(path), _p(log))
+        r = res[0]
+        return dict(result=r, path=path[:int(r["path_len"])], log=log[:min(int(r["n_expanded"]), max_log)])
+
+
+def mt64_uniform(seed, n):
+    out = np.empty(n, np.float64)
+    lib().twin_mt64_uniform(C.c_uint64(seed), C.c_long(n), _p(out))
+    return out
