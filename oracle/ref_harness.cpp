@@ -12,6 +12,13 @@
 //        (algo/heuristics.cpp:84-94, out of bounds).  The harness re-points every m_values[i][j]
 //        into a padded copy where index k<0 aliases k+numAngular, which makes the read defined
 //        without touching reference source.  The CUDA path implements the same wrap.
+//  * H15 StatePropagator::GetVoronoiCost indexes GVD::m_pathCostMap unchecked (hybrid_a_star.cpp:102-104,
+//        assert compiled out) and the end of a primitive may overshoot the map by one validator step
+//        (trap H6): rows beyond the grid read past the heap block (ASan: heap-buffer-overflow; the value
+//        depends on the heap layout and decides expansion order).  The harness re-points the grid's
+//        storage into the middle of a zero-filled block (kPadRows rows on either side), so those reads
+//        return 0 without touching reference source.  The CUDA path reads 0 there as well; reads that
+//        stay inside the allocation (a column overflow aliasing the next row) are reproduced as is.
 //  * H1/H2 are properties of how the reference compiles (abs overload, int WrapTheta); the
 //        harness asserts both at load time (ref_selfcheck).
 //
@@ -536,7 +543,10 @@ struct RefHybrid {
 	Ref<RecordingPropagator> propagator;
 	std::vector<double*> paddedBlocks; // H3 padding
 	std::vector<double*> originalBlocks;
+	float* paddedPathCost = nullptr; // H15 padding
+	float* originalPathCost = nullptr;
 };
+constexpr long kPadRows = 64;
 }
 
 void* ref_hybrid_create(void* hw, double minTurningRadius, double directionSwitchingCost, double reverseCostMultiplier,
@@ -575,12 +585,25 @@ void* ref_hybrid_create(void* hw, double minTurningRadius, double directionSwitc
 			h->paddedBlocks.push_back(padded);
 			nh.m_values[i][j] = padded + na;
 		}
+	// H15: zero padding around GVD::m_pathCostMap
+	{
+		auto& grid = h->planner->m_gvd->m_pathCostMap;
+		const long n = (long)grid.rows * grid.columns, pad = kPadRows * grid.columns;
+		h->paddedPathCost = new float[n + 2 * pad]();
+		memcpy(h->paddedPathCost + pad, grid.m_data, n * sizeof(float));
+		h->originalPathCost = grid.m_data;
+		grid.m_data = h->paddedPathCost + pad;
+	}
 	return h;
 }
 
 void ref_hybrid_destroy(void* hh)
 {
 	auto* h = (RefHybrid*)hh;
+	if (h->paddedPathCost) {
+		h->planner->m_gvd->m_pathCostMap.m_data = h->originalPathCost;
+		delete[] h->paddedPathCost;
+	}
 	auto& nh = *h->planner->m_nonHoloHeuristic;
 	size_t idx = 0;
 	for (unsigned i = 0; i < nh.numSpatialX; i++)

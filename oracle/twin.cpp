@@ -222,7 +222,7 @@ void twin_hybrid_expand(void* hh, const float* wfCost, const double* goal, long 
 
 // The loop of k_hybrid_search for one query, sequentially.
 void twin_hybrid_search(void* hh, const float* wfCost, const double* start, const double* goal, uint64_t seed,
-	const ppx_hybrid_limits* limits, ppx_hybrid_result* result, ppx_hybrid_path_state* path, ppx_hybrid_log_entry* log)
+	const ppx_hybrid_limits* limits, ppx_hybrid_result* result, ppx_hybrid_path_state* path, ppx_hybrid_log_entry* log, double* fLog)
 {
 	auto* h = (TwinHybrid*)hh;
 	const HybridDev& P = h->dev;
@@ -260,6 +260,7 @@ void twin_hybrid_search(void* hh, const float* wfCost, const double* start, cons
 			e.key[0] = pk.x; e.key[1] = pk.y; e.key[2] = pk.k;
 			e.direction = (int)(W.meta[n] & 3u);
 			e.pose[0] = par.x; e.pose[1] = par.y; e.pose[2] = par.th;
+			if (fLog) { fLog[2 * (S.nExpanded - 1)] = W.g[n]; fLog[2 * (S.nExpanded - 1) + 1] = W.f[n]; }
 		}
 		int want = rs_shot_wanted(rng, hCost) ? 1 : 0;
 		S.nRsAttempts += want;

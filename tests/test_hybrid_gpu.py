@@ -46,6 +46,20 @@ def test_heuristics(planner, fx):
     assert_close_rel(v, fx["heur_combined"], REL, "combined heuristic")
 
 
+def _keys_match(keys, ref_keys, ref_poses, spatial=1.0, angular=0.0872, eps=1e-9):
+    """Discrete poses must be identical, except for a component whose REFERENCE continuous value lies
+    within eps of a discretisation boundary: there the reference's own key flips with the last ulp of
+    its libm (e.g. a Reeds-Shepp shot ending on a goal with an integer coordinate), so either
+    neighbouring cell is accepted."""
+    keys, ref_keys = np.atleast_2d(keys), np.atleast_2d(ref_keys)
+    diff = keys != ref_keys
+    if not diff.any():
+        return True
+    q = np.atleast_2d(ref_poses) / np.array([spatial, spatial, angular])
+    near = np.abs(q - np.round(q)) < eps
+    return bool((near | ~diff).all() and (np.abs(keys - ref_keys)[:, :2] <= 1).all())
+
+
 def test_expand(planner, fx):
     cnt, ch, ph = planner.expand(fx["heur_goal"], fx["ex_parents"], fx["ex_seeds"])
     assert np.array_equal(cnt, fx["ex_n"])
@@ -53,12 +67,13 @@ def test_expand(planner, fx):
     for i in range(len(cnt)):
         n = cnt[i]
         c = ch[i, :n]
-        assert np.array_equal(c["key"], fx["ex_keys"][i, :n]), i
+        assert _keys_match(c["key"], fx["ex_keys"][i, :n], fx["ex_poses"][i, :n]), i
         assert np.array_equal(c["direction"], fx["ex_dirs"][i, :n]), i
         assert np.array_equal(c["kind"], fx["ex_kinds"][i, :n]), i
         assert np.abs(c["pose"] - fx["ex_poses"][i, :n]).max(initial=0) < 1e-9, i
         assert_close_rel(c["cost"], fx["ex_costs"][i, :n], REL, f"cost {i}")
-        assert_close_rel(c["heuristic"], fx["ex_heuristics"][i, :n], REL, f"heuristic {i}")
+        hr = fx["ex_heuristics"][i, :n]
+        assert np.all(np.abs(c["heuristic"] - hr) <= 1e-9 + REL * np.abs(hr)), f"heuristic {i}"
 
 
 def _check_query(fx, i, res, path, log):
@@ -117,13 +132,13 @@ def test_search_live_reference(ctx, ref, planner):
             goals.append(p[1])
     starts, goals = np.array(starts), np.array(goals)
     seeds = np.arange(200, dtype=np.uint64) + 5000
-    out = planner.search(starts, goals, seeds, max_path=256, max_log=4096)
+    out = planner.search(starts, goals, seeds, max_path=256, max_log=12000)
     differing = []
     for i in range(200):
         r = H.search(starts[i], goals[i], int(seeds[i]))
         res = out["results"][i]
         n = r["n_expanded"]
-        same = (int(res["status"]) == r["status"] and int(res["n_expanded"]) == n and n <= 4096
+        same = (int(res["status"]) == r["status"] and int(res["n_expanded"]) == n and n <= 12000
                 and np.array_equal(out["log"][i]["key"][:n], r["exp_keys"][:, :3]))
         if not same:
             differing.append(i)

@@ -112,9 +112,11 @@ class Hybrid:
         log = np.zeros(max_log, HYBRID_LOG_ENTRY)
         s = np.ascontiguousarray(start, np.float64)
         g = np.ascontiguousarray(goal, np.float64)
-        lib().twin_hybrid_search(self.h, _p(wf), _p(s), _p(g), C.c_uint64(seed), C.byref(lim), _p(res), _p(path), _p(log))
+        gf = np.zeros((max_log, 2), np.float64)
+        lib().twin_hybrid_search(self.h, _p(wf), _p(s), _p(g), C.c_uint64(seed), C.byref(lim), _p(res), _p(path), _p(log), _p(gf))
         r = res[0]
-        return dict(result=r, path=path[:int(r["path_len"])], log=log[:min(int(r["n_expanded"]), max_log)])
+        n = min(int(r["n_expanded"]), max_log)
+        return dict(result=r, path=path[:int(r["path_len"])], log=log[:n], gf=gf[:n])
 
 
 def mt64_uniform(seed, n):
