@@ -229,13 +229,13 @@ void twin_hybrid_search(void* hh, const float* wfCost, const double* start, cons
 	MapDev map = h->world->dev();
 	const int tableSize = h->tx * h->ty * 7;
 	const int maxNodes = limits->max_nodes > 0 ? limits->max_nodes : 2 * tableSize;
-	std::vector<double> pose(3 * (size_t)maxNodes), g(maxNodes), f(maxNodes), length(maxNodes), heapF(maxNodes);
+	std::vector<double> pose(3 * (size_t)maxNodes), g(maxNodes), f(maxNodes), hv(maxNodes), length(maxNodes), heapF(maxNodes);
 	std::vector<int> parent(maxNodes), keyIdx(maxNodes);
 	std::vector<uint32_t> meta(maxNodes), heapSeq(maxNodes), heapNode(maxNodes), table(tableSize, 0u);
 	std::vector<float> lastv(maxNodes);
 	std::vector<unsigned long long> mt(312);
 	SearchWs W;
-	W.pose = pose.data(); W.g = g.data(); W.f = f.data(); W.parent = parent.data(); W.keyIdx = keyIdx.data();
+	W.pose = pose.data(); W.g = g.data(); W.f = f.data(); W.h = hv.data(); W.parent = parent.data(); W.keyIdx = keyIdx.data();
 	W.meta = meta.data(); W.last = lastv.data(); W.length = length.data(); W.heapF = heapF.data();
 	W.heapSeq = heapSeq.data(); W.heapNode = heapNode.data(); W.table = table.data(); W.mt = mt.data();
 	W.maxNodes = maxNodes; W.tx = h->tx; W.ty = h->ty; W.x0 = h->x0; W.y0 = h->y0;
@@ -243,7 +243,7 @@ void twin_hybrid_search(void* hh, const float* wfCost, const double* start, cons
 	Mt64 rng { W.mt, &S.mtIdx };
 	rng.seed(seed);
 	Pose st = { start[0], start[1], start[2] }, gl = { goal[0], goal[1], goal[2] };
-	search_init(P, W, S, st);
+	search_init(P, W, S, st, combined_heuristic(P, map, wfCost, gl, st));
 	while (S.status == PPX_SEARCH_RUNNING) {
 		if (limits->max_expansions > 0 && S.nExpanded >= limits->max_expansions) {
 			S.status = PPX_ERR_LIMIT;
@@ -254,7 +254,7 @@ void twin_hybrid_search(void* hh, const float* wfCost, const double* start, cons
 			break;
 		Pose par = { W.pose[3 * n], W.pose[3 * n + 1], W.pose[3 * n + 2] };
 		Key3 pk = discretize_pose(P, par);
-		double hCost = combined_heuristic(P, map, wfCost, gl, par);
+		double hCost = W.h[n];
 		if (log && S.nExpanded <= limits->max_log) {
 			ppx_hybrid_log_entry& e = log[S.nExpanded - 1];
 			e.key[0] = pk.x; e.key[1] = pk.y; e.key[2] = pk.k;

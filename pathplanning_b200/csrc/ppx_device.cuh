@@ -6,6 +6,12 @@
 #include "ppx_hd.h"
 #include "ppx.h"
 
+// A translation unit whose warps diverge widely (the per-query search kernel) defines PPX_SINCOS as
+// a single out-of-line copy to keep its instruction footprint small; the edge kernels inline it.
+#ifndef PPX_SINCOS
+#define PPX_SINCOS sincos
+#endif
+
 #define PPX_PI 3.14159265358979323846
 #define PPX_PI_2 1.57079632679489661923
 #define PPX_2PI (2 * PPX_PI)
@@ -159,7 +165,7 @@ PPX_HD Pose rs_advance(const Pose& k, double sK, double cK, int steer, int dir, 
 		turnAngle = -turnAngle;
 	double phi = turnAngle / 2;
 	double sinPhi, cosPhi;
-	sincos(phi, &sinPhi, &cosPhi);
+	PPX_SINCOS(phi, &sinPhi, &cosPhi);
 	double L = 2 * sinPhi * r;
 	double x = L * cosPhi;
 	double y = L * sinPhi;
@@ -184,7 +190,7 @@ struct RSWalker {
 	PPX_HD void init(const Pose& start)
 	{
 		k = start;
-		sincos(k.th, &sK, &cK);
+		PPX_SINCOS(k.th, &sK, &cK);
 		lenAcc = 0.0;
 		m = 0;
 	}
@@ -207,7 +213,7 @@ struct RSWalker {
 			if (lenEnd >= target)
 				return p;
 			k = p;
-			sincos(k.th, &sK, &cK);
+			PPX_SINCOS(k.th, &sK, &cK);
 			lenAcc = lenEnd;
 			m++;
 		}
@@ -429,9 +435,9 @@ struct CSteer {
 		dir = e.direction;
 		curved = fabs(kappa) > 1e-9;
 		if (curved)
-			sincos(beta + start.th, &sB0, &cB0);
+			PPX_SINCOS(beta + start.th, &sB0, &cB0);
 		else
-			sincos(start.th, &sT0, &cT0);
+			PPX_SINCOS(start.th, &sT0, &cT0);
 	}
 
 	// PathConstantSteer::Interpolate -> KinematicBicycleModel::ConstantSteer(m_init, steering, m_length*ratio, dir)
@@ -444,7 +450,7 @@ struct CSteer {
 		if (curved) {
 			to.th += dist * kappa;
 			double s1, c1;
-			sincos(beta + to.th, &s1, &c1);
+			PPX_SINCOS(beta + to.th, &s1, &c1);
 			to.x += 1 / kappa * (s1 - sB0);
 			to.y += 1 / kappa * (-c1 + cB0);
 		} else {
@@ -757,14 +763,14 @@ PPX_HD void rs_solve(const Pose& start, const Pose& goal, double r, float rev, f
 	// GetGoalArray (:518-535): newGoal = goal - start (2dplane.h:64-78), scaled by 1/r
 	double dx = goal.x - start.x, dy = goal.y - start.y;
 	double sN, cN;
-	sincos(-start.th, &sN, &cN);
+	PPX_SINCOS(-start.th, &sN, &cN);
 	double gx = cN * dx + (-sN) * dy;
 	double gy = sN * dx + cN * dy;
 	double gth = wrap_theta(wrap_theta(goal.th - start.th));
 	gx = gx / r;
 	gy = gy / r;
 	double sG, cG;
-	sincos(gth, &sG, &cG);
+	PPX_SINCOS(gth, &sG, &cG);
 
 	float bestCost = __int_as_float(0x7f800000);
 	double bestLen = PPX_INF;

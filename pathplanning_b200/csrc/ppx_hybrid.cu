@@ -12,10 +12,18 @@
 #include <algorithm>
 #include <unordered_map>
 #include <vector>
+#include <cuda_runtime.h>
+// One out-of-line sincos for this translation unit: the search kernel's warps each sit in a different
+// phase of a different query, so its instruction footprint -- not arithmetic -- is what stalls it
+// (ncu r1c: 6.6 "no instruction" stall cycles per issued instruction with everything inlined).
+__device__ __noinline__ void ppx_sincos_ool(double x, double* s, double* c);
+#define PPX_SINCOS ppx_sincos_ool
 #include "ppx_ctx.h"
 #include "ppx_hybrid_host.h"
 
 using namespace ppx;
+
+__device__ __noinline__ void ppx_sincos_ool(double x, double* s, double* c) { sincos(x, s, c); }
 
 int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored);
 
@@ -33,6 +41,7 @@ struct ppx_hybrid {
 	size_t wfBytes = 0;
 	void* d_io = nullptr;
 	size_t ioBytes = 0;
+	void* d_consts = nullptr;
 };
 
 namespace {
@@ -147,7 +156,7 @@ __host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t
 __host__ __device__ inline size_t ws_bytes(int maxNodes, int tableSize)
 {
 	size_t n = (size_t)maxNodes;
-	return align16(n * 24) + 4 * align16(n * 8) + 6 * align16(n * 4) + align16((size_t)tableSize * 4) + align16(312 * 8);
+	return align16(n * 24) + 5 * align16(n * 8) + 6 * align16(n * 4) + align16((size_t)tableSize * 4) + align16(312 * 8);
 }
 
 __device__ inline SearchWs ws_carve(char* base, const WsLayout& L)
@@ -158,6 +167,7 @@ __device__ inline SearchWs ws_carve(char* base, const WsLayout& L)
 	W.pose = (double*)p; p += align16(n * 24);
 	W.g = (double*)p; p += align16(n * 8);
 	W.f = (double*)p; p += align16(n * 8);
+	W.h = (double*)p; p += align16(n * 8);
 	W.length = (double*)p; p += align16(n * 8);
 	W.heapF = (double*)p; p += align16(n * 8);
 	W.mt = (unsigned long long*)p; p += align16(312 * 8);
@@ -173,8 +183,25 @@ __device__ inline SearchWs ws_carve(char* base, const WsLayout& L)
 	return W;
 }
 
+// Out-of-line copies for the search kernel (see the note on PPX_SINCOS above).
+__device__ __noinline__ double hy_heuristic(const HybridDev& P, const MapDev& map, const float* wf, const Pose& goal, const Pose& s)
+{
+	return combined_heuristic(P, map, wf, goal, s);
+}
+__device__ __noinline__ void hy_rs_child(const HybridDev& P, const MapDev& map, const Pose& parent, const Pose& goal, Child& out)
+{
+	rs_child(P, map, parent, goal, out);
+}
+
+// Parameters of the search kernel live in device memory: the out-of-line helpers take them by
+// reference, and a reference to a by-value kernel parameter would force a local-memory copy.
+struct SearchConsts {
+	HybridDev P;
+	MapDev map;
+};
+
 // The graph search of one query per warp.
-__global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(HybridDev P, MapDev map, int64_t nq,
+__global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const SearchConsts* __restrict__ consts, int64_t nq,
 	const double* __restrict__ starts, const double* __restrict__ goals, const unsigned long long* __restrict__ seeds,
 	const int* __restrict__ wfSlot, const float* __restrict__ wfCost, WsLayout L, char* __restrict__ slabs,
 	ppx_hybrid_limits limits, ppx_hybrid_result* __restrict__ results, ppx_hybrid_path_state* __restrict__ paths,
@@ -182,6 +209,8 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(HybridDev P
 {
 	__shared__ Child s_child[kSearchWarps][kMaxChildren];
 	__shared__ double s_h[kSearchWarps][kMaxChildren];
+	const HybridDev& P = consts->P;
+	const MapDev& map = consts->map;
 	const unsigned lane = threadIdx.x & 31;
 	const int wib = threadIdx.x >> 5;
 	const size_t gwarp = (size_t)blockIdx.x * kSearchWarps + wib;
@@ -207,7 +236,7 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(HybridDev P
 		Mt64 rng { W.mt, &S.mtIdx };
 		if (lane == 0) {
 			rng.seed(seeds ? seeds[q] : 0ull);
-			search_init(P, W, S, start);
+			search_init(P, W, S, start, hy_heuristic(P, map, wf, goal, start));
 		}
 		__syncwarp();
 		int status = __shfl_sync(0xffffffffu, S.status, 0);
@@ -227,7 +256,7 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(HybridDev P
 			// node n was written by lane 0 in an earlier iteration (ordered by the __syncwarp below)
 			const Pose parent = { W.pose[3 * n], W.pose[3 * n + 1], W.pose[3 * n + 2] };
 			const Key3 pk = discretize_pose(P, parent);
-			const double hCost = combined_heuristic(P, map, wf, goal, parent);
+			const double hCost = W.h[n];
 			int want = 0;
 			if (lane == 0) {
 				if (log && S.nExpanded <= limits.max_log) {
@@ -247,10 +276,13 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(HybridDev P
 			const int nslots = 2 * P.numDeltas + want;
 			if ((int)lane < nslots) {
 				Child c;
-				make_child(P, map, parent, pk, goal, (int)lane, c);
+				if ((int)lane < 2 * P.numDeltas)
+					csteer_child(P, map, parent, pk, (int)lane >> 1, (int)lane & 1, c);
+				else
+					hy_rs_child(P, map, parent, goal, c);
 				double h = 0.0;
 				if (c.ok)
-					h = combined_heuristic(P, map, wf, goal, c.pose);
+					h = hy_heuristic(P, map, wf, goal, c.pose);
 				myChildren[lane] = c;
 				myH[lane] = h;
 			}
@@ -358,14 +390,18 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 	L.tableSize = h->tx * h->ty * 7;
 	L.maxNodes = limits.max_nodes > 0 ? limits.max_nodes : 2 * L.tableSize;
 	L.bytes = (ws_bytes(L.maxNodes, L.tableSize) + 255) & ~(size_t)255;
-	// as many queries in flight as fit: 16 warps per SM, at most 12 GB of slabs
-	int64_t warps = std::min<int64_t>(nq, (int64_t)ctx->num_sms * 16);
+	// as many queries in flight as are resident (255 registers -> 8 warps per SM), at most 12 GB of slabs
+	int64_t warps = std::min<int64_t>(nq, (int64_t)ctx->num_sms * 8);
 	const size_t budget = (size_t)12 << 30;
 	warps = std::max<int64_t>(1, std::min<int64_t>(warps, (int64_t)(budget / L.bytes)));
 	int ctas = (int)((warps + kSearchWarps - 1) / kSearchWarps);
 	PPX_CHECK(grow(ctx, &h->d_slabs, &h->slabBytes, (size_t)ctas * kSearchWarps * L.bytes));
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
-	k_hybrid_search<<<ctas, kSearchWarps * 32, 0, ctx->stream>>>(h->dev, ctx->map_dev(), nq, d_starts, d_goals,
+	SearchConsts consts { h->dev, ctx->map_dev() };
+	if (!h->d_consts)
+		PPX_CUDA(ctx, cudaMalloc(&h->d_consts, sizeof(SearchConsts)));
+	PPX_CUDA(ctx, cudaMemcpyAsync(h->d_consts, &consts, sizeof(SearchConsts), cudaMemcpyHostToDevice, ctx->stream));
+	k_hybrid_search<<<ctas, kSearchWarps * 32, 0, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, d_starts, d_goals,
 		(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, (char*)h->d_slabs, limits, d_results, d_paths, d_log, ctx->d_queue);
 	PPX_LAUNCHED(ctx);
 	return PPX_OK;
@@ -418,6 +454,7 @@ int ppx_hybrid_destroy(ppx_hybrid* h)
 	cudaFree(h->d_slabs);
 	cudaFree(h->d_wf);
 	cudaFree(h->d_io);
+	cudaFree(h->d_consts);
 	delete h;
 	return PPX_OK;
 }

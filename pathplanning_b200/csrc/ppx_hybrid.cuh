@@ -126,9 +126,9 @@ PPX_HD void csteer_child(const HybridDev& P, const MapDev& map, const Pose& pare
 	p.dir = direction;
 	p.curved = fabs(p.kappa) > 1e-9;
 	if (p.curved)
-		sincos(p.beta + p.start.th, &p.sB0, &p.cB0);
+		PPX_SINCOS(p.beta + p.start.th, &p.sB0, &p.cB0);
 	else
-		sincos(p.start.th, &p.sT0, &p.cT0);
+		PPX_SINCOS(p.start.th, &p.sT0, &p.cT0);
 	out.kind = 0;
 	out.dir = direction; // PathConstantSteer::GetDirection
 	float last;
@@ -226,7 +226,7 @@ PPX_HD double nonholo_heuristic(const HybridDev& P, const Pose& goal, const Pose
 	// delta = m_goal - state (2dplane.h:64-78)
 	double dx = goal.x - state.x, dy = goal.y - state.y;
 	double s, c;
-	sincos(-state.th, &s, &c);
+	PPX_SINCOS(-state.th, &s, &c);
 	double px = c * dx + (-s) * dy;
 	double py = s * dx + c * dy;
 	double dth = wrap_theta(wrap_theta(goal.th - state.th));
@@ -331,6 +331,7 @@ struct SearchWs {
 	double* pose; // [maxNodes][3] continuousPose
 	double* g; // pathCost
 	double* f; // totalCost
+	double* h; // heuristic value of the node's state (what GetNeighborStates recomputes as hCost)
 	int* parent;
 	int* keyIdx; // table index of the node's discrete pose
 	uint32_t* meta; // dir (bits 0-1) | kind (bit 2) | child slot (bits 3-7) | dead (bit 8)
@@ -427,7 +428,7 @@ PPX_HD int heap_pop(const SearchWs& W, SearchState& S)
 }
 
 PPX_HD int node_alloc(const SearchWs& W, SearchState& S, const Pose& pose, int keyIdx, int parent, double g, double f,
-	uint32_t meta, float last, double length)
+	double h, uint32_t meta, float last, double length)
 {
 	if (S.numNodes >= W.maxNodes) {
 		S.status = PPX_ERR_CAPACITY;
@@ -439,6 +440,7 @@ PPX_HD int node_alloc(const SearchWs& W, SearchState& S, const Pose& pose, int k
 	W.pose[3 * n + 2] = pose.th;
 	W.g[n] = g;
 	W.f[n] = f;
+	W.h[n] = h;
 	W.parent[n] = parent;
 	W.keyIdx[n] = keyIdx;
 	W.meta[n] = meta;
@@ -448,7 +450,7 @@ PPX_HD int node_alloc(const SearchWs& W, SearchState& S, const Pose& pose, int k
 }
 
 // AStar::InitializeSearch, a_star.h:350-364 (the table must be zeroed by the caller)
-PPX_HD void search_init(const HybridDev& P, const SearchWs& W, SearchState& S, const Pose& start)
+PPX_HD void search_init(const HybridDev& P, const SearchWs& W, SearchState& S, const Pose& start, double hStart)
 {
 	S.numNodes = 0;
 	S.heapSize = 0;
@@ -463,7 +465,7 @@ PPX_HD void search_init(const HybridDev& P, const SearchWs& W, SearchState& S, c
 		S.status = PPX_ERR_CAPACITY;
 		return;
 	}
-	int n = node_alloc(W, S, start, ki, -1, 0.0, 0.0, 2u, 1.0f, 0.0);
+	int n = node_alloc(W, S, start, ki, -1, 0.0, 0.0, hStart, 2u, 1.0f, 0.0); // root: pathCost = totalCost = 0
 	if (n < 0)
 		return;
 	heap_push(W, S, 0.0, n);
@@ -509,7 +511,7 @@ PPX_HD void consume_child(const SearchWs& W, SearchState& S, int parentNode, dou
 	uint32_t e = W.table[ki];
 	uint32_t meta = (uint32_t)(c.dir & 3) | ((uint32_t)(c.kind & 1) << 2) | ((uint32_t)(slot & 31) << 3);
 	if (e == 0u) {
-		int n = node_alloc(W, S, c.pose, ki, parentNode, g, f, meta, c.last, c.length);
+		int n = node_alloc(W, S, c.pose, ki, parentNode, g, f, h, meta, c.last, c.length);
 		if (n < 0)
 			return;
 		heap_push(W, S, f, n);
@@ -518,7 +520,7 @@ PPX_HD void consume_child(const SearchWs& W, SearchState& S, int parentNode, dou
 		int fn = (int)(e - 2u);
 		Pose fp = { W.pose[3 * fn], W.pose[3 * fn + 1], W.pose[3 * fn + 2] };
 		if (identical_poses(fp, c.pose) && W.f[fn] > f) {
-			int n = node_alloc(W, S, c.pose, ki, parentNode, g, f, meta, c.last, c.length);
+			int n = node_alloc(W, S, c.pose, ki, parentNode, g, f, h, meta, c.last, c.length);
 			if (n < 0)
 				return;
 			W.meta[fn] |= 0x100u; // m_frontier.Remove(frontierNode)
