@@ -327,6 +327,63 @@ int ppx_hybrid_search_dev(ppx_hybrid* h, int64_t nq, const double* d_starts, con
 	const uint64_t* d_seeds, const ppx_hybrid_limits* limits, ppx_hybrid_result* d_results,
 	ppx_hybrid_path_state* d_paths, ppx_hybrid_log_entry* d_log);
 
+/* ------------------------------------------------------------------------------------------ */
+/* A10: Tree::GetNearestNode / GetNearestNodes  (utils/tree.h:73-116) as exact brute-force k-NN  */
+/*
+ * Replaces the flann::Index<L2_Simple<double>> kd-tree (utils/tree.h:44,174): squared Euclidean
+ * distance over the raw state coordinates (dim = 2 for Point2d, 3 for Pose2d: x, y, theta), exact,
+ * neighbours by increasing distance, equal distances by increasing point index.
+ *   indices  nqueries * k point indices (-1 where fewer than k points exist)
+ *   dist2    optional nqueries * k squared distances
+ */
+int ppx_knn(ppx_ctx* ctx, int32_t dim, int64_t npoints, const double* points, int64_t nqueries, const double* queries,
+	int32_t k, int32_t* indices, double* dist2);
+int ppx_knn_dev(ppx_ctx* ctx, int32_t dim, int64_t npoints, const double* d_points, int64_t nqueries,
+	const double* d_queries, int32_t k, int32_t* d_indices, double* d_dist2);
+
+/* ------------------------------------------------------------------------------------------ */
+/* A11: RRT / RRT* (algo/rrt.h:55-95,125-140, algo/rrt_star.h:53-112,136-160), batched over trees  */
+/*
+ * One tree per CTA, the reference's loop run verbatim: goal-biased sample from the tree's private
+ * std::mt19937_64 (state_space_se2.cpp:27-38, utils/random.h, trap H4) -> nearest node (exact
+ * brute-force scan, ties to the lower index) -> SteerTowards (Connect + Truncate to
+ * max_connection_distance) -> IsPathValid -> [RRT*: k = max(1, (unsigned)log(size)) nearest nodes,
+ * SteerExactly + cost + IsPathValid per candidate, best parent; NO rewiring, trap H12] -> Tree::Extend
+ * with its duplicate-state rule (utils/tree.h:124-146) -> goal test.
+ */
+typedef struct ppx_rrt_params {
+	int32_t dim; /* 2: Point2d states (RRTR2 / RRTStarR2); 3: Pose2d states */
+	int32_t connection; /* 0 PathConnectionR2 / PathConnectionSE2 (straight), 1 PathConnectionReedsShepp (dim 3) */
+	int32_t star; /* 0 RRT (goal test |state - goal| < 1, dim 2 only), 1 RRT* (exact-equality goal test) */
+	int32_t validator; /* 0 StateValidatorFree (every path valid), 1 StateValidatorOccupancyMap on the uploaded map (dim 3) */
+	uint32_t max_iteration; /* RRTParameters::maxIteration */
+	uint32_t max_nodes; /* RRTParameters::maxNumberTreeNode */
+	double max_connection_distance;
+	double goal_bias;
+	double min_turning_radius; /* PathConnectionReedsShepp(minTurningRadius), unit cost multipliers */
+	double lb[3], ub[3]; /* StateSpace bounds used by SampleUniform */
+} ppx_rrt_params;
+
+typedef struct ppx_rrt_result {
+	int32_t status; /* 0 Success, -1 Failure (iteration or node limit), PPX_ERR_CAPACITY */
+	int32_t iterations; /* loop turns taken (the reference's count) */
+	int32_t n_nodes; /* Tree::Size() */
+	int32_t solution; /* node index of the solution, -1 */
+	int32_t path_len; /* nodes on the chain root..solution */
+	int32_t n_edges_checked; /* IsPathValid calls */
+	double solution_cost; /* RRT*: costFromGoal of the solution node */
+} ppx_rrt_result;
+
+/*
+ * starts / goals: ntrees * 3 doubles (x, y, theta; theta ignored for dim 2); seeds: ntrees.
+ * Optional outputs, each with node_capacity entries per tree (node_capacity >= max_nodes + 2 to
+ * receive whole trees): nodes (3 doubles per node, insertion order = flann point order),
+ * parents (int32, -1 for the root), costs (RRT*: NodeInfo::costFromGoal).
+ */
+int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_params* vp, int64_t ntrees,
+	const double* starts, const double* goals, const uint64_t* seeds, ppx_rrt_result* results, int64_t node_capacity,
+	double* nodes, int32_t* parents, double* costs);
+
 #ifdef __cplusplus
 }
 #endif

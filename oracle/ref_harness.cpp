@@ -906,6 +906,197 @@ int ref_rrtstar_r2_free(const double* lb, const double* ub, const double* start,
 	return (int)st;
 }
 
+// Same as above with the whole tree dumped: nodes in flann insertion order, parent indices, RRT*
+// costs, iteration count is not observable from outside (the loop counter is a local).
+int ref_rrt_r2_run(const double* lb, const double* ub, const double* start, const double* goal, uint64_t seed,
+	unsigned maxIteration, unsigned maxNodes, double maxConnectionDistance, double goalBias, int star,
+	long cap, long* nodes, double* nodes_xy, int* parents, double* costs, long* path_len, double* path_xy)
+{
+	auto space = makeRef<StateSpaceR2>(std::array<Point2d, 2> { Point2d(lb[0], lb[1]), Point2d(ub[0], ub[1]) });
+	Ref<StateValidator<Point2d, 2, double>> validator = makeRef<StateValidatorFree<Point2d, 2, double>>(space);
+	Ref<PathConnection<Point2d>> conn = makeRef<PathConnectionR2>();
+	std::vector<Point2d> path;
+	Status st;
+	auto dump = [&](auto& rrt, bool withCost) {
+		auto& tree = rrt.m_tree;
+		long n = (long)tree.m_kdTree.size();
+		*nodes = (long)tree.Size();
+		std::unordered_map<const void*, int> indexOf;
+		for (long i = 0; i < n; i++) {
+			Point2d pt(tree.m_kdTree.getPoint(i));
+			indexOf[tree.m_exploredNodeMap[pt]] = (int)i;
+		}
+		for (long i = 0; i < n && i < cap; i++) {
+			Point2d pt(tree.m_kdTree.getPoint(i));
+			auto* node = tree.m_exploredNodeMap[pt];
+			nodes_xy[2 * i] = pt.x();
+			nodes_xy[2 * i + 1] = pt.y();
+			auto* parent = node->GetParent();
+			parents[i] = parent ? indexOf[parent] : -1;
+			if constexpr (std::is_same_v<std::decay_t<decltype(rrt)>, RRTStarR2>)
+				costs[i] = (*node)->info.costFromGoal;
+			else
+				costs[i] = 0.0;
+		}
+	};
+	if (star) {
+		RRTStarR2 rrt(space, validator, conn);
+		RRTStarParameters p;
+		p.maxIteration = maxIteration;
+		p.maxNumberTreeNode = maxNodes;
+		p.maxConnectionDistance = maxConnectionDistance;
+		p.goalBias = goalBias;
+		rrt.SetParameters(p);
+		rrt.SetInitState(Point2d(start[0], start[1]));
+		rrt.SetGoalState(Point2d(goal[0], goal[1]));
+		SeedRandom(seed);
+		st = rrt.SearchPath();
+		dump(rrt, true);
+		path = rrt.GetPath();
+	} else {
+		RRTR2 rrt(space, validator, conn);
+		RRTParameters p;
+		p.maxIteration = maxIteration;
+		p.maxNumberTreeNode = maxNodes;
+		p.maxConnectionDistance = maxConnectionDistance;
+		p.goalBias = goalBias;
+		rrt.SetParameters(p);
+		rrt.SetInitState(Point2d(start[0], start[1]));
+		rrt.SetGoalState(Point2d(goal[0], goal[1]));
+		SeedRandom(seed);
+		st = rrt.SearchPath();
+		dump(rrt, false);
+		path = rrt.GetPath();
+	}
+	*path_len = (long)path.size();
+	for (long i = 0; i < (long)path.size() && i < cap; i++) {
+		path_xy[2 * i] = path[i].x();
+		path_xy[2 * i + 1] = path[i].y();
+	}
+	return (int)st;
+}
+
+// RRT* over Pose2d.  The reference's own template does not compile for Pose2d (rrt_star.h:181 is
+// commented out; utils/tree.h:88,111 cast double* to State), so this is a RESTATEMENT of the loop of
+// rrt_star.h:53-112 and of Tree (utils/tree.h:59-146) -- "port", parity unpinned -- that calls the
+// reference's own components for everything else: Random<double>, StateSpaceSE2::SampleUniform,
+// PathConnectionReedsShepp / PathConnectionSE2 (Connect, Truncate with trap H9, GetLength,
+// GetFinalState), StateValidatorOccupancyMap::IsPathValid or StateValidatorFree, std::equal_to<Pose2d>.
+// Nearest neighbours: flann::L2_Simple over (x, y, theta), ties to the lower insertion index.
+int ref_rrtstar_se2_restated(void* hw /* null: free-space validator */, const double* lb, const double* ub, const double* start,
+	const double* goal, uint64_t seed, unsigned maxIteration, unsigned maxNodes, double maxConnectionDistance, double goalBias,
+	int reedsShepp, double rmin, long cap, long* nodes, double* nodes_xyt, int* parents, double* costs, long* iterations,
+	long* edges_checked, double* seconds)
+{
+	auto space = makeRef<StateSpaceSE2>(std::array<Pose2d, 2> { Pose2d(lb[0], lb[1], lb[2]), Pose2d(ub[0], ub[1], ub[2]) });
+	Ref<StateValidator<Pose2d, 3, double>> validator;
+	if (hw)
+		validator = ((RefWorld*)hw)->validator;
+	else
+		validator = makeRef<StateValidatorFree<Pose2d, 3, double>>(space);
+	Ref<PathConnection<Pose2d>> conn;
+	if (reedsShepp)
+		conn = makeRef<PathConnectionReedsShepp>(rmin);
+	else
+		conn = makeRef<PathConnectionSE2>();
+	Pose2d init, goalState;
+	init.position = Point2d(start[0], start[1]);
+	init.theta = start[2];
+	goalState.position = Point2d(goal[0], goal[1]);
+	goalState.theta = goal[2];
+	std::vector<Pose2d> states;
+	std::vector<int> parent;
+	std::vector<double> costFromGoal;
+	std::equal_to<Pose2d> equal;
+	auto find = [&](const Pose2d& s) {
+		for (size_t i = 0; i < states.size(); i++)
+			if (equal(states[i], s))
+				return (int)i;
+		return -1;
+	};
+	auto knn = [&](const Pose2d& q, unsigned k) {
+		std::vector<std::pair<double, int>> all(states.size());
+		for (size_t i = 0; i < states.size(); i++) {
+			double a[3] = { q.x(), q.y(), q.theta }, b[3] = { states[i].x(), states[i].y(), states[i].theta };
+			double d = 0;
+			for (int c = 0; c < 3; c++) {
+				double diff = a[c] - b[c];
+				d += diff * diff;
+			}
+			all[i] = { d, (int)i };
+		}
+		size_t n = std::min<size_t>(k, all.size());
+		std::partial_sort(all.begin(), all.begin() + n, all.end());
+		all.resize(n);
+		return all;
+	};
+	SeedRandom(seed);
+	auto t0 = std::chrono::steady_clock::now();
+	states.push_back(init);
+	parent.push_back(-1);
+	costFromGoal.push_back(0.0);
+	int count = -1, status = -1;
+	long edges = 0;
+	while (true) {
+		count++;
+		if (count > (int)maxIteration)
+			break;
+		if (states.size() > maxNodes)
+			break;
+		Pose2d randomState = Random<double>::SampleUniform(0, 1) < goalBias ? goalState : space->SampleUniform();
+		int nearest = knn(randomState, 1)[0].second;
+		auto pathNearToNew = conn->Connect(states[nearest], randomState);
+		if (pathNearToNew->GetLength() > 0) {
+			double ratio = std::clamp(maxConnectionDistance / pathNearToNew->GetLength(), 0.0, 1.0);
+			pathNearToNew->Truncate(ratio);
+		}
+		edges++;
+		if (!validator->IsPathValid(*pathNearToNew))
+			continue;
+		const Pose2d newState = pathNearToNew->GetFinalState();
+		unsigned int nn = std::max<unsigned int>(1, log(states.size()));
+		auto near = knn(newState, nn);
+		int bestParent = -1;
+		double bestCost = std::numeric_limits<double>::infinity();
+		for (auto& [d, node] : near) {
+			auto pathParentToNew = conn->Connect(states[node], newState);
+			double cost = costFromGoal[node] + pathParentToNew->GetLength();
+			if (cost < bestCost) {
+				edges++;
+				if (validator->IsPathValid(*pathParentToNew)) {
+					bestParent = node;
+					bestCost = cost;
+				}
+			}
+		}
+		int node = find(newState);
+		if (node < 0) {
+			node = (int)states.size();
+			states.push_back(newState);
+			parent.push_back(bestParent >= 0 ? bestParent : near[0].second);
+			costFromGoal.push_back(0.0);
+		}
+		costFromGoal[node] = bestCost;
+		if (equal(newState, goalState)) {
+			status = 0;
+			break;
+		}
+	}
+	if (seconds)
+		*seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	*nodes = (long)states.size();
+	*iterations = count;
+	*edges_checked = edges;
+	for (long i = 0; i < (long)states.size() && i < cap; i++) {
+		nodes_xyt[3 * i] = states[i].x();
+		nodes_xyt[3 * i + 1] = states[i].y();
+		nodes_xyt[3 * i + 2] = states[i].theta;
+		parents[i] = parent[i];
+		costs[i] = costFromGoal[i];
+	}
+	return status;
+}
+
 // Raw draws from the reference RNG wrapper after seeding (pins H4: one 64-bit draw per sample,
 // SampleUniform = lb + (ub-lb)*u).
 void ref_random_uniform(uint64_t seed, long n, double lb, double ub, double* out)

@@ -11,7 +11,7 @@ from dataclasses import dataclass, field
 
 import numpy as np
 
-from .lib import ppx, MapDescC, ValidatorParamsC, RSCostParamsC, HybridParamsC, HybridLimitsC
+from .lib import ppx, MapDescC, ValidatorParamsC, RSCostParamsC, HybridParamsC, HybridLimitsC, RRTParamsC
 
 RS_EDGE = np.dtype([("start", "<f8", (3,)), ("len", "<f8", (5,)), ("code", "<u8")], align=True)
 CSTEER_EDGE = np.dtype([("start", "<f8", (3,)), ("length", "<f8"), ("beta", "<f8"), ("cos_beta", "<f8"),
@@ -28,6 +28,9 @@ HYBRID_LOG_ENTRY = np.dtype([("key", "<i4", (3,)), ("direction", "<i4"), ("pose"
 assert HYBRID_CHILD.itemsize == 72 and HYBRID_RESULT.itemsize == 40 and HYBRID_PATH_STATE.itemsize == 40
 assert HYBRID_LOG_ENTRY.itemsize == 40
 MAX_CHILDREN = 19
+RRT_RESULT = np.dtype([("status", "<i4"), ("iterations", "<i4"), ("n_nodes", "<i4"), ("solution", "<i4"), ("path_len", "<i4"),
+                       ("n_edges_checked", "<i4"), ("solution_cost", "<f8")], align=True)
+assert RRT_RESULT.itemsize == 32
 
 
 class PPXError(RuntimeError):
@@ -263,6 +266,42 @@ class Context:
         explored = np.empty((n, rows, cols), dtype=np.uint8) if want_explored else None
         self._check(ppx.ppx_wavefront(self._h, n, _ptr(goals), _ptr(cost), _ptr(explored)))
         return (cost, explored.astype(bool)) if want_explored else cost
+
+    # ---- A10 ----------------------------------------------------------------------------------
+    def knn(self, points, queries, k):
+        """Exact k nearest neighbours (Tree::GetNearestNodes) -> (indices (nq,k) int32, dist2 (nq,k))."""
+        points = np.ascontiguousarray(points, np.float64)
+        queries = np.ascontiguousarray(queries, np.float64)
+        dim = queries.shape[1]
+        nq = len(queries)
+        idx = np.empty((nq, k), np.int32)
+        d2 = np.empty((nq, k), np.float64)
+        self._check(ppx.ppx_knn(self._h, dim, len(points), _ptr(points), nq, _ptr(queries), k, _ptr(idx), _ptr(d2)))
+        return idx, d2
+
+    # ---- A11 ----------------------------------------------------------------------------------
+    def rrt_run(self, starts, goals, seeds, lb, ub, dim=2, connection=0, star=1, validator=0, max_iteration=100,
+                max_nodes=10000, max_connection_distance=0.1, goal_bias=0.05, min_turning_radius=1.0, vp=None,
+                want_trees=True):
+        """RRT / RRT* (algo/rrt.h, algo/rrt_star.h), one tree per (start, goal, seed)."""
+        starts, goals = _f64(starts), _f64(goals)
+        seeds = np.ascontiguousarray(seeds, np.uint64)
+        nt = len(starts)
+        p = RRTParamsC(dim, connection, star, validator, max_iteration, max_nodes, max_connection_distance, goal_bias,
+                       min_turning_radius)
+        lb3 = list(lb) + [0.0] * (3 - len(lb))
+        ub3 = list(ub) + [0.0] * (3 - len(ub))
+        p.lb[:] = lb3
+        p.ub[:] = ub3
+        v = (vp or ValidatorParams()).to_c()
+        res = np.zeros(nt, RRT_RESULT)
+        cap = max_nodes + 2 if want_trees else 0
+        nodes = np.zeros((nt, cap, 3)) if want_trees else None
+        parents = np.zeros((nt, cap), np.int32) if want_trees else None
+        costs = np.zeros((nt, cap)) if want_trees else None
+        self._check(ppx.ppx_rrt_run(self._h, C.byref(p), C.byref(v), nt, _ptr(starts), _ptr(goals), _ptr(seeds), _ptr(res), cap,
+                                    _ptr(nodes), _ptr(parents), _ptr(costs)))
+        return dict(results=res, nodes=nodes, parents=parents, costs=costs)
 
 
 @dataclass

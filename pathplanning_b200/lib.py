@@ -36,6 +36,12 @@ class HybridParamsC(C.Structure):
                 ("spatial_resolution", C.c_double), ("angular_resolution", C.c_double)]
 
 
+class RRTParamsC(C.Structure):
+    _fields_ = [("dim", C.c_int32), ("connection", C.c_int32), ("star", C.c_int32), ("validator", C.c_int32),
+                ("max_iteration", C.c_uint32), ("max_nodes", C.c_uint32), ("max_connection_distance", C.c_double),
+                ("goal_bias", C.c_double), ("min_turning_radius", C.c_double), ("lb", C.c_double * 3), ("ub", C.c_double * 3)]
+
+
 class HybridLimitsC(C.Structure):
     _fields_ = [("max_nodes", C.c_int32), ("max_expansions", C.c_int32), ("max_path", C.c_int32), ("max_log", C.c_int32)]
 
@@ -71,6 +77,9 @@ _SIGS = {
     "ppx_rs_interpolate": (C.c_int, [_p, _i64, _p, C.c_double, C.c_int32, _p, _p]),
     "ppx_wavefront": (C.c_int, [_p, _i64, _p, _p, _p]),
     "ppx_wavefront_dev": (C.c_int, [_p, _i64, _p, _p, _p]),
+    "ppx_knn": (C.c_int, [_p, C.c_int32, _i64, _p, _i64, _p, C.c_int32, _p, _p]),
+    "ppx_knn_dev": (C.c_int, [_p, C.c_int32, _i64, _p, _i64, _p, C.c_int32, _p, _p]),
+    "ppx_rrt_run": (C.c_int, [_p, C.POINTER(RRTParamsC), _p, _i64, _p, _p, _p, _p, _i64, _p, _p, _p]),
     "ppx_hybrid_create": (C.c_int, [_p, C.POINTER(HybridParamsC), C.POINTER(ValidatorParamsC), C.POINTER(_p)]),
     "ppx_hybrid_destroy": (C.c_int, [_p]),
     "ppx_hybrid_table": (C.c_int, [_p, _p, _p, _p]),

@@ -323,3 +323,46 @@ class Hybrid:
         v, nh, ob = np.empty(n), np.empty(n), np.empty(n)
         lib().ref_hybrid_heuristic(self.h, C.c_long(n), _p(poses), _p(v), _p(nh), _p(ob))
         return v, nh, ob
+
+
+# ---- Tree / RRT ---------------------------------------------------------------------------------
+def tree_knn_r2(points, queries, k):
+    """Tree<Point2d,2>::GetNearestNodes of the reference over the brute-force flann stand-in."""
+    points = np.ascontiguousarray(points, np.float64)
+    queries = np.ascontiguousarray(queries, np.float64)
+    out = np.empty((len(queries), k), np.int32)
+    lib().ref_tree_knn_r2(C.c_long(len(points)), _p(points), C.c_long(len(queries)), _p(queries), C.c_int(k), _p(out))
+    return out
+
+
+def rrt_r2_run(lb, ub, start, goal, seed, max_iteration, max_nodes, max_connection_distance, goal_bias, star):
+    """RRTR2 / RRTStarR2 (the reference templates) in free space; returns the whole tree."""
+    cap = max_nodes + 8
+    n, plen = C.c_long(), C.c_long()
+    xy = np.zeros((cap, 2), np.float64)
+    parents = np.zeros(cap, np.int32)
+    costs = np.zeros(cap, np.float64)
+    pxy = np.zeros((cap, 2), np.float64)
+    st = lib().ref_rrt_r2_run((C.c_double * 2)(*lb), (C.c_double * 2)(*ub), (C.c_double * 2)(*start), (C.c_double * 2)(*goal),
+                              C.c_uint64(seed), C.c_uint(max_iteration), C.c_uint(max_nodes), C.c_double(max_connection_distance),
+                              C.c_double(goal_bias), C.c_int(star), C.c_long(cap), C.byref(n), _p(xy), _p(parents), _p(costs),
+                              C.byref(plen), _p(pxy))
+    return dict(status=st, n_nodes=n.value, nodes=xy[:n.value], parents=parents[:n.value], costs=costs[:n.value], path=pxy[:plen.value])
+
+
+def rrtstar_se2_restated(world, lb, ub, start, goal, seed, max_iteration, max_nodes, max_connection_distance, goal_bias,
+                         reeds_shepp, rmin=2.0):
+    """RRT* over Pose2d: restated loop + the reference's own sampling / connection / validator (see ref_harness.cpp)."""
+    cap = max_nodes + 8
+    n, it, edges = C.c_long(), C.c_long(), C.c_long()
+    sec = C.c_double()
+    xyt = np.zeros((cap, 3), np.float64)
+    parents = np.zeros(cap, np.int32)
+    costs = np.zeros(cap, np.float64)
+    st = lib().ref_rrtstar_se2_restated(world.h if world is not None else None, _d3(lb), _d3(ub), _d3(start), _d3(goal),
+                                        C.c_uint64(seed), C.c_uint(max_iteration), C.c_uint(max_nodes),
+                                        C.c_double(max_connection_distance), C.c_double(goal_bias), C.c_int(reeds_shepp),
+                                        C.c_double(rmin), C.c_long(cap), C.byref(n), _p(xyt), _p(parents), _p(costs),
+                                        C.byref(it), C.byref(edges), C.byref(sec))
+    return dict(status=st, n_nodes=n.value, iterations=it.value, edges_checked=edges.value, seconds=sec.value,
+                nodes=xyt[:n.value], parents=parents[:n.value], costs=costs[:n.value])
