@@ -106,6 +106,54 @@ def run_reference(args, per_core):
     return n / sec, sec * 1e3, cores, sample
 
 
+def _ref_hybrid_worker(queries, conn):
+    """Child process: the reference's wavefront + GVD update + graph search (hybrid_a_star.cpp:248-257) per query."""
+    import refapi
+    from pathplanning_b200 import synth
+    try:
+        cfg = synth.C2
+        w = refapi.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+        for r in synth.config_rects(cfg):
+            w.add_rectangle(*r)
+        w.update()
+        w.set_validator_params(RADIUS, MIN_STEP)
+        H = refapi.Hybrid(w)
+        t0 = time.perf_counter()
+        ok = 0
+        for s, g, seed in queries:
+            ok += H.search(s, g, seed)["status"] == 0
+        conn.send((time.perf_counter() - t0, ok))
+    except Exception as e:  # pragma: no cover
+        conn.send(e)
+    conn.close()
+
+
+def run_reference_hybrid(starts, goals, seeds, per_core):
+    """plans/s of the reference on all host cores (one process per core) over the first per_core*cores queries."""
+    import multiprocessing as mp
+    cores = host_cores()
+    n = min(len(starts), per_core * cores)
+    ctxmp = mp.get_context("fork")
+    procs, pipes = [], []
+    for c in range(cores):
+        idx = range(c, n, cores)
+        qs = [(tuple(starts[i]), tuple(goals[i]), int(seeds[i])) for i in idx]
+        a, b = ctxmp.Pipe(duplex=False)
+        p = ctxmp.Process(target=_ref_hybrid_worker, args=(qs, b))
+        p.start()
+        procs.append(p)
+        pipes.append(a)
+    results = [a.recv() for a in pipes]
+    for p in procs:
+        p.join()
+    for r in results:
+        if isinstance(r, Exception):
+            raise r
+    sec = max(r[0] for r in results)
+    return {"value": n / sec, "unit": "plans/s", "cores": cores, "kind": "reference",
+            "sample": f"first {n} of the 4096 queries, wavefront + GVD update + graph search each, one process per core"}
+
+
 def reference_main(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -173,6 +221,116 @@ class ClockSampler(threading.Thread):
     def summary(self):
         return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def c4_queries(ctx, pp, n, seed=12345):
+    """BASELINE config C4: n (start, goal) pairs uniform in +-18.5 m with uniform heading, rejection-sampled with
+    IsStateValid on the C2 map; query q uses RNG seed 1000 + q."""
+    rng = np.random.default_rng(seed)
+    vp = pp.ValidatorParams(RADIUS, MIN_STEP)
+    pts = np.empty((0, 3))
+    while len(pts) < 2 * n:
+        p = np.stack([rng.uniform(-18.5, 18.5, 4 * n), rng.uniform(-18.5, 18.5, 4 * n), rng.uniform(-np.pi, np.pi, 4 * n)], 1)
+        pts = np.concatenate([pts, p[ctx.is_state_valid(p, vp)]])
+    return pts[:n].copy(), pts[n:2 * n].copy(), (np.arange(n) + 1000).astype(np.uint64)
+
+
+def hybrid_section(args, rank, world, local_rank, stream):
+    """Config C4: 4096 Hybrid A* queries on the C2 map, sharded by query over the ranks (strong scaling), results
+    gathered with one NCCL all_gather of the fixed-size result records."""
+    import torch
+    import torch.distributed as dist
+    import pathplanning_b200 as pp
+    from pathplanning_b200 import synth
+    from pathplanning_b200.lib import ppx, HybridLimitsC
+    from pathplanning_b200.api import HYBRID_RESULT
+    dev = torch.device("cuda", local_rank)
+    ctx = pp.Context(local_rank)
+    ctx.set_stream(stream.cuda_stream)
+    cfg = synth.C2
+    occ = synth.rasterize_rectangles(synth.config_rects(cfg), cfg["lb"], cfg["ub"], cfg["resolution"])
+    sq = synth.exact_sqdist(occ)
+    rows, cols, origin = synth.map_geometry(cfg["lb"], cfg["ub"], cfg["resolution"])
+    ctx.upload_map(pp.MapDesc(rows=rows, cols=cols, resolution=cfg["resolution"], world_origin=origin, lb=cfg["lb"], ub=cfg["ub"]),
+                   sq, occ, None)
+    planner = pp.HybridAStar(ctx, pp.HybridParams(), pp.ValidatorParams(RADIUS, MIN_STEP))
+    nq = args.hybrid_queries
+    starts, goals, seeds = c4_queries(ctx, pp, nq)
+    lo, hi = rank * nq // world, (rank + 1) * nq // world
+    m = hi - lo
+    d_s = torch.from_numpy(starts[lo:hi].copy()).to(dev)
+    d_g = torch.from_numpy(goals[lo:hi].copy()).to(dev)
+    d_seed = torch.from_numpy(seeds[lo:hi].astype(np.int64)).to(dev)
+    d_res = torch.zeros(m * HYBRID_RESULT.itemsize, dtype=torch.uint8, device=dev)
+    lim = HybridLimitsC(0, 0, 0, 0)
+    launches0 = ctx.launch_count
+
+    def run_dev():
+        rc = ppx.ppx_hybrid_search_dev(planner.handle, m, d_s.data_ptr(), d_g.data_ptr(), d_seed.data_ptr(), ctypes.byref(lim),
+                                       d_res.data_ptr(), None, None)
+        assert rc == 0, ppx.ppx_last_error(ctx.handle)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    run_dev()  # warm-up (allocates the workspaces)
+    barrier()
+    reps = 3
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(reps):
+        run_dev()
+    ev1.record(stream)
+    barrier()
+    t = torch.tensor([ev0.elapsed_time(ev1) / reps], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_dev = float(t.item())
+    launches = (ctx.launch_count - launches0) // (reps + 1)
+    # through the host-buffer call (goal de-duplication, H2D, wavefronts, search, D2H of results + paths)
+    planner.search(starts[lo:hi], goals[lo:hi], seeds[lo:hi], max_path=128)
+    barrier()
+    t0 = time.perf_counter()
+    out = planner.search(starts[lo:hi], goals[lo:hi], seeds[lo:hi], max_path=128)
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    res = out["results"]
+    # gather of the fixed-size records: the only collective of the path
+    gather_ms = 0.0
+    solved = int((res["status"] == 0).sum())
+    expanded = int(res["n_expanded"].sum())
+    if world > 1:
+        parts = [torch.zeros_like(d_res) for _ in range(world)] if all((r + 1) * nq // world - r * nq // world == m for r in range(world)) else None
+        if parts is not None:
+            torch.cuda.synchronize()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record()
+            dist.all_gather(parts, d_res)
+            g1.record()
+            torch.cuda.synchronize()
+            gather_ms = g0.elapsed_time(g1)
+            allres = np.concatenate([p.cpu().numpy().view(HYBRID_RESULT) for p in parts])
+            solved, expanded = int((allres["status"] == 0).sum()), int(allres["n_expanded"].sum())
+    section = {
+        "metric": "batched Hybrid A* plans/s", "workload": f"C4: {nq} independent start/goal queries on the C2 parking lot (400x400 @0.1m), "
+        "wavefront + graph search per query, sharded by query", "scaling": "strong", "queries_per_gpu": m,
+        "value": nq / (ms_dev * 1e-3), "unit": "plans/s", "ms": ms_dev,
+        "e2e": {"value": nq / float(te.item()), "unit": "plans/s", "h2d_bytes": int(m * 56), "d2h_bytes": int(m * (40 + 128 * 40))},
+        "solved": solved, "expansions": expanded, "gather_ms": gather_ms, "gpu_launches": int(launches),
+        "note": "smoothing (SURVEY N2) is not part of this figure, neither here nor in the CPU figure",
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            section["cpu_baseline"] = run_reference_hybrid(starts, goals, seeds, args.cpu_plans_per_core)
+        except Exception as e:  # pragma: no cover
+            section["cpu_baseline"] = {"unavailable": f"{type(e).__name__}: {e}"}
+    planner.close()
+    ctx.close()
+    return section
 
 
 def ours_main(args):
@@ -332,6 +490,13 @@ def ours_main(args):
     e2e_value = world * n * e2e_steps / float(te.item())
     sampler.stop()
 
+    hybrid = None
+    if not args.no_hybrid:
+        try:
+            hybrid = hybrid_section(args, rank, world, local_rank, stream)
+        except Exception as e:  # pragma: no cover
+            hybrid = {"error": f"{type(e).__name__}: {e}"}
+
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
@@ -358,6 +523,7 @@ def ours_main(args):
                     "steps": e2e_steps},
             "gpu_launches": launches,
             "clocks": sampler.summary(),
+            "hybrid": hybrid,
         }
         print(json.dumps(line))
     if world > 1:
@@ -374,6 +540,9 @@ def main():
     ap.add_argument("--mode", default="check", choices=["check", "solve_check"])
     ap.add_argument("--cpu-edges-per-core", type=int, default=250_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-hybrid", action="store_true", help="skip the Hybrid A* (config C4) section of the JSON line")
+    ap.add_argument("--hybrid-queries", type=int, default=4096)
+    ap.add_argument("--cpu-plans-per-core", type=int, default=16)
     args = ap.parse_args()
     if args.impl == "reference":
         reference_main(args)
