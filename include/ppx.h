@@ -51,6 +51,9 @@ int ppx_ctx_destroy(ppx_ctx* ctx);
 /* Use the caller's cudaStream_t (NULL = back to the context's own stream). */
 int ppx_ctx_set_stream(ppx_ctx* ctx, void* cuda_stream);
 int ppx_ctx_synchronize(ppx_ctx* ctx);
+/* Options: "rs_filter" (default 1; 0 = the Reeds-Shepp edge checker evaluates every sample with the
+ * exact FP64 restatement, for A/B tests of the FP32 cell filter). */
+int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value);
 const char* ppx_last_error(const ppx_ctx* ctx);
 /* Number of kernels this context launched since creation (bench.py's gpu_launches). */
 int64_t ppx_ctx_launch_count(const ppx_ctx* ctx);
@@ -151,6 +154,14 @@ int ppx_check_edges_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double
 	const ppx_validator_params* vp, uint8_t* valid, float* last, uint32_t* samples);
 int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, double min_turning_radius,
 	const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, uint32_t* d_samples);
+
+/* Diagnostic twin of ppx_check_edges_rs: same results, and for every sample the FP32 cell filter
+ * certified it also evaluates the exact FP64 position.  counters[0..2] = certified samples, samples
+ * sent to the exact path, certified samples whose exact cell differs (must be 0);
+ * *max_dev_cells = max |filtered - exact| position over certified samples, in cells. */
+int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
+	const ppx_validator_params* vp, uint8_t* valid, float* last, uint32_t* samples, uint64_t* counters,
+	float* max_dev_cells);
 
 int ppx_check_edges_csteer(ppx_ctx* ctx, int64_t n, const ppx_csteer_edge* edges, const ppx_validator_params* vp,
 	uint8_t* valid, float* last, double* final_pose /* 3n, after Truncate(last) when invalid; may be NULL */);

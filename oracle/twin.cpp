@@ -13,6 +13,7 @@
 #include <vector>
 #include <cstdio>
 #include "ppx_device.cuh"
+#include "ppx_fastlane.cuh"
 #include "ppx_hybrid_host.h"
 
 using namespace ppx;
@@ -70,6 +71,10 @@ void* twin_world_create(const ppx_map_desc* desc, const int32_t* sqdist, const i
 
 void twin_world_destroy(void* h) { delete (TwinWorld*)h; }
 
+static double* g_audit = nullptr; // [max deviation (cells), certified, parked, parked: near cell border, parked: map-border rule, parked: slow-only edge]
+void twin_set_audit(double* a) { g_audit = a; }
+
+// impl 2: filtered FP32 lane machine with exact fallback (RSFastLane)
 // impl 0: thread-per-edge walker (rs_is_path_valid); impl 1: micro-step lane machine (RSLane)
 void twin_check_rs(void* h, long n, const ppx_rs_edge* edges, double r, float radius, float minStep, int impl,
 	uint8_t* valid, float* last, uint32_t* samples, uint32_t* microsteps)
@@ -89,6 +94,58 @@ void twin_check_rs(void* h, long n, const ppx_rs_edge* edges, double r, float ra
 			last[i] = l;
 			if (samples) samples[i] = ns;
 			if (microsteps) microsteps[i] = 0;
+		} else if (impl == 2) {
+			// filtered lane machine (ppx_fastlane.cuh) run sequentially: parked samples go straight to the exact path
+			LenArray L { edges[i].len };
+			FastMap fm = fast_map_derive(w->desc);
+			RSFastLane<LenArray> lane;
+			lane.begin(L, fm, map, start, (uint32_t)edges[i].code, r);
+			RSSeg seg;
+			for (int j = 0; j < 5; j++)
+				seg.len[j] = edges[i].len[j];
+			seg.code = (uint32_t)edges[i].code;
+			const float inv_r = (float)(1.0 / r), rc = (float)(r * fm.inv_resd);
+			unsigned steps = 0, parkedCount = 0;
+			double ex, ey;
+			while (true) {
+				steps++;
+				int rcode = 2;
+				double lengthAtSample = lane.length;
+				if (!lane.slowOnly) {
+					if (!lane.advance(L, r, inv_r, rc, fm.inv_res))
+						continue;
+					rcode = lane.sample(map, fm, radius, minStep);
+				}
+				if (rcode == 2) {
+					parkedCount++;
+					if (g_audit && !lane.slowOnly) {
+						float fx = floorf(lane.px), fy = floorf(lane.py), gx = lane.px - fx, gy = lane.py - fy;
+						bool near = fminf(gx, gy) < kCellEps || fmaxf(gx, gy) > 1.0f - kCellEps;
+						g_audit[near ? 3 : 4] += 1; // 3: near a cell border, 4: border / interior rule
+					} else if (g_audit)
+						g_audit[5] += 1; // slow-only edge
+					if (rs_exact_sample(lane, map, start, seg, r, radius, minStep, &ex, &ey))
+						break;
+					continue;
+				}
+				if (g_audit) { // exact position of the certified sample
+					RSWalker wk;
+					wk.init(start);
+					Pose p = wk.at(seg, r, (lengthAtSample / lane.pathLength) * lane.pathLength);
+					double dx = (p.x - map.ox) / map.resd - lane.rowb - (double)lane.px;
+					double dy = (p.y - map.oy) / map.resd - lane.colb - (double)lane.py;
+					double dev = fmax(fabs(dx), fabs(dy));
+					if (dev > g_audit[0]) g_audit[0] = dev;
+					g_audit[1] += 1;
+				}
+				if (rcode == 1)
+					break;
+			}
+			if (g_audit) g_audit[2] += parkedCount;
+			valid[i] = lane.verdict;
+			last[i] = lane.last;
+			if (samples) samples[i] = lane.ns;
+			if (microsteps) microsteps[i] = steps;
 		} else {
 			LenArray L { edges[i].len };
 			RSLane<LenArray> lane;

@@ -161,6 +161,9 @@ class Context:
     def synchronize(self):
         self._check(ppx.ppx_ctx_synchronize(self._h))
 
+    def set_option(self, name, value):
+        self._check(ppx.ppx_ctx_set_option(self._h, name.encode(), int(value)))
+
     @property
     def launch_count(self):
         return int(ppx.ppx_ctx_launch_count(self._h))
@@ -197,6 +200,21 @@ class Context:
         self._check(ppx.ppx_check_edges_rs(self._h, n, _ptr(edges), float(min_turning_radius), C.byref(v),
                                            _ptr(valid), _ptr(last), _ptr(samples)))
         return (valid.astype(bool), last, samples) if want_samples else (valid.astype(bool), last)
+
+    def check_edges_rs_audit(self, edges, min_turning_radius, vp: ValidatorParams):
+        """check_edges_rs plus the audit of the FP32 cell filter (ppx_check_edges_rs_audit)."""
+        edges = np.ascontiguousarray(edges, dtype=RS_EDGE)
+        n = len(edges)
+        valid = np.empty(n, dtype=np.uint8)
+        last = np.empty(n, dtype=np.float32)
+        samples = np.empty(n, dtype=np.uint32)
+        counters = np.zeros(3, dtype=np.uint64)
+        dev = np.zeros(1, dtype=np.float32)
+        v = vp.to_c()
+        self._check(ppx.ppx_check_edges_rs_audit(self._h, n, _ptr(edges), float(min_turning_radius), C.byref(v),
+                                                 _ptr(valid), _ptr(last), _ptr(samples), _ptr(counters), _ptr(dev)))
+        return dict(valid=valid.astype(bool), last=last, samples=samples, certified=int(counters[0]),
+                    parked=int(counters[1]), cell_mismatch=int(counters[2]), max_dev_cells=float(dev[0]))
 
     def check_edges_csteer(self, edges, vp: ValidatorParams, want_final=False):
         edges = np.ascontiguousarray(edges, dtype=CSTEER_EDGE)

@@ -123,6 +123,17 @@ int ppx_ctx_synchronize(ppx_ctx* ctx)
 	return PPX_OK;
 }
 
+int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value)
+{
+	if (!ctx || !name)
+		return PPX_ERR_INVALID;
+	if (!strcmp(name, "rs_filter")) {
+		ctx->rs_filter = value != 0;
+		return PPX_OK;
+	}
+	return ppx_fail(ctx, PPX_ERR_INVALID, "unknown option %s", name);
+}
+
 const char* ppx_last_error(const ppx_ctx* ctx) { return ctx ? ctx->error.c_str() : "null context"; }
 
 int64_t ppx_ctx_launch_count(const ppx_ctx* ctx) { return ctx ? ctx->launches : 0; }

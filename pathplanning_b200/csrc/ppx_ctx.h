@@ -15,6 +15,7 @@ struct ppx_ctx {
 	int num_sms = 0;
 	std::string error;
 	int64_t launches = 0;
+	int rs_filter = 1; // 0: k_check_rs evaluates every sample with the exact FP64 path (A/B tests)
 
 	// world model
 	bool has_map = false;

@@ -8,7 +8,9 @@
 // staged through shared memory with one bulk (TMA) copy per CTA tile so that the 72-byte AoS
 // records are read from HBM fully coalesced.
 #include <algorithm>
+#include <cstring>
 #include "ppx_ctx.h"
+#include "ppx_fastlane.cuh"
 
 using namespace ppx;
 
@@ -45,32 +47,95 @@ struct SmemLen {
 	__device__ __forceinline__ double get(int i) const { return col[i * kThreads]; }
 };
 
-// A7 on Reeds-Shepp edges, re-converging form: every lane runs the RSLane micro-step machine
-// (ppx_device.cuh) on its own edge; finished lanes are refilled by warp vote from the warp's chunk
-// of the edge queue (chunks of kGrab edges are taken from one global counter), so the 32 lanes of
-// a warp stay on one instruction stream although edges need between 1 and ~200 samples.
+// A7 on Reeds-Shepp edges, re-converging + filtered form.  Every lane runs the RSFastLane micro-step
+// machine (ppx_fastlane.cuh: FP32 positions, certified cells) on its own edge; finished lanes are
+// refilled by warp vote from the warp's chunk of the edge queue (chunks of kGrab edges are taken from
+// one global counter), so the 32 lanes of a warp stay on one instruction stream although edges need
+// between 1 and ~200 samples.  Samples the filter cannot certify PARK their lane; when kParkBatch
+// lanes of the warp are parked (or nothing else is runnable) the warp evaluates those samples with
+// the exact FP64 restatement of the reference (rs_exact_sample) in one divergent pass.
 constexpr int kGrab = 128;
 constexpr int kCheckCtasPerSm = 8;
+constexpr int kParkBatch = 8;
+constexpr int kRefillBatch = 4;
 
-__global__ void __launch_bounds__(kThreads, kCheckCtasPerSm) k_check_rs(MapDev map, int64_t n, const ppx_rs_edge* __restrict__ edges, double r,
-	float minSafeRadius, float minStep, uint8_t* __restrict__ valid, float* __restrict__ last, uint32_t* __restrict__ samples,
-	unsigned long long* __restrict__ queue)
+struct AuditOut {
+	unsigned long long certified; // samples decided by the filter
+	unsigned long long parked; // samples decided by the exact path
+	unsigned long long cell_mismatch; // certified samples whose exact cell differs (must be 0)
+	unsigned int max_dev_bits; // max |fast - exact| position, cells, as float bits
+};
+
+// State of IsPathValid's loop that the exact path reads and writes, passed by value so that the
+// lane machine stays in registers across the out-of-line call.
+struct ExactIO {
+	double pathLength, length, lastValidLength;
+	unsigned ns;
+	float last;
+	bool verdict, done;
+};
+
+__device__ __noinline__ ExactIO exact_sample_lane(ExactIO io, uint32_t code, const double* __restrict__ lencol, MapDev map,
+	const ppx_rs_edge* __restrict__ e, double r, float minSafeRadius, float minStep)
+{
+	Pose start = { e->start[0], e->start[1], e->start[2] };
+	RSSeg seg;
+	#pragma unroll
+	for (int i = 0; i < 5; i++)
+		seg.len[i] = lencol[i * kThreads];
+	seg.code = code;
+	double ex, ey;
+	io.done = rs_exact_sample(io, map, start, seg, r, minSafeRadius, minStep, &ex, &ey);
+	return io;
+}
+
+// audit only: exact position of the sample the lane has just certified, compared with (px, py)
+__device__ __noinline__ void audit_sample(const RSFastLane<SmemLen>& lane, const SmemLen& L, const MapDev& map,
+	const FastMap& fm, const ppx_rs_edge* __restrict__ e, double r, double lengthAtSample, AuditOut* out)
+{
+	Pose start = { e->start[0], e->start[1], e->start[2] };
+	RSSeg seg;
+	for (int i = 0; i < 5; i++)
+		seg.len[i] = L.get(i);
+	seg.code = lane.code;
+	RSWalker w;
+	w.init(start);
+	Pose p = w.at(seg, r, (lengthAtSample / lane.pathLength) * lane.pathLength);
+	int row = trunc_i32((p.x - map.ox) / map.resd), col = trunc_i32((p.y - map.oy) / map.resd);
+	int frow = lane.rowb + (int)floorf(lane.px), fcol = lane.colb + (int)floorf(lane.py);
+	double dx = (p.x - map.ox) / map.resd - (double)lane.rowb - (double)lane.px;
+	double dy = (p.y - map.oy) / map.resd - (double)lane.colb - (double)lane.py;
+	float dev = (float)fmax(fabs(dx), fabs(dy));
+	atomicMax(&out->max_dev_bits, __float_as_uint(dev));
+	atomicAdd(&out->certified, 1ull);
+	if (row != frow || col != fcol)
+		atomicAdd(&out->cell_mismatch, 1ull);
+}
+
+template <bool kAudit>
+__global__ void __launch_bounds__(kThreads, kCheckCtasPerSm) k_check_rs(MapDev map, FastMap fm, int64_t n,
+	const ppx_rs_edge* __restrict__ edges, double r, float minSafeRadius, float minStep, uint8_t* __restrict__ valid,
+	float* __restrict__ last, uint32_t* __restrict__ samples, unsigned long long* __restrict__ queue, AuditOut* audit)
 {
 	__shared__ double s_len[5][kThreads];
 	const unsigned lane_id = threadIdx.x & 31;
 	const unsigned lt_mask = (1u << lane_id) - 1;
 	double* mycol = &s_len[0][threadIdx.x];
 	SmemLen L { mycol };
-	RSLane<SmemLen> lane;
-	bool active = false;
+	RSFastLane<SmemLen> lane;
+	int state = LANE_IDLE;
 	int64_t idx = 0;
 	int64_t cursor = 0, limit = 0; // warp-uniform
 	bool exhausted = false; // warp-uniform
+	const float inv_r = (float)(1.0 / r);
+	const float rc = (float)(r * fm.inv_resd);
 
 	while (true) {
-		unsigned idle = __ballot_sync(0xffffffffu, !active);
-		if (idle) {
-			if (cursor >= limit && !exhausted) {
+		unsigned idle = __ballot_sync(0xffffffffu, state == LANE_IDLE);
+		unsigned parked = __ballot_sync(0xffffffffu, state == LANE_PARKED);
+		unsigned running = ~(idle | parked);
+		if (!exhausted && (__popc(idle) >= kRefillBatch || !running)) {
+			if (cursor >= limit) {
 				unsigned long long base = 0;
 				if (lane_id == 0)
 					base = atomicAdd(queue, (unsigned long long)kGrab);
@@ -84,33 +149,66 @@ __global__ void __launch_bounds__(kThreads, kCheckCtasPerSm) k_check_rs(MapDev m
 			}
 			int64_t avail = limit - cursor;
 			int rank = __popc(idle & lt_mask);
-			if (!active && rank < avail) {
+			if (state == LANE_IDLE && rank < avail) {
 				idx = cursor + rank;
 				const ppx_rs_edge* e = edges + idx;
 				Pose start = { e->start[0], e->start[1], e->start[2] };
 				#pragma unroll
 				for (int i = 0; i < 5; i++)
 					mycol[i * kThreads] = e->len[i];
-				lane.begin(L, start, (uint32_t)e->code, r);
-				active = true;
+				lane.begin(L, fm, map, start, (uint32_t)e->code, r);
+				state = lane.slowOnly ? LANE_PARKED : LANE_ACTIVE;
 			}
 			int need = __popc(idle);
 			cursor += need < avail ? need : avail;
-			if (!__any_sync(0xffffffffu, active)) {
-				if (exhausted)
-					break;
-				continue;
-			}
+			idle = __ballot_sync(0xffffffffu, state == LANE_IDLE);
+			parked = __ballot_sync(0xffffffffu, state == LANE_PARKED);
+			running = ~(idle | parked);
 		}
-		double arg = active ? lane.pre(L, r) : 0.0;
-		double s, c;
-		sincos(arg, &s, &c);
-		if (active && lane.post(map, s, c, r, minSafeRadius, minStep)) {
-			valid[idx] = lane.verdict ? 1 : 0;
-			last[idx] = lane.last;
-			if (samples)
-				samples[idx] = lane.ns;
-			active = false;
+		if (parked && (__popc(parked) >= kParkBatch || !running)) {
+			if (state == LANE_PARKED) {
+				ExactIO io { lane.pathLength, lane.length, lane.lastValidLength, lane.ns, 0.0f, false, false };
+				io = exact_sample_lane(io, lane.code, mycol, map, edges + idx, r, minSafeRadius, minStep);
+				lane.length = io.length;
+				lane.lastValidLength = io.lastValidLength;
+				lane.ns = io.ns;
+				lane.verdict = io.verdict;
+				lane.last = io.last;
+				if (kAudit)
+					atomicAdd(&audit->parked, 1ull);
+				state = LANE_ACTIVE;
+				if (io.done) {
+					valid[idx] = lane.verdict ? 1 : 0;
+					last[idx] = lane.last;
+					if (samples)
+						samples[idx] = lane.ns;
+					state = LANE_IDLE;
+				} else if (lane.slowOnly)
+					state = LANE_PARKED;
+			}
+			continue;
+		}
+		if (!running) {
+			if (exhausted)
+				break;
+			continue;
+		}
+		if (state == LANE_ACTIVE) {
+			if (lane.advance(L, r, inv_r, rc, fm.inv_res)) {
+				double lengthAtSample = lane.length;
+				int rcode = lane.sample(map, fm, minSafeRadius, minStep);
+				if (kAudit && rcode != 2)
+					audit_sample(lane, L, map, fm, edges + idx, r, lengthAtSample, audit);
+				if (rcode == 2)
+					state = LANE_PARKED;
+				else if (rcode == 1) {
+					valid[idx] = lane.verdict ? 1 : 0;
+					last[idx] = lane.last;
+					if (samples)
+						samples[idx] = lane.ns;
+					state = LANE_IDLE;
+				}
+			}
 		}
 	}
 }
@@ -265,9 +363,49 @@ int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 	if (n == 0)
 		return PPX_OK;
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
-	k_check_rs<<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_edges,
-		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue);
+	FastMap fm = fast_map_derive(ctx->desc);
+	if (!ctx->rs_filter)
+		fm.enabled = 0;
+	k_check_rs<false><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
+		nullptr);
 	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
+int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
+	const ppx_validator_params* vp, uint8_t* valid, float* last, uint32_t* samples, uint64_t* counters, float* max_dev_cells)
+{
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n > 0 && vp && edges && valid && last && samples && counters && max_dev_cells, "bad arguments");
+	ppx_rs_edge* d_edges;
+	uint8_t* d_valid;
+	float* d_last;
+	uint32_t* d_samples;
+	AuditOut* d_audit;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * sizeof(ppx_rs_edge), (void**)&d_edges));
+	PPX_CHECK(ppx_scratch(ctx, 1, n, (void**)&d_valid));
+	PPX_CHECK(ppx_scratch(ctx, 2, n * sizeof(float), (void**)&d_last));
+	PPX_CHECK(ppx_scratch(ctx, 3, n * sizeof(uint32_t), (void**)&d_samples));
+	PPX_CHECK(ppx_scratch(ctx, 4, sizeof(AuditOut), (void**)&d_audit));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_edges, edges, n * sizeof(ppx_rs_edge), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(d_audit, 0, sizeof(AuditOut), ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
+	FastMap fm = fast_map_derive(ctx->desc);
+	k_check_rs<true><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
+		d_audit);
+	PPX_LAUNCHED(ctx);
+	AuditOut h {};
+	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(last, d_last, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(samples, d_samples, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(&h, d_audit, sizeof(AuditOut), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	counters[0] = h.certified;
+	counters[1] = h.parked;
+	counters[2] = h.cell_mismatch;
+	memcpy(max_dev_cells, &h.max_dev_bits, 4);
 	return PPX_OK;
 }
 

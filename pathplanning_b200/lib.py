@@ -54,6 +54,7 @@ _SIGS = {
     "ppx_ctx_destroy": (C.c_int, [_p]),
     "ppx_ctx_set_stream": (C.c_int, [_p, _p]),
     "ppx_ctx_synchronize": (C.c_int, [_p]),
+    "ppx_ctx_set_option": (C.c_int, [_p, C.c_char_p, _i64]),
     "ppx_last_error": (C.c_char_p, [_p]),
     "ppx_ctx_launch_count": (C.c_int64, [_p]),
     "ppx_dev_alloc": (C.c_int, [_p, C.c_uint64, C.POINTER(_p)]),
@@ -65,6 +66,7 @@ _SIGS = {
     "ppx_map_upload": (C.c_int, [_p, C.POINTER(MapDescC), _p, _p, _p]),
     "ppx_is_state_valid": (C.c_int, [_p, _i64, _p, C.POINTER(ValidatorParamsC), _p]),
     "ppx_check_edges_rs": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p]),
+    "ppx_check_edges_rs_audit": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p, _p, _p]),
     "ppx_check_edges_rs_dev": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p]),
     "ppx_check_edges_csteer": (C.c_int, [_p, _i64, _p, C.POINTER(ValidatorParamsC), _p, _p, _p]),
     "ppx_check_edges_line": (C.c_int, [_p, _i64, _p, C.POINTER(ValidatorParamsC), _p, _p]),

@@ -141,3 +141,79 @@ def test_live_reference_large(ctx, ref):
     v, l, s = ctx.check_edges_rs(edges, 2.0, pp.ValidatorParams(1.0, 0.1), want_samples=True)
     assert np.array_equal(v, rr["valid"]) and np.array_equal(s.astype(np.int64), rr["samples"].astype(np.int64))
     w.close()
+
+
+# ---- the FP32 cell filter of k_check_rs (ppx_fastlane.cuh) ------------------------------------
+@pytest.fixture(scope="module")
+def c3_edges(ctx, ref):
+    """C3 map (2000x2000) + 200k pre-solved Reeds-Shepp edges of the bench workload, solved and
+    checked by the compiled reference."""
+    from pathplanning_b200 import synth
+    cfg = synth.C3
+    w = ref.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    for r in synth.config_rects(cfg):
+        w.add_rectangle(*r)
+    w.update()
+    occ, sq = w.grids()
+    ctx.upload_map(w.map_desc(), sq, occ, None)
+    s, g = synth.random_rs_queries(200000, seed=4242)
+    rr = w.check_rs_edges(s, g, 2.0)
+    w.close()
+    return pp.make_rs_edges(s, rr["steer"], rr["dir"], rr["len"]), rr
+
+
+def test_rs_filter_matches_reference_c3(ctx, c3_edges):
+    edges, rr = c3_edges
+    v, l, s = ctx.check_edges_rs(edges, 2.0, pp.ValidatorParams(1.0, 0.1), want_samples=True)
+    assert np.array_equal(v, rr["valid"])
+    assert np.array_equal(s.astype(np.int64), rr["samples"].astype(np.int64))
+    assert_close_rel(l, rr["last"], REL, "last")
+
+
+@pytest.mark.parametrize("radius,step", [(1.0, 0.1), (0.3, 0.05), (2.5, 0.4)])
+def test_rs_filter_ab_exact(ctx, c3_edges, radius, step):
+    """Filter on vs. off (every sample through the exact FP64 path): bit-identical outputs."""
+    edges, _ = c3_edges
+    vp = pp.ValidatorParams(radius, step)
+    a = ctx.check_edges_rs(edges, 2.0, vp, want_samples=True)
+    ctx.set_option("rs_filter", 0)
+    try:
+        b = ctx.check_edges_rs(edges, 2.0, vp, want_samples=True)
+    finally:
+        ctx.set_option("rs_filter", 1)
+    assert np.array_equal(a[0], b[0])
+    assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
+    assert np.array_equal(a[2], b[2])
+
+
+def test_rs_filter_audit(ctx, c3_edges):
+    """Every certified sample re-evaluated exactly on the device: same cell, and the FP32 position
+    error stays far below the certification margin kCellEps = 2.5e-3 cells."""
+    edges, rr = c3_edges
+    a = ctx.check_edges_rs_audit(edges, 2.0, pp.ValidatorParams(1.0, 0.1))
+    assert np.array_equal(a["valid"], rr["valid"])
+    assert a["cell_mismatch"] == 0
+    assert a["certified"] + a["parked"] == int(a["samples"].sum())
+    assert a["parked"] < 0.05 * a["certified"]
+    assert a["max_dev_cells"] < 2.5e-3 / 4, a["max_dev_cells"]
+    print("audit:", {k: a[k] for k in ("certified", "parked", "cell_mismatch", "max_dev_cells")})
+
+
+def test_rs_filter_odd_edges(ctx, c3_edges):
+    """Edges the filter must hand to the exact path: out-of-map starts, huge headings, near-border paths."""
+    _, _ = c3_edges
+    rng = np.random.default_rng(5)
+    n = 4000
+    starts = np.stack([rng.uniform(-104, 104, n), rng.uniform(-104, 104, n), rng.uniform(-50, 50, n)], 1)
+    d, a = rng.uniform(0.0, 30, n), rng.uniform(-np.pi, np.pi, n)
+    goals = np.stack([starts[:, 0] + d * np.cos(a), starts[:, 1] + d * np.sin(a), rng.uniform(-np.pi, np.pi, n)], 1)
+    vp = pp.ValidatorParams(1.0, 0.1)
+    sol = ctx.rs_solve(starts, goals, pp.RSCostParams(2.0))
+    a = ctx.check_edges_rs(sol["edges"], 2.0, vp, want_samples=True)
+    ctx.set_option("rs_filter", 0)
+    try:
+        b = ctx.check_edges_rs(sol["edges"], 2.0, vp, want_samples=True)
+    finally:
+        ctx.set_option("rs_filter", 1)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])
+    assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
