@@ -55,7 +55,7 @@ struct SmemLen {
 // lanes of the warp are parked (or nothing else is runnable) the warp evaluates those samples with
 // the exact FP64 restatement of the reference (rs_exact_sample) in one divergent pass.
 constexpr int kGrab = 128;
-constexpr int kCheckCtasPerSm = 8;
+constexpr int kCheckCtasPerSm = 6; // 80 registers, no spills; 24 warps/SM measured best (r1g sweep)
 constexpr int kParkBatch = 8;
 constexpr int kRefillBatch = 4;
 
@@ -112,8 +112,8 @@ __device__ __noinline__ void audit_sample(const RSFastLane<SmemLen>& lane, const
 		atomicAdd(&out->cell_mismatch, 1ull);
 }
 
-template <bool kAudit>
-__global__ void __launch_bounds__(kThreads, kCheckCtasPerSm) k_check_rs(MapDev map, FastMap fm, int64_t n,
+template <bool kAudit, int kCtas>
+__global__ void __launch_bounds__(kThreads, kCtas) k_check_rs(MapDev map, FastMap fm, int64_t n,
 	const ppx_rs_edge* __restrict__ edges, double r, float minSafeRadius, float minStep, uint8_t* __restrict__ valid,
 	float* __restrict__ last, uint32_t* __restrict__ samples, unsigned long long* __restrict__ queue, AuditOut* audit)
 {
@@ -366,7 +366,7 @@ int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 	FastMap fm = fast_map_derive(ctx->desc);
 	if (!ctx->rs_filter)
 		fm.enabled = 0;
-	k_check_rs<false><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+	k_check_rs<false, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
 		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
 		nullptr);
 	PPX_LAUNCHED(ctx);
@@ -392,7 +392,7 @@ int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, 
 	PPX_CUDA(ctx, cudaMemsetAsync(d_audit, 0, sizeof(AuditOut), ctx->stream));
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
 	FastMap fm = fast_map_derive(ctx->desc);
-	k_check_rs<true><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+	k_check_rs<true, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
 		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
 		d_audit);
 	PPX_LAUNCHED(ctx);

@@ -182,7 +182,8 @@ struct RSFastLane {
 		if (!(d >= minSafeRadius)) { // IsStateValid false
 			ns++;
 			verdict = false;
-			last = (float)(lastValidLength / pathLength);
+			// 0 / pathLength == 0 exactly; spares the division's slow path for the common first-sample failure
+			last = lastValidLength == 0.0 ? 0.0f : (float)(lastValidLength / pathLength);
 			return 1;
 		}
 		float deltaLength = d - minSafeRadius;
