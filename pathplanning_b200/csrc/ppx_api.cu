@@ -36,6 +36,20 @@ int ppx_scratch(ppx_ctx* ctx, int slot, size_t bytes, void** out)
 	return PPX_OK;
 }
 
+int ppx_pipeline_init(ppx_ctx* ctx)
+{
+	if (ctx->s_h2d)
+		return PPX_OK;
+	PPX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->s_h2d, cudaStreamNonBlocking));
+	PPX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->s_d2h, cudaStreamNonBlocking));
+	PPX_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming));
+	for (int i = 0; i < ppx_ctx::kMaxChunks; i++) {
+		PPX_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_h2d[i], cudaEventDisableTiming));
+		PPX_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_k[i], cudaEventDisableTiming));
+	}
+	return PPX_OK;
+}
+
 namespace {
 // GVD::ObstacleDistanceMap::GetDistanceToNearestObstacle, gvd.h:38:
 //   std::sqrt(m_distance[row][col]) * resolution   -- sqrt(int) is the double overload, the
@@ -79,7 +93,7 @@ int ppx_ctx_create(int device, ppx_ctx** out)
 	PPX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
 	ctx->stream = ctx->own_stream;
 	PPX_CUDA(ctx, cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device));
-	PPX_CUDA(ctx, cudaMalloc(&ctx->d_queue, 64));
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_queue, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
 	*out = ctx;
 	return PPX_OK;
 }
@@ -102,6 +116,15 @@ int ppx_ctx_destroy(ppx_ctx* ctx)
 	cudaFree(ctx->d_wf_goals);
 	for (auto& s : ctx->scratch)
 		cudaFree(s.ptr);
+	if (ctx->s_h2d) {
+		cudaStreamDestroy(ctx->s_h2d);
+		cudaStreamDestroy(ctx->s_d2h);
+		cudaEventDestroy(ctx->ev_start);
+		for (int i = 0; i < ppx_ctx::kMaxChunks; i++) {
+			cudaEventDestroy(ctx->ev_h2d[i]);
+			cudaEventDestroy(ctx->ev_k[i]);
+		}
+	}
 	cudaStreamDestroy(ctx->own_stream);
 	delete ctx;
 	return PPX_OK;

@@ -33,7 +33,12 @@ struct ppx_ctx {
 		size_t bytes = 0;
 	};
 	Scratch scratch[8];
-	unsigned long long* d_queue = nullptr; // work-queue cursor of the lane-refill kernels
+	unsigned long long* d_queue = nullptr; // work-queue cursors of the lane-refill kernels (kMaxChunks of them)
+	// copy/compute pipeline of the host-buffer entry points: H2D and D2H run on their own streams
+	// (the two copy engines) and are chained to the kernels on `stream` by events, chunk by chunk
+	static constexpr int kMaxChunks = 16;
+	cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+	cudaEvent_t ev_h2d[kMaxChunks] {}, ev_k[kMaxChunks] {}, ev_start = nullptr;
 
 	// non-holonomic table (A9)
 	bool has_nonholo = false;
@@ -68,6 +73,7 @@ struct ppx_ctx {
 
 int ppx_fail(ppx_ctx* ctx, int code, const char* fmt, ...);
 int ppx_scratch(ppx_ctx* ctx, int slot, size_t bytes, void** out);
+int ppx_pipeline_init(ppx_ctx* ctx);
 
 #define PPX_CUDA(ctx, call)                                                                           \
 	do {                                                                                              \

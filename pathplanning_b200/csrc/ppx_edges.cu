@@ -355,6 +355,19 @@ int ppx_is_state_valid(ppx_ctx* ctx, int64_t n, const double* poses, const ppx_v
 	return PPX_OK;
 }
 
+static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, double min_turning_radius,
+	const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, uint32_t* d_samples, int queueSlot)
+{
+	FastMap fm = fast_map_derive(ctx->desc);
+	if (!ctx->rs_filter)
+		fm.enabled = 0;
+	k_check_rs<false, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples,
+		ctx->d_queue + queueSlot, nullptr);
+	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
 int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, double min_turning_radius,
 	const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, uint32_t* d_samples)
 {
@@ -363,14 +376,7 @@ int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 	if (n == 0)
 		return PPX_OK;
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
-	FastMap fm = fast_map_derive(ctx->desc);
-	if (!ctx->rs_filter)
-		fm.enabled = 0;
-	k_check_rs<false, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
-		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
-		nullptr);
-	PPX_LAUNCHED(ctx);
-	return PPX_OK;
+	return launch_check_rs(ctx, n, d_edges, min_turning_radius, vp, d_valid, d_last, d_samples, 0);
 }
 
 int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
@@ -409,6 +415,9 @@ int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, 
 	return PPX_OK;
 }
 
+// Host-buffer entry: the batch is cut into chunks; chunk c's H2D copy (stream s_h2d), kernel (ctx->stream)
+// and D2H copies (stream s_d2h) are chained by events, so that the copy engines and the SMs work on
+// different chunks at the same time.  With pinned host buffers the call runs at PCIe H2D speed.
 int ppx_check_edges_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
 	const ppx_validator_params* vp, uint8_t* valid, float* last, uint32_t* samples)
 {
@@ -425,12 +434,31 @@ int ppx_check_edges_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double
 	PPX_CHECK(ppx_scratch(ctx, 2, n * sizeof(float), (void**)&d_last));
 	if (samples)
 		PPX_CHECK(ppx_scratch(ctx, 3, n * sizeof(uint32_t), (void**)&d_samples));
-	PPX_CUDA(ctx, cudaMemcpyAsync(d_edges, edges, n * sizeof(ppx_rs_edge), cudaMemcpyHostToDevice, ctx->stream));
-	PPX_CHECK(ppx_check_edges_rs_dev(ctx, n, d_edges, min_turning_radius, vp, d_valid, d_last, d_samples));
-	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
-	PPX_CUDA(ctx, cudaMemcpyAsync(last, d_last, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
-	if (samples)
-		PPX_CUDA(ctx, cudaMemcpyAsync(samples, d_samples, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CHECK(ppx_pipeline_init(ctx));
+	const int64_t minChunk = 250000; // a launch has a fixed tail of ~0.1 ms (its longest sample chains): few, large chunks
+	int nchunks = (int)std::min<int64_t>(ppx_ctx::kMaxChunks, std::max<int64_t>(1, n / minChunk));
+	int64_t chunk = (n + nchunks - 1) / nchunks;
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, ppx_ctx::kMaxChunks * sizeof(unsigned long long), ctx->stream));
+	PPX_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamWaitEvent(ctx->s_h2d, ctx->ev_start, 0));
+	PPX_CUDA(ctx, cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_start, 0));
+	for (int c = 0; c < nchunks; c++) {
+		int64_t off = c * chunk, m = std::min(chunk, n - off);
+		if (m <= 0)
+			break;
+		PPX_CUDA(ctx, cudaMemcpyAsync(d_edges + off, edges + off, m * sizeof(ppx_rs_edge), cudaMemcpyHostToDevice, ctx->s_h2d));
+		PPX_CUDA(ctx, cudaEventRecord(ctx->ev_h2d[c], ctx->s_h2d));
+		PPX_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_h2d[c], 0));
+		PPX_CHECK(launch_check_rs(ctx, m, d_edges + off, min_turning_radius, vp, d_valid + off, d_last + off,
+			d_samples ? d_samples + off : nullptr, c));
+		PPX_CUDA(ctx, cudaEventRecord(ctx->ev_k[c], ctx->stream));
+		PPX_CUDA(ctx, cudaStreamWaitEvent(ctx->s_d2h, ctx->ev_k[c], 0));
+		PPX_CUDA(ctx, cudaMemcpyAsync(valid + off, d_valid + off, m, cudaMemcpyDeviceToHost, ctx->s_d2h));
+		PPX_CUDA(ctx, cudaMemcpyAsync(last + off, d_last + off, m * sizeof(float), cudaMemcpyDeviceToHost, ctx->s_d2h));
+		if (samples)
+			PPX_CUDA(ctx, cudaMemcpyAsync(samples + off, d_samples + off, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->s_d2h));
+	}
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->s_d2h));
 	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	return PPX_OK;
 }
