@@ -11,6 +11,15 @@
 #ifndef PPX_SINCOS
 #define PPX_SINCOS sincos
 #endif
+// Same for the other libm calls of the Reeds-Shepp solver (fmod alone inlines to ~70 instructions,
+// 25 times over the 12 formulas).
+#ifndef PPX_FMOD
+#define PPX_FMOD fmod
+#define PPX_ATAN2 atan2
+#define PPX_ACOS acos
+#define PPX_ASIN asin
+#define PPX_SIN sin
+#endif
 
 #define PPX_PI 3.14159265358979323846
 #define PPX_PI_2 1.57079632679489661923
@@ -66,7 +75,7 @@ PPX_HD float std_maxf(float a, float b) { return (a < b) ? b : a; }
 // Maths::Modulo, utils/maths.h:9-16
 PPX_HD double modulo(double in, double mod)
 {
-	double out = fmod(in, mod);
+	double out = PPX_FMOD(in, mod);
 	if (out < 0)
 		out += mod;
 	return out;
@@ -612,7 +621,7 @@ PPX_HD float rs_compute_cost(const RSSeg& seg, double mLength, double r, float r
 struct RSGoalTerms {
 	double gth; // goal.theta of the mirrored goal
 	double xi, eta; // x -/+ sin(theta), y - 1 +/- cos(theta)
-	double u1sq, u1, phi; // xi^2+eta^2, sqrt, atan2(eta, xi)
+	double u1sq, u1, phi; // xi^2+eta^2, sqrt, PPX_ATAN2(eta, xi)
 };
 
 // GetMotionLengths (:537-569) for base word `base` on the mirrored goal.  `a` holds the terms of
@@ -631,7 +640,7 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 	}
 	case 1: { // LfSfRf :39-59 (the `u1squared < 4` branch has no return: NaN flows on)
 		u = sqrt(b.u1sq - 4);
-		double phi = atan2(2.0, u);
+		double phi = PPX_ATAN2(2.0, u);
 		t = wrap_angle(b.phi + phi);
 		v = wrap_angle(t - b.gth);
 		if (angle_invalid(t) || angle_invalid(v))
@@ -641,7 +650,7 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 	case 2: { // LfRbLf :61-84
 		if (a.u1 > 4)
 			return INF;
-		double alpha = acos(a.u1 / 4.0);
+		double alpha = PPX_ACOS(a.u1 / 4.0);
 		t = modulo(PPX_PI_2 + alpha + a.phi, 2 * PPX_PI);
 		u = modulo(PPX_PI - 2 * alpha, 2 * PPX_PI);
 		v = modulo(a.gth - t - u, 2 * PPX_PI);
@@ -652,7 +661,7 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 	case 3: { // LfRbLb :86-106
 		if (a.u1 > 4)
 			return INF;
-		double alpha = acos(a.u1 / 4.0);
+		double alpha = PPX_ACOS(a.u1 / 4.0);
 		t = modulo(PPX_PI_2 + alpha + a.phi, 2 * PPX_PI);
 		u = modulo(PPX_PI - 2 * alpha, 2 * PPX_PI);
 		v = modulo(t + u - a.gth, 2 * PPX_PI);
@@ -661,9 +670,9 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 	case 4: { // LfRfLb :108-129
 		if (a.u1 > 4)
 			return INF;
-		u = acos((8 - a.u1 * a.u1) / 8.0);
-		double va = sin(u);
-		double alpha = asin(2 * va / a.u1);
+		u = PPX_ACOS((8 - a.u1 * a.u1) / 8.0);
+		double va = PPX_SIN(u);
+		double alpha = PPX_ASIN(2 * va / a.u1);
 		t = modulo(PPX_PI_2 - alpha + a.phi, 2 * PPX_PI);
 		v = modulo(t - u - a.gth, 2 * PPX_PI);
 		return t + u + v;
@@ -672,12 +681,12 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 		if (b.u1 > 4)
 			return INF;
 		if (b.u1 > 2) {
-			double alpha = acos(b.u1 / 4 - 0.5);
+			double alpha = PPX_ACOS(b.u1 / 4 - 0.5);
 			t = modulo(PPX_PI_2 + b.phi - alpha, 2 * PPX_PI);
 			u = modulo(PPX_PI - alpha, 2 * PPX_PI);
 			v = modulo(b.gth - t + 2 * u, 2 * PPX_PI);
 		} else {
-			double alpha = acos(b.u1 / 4 + 0.5);
+			double alpha = PPX_ACOS(b.u1 / 4 + 0.5);
 			t = modulo(PPX_PI_2 + b.phi + alpha, 2 * PPX_PI);
 			u = modulo(alpha, 2 * PPX_PI);
 			v = modulo(b.gth - t + 2 * u, 2 * PPX_PI);
@@ -690,9 +699,9 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 		double va1 = 1.25 - b.u1 * b.u1 / 16; // 1.25f literal is exact
 		if (va1 < 0 || va1 > 1)
 			return INF;
-		u = acos(va1);
-		double va2 = sin(u);
-		double alpha = asin(2 * va2 / b.u1);
+		u = PPX_ACOS(va1);
+		double va2 = PPX_SIN(u);
+		double alpha = PPX_ASIN(2 * va2 / b.u1);
 		t = modulo(PPX_PI_2 + b.phi + alpha, 2 * PPX_PI);
 		v = modulo(t - b.gth, 2 * PPX_PI);
 		return t + u + u + v;
@@ -703,7 +712,7 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 		u = sqrt(a.u1sq - 4) - 2;
 		if (u < 0)
 			return INF;
-		double alpha = atan2(2.0, u + 2);
+		double alpha = PPX_ATAN2(2.0, u + 2);
 		t = modulo(PPX_PI_2 + a.phi + alpha, 2 * PPX_PI);
 		v = modulo(t + PPX_PI_2 - a.gth, 2 * PPX_PI);
 		return t + PPX_PI_2 + u + v;
@@ -722,7 +731,7 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 		u = sqrt(a.u1sq - 4) - 2;
 		if (u < 0)
 			return INF;
-		double alpha = atan2(u + 2, 2.0);
+		double alpha = PPX_ATAN2(u + 2, 2.0);
 		t = modulo(PPX_PI_2 + a.phi - alpha, 2 * PPX_PI);
 		v = modulo(t - PPX_PI_2 - a.gth, 2 * PPX_PI);
 		return t + u + PPX_PI_2 + v;
@@ -741,7 +750,7 @@ PPX_HD double rs_motion_lengths(int base, const RSGoalTerms& a, const RSGoalTerm
 		u = sqrt(b.u1sq - 4) - 4;
 		if (u < 0)
 			return INF;
-		double alpha = atan2(2.0, u + 4);
+		double alpha = PPX_ATAN2(2.0, u + 4);
 		t = modulo(PPX_PI_2 + b.phi + alpha, 2 * PPX_PI);
 		v = modulo(t - b.gth, 2 * PPX_PI);
 		return t + u + v + PPX_PI;
@@ -795,8 +804,8 @@ PPX_HD void rs_solve(const Pose& start, const Pose& goal, double r, float rev, f
 		b.u1sq = b.xi * b.xi + b.eta * b.eta;
 		a.u1 = sqrt(a.u1sq);
 		b.u1 = sqrt(b.u1sq);
-		a.phi = atan2(a.eta, a.xi);
-		b.phi = atan2(b.eta, b.xi);
+		a.phi = PPX_ATAN2(a.eta, a.xi);
+		b.phi = PPX_ATAN2(b.eta, b.xi);
 		#pragma unroll 1
 		for (int base = 0; base < 12; base++) {
 			double t = 0, u = 0, v = 0;

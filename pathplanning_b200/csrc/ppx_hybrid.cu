@@ -17,13 +17,29 @@
 // phase of a different query, so its instruction footprint -- not arithmetic -- is what stalls it
 // (ncu r1c: 6.6 "no instruction" stall cycles per issued instruction with everything inlined).
 __device__ __noinline__ void ppx_sincos_ool(double x, double* s, double* c);
+__device__ __noinline__ double ppx_fmod_ool(double a, double b);
+__device__ __noinline__ double ppx_atan2_ool(double y, double x);
+__device__ __noinline__ double ppx_acos_ool(double x);
+__device__ __noinline__ double ppx_asin_ool(double x);
+__device__ __noinline__ double ppx_sin_ool(double x);
 #define PPX_SINCOS ppx_sincos_ool
+#define PPX_FMOD ppx_fmod_ool
+#define PPX_ATAN2 ppx_atan2_ool
+#define PPX_ACOS ppx_acos_ool
+#define PPX_ASIN ppx_asin_ool
+#define PPX_SIN ppx_sin_ool
+#include <cstdlib>
 #include "ppx_ctx.h"
 #include "ppx_hybrid_host.h"
 
 using namespace ppx;
 
 __device__ __noinline__ void ppx_sincos_ool(double x, double* s, double* c) { sincos(x, s, c); }
+__device__ __noinline__ double ppx_fmod_ool(double a, double b) { return fmod(a, b); }
+__device__ __noinline__ double ppx_atan2_ool(double y, double x) { return atan2(y, x); }
+__device__ __noinline__ double ppx_acos_ool(double x) { return acos(x); }
+__device__ __noinline__ double ppx_asin_ool(double x) { return asin(x); }
+__device__ __noinline__ double ppx_sin_ool(double x) { return sin(x); }
 
 int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored);
 
@@ -200,12 +216,66 @@ struct SearchConsts {
 	MapDev map;
 };
 
+// Schedule of a batch: queries are independent, and the batch ends when its longest query does.  A
+// query whose start cell the goal's wavefront never reached exhausts its whole reachable state set
+// (about 7000 expansions on C2, 10x the mean), and otherwise the expansion count grows with the
+// wavefront cost-to-go of the start cell -- both are known before the search starts.  One CTA
+// bucket-sorts the queries by that key, largest first (unreached = +inf first).
+constexpr int kOrderBins = 1024;
+__global__ void __launch_bounds__(1024) k_query_order(MapDev map, int64_t nq, const double* __restrict__ starts,
+	const int* __restrict__ wfSlot, const float* __restrict__ wfCost, float* __restrict__ keys, int* __restrict__ order)
+{
+	__shared__ unsigned s_bins[kOrderBins + 1];
+	__shared__ float s_max;
+	const size_t cells = (size_t)map.rows * map.cols;
+	const float INF = __int_as_float(0x7f800000);
+	if (threadIdx.x == 0)
+		s_max = 0.0f;
+	for (int i = threadIdx.x; i <= kOrderBins; i += blockDim.x)
+		s_bins[i] = 0u;
+	__syncthreads();
+	for (int64_t q = threadIdx.x; q < nq; q += blockDim.x) {
+		int row = trunc_i32((starts[3 * q] - map.ox) / map.resd);
+		int col = trunc_i32((starts[3 * q + 1] - map.oy) / map.resd);
+		float key = INF;
+		if (row >= 0 && row < map.rows && col >= 0 && col < map.cols)
+			key = wfCost[(size_t)(wfSlot ? wfSlot[q] : q) * cells + (size_t)row * map.cols + col];
+		if (!(key >= 0.0f))
+			key = INF;
+		keys[q] = key;
+		if (key < INF)
+			atomicMax((int*)&s_max, __float_as_int(key)); // non-negative floats order like their bits
+	}
+	__syncthreads();
+	const float scale = s_max > 0.0f ? (float)(kOrderBins - 1) / s_max : 0.0f;
+	for (int64_t q = threadIdx.x; q < nq; q += blockDim.x) {
+		float key = keys[q];
+		int bin = key < INF ? min(kOrderBins - 1, (int)(key * scale)) : kOrderBins;
+		atomicAdd(&s_bins[bin], 1u);
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) { // descending exclusive scan (1025 bins)
+		unsigned acc = 0;
+		for (int b = kOrderBins; b >= 0; b--) {
+			unsigned c = s_bins[b];
+			s_bins[b] = acc;
+			acc += c;
+		}
+	}
+	__syncthreads();
+	for (int64_t q = threadIdx.x; q < nq; q += blockDim.x) {
+		float key = keys[q];
+		int bin = key < INF ? min(kOrderBins - 1, (int)(key * scale)) : kOrderBins;
+		order[atomicAdd(&s_bins[bin], 1u)] = (int)q;
+	}
+}
+
 // The graph search of one query per warp.
 __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const SearchConsts* __restrict__ consts, int64_t nq,
 	const double* __restrict__ starts, const double* __restrict__ goals, const unsigned long long* __restrict__ seeds,
 	const int* __restrict__ wfSlot, const float* __restrict__ wfCost, WsLayout L, char* __restrict__ slabs,
 	ppx_hybrid_limits limits, ppx_hybrid_result* __restrict__ results, ppx_hybrid_path_state* __restrict__ paths,
-	ppx_hybrid_log_entry* __restrict__ logs, unsigned long long* __restrict__ queue)
+	ppx_hybrid_log_entry* __restrict__ logs, unsigned long long* __restrict__ queue, const int* __restrict__ order)
 {
 	__shared__ Child s_child[kSearchWarps][kMaxChildren];
 	__shared__ double s_h[kSearchWarps][kMaxChildren];
@@ -226,6 +296,8 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const Searc
 		q = __shfl_sync(0xffffffffu, q, 0);
 		if (q >= nq)
 			break;
+		if (order)
+			q = order[q]; // longest-expected-first schedule (k_query_order); results do not depend on it
 		for (int i = (int)lane; i < L.tableSize; i += 32)
 			W.table[i] = 0u;
 		__syncwarp();
@@ -391,7 +463,8 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 	L.maxNodes = limits.max_nodes > 0 ? limits.max_nodes : 2 * L.tableSize;
 	L.bytes = (ws_bytes(L.maxNodes, L.tableSize) + 255) & ~(size_t)255;
 	// as many queries in flight as are resident (255 registers -> 8 warps per SM), at most 12 GB of slabs
-	int64_t warps = std::min<int64_t>(nq, (int64_t)ctx->num_sms * 8);
+	static const int wps = getenv("PPX_SEARCH_WPS") ? atoi(getenv("PPX_SEARCH_WPS")) : 8;
+	int64_t warps = std::min<int64_t>(nq, (int64_t)ctx->num_sms * wps);
 	const size_t budget = (size_t)12 << 30;
 	warps = std::max<int64_t>(1, std::min<int64_t>(warps, (int64_t)(budget / L.bytes)));
 	int ctas = (int)((warps + kSearchWarps - 1) / kSearchWarps);
@@ -401,8 +474,17 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 	if (!h->d_consts)
 		PPX_CUDA(ctx, cudaMalloc(&h->d_consts, sizeof(SearchConsts)));
 	PPX_CUDA(ctx, cudaMemcpyAsync(h->d_consts, &consts, sizeof(SearchConsts), cudaMemcpyHostToDevice, ctx->stream));
+	int* d_order = nullptr;
+	if (nq > warps && nq < (int64_t)1 << 31) { // more queries than resident warps: schedule the long ones first
+		float* d_keys;
+		PPX_CHECK(ppx_scratch(ctx, 6, (size_t)nq * 8, (void**)&d_keys));
+		d_order = (int*)(d_keys + nq);
+		k_query_order<<<1, 1024, 0, ctx->stream>>>(ctx->map_dev(), nq, d_starts, d_wfSlot, d_wf, d_keys, d_order);
+		PPX_LAUNCHED(ctx);
+	}
 	k_hybrid_search<<<ctas, kSearchWarps * 32, 0, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, d_starts, d_goals,
-		(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, (char*)h->d_slabs, limits, d_results, d_paths, d_log, ctx->d_queue);
+		(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, (char*)h->d_slabs, limits, d_results, d_paths, d_log, ctx->d_queue,
+		d_order);
 	PPX_LAUNCHED(ctx);
 	return PPX_OK;
 }

@@ -36,7 +36,8 @@ def main():
     t0 = time.perf_counter()
     planner = pp.HybridAStar(ctx, pp.HybridParams(), pp.ValidatorParams(1.0, 0.1))
     print(f"ppx_hybrid_create (table build): {(time.perf_counter() - t0) * 1e3:.1f} ms")
-    for n in (1, 64, 512, 4096):
+    sizes = [int(a) for a in sys.argv[1:]] or [1, 64, 512, 4096]
+    for n in sizes:
         starts, goals = c2_queries(ctx, n)
         seeds = (np.arange(n) + 1000).astype(np.uint64)
         for rep in range(2):
