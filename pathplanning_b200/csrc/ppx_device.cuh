@@ -846,4 +846,94 @@ PPX_HD void rs_solve(const Pose& start, const Pose& goal, double r, float rev, f
 	out.cost = rs_compute_cost(out.seg, out.mLength, r, rev, fwd, sw);
 }
 
+
+#ifdef __CUDACC__
+// Solver::GetOptimalPath evaluated by a whole warp: the 48 words are independent, lane L takes word
+// L and (lanes 0..15) word 32 + L.  The reference's scan in enum order with a strict `<` keeps the
+// first word of minimal float cost, i.e. the minimum of (cost, word) in lexicographic order over
+// the words whose cost compares below +inf (NaN and +inf never win, trap H8); the warp takes the
+// same minimum by shuffles.  All lanes return the same solution.  Must be called converged.
+__device__ __forceinline__ void rs_solve_warp(const Pose& start, const Pose& goal, double r, float rev, float fwd, float sw,
+	RSSolution& out)
+{
+	const unsigned lane = threadIdx.x & 31;
+	double dx = goal.x - start.x, dy = goal.y - start.y;
+	double sN, cN;
+	PPX_SINCOS(-start.th, &sN, &cN);
+	double gx = cN * dx + (-sN) * dy;
+	double gy = sN * dx + cN * dy;
+	double gth = wrap_theta(wrap_theta(goal.th - start.th));
+	gx = gx / r;
+	gy = gy / r;
+	double sG, cG;
+	PPX_SINCOS(gth, &sG, &cG);
+	const int q = lane & 3;
+	double x = (q & 1) ? -gx : gx;
+	double y = (q & 2) ? -gy : gy;
+	bool flipTh = (q == 1 || q == 2);
+	double th = wrap_theta(flipTh ? -gth : gth);
+	double sq = flipTh ? -sG : sG;
+	RSGoalTerms a, b;
+	a.gth = b.gth = th;
+	a.xi = x - sq;
+	a.eta = y - 1 + cG;
+	b.xi = x + sq;
+	b.eta = y - 1 - cG;
+	a.u1sq = a.xi * a.xi + a.eta * a.eta;
+	b.u1sq = b.xi * b.xi + b.eta * b.eta;
+	a.u1 = sqrt(a.u1sq);
+	b.u1 = sqrt(b.u1sq);
+	a.phi = PPX_ATAN2(a.eta, a.xi);
+	b.phi = PPX_ATAN2(b.eta, b.xi);
+	const float INF = __int_as_float(0x7f800000);
+	float bestCost = INF;
+	int bestWord = 64;
+	double bt = 0, bu = 0, bv = 0;
+	#pragma unroll 1
+	for (int round = 0; round < 2; round++) {
+		int word = round * 32 + (int)lane;
+		if (word < 48) {
+			double t = 0, u = 0, v = 0;
+			double length = rs_motion_lengths(word >> 2, a, b, t, u, v);
+			if (length != PPX_INF) {
+				RSSeg seg;
+				double mLength = rs_build_segment(word, t, u, v, seg);
+				float cost = rs_compute_cost(seg, mLength, r, rev, fwd, sw);
+				if (cost < bestCost) { // the lane's round-1 word is the larger one: strict < keeps enum order
+					bestCost = cost;
+					bestWord = word;
+					bt = t; bu = u; bv = v;
+				}
+			}
+		}
+	}
+	#pragma unroll
+	for (int off = 16; off > 0; off >>= 1) {
+		float oc = __shfl_xor_sync(0xffffffffu, bestCost, off);
+		int ow = __shfl_xor_sync(0xffffffffu, bestWord, off);
+		double ot = __shfl_xor_sync(0xffffffffu, bt, off);
+		double ou = __shfl_xor_sync(0xffffffffu, bu, off);
+		double ov = __shfl_xor_sync(0xffffffffu, bv, off);
+		if (oc < bestCost || (oc == bestCost && ow < bestWord)) {
+			bestCost = oc;
+			bestWord = ow;
+			bt = ot; bu = ou; bv = ov;
+		}
+	}
+	if (!(bestCost < INF))
+		bestWord = -1;
+	out.word = bestWord;
+	if (bestWord < 0) {
+		for (int i = 0; i < 5; i++)
+			out.seg.len[i] = PPX_INF;
+		out.seg.code = 0xAAAAA;
+		out.mLength = 0.0;
+		out.cost = INF;
+		return;
+	}
+	out.mLength = rs_build_segment(bestWord, bt, bu, bv, out.seg);
+	out.cost = rs_compute_cost(out.seg, out.mLength, r, rev, fwd, sw);
+}
+#endif
+
 }

@@ -204,9 +204,13 @@ __device__ __noinline__ double hy_heuristic(const HybridDev& P, const MapDev& ma
 {
 	return combined_heuristic(P, map, wf, goal, s);
 }
-__device__ __noinline__ void hy_rs_child(const HybridDev& P, const MapDev& map, const Pose& parent, const Pose& goal, Child& out)
+__device__ __noinline__ void hy_rs_child(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out)
 {
-	rs_child(P, map, parent, goal, out);
+	rs_child_from(P, map, parent, sol, out);
+}
+__device__ __noinline__ void hy_rs_solve_warp(const HybridDev& P, const Pose& parent, const Pose& goal, RSSolution& sol)
+{
+	rs_solve_warp(parent, goal, P.rmin, P.revF, P.fwdF, P.swF, sol);
 }
 
 // Parameters of the search kernel live in device memory: the out-of-line helpers take them by
@@ -346,12 +350,15 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const Searc
 			}
 			want = __shfl_sync(0xffffffffu, want, 0);
 			const int nslots = 2 * P.numDeltas + want;
+			RSSolution sol;
+			if (want) // warp-uniform: the 48 Reeds-Shepp words are evaluated by the 32 lanes
+				hy_rs_solve_warp(P, parent, goal, sol);
 			if ((int)lane < nslots) {
 				Child c;
 				if ((int)lane < 2 * P.numDeltas)
 					csteer_child(P, map, parent, pk, (int)lane >> 1, (int)lane & 1, c);
 				else
-					hy_rs_child(P, map, parent, goal, c);
+					hy_rs_child(P, map, parent, sol, c);
 				double h = 0.0;
 				if (c.ok)
 					h = hy_heuristic(P, map, wf, goal, c.pose);

@@ -189,10 +189,17 @@ PPX_HD Pose rs_interpolate(const Pose& start, const RSSeg& seg, double r, double
 }
 
 // StatePropagator::GetReedsSheppChild, hybrid_a_star.cpp:149-173
+PPX_HD void rs_child_from(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out);
 PPX_HD void rs_child(const HybridDev& P, const MapDev& map, const Pose& parent, const Pose& goal, Child& out)
 {
 	RSSolution sol;
 	rs_solve(parent, goal, P.rmin, P.revF, P.fwdF, P.swF, 0, sol);
+	rs_child_from(P, map, parent, sol, out);
+}
+
+// ... given the optimal segment (the search kernel solves it with the whole warp, rs_solve_warp)
+PPX_HD void rs_child_from(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out)
+{
 	const double pathLength = sol.mLength * P.rmin; // PathSegment::GetLength(minTurningRadius)
 	out.kind = 1;
 	out.last = 1.0f;
