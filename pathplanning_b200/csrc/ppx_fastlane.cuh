@@ -243,4 +243,81 @@ PPX_HD bool rs_exact_sample(Lane& lane, const MapDev& map, const Pose& start, co
 	return true;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// IsPathValid on a constant-steer primitive (csteer_is_path_valid) with the same cell filter: the
+// sample at arc length `length` is  start + chord * (cos, sin)(beta + theta0 + h),  h = dist*kappa/2,
+// chord = dist * sin(h)/h  (the chord form of kinematic_bicycle_model.cpp:5-32; unlike the difference
+// of sines it does not cancel for small curvatures).  Uncertified samples are evaluated exactly in
+// place: one primitive per thread, nothing to batch.
+PPX_HD bool csteer_is_path_valid_filtered(const MapDev& map, const FastMap& fm, const CSteer& p, float minSafeRadius,
+	float minStep, float* last, unsigned* samples)
+{
+	const double pathLength = p.length;
+	double ux = (p.start.x - map.ox) * fm.inv_resd;
+	double uy = (p.start.y - map.oy) * fm.inv_resd;
+	bool usable = fm.enabled && fabs(ux) < 1e6 && fabs(uy) < 1e6 && fabs(p.start.th) < 1e4 && pathLength > 0.0
+		&& pathLength * fm.inv_resd < (double)kFastMaxCells && fabs(p.cosBeta) > 0.05 && fabs(p.kappa) < 1e3 && fabs(p.beta) < 10.0;
+	if (!usable)
+		return csteer_is_path_valid(map, p, minSafeRadius, minStep, last, samples);
+	const double fx0 = floor(ux), fy0 = floor(uy);
+	const int rowb = (int)fx0, colb = (int)fy0;
+	const float kx = (float)(ux - fx0), ky = (float)(uy - fy0);
+	double a0 = (p.curved ? p.beta : 0.0) + p.start.th; // the straight branch moves along theta0
+	a0 = a0 - PPX_2PI * rint(a0 * (1.0 / PPX_2PI));
+	const float A = (float)a0;
+	const float kap = p.curved ? (float)p.kappa : 0.0f, invCos = (float)(1.0 / p.cosBeta);
+	const float sgn = p.dir == 1 ? -1.0f : 1.0f;
+	float dist = 0.0f;
+	unsigned ns = 0;
+	double lastValidLength = 0.0, length = 0.0;
+	bool ok = true;
+	while (length < pathLength) {
+		float d = sgn * (float)length * invCos;
+		float h = 0.5f * d * kap;
+		float sinc = fabsf(h) < 1e-3f ? 1.0f - h * h * (1.0f / 6.0f) : PPX_FSIN(h) / h;
+		float chord = d * fm.inv_res * sinc;
+		float ang = fast_wrap(A + h);
+		float px = kx + chord * PPX_FCOS(ang), py = ky + chord * PPX_FSIN(ang);
+		float fx = floorf(px), fy = floorf(py);
+		float gx = px - fx, gy = py - fy;
+		bool near = fminf(gx, gy) < kCellEps || fmaxf(gx, gy) > 1.0f - kCellEps;
+		int row = rowb + (int)fx, col = colb + (int)fy;
+		int ib = imin(imin(row - fm.rb0, fm.rb1 - row), imin(col - fm.cb0, fm.cb1 - col));
+		bool certified = !near && ib >= 0 && fabsf(h) < 3.0f;
+		bool valid = false;
+		float deltaLength = 0.0f;
+		if (certified) {
+			dist = PPX_LDG(map.clearance + (size_t)row * map.cols + col);
+			valid = dist >= minSafeRadius;
+			deltaLength = dist - minSafeRadius;
+			if (valid && !(deltaLength <= (float)ib * map.res))
+				certified = false; // the distance to the border may limit the step
+		}
+		ns++;
+		if (certified) {
+			if (!valid) {
+				*last = lastValidLength == 0.0 ? 0.0f : (float)(lastValidLength / pathLength);
+				ok = false;
+				break;
+			}
+			lastValidLength = length;
+			length += (double)std_maxf(deltaLength, minStep);
+		} else { // exact sample, csteer_is_path_valid's loop body
+			Pose s = p.at(length / pathLength);
+			if (!is_state_valid(map, s.x, s.y, s.th, minSafeRadius, &dist)) {
+				*last = (float)(lastValidLength / pathLength);
+				ok = false;
+				break;
+			}
+			lastValidLength = length;
+			length += next_step(map, s.x, s.y, dist, minSafeRadius, minStep);
+		}
+	}
+	if (ok)
+		*last = 1.0f;
+	if (samples) *samples = ns;
+	return ok;
+}
+
 }

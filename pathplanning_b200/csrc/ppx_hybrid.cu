@@ -218,6 +218,7 @@ __device__ __noinline__ void hy_rs_solve_warp(const HybridDev& P, const Pose& pa
 struct SearchConsts {
 	HybridDev P;
 	MapDev map;
+	FastMap fm; // FP32 cell filter of the primitives' collision checks (ppx_fastlane.cuh)
 };
 
 // Schedule of a batch: queries are independent, and the batch ends when its longest query does.  A
@@ -356,7 +357,7 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const Searc
 			if ((int)lane < nslots) {
 				Child c;
 				if ((int)lane < 2 * P.numDeltas)
-					csteer_child(P, map, parent, pk, (int)lane >> 1, (int)lane & 1, c);
+					csteer_child(P, map, parent, pk, (int)lane >> 1, (int)lane & 1, c, &consts->fm);
 				else
 					hy_rs_child(P, map, parent, sol, c);
 				double h = 0.0;
@@ -477,7 +478,9 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 	int ctas = (int)((warps + kSearchWarps - 1) / kSearchWarps);
 	PPX_CHECK(grow(ctx, &h->d_slabs, &h->slabBytes, (size_t)ctas * kSearchWarps * L.bytes));
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
-	SearchConsts consts { h->dev, ctx->map_dev() };
+	SearchConsts consts { h->dev, ctx->map_dev(), fast_map_derive(ctx->desc) };
+	if (!ctx->rs_filter)
+		consts.fm.enabled = 0;
 	if (!h->d_consts)
 		PPX_CUDA(ctx, cudaMalloc(&h->d_consts, sizeof(SearchConsts)));
 	PPX_CUDA(ctx, cudaMemcpyAsync(h->d_consts, &consts, sizeof(SearchConsts), cudaMemcpyHostToDevice, ctx->stream));

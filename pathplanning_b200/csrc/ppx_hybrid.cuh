@@ -5,6 +5,7 @@
 // the parity traps of SURVEY.md section 8 (H2, H3, H4, H7, H10, H11) are reproduced, not fixed.
 #pragma once
 #include "ppx_device.cuh"
+#include "ppx_fastlane.cuh"
 
 namespace ppx {
 
@@ -115,7 +116,7 @@ struct Child {
 
 // StatePropagator::GetConstantSteerChild, hybrid_a_star.cpp:111-147
 PPX_HD void csteer_child(const HybridDev& P, const MapDev& map, const Pose& parent, const Key3& parentKey, int deltaIdx,
-	int direction, Child& out)
+	int direction, Child& out, const FastMap* fm = nullptr)
 {
 	CSteer p;
 	p.start = parent;
@@ -132,7 +133,8 @@ PPX_HD void csteer_child(const HybridDev& P, const MapDev& map, const Pose& pare
 	out.kind = 0;
 	out.dir = direction; // PathConstantSteer::GetDirection
 	float last;
-	bool valid = csteer_is_path_valid(map, p, P.minSafeRadius, P.minStep, &last, nullptr);
+	bool valid = fm ? csteer_is_path_valid_filtered(map, *fm, p, P.minSafeRadius, P.minStep, &last, nullptr)
+	                : csteer_is_path_valid(map, p, P.minSafeRadius, P.minStep, &last, nullptr);
 	out.last = last;
 	if (valid) {
 		out.pose = p.at(1.0); // m_final of the constructor
