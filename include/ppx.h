@@ -96,6 +96,13 @@ typedef struct ppx_map_desc {
 int ppx_map_upload(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* sqdist, const int32_t* occupancy,
 	const float* pathcost);
 
+/* N1: cold build of GVD::ObstacleDistanceMap (state_validator/gvd.cpp:30-89,105-118) on the device:
+ * uploads the occupancy grid (>= 0 occupied) and computes the squared cell distance to the nearest
+ * occupied cell (exact Euclidean distance transform, INT_MAX on a map without obstacles), then
+ * proceeds like ppx_map_upload.  sqdist_out (rows*cols, may be NULL) receives the distance grid. */
+int ppx_map_build(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* occupancy, const float* pathcost,
+	int32_t* sqdist_out);
+
 /* StateValidatorOccupancyMap public fields (state_validator_occupancy_map.h:27-28). */
 typedef struct ppx_validator_params {
 	float min_safe_radius;

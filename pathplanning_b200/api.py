@@ -182,6 +182,19 @@ class Context:
         self._check(ppx.ppx_map_upload(self._h, C.byref(d), _ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2])))
         self.map = desc
 
+    def build_map(self, desc: MapDesc, occupancy, pathcost=None, want_sqdist=True):
+        """ppx_map_build: occupancy grid in, obstacle squared-distance map computed on the device (N1)."""
+        cells = desc.rows * desc.cols
+        occ = np.ascontiguousarray(occupancy, dtype=np.int32).reshape(-1)
+        if occ.size != cells:
+            raise ValueError(f"occupancy has {occ.size} cells, expected {cells}")
+        pc = None if pathcost is None else np.ascontiguousarray(pathcost, dtype=np.float32).reshape(-1)
+        sq = np.empty(cells, dtype=np.int32) if want_sqdist else None
+        d = desc.to_c()
+        self._check(ppx.ppx_map_build(self._h, C.byref(d), _ptr(occ), _ptr(pc), _ptr(sq)))
+        self.map = desc
+        return None if sq is None else sq.reshape(desc.rows, desc.cols)
+
     # ---- A7 -----------------------------------------------------------------------------------
     def is_state_valid(self, poses, vp: ValidatorParams):
         poses = _f64(poses)

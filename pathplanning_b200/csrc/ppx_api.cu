@@ -72,6 +72,57 @@ __global__ void k_occupied(const int* __restrict__ occupancy, uint8_t* __restric
 }
 }
 
+// (Re)allocates the world-model grids for desc's size; a new size resets to the defaults of an empty
+// map: free cells (-1), zero potential.
+int ppx_map_alloc(ppx_ctx* ctx, const ppx_map_desc* desc)
+{
+	PPX_CUDA(ctx, cudaSetDevice(ctx->device));
+	size_t cells = (size_t)desc->rows * desc->cols;
+	if (cells == ctx->cells)
+		return PPX_OK;
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	cudaFree(ctx->d_sqdist);
+	cudaFree(ctx->d_occupancy);
+	cudaFree(ctx->d_pathcost);
+	cudaFree(ctx->d_clearance);
+	cudaFree(ctx->d_occ8);
+	ctx->d_occ8 = nullptr;
+	ctx->d_sqdist = ctx->d_occupancy = nullptr;
+	ctx->d_pathcost = ctx->d_clearance = nullptr;
+	ctx->cells = 0;
+	ctx->has_map = false;
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_sqdist, cells * sizeof(int32_t)));
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_occupancy, cells * sizeof(int32_t)));
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_pathcost, cells * sizeof(float)));
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_clearance, cells * sizeof(float)));
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_occ8, cells));
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_occ8, 0, cells, ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_occupancy, 0xff, cells * sizeof(int32_t), ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_pathcost, 0, cells * sizeof(float), ctx->stream));
+	ctx->cells = cells;
+	return PPX_OK;
+}
+
+// Derived grids (clearance from sqdist, occ8 from occupancy) after the device copies changed.
+int ppx_map_derive(ppx_ctx* ctx, const ppx_map_desc* desc, bool newSqdist, bool newOccupancy)
+{
+	size_t cells = (size_t)desc->rows * desc->cols;
+	ctx->desc = *desc;
+	int threads = 256;
+	int blocks = (int)std::min<size_t>((cells + threads - 1) / threads, (size_t)ctx->num_sms * 8);
+	if (newSqdist) {
+		k_clearance<<<blocks, threads, 0, ctx->stream>>>(ctx->d_sqdist, ctx->d_clearance, cells, desc->resolution);
+		PPX_LAUNCHED(ctx);
+	}
+	if (newOccupancy) {
+		k_occupied<<<blocks, threads, 0, ctx->stream>>>(ctx->d_occupancy, ctx->d_occ8, cells);
+		PPX_LAUNCHED(ctx);
+	}
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	ctx->has_map = true;
+	return PPX_OK;
+}
+
 extern "C" {
 
 int ppx_version(void) { return PPX_VERSION; }
@@ -219,52 +270,17 @@ int ppx_map_upload(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* sqdist
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, desc->rows > 0 && desc->cols > 0, "map size must be positive");
 	PPX_REQUIRE(ctx, desc->resolution > 0.0f, "resolution must be positive");
-	PPX_CUDA(ctx, cudaSetDevice(ctx->device));
 	size_t cells = (size_t)desc->rows * desc->cols;
-	if (cells != ctx->cells) {
-		PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-		cudaFree(ctx->d_sqdist);
-		cudaFree(ctx->d_occupancy);
-		cudaFree(ctx->d_pathcost);
-		cudaFree(ctx->d_clearance);
-		cudaFree(ctx->d_occ8);
-		ctx->d_occ8 = nullptr;
-		ctx->d_sqdist = ctx->d_occupancy = nullptr;
-		ctx->d_pathcost = ctx->d_clearance = nullptr;
-		PPX_CUDA(ctx, cudaMalloc(&ctx->d_sqdist, cells * sizeof(int32_t)));
-		PPX_CUDA(ctx, cudaMalloc(&ctx->d_occupancy, cells * sizeof(int32_t)));
-		PPX_CUDA(ctx, cudaMalloc(&ctx->d_pathcost, cells * sizeof(float)));
-		PPX_CUDA(ctx, cudaMalloc(&ctx->d_clearance, cells * sizeof(float)));
-		PPX_CUDA(ctx, cudaMalloc(&ctx->d_occ8, cells));
-		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_occ8, 0, cells, ctx->stream));
-		// defaults of an empty map: INT_MAX distance (gvd.cpp:22), free cells (-1), zero potential
-		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_occupancy, 0xff, cells * sizeof(int32_t), ctx->stream));
-		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_pathcost, 0, cells * sizeof(float), ctx->stream));
-		ctx->cells = cells;
-		ctx->has_map = false;
-		if (!sqdist)
-			return ppx_fail(ctx, PPX_ERR_INVALID, "first upload of a map of this size needs sqdist");
-	}
-	ctx->desc = *desc;
-	if (sqdist) {
+	if (cells != ctx->cells && !sqdist)
+		return ppx_fail(ctx, PPX_ERR_INVALID, "first upload of a map of this size needs sqdist");
+	PPX_CHECK(ppx_map_alloc(ctx, desc));
+	if (sqdist)
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_sqdist, sqdist, cells * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
-		int threads = 256;
-		int blocks = (int)std::min<size_t>((cells + threads - 1) / threads, (size_t)ctx->num_sms * 8);
-		k_clearance<<<blocks, threads, 0, ctx->stream>>>(ctx->d_sqdist, ctx->d_clearance, cells, desc->resolution);
-		PPX_LAUNCHED(ctx);
-	}
-	if (occupancy) {
+	if (occupancy)
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_occupancy, occupancy, cells * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
-		int threads = 256;
-		int blocks = (int)std::min<size_t>((cells + threads - 1) / threads, (size_t)ctx->num_sms * 8);
-		k_occupied<<<blocks, threads, 0, ctx->stream>>>(ctx->d_occupancy, ctx->d_occ8, cells);
-		PPX_LAUNCHED(ctx);
-	}
 	if (pathcost)
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_pathcost, pathcost, cells * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-	ctx->has_map = true;
-	return PPX_OK;
+	return ppx_map_derive(ctx, desc, sqdist != nullptr, occupancy != nullptr);
 }
 
 } // extern "C"

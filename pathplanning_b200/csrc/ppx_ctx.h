@@ -74,6 +74,8 @@ struct ppx_ctx {
 int ppx_fail(ppx_ctx* ctx, int code, const char* fmt, ...);
 int ppx_scratch(ppx_ctx* ctx, int slot, size_t bytes, void** out);
 int ppx_pipeline_init(ppx_ctx* ctx);
+int ppx_map_alloc(ppx_ctx* ctx, const ppx_map_desc* desc);
+int ppx_map_derive(ppx_ctx* ctx, const ppx_map_desc* desc, bool newSqdist, bool newOccupancy);
 
 #define PPX_CUDA(ctx, call)                                                                           \
 	do {                                                                                              \

@@ -64,6 +64,7 @@ _SIGS = {
     "ppx_memcpy_h2d": (C.c_int, [_p, _p, _p, C.c_uint64]),
     "ppx_memcpy_d2h": (C.c_int, [_p, _p, _p, C.c_uint64]),
     "ppx_map_upload": (C.c_int, [_p, C.POINTER(MapDescC), _p, _p, _p]),
+    "ppx_map_build": (C.c_int, [_p, C.POINTER(MapDescC), _p, _p, _p]),
     "ppx_is_state_valid": (C.c_int, [_p, _i64, _p, C.POINTER(ValidatorParamsC), _p]),
     "ppx_check_edges_rs": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p]),
     "ppx_check_edges_rs_audit": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p, _p, _p]),
