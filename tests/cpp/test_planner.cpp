@@ -1,0 +1,124 @@
+// C++ host-side tests of include/ppx_planner.hpp, written after the reference's own tests
+// (planner/tests/test_hybrid_a_star.cpp:9-37, test_reeds_shepp.cpp:7-27) plus a validator case.
+// Built by tests/cpp/Makefile against pathplanning_b200/libppx.so; needs a CUDA device to RUN
+// (tests/test_cpp_host.py runs it under the gpu marker and only compiles/links it on CPU).
+#include <cassert>
+#include <cstdio>
+#include <cstdlib>
+#include "ppx_planner.hpp"
+
+#define CHECK(cond)                                                              \
+	do {                                                                         \
+		if (!(cond)) {                                                           \
+			std::fprintf(stderr, "%s:%d: CHECK failed: %s\n", __FILE__, __LINE__, #cond); \
+			std::exit(1);                                                        \
+		}                                                                        \
+	} while (0)
+
+namespace Planner {
+
+// test_hybrid_a_star.cpp:9-37: empty 20 m x 20 m map at 0.1 m, default parameters
+void TestHybridAStar(const Ref<Device>& dev)
+{
+	Pose2d lb(-10, -10, -M_PI), ub(10, 10, M_PI);
+	auto map = std::make_shared<OccupancyMap>(dev, 0.1f, 20.0f, 20.0f, lb, ub);
+	auto stateValidator = std::make_shared<StateValidatorOccupancyMap>(map);
+
+	HybridAStar hybridAStar;
+	CHECK(hybridAStar.Initialize(stateValidator));
+
+	Pose2d start = { 0.0, 0.0, 0.0 };
+	Pose2d goal = { 8.0, 8.0, 0.78 };
+	hybridAStar.SetInitState(start);
+	hybridAStar.SetGoalState(goal);
+
+	CHECK(hybridAStar.SearchPath() == Status::Success);
+	std::vector<Pose2d> path = hybridAStar.GetPath();
+
+	CHECK(!path.empty());
+	double spatialTolerance = 1e-1;
+	double angularTolerance = 5 * M_PI / 180;
+	CHECK(std::hypot(path.front().x() - start.x(), path.front().y() - start.y()) < spatialTolerance);
+	CHECK(std::fabs(path.front().theta - start.theta) < angularTolerance);
+	CHECK(std::hypot(path.back().x() - goal.x(), path.back().y() - goal.y()) < spatialTolerance);
+	CHECK(std::fabs(path.back().theta - goal.theta) < angularTolerance);
+	CHECK(hybridAStar.GetGraphSearchOptimalCost() >= std::hypot(8.0, 8.0) - 1e-9);
+	std::printf("hybrid A*: %zu states, cost %.4f, %d expansions\n", path.size(), hybridAStar.GetGraphSearchOptimalCost(),
+		hybridAStar.GetStats().numExpandedNodes);
+
+	// a wall across the map with no gap: the goal becomes unreachable -> Status::Failure
+	int r0, c0;
+	for (double y = -10.0; y < 10.0; y += 0.05) {
+		if (map->WorldPositionToGridCell(4.0, y, r0, c0))
+			map->SetOccupied(r0, c0, 1);
+	}
+	CHECK(hybridAStar.Initialize(stateValidator)); // re-uploads the edited map
+	CHECK(hybridAStar.SearchPath() == Status::Failure);
+	CHECK(hybridAStar.GetPath().empty());
+
+	// batch of queries on the walled map: left-side goals stay reachable
+	std::vector<Status> st;
+	std::vector<std::vector<Pose2d>> paths;
+	std::vector<double> costs;
+	hybridAStar.SearchPathBatch({ start, start, start }, { Pose2d(-6, 5, 1.0), goal, Pose2d(0, -7, -2.0) }, { 1, 2, 3 }, st, paths, costs);
+	CHECK(st[0] == Status::Success && st[1] == Status::Failure && st[2] == Status::Success);
+	CHECK(std::isinf(costs[1]) && costs[0] > 0 && costs[2] > 0);
+}
+
+// test_reeds_shepp.cpp:7-27: the constructed path leads to the final state
+void TestReedsShepp(const Ref<Device>& dev, const Pose2d& start, const Pose2d& goal)
+{
+	PathConnectionReedsShepp connection(dev, 1.0);
+	auto path = connection.Connect(start, goal);
+	CHECK(path->GetWord() >= 0);
+	double tol = 1e-6;
+	Pose2d end = path->GetFinalState();
+	CHECK(std::abs(end.x() - goal.x()) < tol);
+	CHECK(std::abs(end.y() - goal.y()) < tol);
+	CHECK(std::abs(end.theta - goal.theta) < tol * M_PI / 180.0);
+	CHECK(path->GetLength() >= std::hypot(goal.x() - start.x(), goal.y() - start.y()) - 1e-9);
+}
+
+// StateValidatorOccupancyMap on a map with one obstacle: IsStateValid / IsPathValid / last ratio
+void TestValidator(const Ref<Device>& dev)
+{
+	Pose2d lb(-10, -10, -M_PI), ub(10, 10, M_PI);
+	auto map = std::make_shared<OccupancyMap>(dev, 0.1f, 20.0f, 20.0f, lb, ub);
+	int r, c;
+	CHECK(map->WorldPositionToGridCell(5.0, 0.0, r, c));
+	map->SetOccupied(r, c);
+	map->Update();
+	CHECK(map->GetDistanceToNearestObstacle(r, c) == 0.0f);
+	CHECK(std::fabs(map->GetDistanceToNearestObstacle(r - 30, c) - 3.0f) < 1e-5f);
+	StateValidatorOccupancyMap validator(map);
+	validator.minSafeRadius = 1.0f;
+	CHECK(validator.IsStateValid(Pose2d(0, 0, 0)));
+	CHECK(!validator.IsStateValid(Pose2d(4.5, 0.2, 0)));
+	CHECK(!validator.IsStateValid(Pose2d(10.5, 0, 0))); // out of bounds
+	PathConnectionReedsShepp connection(dev, 2.0);
+	auto through = connection.Connect(Pose2d(0, 0, 0), Pose2d(9, 0, 0)); // straight through the obstacle
+	float last = -1.0f;
+	CHECK(!validator.IsPathValid(*through, &last));
+	CHECK(last > 0.3f && last < 0.45f); // stops about 1 m before x = 5 on a 9 m path
+	auto clear = connection.Connect(Pose2d(0, 3, 0), Pose2d(9, 3, 0));
+	CHECK(validator.IsPathValid(*clear, &last) && last == 1.0f);
+	// the obstacle heuristic: behind the obstacle the cost-to-go is at least the Euclidean distance
+	ObstaclesHeuristic h(map, 1.0, 1.0);
+	h.Update(Pose2d(9, 0, 0));
+	CHECK(h.GetHeuristicValue(Pose2d(0, 0, 0)) >= 9.0 - 1e-9);
+	CHECK(h.GetHeuristicValue(Pose2d(9, 0, 0)) == 0.0);
+}
+
+}
+
+int main()
+{
+	auto dev = std::make_shared<Planner::Device>(0);
+	Planner::TestReedsShepp(dev, Planner::Pose2d(0, 0, 0), Planner::Pose2d(5, 5, M_PI / 2));
+	Planner::TestReedsShepp(dev, Planner::Pose2d(1, -2, 0.3), Planner::Pose2d(-3, 0.5, -2.0));
+	Planner::TestReedsShepp(dev, Planner::Pose2d(0, 0, 0), Planner::Pose2d(0.1, 1.5, M_PI));
+	Planner::TestValidator(dev);
+	Planner::TestHybridAStar(dev);
+	std::printf("test_planner: all checks passed\n");
+	return 0;
+}
