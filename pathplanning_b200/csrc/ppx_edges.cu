@@ -57,7 +57,7 @@ struct SmemLen {
 constexpr int kGrab = 128;
 constexpr int kCheckCtasPerSm = 6; // 80 registers, no spills; 24 warps/SM measured best (r1g sweep)
 constexpr int kParkBatch = 8;
-constexpr int kRefillBatch = 4;
+constexpr int kRefillBatch = 8;
 
 struct AuditOut {
 	unsigned long long certified; // samples decided by the filter

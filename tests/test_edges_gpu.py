@@ -188,14 +188,14 @@ def test_rs_filter_ab_exact(ctx, c3_edges, radius, step):
 
 def test_rs_filter_audit(ctx, c3_edges):
     """Every certified sample re-evaluated exactly on the device: same cell, and the FP32 position
-    error stays far below the certification margin kCellEps = 2.5e-3 cells."""
+    error stays far below the certification margin kCellEps = 1e-3 cells."""
     edges, rr = c3_edges
     a = ctx.check_edges_rs_audit(edges, 2.0, pp.ValidatorParams(1.0, 0.1))
     assert np.array_equal(a["valid"], rr["valid"])
     assert a["cell_mismatch"] == 0
     assert a["certified"] + a["parked"] == int(a["samples"].sum())
     assert a["parked"] < 0.05 * a["certified"]
-    assert a["max_dev_cells"] < 2.5e-3 / 4, a["max_dev_cells"]
+    assert a["max_dev_cells"] < 1e-3 / 4, a["max_dev_cells"]
     print("audit:", {k: a[k] for k in ("certified", "parked", "cell_mismatch", "max_dev_cells")})
 
 
