@@ -88,6 +88,10 @@ struct RSFastLane {
 	bool verdict;
 	float last;
 	float px, py; // last evaluated fast position (audit)
+	// cached constants of motion m (load_motion)
+	double lm;
+	float ml, sgnAdv, sgnTurn;
+	bool have, straight;
 
 	PPX_HD int steer(int i) const { return (code >> (4 * i)) & 3; }
 	PPX_HD int dir(int i) const { return (code >> (4 * i + 2)) & 3; }
@@ -118,6 +122,7 @@ struct RSFastLane {
 		odd |= !(fabs(ux) < 1e6) || !(fabs(uy) < 1e6) || !(fabs(th) < 1e4);
 		odd |= !(pathLength > 0.0) || !(pathLength * fm.inv_resd < (double)kFastMaxCells) || !(r > 1e-3) || !fm.enabled;
 		slowOnly = odd;
+		load_motion(L, r);
 		if (odd) {
 			rowb = colb = 0;
 			kx = ky = thK = 0.0f;
@@ -132,26 +137,29 @@ struct RSFastLane {
 		thK = (float)th;
 	}
 
+	// Motion m's constants, cached between knot commits (the motion changes ~once per 3 micro-steps).
+	PPX_HD void load_motion(const LenStore& L, double r)
+	{
+		have = valid(L, m);
+		lm = have ? L.get(m) * r : 0.0; // motionLength, path_reeds_shepp.cpp:25
+		ml = (float)lm;
+		int st = steer(m), dr = dir(m);
+		straight = (st == 1) || !have;
+		sgnAdv = dr == 1 ? -1.0f : 1.0f; // Backward
+		sgnTurn = st == 2 ? -1.0f : 1.0f; // Right
+	}
+
 	// One micro-step: advance along motion m towards the current sample target.  Returns
 	//   0: knot committed (or nothing to do), 1: a sample position (px, py) is ready.
 	PPX_HD int advance(const LenStore& L, double r, float inv_r, float rc, float inv_res)
 	{
-		bool have = valid(L, m);
-		double lm = have ? L.get(m) * r : 0.0; // motionLength, path_reeds_shepp.cpp:25
-		float ml = (float)lm;
 		float rem = (float)(length - lenAcc);
 		bool full = have && rem > ml;
-		float adv = have ? fminf(rem, ml) : 0.0f;
-		int st = steer(m), dr = dir(m);
-		if (dr == 1)
-			adv = -adv;
-		bool straight = (st == 1) || !have;
-		float a = adv * inv_r; // signed turn angle of the (partial) motion
-		if (st == 2)
-			a = -a;
+		float adv = sgnAdv * fminf(rem, ml); // ml == 0 without a motion
+		float a = adv * inv_r * sgnTurn; // signed heading change of the (partial) motion
 		float phi = 0.5f * a;
 		float ang = fast_wrap(straight ? thK : thK + phi);
-		float chord = (2.0f * rc) * PPX_FSIN(straight ? 0.0f : (st == 2 ? -phi : phi));
+		float chord = (2.0f * rc) * PPX_FSIN(sgnTurn * phi);
 		float Lc = straight ? adv * inv_res : chord;
 		px = kx + Lc * PPX_FCOS(ang);
 		py = ky + Lc * PPX_FSIN(ang);
@@ -163,6 +171,7 @@ struct RSFastLane {
 			thK = fast_wrap(thK + a);
 		lenAcc += lm;
 		m++;
+		load_motion(L, r);
 		return 0;
 	}
 
