@@ -323,6 +323,30 @@ def hybrid_section(args, rank, world, local_rank, stream):
         "solved": solved, "expansions": expanded, "gather_ms": gather_ms, "gpu_launches": int(launches),
         "note": "smoothing (SURVEY N2) is not part of this figure, neither here nor in the CPU figure",
     }
+    if world > 1:
+        # weak-scaling companion: every rank searches all nq queries (4096 per GPU); a strong-scaled shard of
+        # 4096/N queries is bounded below by its longest single query (a chain of ~7000 dependent expansions)
+        d_sw = torch.from_numpy(starts.copy()).to(dev)
+        d_gw = torch.from_numpy(goals.copy()).to(dev)
+        d_seedw = torch.from_numpy(seeds.astype(np.int64)).to(dev)
+        d_resw = torch.zeros(nq * HYBRID_RESULT.itemsize, dtype=torch.uint8, device=dev)
+
+        def run_weak():
+            rc = ppx.ppx_hybrid_search_dev(planner.handle, nq, d_sw.data_ptr(), d_gw.data_ptr(), d_seedw.data_ptr(),
+                                           ctypes.byref(lim), d_resw.data_ptr(), None, None)
+            assert rc == 0, ppx.ppx_last_error(ctx.handle)
+
+        run_weak()
+        barrier()
+        w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0.record(stream)
+        run_weak()
+        w1.record(stream)
+        barrier()
+        tw = torch.tensor([w0.elapsed_time(w1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+        section["weak"] = {"queries_per_gpu": nq, "value": world * nq / (float(tw.item()) * 1e-3), "unit": "plans/s",
+                           "ms": float(tw.item())}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             section["cpu_baseline"] = run_reference_hybrid(starts, goals, seeds, args.cpu_plans_per_core)
@@ -358,6 +382,9 @@ def ours_main(args):
 
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # stdout carries exactly one JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION) off it
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = pp.Context(local_rank)
     # A dedicated (non-null) stream shared by torch and the context: ppx_ctx_set_stream(NULL) means
@@ -374,7 +401,12 @@ def ours_main(args):
     sq = synth.exact_sqdist(occ)
     rows, cols, origin = synth.map_geometry(cfg["lb"], cfg["ub"], cfg["resolution"])
     desc = pp.MapDesc(rows=rows, cols=cols, resolution=cfg["resolution"], world_origin=origin, lb=cfg["lb"], ub=cfg["ub"])
-    ctx.upload_map(desc, sq, occ, None)
+    # the obstacle distance map is built on the device (ppx_map_build) and checked against the host EDT
+    ctx.build_map(desc, occ)
+    t0 = time.perf_counter()
+    sq_dev = ctx.build_map(desc, occ)
+    map_build_ms = (time.perf_counter() - t0) * 1e3
+    assert np.array_equal(sq_dev, sq), "device distance map differs from the exact EDT"
     vp = pp.ValidatorParams(RADIUS, MIN_STEP).to_c()
     cp = pp.RSCostParams(RMIN).to_c()
 
@@ -519,6 +551,8 @@ def ours_main(args):
                          "traffic": traffic, "peak_source": peak_src, "bytes_per_edge": bytes_per_edge,
                          "note": "FP64-issue / dependent-L2-latency bound, not HBM bound (DESIGN.md)"},
             "cpu_baseline": cpu_baseline,
+            "map_build": {"ms": map_build_ms, "cells": int(rows * cols),
+                          "what": "ppx_map_build host call: H2D occupancy + device EDT + derived grids + D2H distance map"},
             "e2e": {"value": e2e_value, "unit": "edges/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps},
             "gpu_launches": launches,
