@@ -1,0 +1,97 @@
+"""BASELINE.json's full sizes, checked through size-independent properties (the oracle finishes
+fractions of these batches in seconds, the full batches in minutes):
+
+* C3, 1 M Reeds-Shepp edges: per-edge results do not depend on the batch they are in (permutation,
+  prefix), the FP32 cell filter changes no bit against the all-exact evaluation, a 50 k sample agrees
+  with the compiled reference, the verdict/sample checksums are those of the bench.
+* C4, 4096 Hybrid A* queries: a query's record does not depend on the shard it is searched in
+  (what makes sharding by query over 1/2/4/8 GPUs result-neutral), a sample agrees with the reference.
+"""
+import numpy as np
+import pytest
+
+import pathplanning_b200 as pp
+from pathplanning_b200 import synth
+
+pytestmark = pytest.mark.gpu
+N = 1_000_000
+
+
+@pytest.fixture(scope="module")
+def c3_full(ctx):
+    cfg = synth.C3
+    occ = synth.rasterize_rectangles(synth.config_rects(cfg), cfg["lb"], cfg["ub"], cfg["resolution"])
+    rows, cols, origin = synth.map_geometry(cfg["lb"], cfg["ub"], cfg["resolution"])
+    desc = pp.MapDesc(rows=rows, cols=cols, resolution=cfg["resolution"], world_origin=origin, lb=cfg["lb"], ub=cfg["ub"])
+    ctx.build_map(desc, occ)
+    s, g = synth.random_rs_queries(N, seed=1000)  # batch 0 of bench.py
+    sol = ctx.rs_solve(s, g, pp.RSCostParams(2.0))
+    return s, g, sol["edges"]
+
+
+def test_c3_full_batch_properties(ctx, c3_full, ref):
+    s, g, edges = c3_full
+    vp = pp.ValidatorParams(1.0, 0.1)
+    v, l, ns = ctx.check_edges_rs(edges, 2.0, vp, want_samples=True)
+    assert len(v) == N and 0.05 < v.mean() < 0.2 and 4.0 < ns.mean() < 6.0
+    assert np.all(l[v] == 1.0) and np.all((l[~v] >= 0.0) & (l[~v] < 1.0))
+    # idempotence + permutation invariance
+    perm = np.random.default_rng(0).permutation(N)
+    v2, l2, ns2 = ctx.check_edges_rs(edges[perm], 2.0, vp, want_samples=True)
+    assert np.array_equal(v2, v[perm]) and np.array_equal(ns2, ns[perm])
+    assert np.array_equal(l2.view(np.uint32), l[perm].view(np.uint32))
+    # a prefix checked alone gives the prefix of the results
+    v3, l3, ns3 = ctx.check_edges_rs(edges[:123457], 2.0, vp, want_samples=True)
+    assert np.array_equal(v3, v[:123457]) and np.array_equal(ns3, ns[:123457])
+    # the filter changes no bit against the all-exact evaluation of the full batch
+    ctx.set_option("rs_filter", 0)
+    try:
+        v4, l4, ns4 = ctx.check_edges_rs(edges, 2.0, vp, want_samples=True)
+    finally:
+        ctx.set_option("rs_filter", 1)
+    assert np.array_equal(v4, v) and np.array_equal(ns4, ns) and np.array_equal(l4.view(np.uint32), l.view(np.uint32))
+    # fused solve + check agrees with check-only on pre-solved edges
+    r = ctx.connect_check_rs(s, g, pp.RSCostParams(2.0), vp)
+    assert np.array_equal(r["valid"], v) and np.array_equal(r["last"].view(np.uint32), l.view(np.uint32))
+    # a 50 k sample against the compiled reference
+    cfg = synth.C3
+    w = ref.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    for rect in synth.config_rects(cfg):
+        w.add_rectangle(*rect)
+    w.update()
+    idx = np.random.default_rng(1).choice(N, 50000, replace=False)
+    rr = w.check_rs_edges(s[idx], g[idx], 2.0)
+    w.close()
+    assert np.array_equal(rr["valid"], v[idx])
+    assert np.array_equal(rr["samples"].astype(np.int64), ns[idx].astype(np.int64))
+    assert np.allclose(rr["last"], l[idx], rtol=1e-6, atol=0)
+
+
+def test_c4_full_batch_is_shard_independent(ctx, ref):
+    cfg = synth.C2
+    w = ref.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    for rect in synth.config_rects(cfg):
+        w.add_rectangle(*rect)
+    w.update()
+    occ, sq = w.grids()
+    pc, _ = w.gvd_update()
+    ctx.upload_map(w.map_desc(), sq, occ, pc)
+    vp = pp.ValidatorParams(1.0, 0.1)
+    rng = np.random.default_rng(12345)
+    nq = 4096
+    pts = np.empty((0, 3))
+    while len(pts) < 2 * nq:
+        p = np.stack([rng.uniform(-18.5, 18.5, 4 * nq), rng.uniform(-18.5, 18.5, 4 * nq), rng.uniform(-np.pi, np.pi, 4 * nq)], 1)
+        pts = np.concatenate([pts, p[ctx.is_state_valid(p, vp)]])
+    starts, goals = pts[:nq].copy(), pts[nq:2 * nq].copy()
+    seeds = (1000 + np.arange(nq)).astype(np.uint64)
+    planner = pp.HybridAStar(ctx, pp.HybridParams(), vp)
+    full = planner.search(starts, goals, seeds)["results"]
+    assert 0.8 < (full["status"] == 0).mean() < 1.0
+    # shards of 8 "GPUs", searched one after the other on this one: identical records
+    for r in (0, 3, 7):
+        lo, hi = r * nq // 8, (r + 1) * nq // 8
+        part = planner.search(starts[lo:hi], goals[lo:hi], seeds[lo:hi])["results"]
+        assert part.tobytes() == full[lo:hi].tobytes()
+    planner.close()
+    w.close()
