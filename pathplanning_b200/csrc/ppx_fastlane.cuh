@@ -329,4 +329,38 @@ PPX_HD bool csteer_is_path_valid_filtered(const MapDev& map, const FastMap& fm, 
 	return ok;
 }
 
+
+// rs_is_path_valid (IsPathValid on one Reeds-Shepp path, sequentially) through the same filter: the
+// lane machine run by a single thread, uncertified samples evaluated exactly in place.
+struct SegLen {
+	const double* p;
+	PPX_HD double get(int i) const { return p[i]; }
+};
+
+PPX_HD bool rs_is_path_valid_filtered(const MapDev& map, const FastMap& fm, const Pose& start, const RSSeg& seg, double r,
+	float minSafeRadius, float minStep, float* last, unsigned* samples)
+{
+	SegLen L { seg.len };
+	RSFastLane<SegLen> lane;
+	lane.begin(L, fm, map, start, seg.code, r);
+	const float inv_r = (float)(1.0 / r), rc = (float)(r * fm.inv_resd);
+	while (true) {
+		int rcode = 2;
+		if (!lane.slowOnly) {
+			if (!lane.advance(L, r, inv_r, rc, fm.inv_res))
+				continue;
+			rcode = lane.sample(map, fm, minSafeRadius, minStep);
+		}
+		if (rcode == 2) {
+			double ex, ey;
+			if (rs_exact_sample(lane, map, start, seg, r, minSafeRadius, minStep, &ex, &ey))
+				break;
+		} else if (rcode == 1)
+			break;
+	}
+	*last = lane.last;
+	if (samples) *samples = lane.ns;
+	return lane.verdict;
+}
+
 }

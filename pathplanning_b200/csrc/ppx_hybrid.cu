@@ -62,6 +62,7 @@ struct ppx_hybrid {
 
 namespace {
 
+constexpr int kGenSlots = 3; // children sets per warp in shared memory (see k_hybrid_search)
 constexpr int kSearchWarps = 4; // warps (queries) per CTA
 
 // NonHolonomicHeuristic::Build, heuristics.cpp:62-73: one Reeds-Shepp solve per table entry
@@ -204,9 +205,10 @@ __device__ __noinline__ double hy_heuristic(const HybridDev& P, const MapDev& ma
 {
 	return combined_heuristic(P, map, wf, goal, s);
 }
-__device__ __noinline__ void hy_rs_child(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out)
+__device__ __noinline__ void hy_rs_child(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out,
+	const FastMap* fm)
 {
-	rs_child_from(P, map, parent, sol, out);
+	rs_child_from(P, map, parent, sol, out, fm);
 }
 __device__ __noinline__ void hy_rs_solve_warp(const HybridDev& P, const Pose& parent, const Pose& goal, RSSolution& sol)
 {
@@ -282,8 +284,15 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const Searc
 	ppx_hybrid_limits limits, ppx_hybrid_result* __restrict__ results, ppx_hybrid_path_state* __restrict__ paths,
 	ppx_hybrid_log_entry* __restrict__ logs, unsigned long long* __restrict__ queue, const int* __restrict__ order)
 {
-	__shared__ Child s_child[kSearchWarps][kMaxChildren];
-	__shared__ double s_h[kSearchWarps][kMaxChildren];
+	// Children of up to kGenSlots nodes per warp: slot 2 holds the children of the node being expanded when
+	// they had to be generated now, slots 0/1 cache the children of frontier nodes generated AHEAD of their
+	// expansion (children are a pure function of the node; only the Reeds-Shepp shot depends on the RNG order).
+	// A generation pass therefore fills up to 30 lanes (3 nodes x 10 primitives) instead of 10, and an
+	// expansion whose node is cached is pop + commit only.
+	__shared__ Child s_child[kSearchWarps][kGenSlots][kMaxChildren - 1];
+	__shared__ double s_h[kSearchWarps][kGenSlots][kMaxChildren - 1];
+	__shared__ Child s_rs[kSearchWarps];
+	__shared__ double s_rsh[kSearchWarps];
 	const HybridDev& P = consts->P;
 	const MapDev& map = consts->map;
 	const unsigned lane = threadIdx.x & 31;
@@ -291,8 +300,8 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const Searc
 	const size_t gwarp = (size_t)blockIdx.x * kSearchWarps + wib;
 	const SearchWs W = ws_carve(slabs + gwarp * L.bytes, L);
 	const size_t cells = (size_t)map.rows * map.cols;
-	Child* myChildren = s_child[wib];
-	double* myH = s_h[wib];
+	const int nCs = 2 * P.numDeltas; // constant-steer children per node
+	const int perPass = min(kGenSlots, 32 / nCs); // nodes one generation pass can take
 
 	while (true) {
 		long long q = 0;
@@ -318,9 +327,13 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const Searc
 		__syncwarp();
 		int status = __shfl_sync(0xffffffffu, S.status, 0);
 		ppx_hybrid_log_entry* log = (logs && limits.max_log > 0) ? logs + (size_t)q * limits.max_log : nullptr;
+		int cache0 = -1, cache1 = -1; // nodes whose children sit in slots 0 / 1 (warp-uniform)
 
 		while (status == PPX_SEARCH_RUNNING) {
 			int n = -1;
+#ifdef PPX_SEARCH_STATS
+			long long tk0 = clock64();
+#endif
 			if (lane == 0) {
 				if (limits.max_expansions > 0 && S.nExpanded >= limits.max_expansions)
 					S.status = PPX_ERR_LIMIT;
@@ -350,30 +363,112 @@ __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const Searc
 				S.nRsAttempts += want;
 			}
 			want = __shfl_sync(0xffffffffu, want, 0);
-			const int nslots = 2 * P.numDeltas + want;
+#ifdef PPX_SEARCH_STATS
+			long long tk1 = clock64();
+#endif
 			RSSolution sol;
 			if (want) // warp-uniform: the 48 Reeds-Shepp words are evaluated by the 32 lanes
 				hy_rs_solve_warp(P, parent, goal, sol);
-			if ((int)lane < nslots) {
+#ifdef PPX_SEARCH_STATS
+			long long tk2 = clock64();
+#endif
+			const int slotP = cache0 == n ? 0 : (cache1 == n ? 1 : 2);
+#ifdef PPX_SEARCH_STATS
+			if (lane == 0) atomicAdd(queue + 8 + (slotP == 2 ? 0 : 1), 1ull);
+#endif
+			if (slotP == 2) {
+				// generation pass: node n (slot 2) and, if there are lanes to spare, the two best frontier nodes
+				int candA = -1, candB = -1;
+				if (perPass >= 2 && lane == 0) {
+					if (S.heapSize > 0)
+						candA = (int)W.heapNode[0];
+					if (perPass >= 3 && S.heapSize > 1) {
+						int i = 1;
+						if (S.heapSize > 2 && heap_before(W.heapF[2], W.heapSeq[2], W.heapF[1], W.heapSeq[1]))
+							i = 2;
+						candB = (int)W.heapNode[i];
+					}
+					if (candA >= 0 && (W.meta[candA] & 0x100u))
+						candA = -1;
+					if (candB >= 0 && (W.meta[candB] & 0x100u))
+						candB = -1;
+				}
+				candA = __shfl_sync(0xffffffffu, candA, 0);
+				candB = __shfl_sync(0xffffffffu, candB, 0);
+				// keep cached candidates where they are, give the others the remaining slots
+				const bool keep0 = cache0 >= 0 && (cache0 == candA || cache0 == candB);
+				const bool keep1 = cache1 >= 0 && (cache1 == candA || cache1 == candB);
+				int gen0 = -1, gen1 = -1; // nodes to generate into slot 0 / slot 1
+				if (candA >= 0 && candA != cache0 && candA != cache1) {
+					if (!keep0) gen0 = candA;
+					else if (!keep1) gen1 = candA;
+				}
+				if (candB >= 0 && candB != cache0 && candB != cache1 && candB != candA) {
+					if (!keep0 && gen0 < 0) gen0 = candB;
+					else if (!keep1 && gen1 < 0) gen1 = candB;
+				}
+				if (!keep0) cache0 = gen0;
+				if (!keep1) cache1 = gen1;
+#ifdef PPX_SEARCH_STATS
+				if (lane == 0) atomicAdd(queue + 10, (unsigned long long)((gen0 >= 0) + (gen1 >= 0)));
+#endif
+				const int t = (int)lane / nCs, cslot = (int)lane % nCs;
+				const int node = t == 0 ? n : (t == 1 ? (gen0 >= 0 ? gen0 : gen1) : (gen0 >= 0 ? gen1 : -1));
+				const int slot = t == 0 ? 2 : (node == gen0 ? 0 : 1);
+				if (t < perPass && node >= 0) {
+					Pose par = parent;
+					Key3 key = pk;
+					if (t > 0) {
+						par = { W.pose[3 * node], W.pose[3 * node + 1], W.pose[3 * node + 2] };
+						key = discretize_pose(P, par);
+					}
+					Child c;
+					csteer_child(P, map, par, key, cslot >> 1, cslot & 1, c, &consts->fm);
+					double h = 0.0;
+					if (c.ok)
+						h = hy_heuristic(P, map, wf, goal, c.pose);
+					s_child[wib][slot][cslot] = c;
+					s_h[wib][slot][cslot] = h;
+				}
+			}
+#ifdef PPX_SEARCH_STATS
+			__syncwarp();
+			long long tk3 = clock64();
+#endif
+			if (want && lane == 0) {
 				Child c;
-				if ((int)lane < 2 * P.numDeltas)
-					csteer_child(P, map, parent, pk, (int)lane >> 1, (int)lane & 1, c, &consts->fm);
-				else
-					hy_rs_child(P, map, parent, sol, c);
-				double h = 0.0;
-				if (c.ok)
-					h = hy_heuristic(P, map, wf, goal, c.pose);
-				myChildren[lane] = c;
-				myH[lane] = h;
+				hy_rs_child(P, map, parent, sol, c, &consts->fm);
+				s_rsh[wib] = c.ok ? hy_heuristic(P, map, wf, goal, c.pose) : 0.0;
+				s_rs[wib] = c;
 			}
 			__syncwarp();
+#ifdef PPX_SEARCH_STATS
+			long long tk4 = clock64();
+#endif
 			if (lane == 0) {
 				const double parentG = W.g[n];
-				for (int s = 0; s < nslots && S.status == PPX_SEARCH_RUNNING; s++)
-					if (myChildren[s].ok)
-						consume_child(W, S, n, parentG, myChildren[s], myH[s], s);
+				const Child* kids = s_child[wib][slotP];
+				const double* kidsH = s_h[wib][slotP];
+				for (int sl = 0; sl < nCs && S.status == PPX_SEARCH_RUNNING; sl++)
+					if (kids[sl].ok)
+						consume_child(W, S, n, parentG, kids[sl], kidsH[sl], sl);
+				if (want && S.status == PPX_SEARCH_RUNNING && s_rs[wib].ok)
+					consume_child(W, S, n, parentG, s_rs[wib], s_rsh[wib], nCs);
 			}
 			__syncwarp();
+			if (slotP == 0) cache0 = -1;
+			if (slotP == 1) cache1 = -1;
+#ifdef PPX_SEARCH_STATS
+			if (lane == 0) {
+				long long tk5 = clock64();
+				atomicAdd(queue + 11, (unsigned long long)(tk1 - tk0));
+				atomicAdd(queue + 12, (unsigned long long)(tk2 - tk1));
+				atomicAdd(queue + 13, (unsigned long long)(tk3 - tk2));
+				atomicAdd(queue + 14, (unsigned long long)(tk4 - tk3));
+				atomicAdd(queue + 15, (unsigned long long)(tk5 - tk4));
+				atomicAdd(queue + 7, (unsigned long long)want);
+			}
+#endif
 			status = __shfl_sync(0xffffffffu, S.status, 0);
 		}
 
@@ -496,6 +591,17 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 		(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, (char*)h->d_slabs, limits, d_results, d_paths, d_log, ctx->d_queue,
 		d_order);
 	PPX_LAUNCHED(ctx);
+#ifdef PPX_SEARCH_STATS
+	{
+		unsigned long long st[9];
+		cudaStreamSynchronize(ctx->stream);
+		cudaMemcpy(st, ctx->d_queue + 7, sizeof(st), cudaMemcpyDeviceToHost);
+		double ne = (double)(st[1] + st[2]);
+		fprintf(stderr, "search stats: %llu passes (misses), %llu hits, %llu generated ahead, %llu rs shots; cycles/expansion: pop+rng %.0f, rs solve %.0f, gen pass %.0f, rs child %.0f, commit %.0f\n",
+			st[1], st[2], st[3], st[0], st[4] / ne, st[5] / ne, st[6] / ne, st[7] / ne, st[8] / ne);
+		cudaMemset(ctx->d_queue + 7, 0, sizeof(st));
+	}
+#endif
 	return PPX_OK;
 }
 

@@ -191,7 +191,8 @@ PPX_HD Pose rs_interpolate(const Pose& start, const RSSeg& seg, double r, double
 }
 
 // StatePropagator::GetReedsSheppChild, hybrid_a_star.cpp:149-173
-PPX_HD void rs_child_from(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out);
+PPX_HD void rs_child_from(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out,
+	const FastMap* fm = nullptr);
 PPX_HD void rs_child(const HybridDev& P, const MapDev& map, const Pose& parent, const Pose& goal, Child& out)
 {
 	RSSolution sol;
@@ -200,14 +201,17 @@ PPX_HD void rs_child(const HybridDev& P, const MapDev& map, const Pose& parent, 
 }
 
 // ... given the optimal segment (the search kernel solves it with the whole warp, rs_solve_warp)
-PPX_HD void rs_child_from(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out)
+PPX_HD void rs_child_from(const HybridDev& P, const MapDev& map, const Pose& parent, const RSSolution& sol, Child& out,
+	const FastMap* fm)
 {
 	const double pathLength = sol.mLength * P.rmin; // PathSegment::GetLength(minTurningRadius)
 	out.kind = 1;
 	out.last = 1.0f;
 	out.length = pathLength;
 	float last;
-	if (!rs_is_path_valid(map, parent, sol.seg, P.rmin, P.minSafeRadius, P.minStep, &last, nullptr)) {
+	bool valid = fm ? rs_is_path_valid_filtered(map, *fm, parent, sol.seg, P.rmin, P.minSafeRadius, P.minStep, &last, nullptr)
+	                : rs_is_path_valid(map, parent, sol.seg, P.rmin, P.minSafeRadius, P.minStep, &last, nullptr);
+	if (!valid) {
 		out.ok = false;
 		return;
 	}
