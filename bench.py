@@ -38,6 +38,26 @@ RADIUS, MIN_STEP = 1.0, 0.1
 WORKLOAD = "C3: 1M Reeds-Shepp edges x disc footprint r=1.0m on 2000x2000 grid @0.1m (parking lot, p=0.5)"
 
 
+_REAL_STDOUT = None
+
+
+def _stdout_to_stderr():
+    """stdout must carry exactly ONE JSON line.  Libraries print there too (NCCL's version banner comes out of
+    ncclCommInitRank whatever NCCL_DEBUG_FILE says), so fd 1 points at stderr while the bench runs and the
+    JSON line is written to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def _emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -160,7 +180,7 @@ def reference_main(args):
         return
     import refapi
     if not refapi.available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libpp_ref.so not built"}))
+        _emit({"impl": "reference", "unavailable": "oracle/_ref/libpp_ref.so not built"})
         return
     value, ms, cores, sample = run_reference(args, per_core=args.cpu_edges_per_core)
     line = {
@@ -172,7 +192,7 @@ def reference_main(args):
         "e2e": {"value": value, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    _emit(line)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -256,7 +276,8 @@ def hybrid_section(args, rank, world, local_rank, stream):
     planner = pp.HybridAStar(ctx, pp.HybridParams(), pp.ValidatorParams(RADIUS, MIN_STEP))
     nq = args.hybrid_queries
     starts, goals, seeds = c4_queries(ctx, pp, nq)
-    lo, hi = rank * nq // world, (rank + 1) * nq // world
+    from pathplanning_b200.shard import shard_range, gather_records
+    lo, hi = shard_range(nq, rank, world)
     m = hi - lo
     d_s = torch.from_numpy(starts[lo:hi].copy()).to(dev)
     d_g = torch.from_numpy(goals[lo:hi].copy()).to(dev)
@@ -304,17 +325,16 @@ def hybrid_section(args, rank, world, local_rank, stream):
     solved = int((res["status"] == 0).sum())
     expanded = int(res["n_expanded"].sum())
     if world > 1:
-        parts = [torch.zeros_like(d_res) for _ in range(world)] if all((r + 1) * nq // world - r * nq // world == m for r in range(world)) else None
-        if parts is not None:
-            torch.cuda.synchronize()
-            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            g0.record()
-            dist.all_gather(parts, d_res)
-            g1.record()
-            torch.cuda.synchronize()
-            gather_ms = g0.elapsed_time(g1)
-            allres = np.concatenate([p.cpu().numpy().view(HYBRID_RESULT) for p in parts])
-            solved, expanded = int((allres["status"] == 0).sum()), int(allres["n_expanded"].sum())
+        local = d_res.cpu().numpy().view(HYBRID_RESULT)  # the device-timed run's records of this shard
+        torch.cuda.synchronize()
+        gather_records(local, nq, device=dev)  # warm-up of the collective
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        allres = gather_records(local, nq, device=dev)
+        g1.record()
+        torch.cuda.synchronize()
+        gather_ms = g0.elapsed_time(g1)
+        solved, expanded = int((allres["status"] == 0).sum()), int(allres["n_expanded"].sum())
     section = {
         "metric": "batched Hybrid A* plans/s", "workload": f"C4: {nq} independent start/goal queries on the C2 parking lot (400x400 @0.1m), "
         "wavefront + graph search per query, sharded by query", "scaling": "strong", "queries_per_gpu": m,
@@ -382,9 +402,6 @@ def ours_main(args):
 
     torch.cuda.set_device(local_rank)
     if world > 1:
-        # stdout carries exactly one JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION) off it
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = pp.Context(local_rank)
     # A dedicated (non-null) stream shared by torch and the context: ppx_ctx_set_stream(NULL) means
@@ -559,7 +576,7 @@ def ours_main(args):
             "clocks": sampler.summary(),
             "hybrid": hybrid,
         }
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
     ctx.close()
@@ -578,6 +595,7 @@ def main():
     ap.add_argument("--hybrid-queries", type=int, default=4096)
     ap.add_argument("--cpu-plans-per-core", type=int, default=16)
     args = ap.parse_args()
+    _stdout_to_stderr()
     if args.impl == "reference":
         reference_main(args)
     else:
