@@ -345,6 +345,19 @@ int ppx_hybrid_search_dev(ppx_hybrid* h, int64_t nq, const double* d_starts, con
 	const uint64_t* d_seeds, const ppx_hybrid_limits* limits, ppx_hybrid_result* d_results,
 	ppx_hybrid_path_state* d_paths, ppx_hybrid_log_entry* d_log);
 
+/*
+ * N3: the "Process graph search path" step of HybridAStar::SearchPath (algo/hybrid_a_star.cpp:260-291) for
+ * the solution chains a search returned: the composite path (paths/path_composite.h:43-100) is resampled
+ * every `path_interpolation` (HybridAStar::pathInterpolation, 0.1f) with its cusp points snapped in
+ * (path_composite.cpp:4-27) -- the pose array the smoother takes.  goals/results/paths are the arrays of
+ * ppx_hybrid_search (paths with capacity max_path per query).  Outputs per query: poses[q*max_points*3 ..],
+ * cusp[q*max_points ..] (1 = cuspIndices member), count[q] = number of samples (0 without a solution, -1 when
+ * max_path cut the chain or max_points does not suffice), lengths[q] (may be NULL) = composite path length.
+ */
+int ppx_hybrid_resample(ppx_hybrid* h, int64_t nq, const double* goals, const ppx_hybrid_result* results,
+	const ppx_hybrid_path_state* paths, int32_t max_path, float path_interpolation, int32_t max_points, double* poses,
+	uint8_t* cusp, int32_t* count, double* lengths);
+
 /* ------------------------------------------------------------------------------------------ */
 /* A10: Tree::GetNearestNode / GetNearestNodes  (utils/tree.h:73-116) as exact brute-force k-NN  */
 /*

@@ -292,8 +292,10 @@ private:
 };
 
 // HybridAStar (algo/hybrid_a_star.h:215-263, hybrid_a_star.cpp:206-304): graph search on the device.
-// Path smoothing (Smoother) is not part of the device path; GetPath() returns the
-// graph-search states (GetGraphSearchPath of the reference).
+// Path smoothing (Smoother) is not part of the device path; GetPath() returns the pose array
+// SearchPath builds for the smoother (hybrid_a_star.cpp:260-291, resampled on the device every
+// pathInterpolation with the cusp points snapped in) -- what the reference's GetPath() returns when
+// smoothing does not succeed (:294-297); GetGraphSearchStates() returns the node states of the solution.
 class HybridAStar {
 public:
 	struct SearchParameters { // hybrid_a_star.h:29-38, same defaults
@@ -358,8 +360,12 @@ public:
 		std::vector<std::vector<Pose2d>> paths;
 		std::vector<double> costs;
 		std::vector<Stats> stats;
-		SearchPathBatch({ m_init }, { m_goal }, { m_seed }, st, paths, costs, &stats);
-		m_path = paths[0];
+		std::vector<std::vector<Pose2d>> resampled;
+		std::vector<std::vector<int>> cusps;
+		SearchPathBatch({ m_init }, { m_goal }, { m_seed }, st, paths, costs, &stats, 1024, &resampled, &cusps);
+		m_states = paths[0];
+		m_path = resampled[0];
+		m_cuspIndices = cusps[0];
 		m_cost = costs[0];
 		m_stats = stats[0];
 		return st[0];
@@ -367,7 +373,8 @@ public:
 	/// n independent queries in one device call (BASELINE config C4)
 	void SearchPathBatch(const std::vector<Pose2d>& inits, const std::vector<Pose2d>& goals, const std::vector<uint64_t>& seeds,
 		std::vector<Status>& status, std::vector<std::vector<Pose2d>>& paths, std::vector<double>& costs,
-		std::vector<Stats>* stats = nullptr, int maxPath = 1024)
+		std::vector<Stats>* stats = nullptr, int maxPath = 1024, std::vector<std::vector<Pose2d>>* resampled = nullptr,
+		std::vector<std::vector<int>>* cuspIndices = nullptr, int maxPoints = 4096)
 	{
 		if (!isInitialized)
 			throw std::runtime_error("HybridAStar: not initialized");
@@ -406,13 +413,40 @@ public:
 				(*stats)[i].numReedsSheppAttempts = res[i].n_rs_attempts;
 			}
 		}
+		if (!resampled)
+			return;
+		// "Process graph search path" (hybrid_a_star.cpp:260-291) on the device
+		std::vector<double> poses(n * (size_t)maxPoints * 3);
+		std::vector<uint8_t> cusp(n * (size_t)maxPoints);
+		std::vector<int32_t> count(n);
+		dev->Check(ppx_hybrid_resample(m_gpu, (int64_t)n, g.data(), res.data(), chain.data(), maxPath, pathInterpolation, maxPoints,
+			poses.data(), cusp.data(), count.data(), nullptr));
+		resampled->assign(n, {});
+		if (cuspIndices)
+			cuspIndices->assign(n, {});
+		for (size_t i = 0; i < n; i++) {
+			if (count[i] < 0)
+				throw std::length_error("HybridAStar: maxPath / maxPoints too small for the solution");
+			for (int k = 0; k < count[i]; k++) {
+				const double* q = &poses[(i * (size_t)maxPoints + k) * 3];
+				Pose2d p;
+				p.px = q[0]; p.py = q[1]; p.theta = q[2];
+				(*resampled)[i].push_back(p);
+				if (cuspIndices && cusp[i * (size_t)maxPoints + k])
+					(*cuspIndices)[i].push_back(k);
+			}
+		}
 	}
 	std::vector<Pose2d> GetPath() const { return m_path; }
-	std::vector<Pose2d> GetGraphSearchPath() const { return m_path; }
+	/// states of the solution's nodes (root .. goal), the vertices of the reference's GetGraphSearchPath()
+	std::vector<Pose2d> GetGraphSearchStates() const { return m_states; }
+	/// indices into GetPath() of the cusp points (the cuspIndices SearchPath hands to the smoother)
+	const std::vector<int>& GetCuspIndices() const { return m_cuspIndices; }
 	double GetGraphSearchOptimalCost() const { return m_cost; }
 	const Stats& GetStats() const { return m_stats; }
 	const SearchParameters& GetSearchParameters() const { return m_params; }
 	bool isInitialized = false;
+	float pathInterpolation = 0.1f; // hybrid_a_star.h:249
 
 private:
 	SearchParameters m_params;
@@ -420,7 +454,8 @@ private:
 	ppx_hybrid* m_gpu = nullptr;
 	Pose2d m_init, m_goal;
 	uint64_t m_seed = 0;
-	std::vector<Pose2d> m_path;
+	std::vector<Pose2d> m_path, m_states;
+	std::vector<int> m_cuspIndices;
 	double m_cost = std::numeric_limits<double>::infinity();
 	Stats m_stats;
 };

@@ -717,6 +717,52 @@ long ref_hybrid_solution(void* hh, long cap, double* poses, int* kinds, double* 
 	return n;
 }
 
+// The "Process graph search path" block of HybridAStar::SearchPath (hybrid_a_star.cpp:260-291) applied to the
+// last search: the composite path of the solution resampled every `pathInterpolation` with the cusp points
+// snapped in, BEFORE smoothing.  The loop is restated here (it is local to SearchPath, which goes on to smooth);
+// every object it uses -- GetCompositePath, GetCuspPointRatios, Interpolate -- is the reference's own.
+// Returns the number of samples (0 without solution); cusp[i] = 1 where i is in cuspIndices.
+long ref_hybrid_resampled(void* hh, float pathInterpolation, long cap, double* poses, uint8_t* cusp, double* path_length)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& pl = *h->planner;
+	if (pl.m_stats.graphSearchStatus < 0)
+		return 0;
+	auto path = pl.m_graphSearch.GetCompositePath();
+	const double pathLength = path->GetLength();
+	if (path_length) *path_length = pathLength;
+	std::vector<double> ratios;
+	std::unordered_set<int> cuspIndices;
+	auto cuspRatios = path->GetCuspPointRatios();
+	cuspRatios.insert(0.0);
+	cuspRatios.insert(1.0);
+	auto cuspRatioIt = cuspRatios.begin();
+	for (double length = 0.0; length <= pathLength; length += pathInterpolation) {
+		double cuspLength = *cuspRatioIt * pathLength;
+		if (length >= cuspLength - pathInterpolation / 2 && length < cuspLength + pathInterpolation / 2) {
+			cuspIndices.insert(ratios.size());
+			ratios.push_back(*cuspRatioIt);
+			cuspRatioIt++;
+		} else {
+			ratios.push_back(length / pathLength);
+		}
+	}
+	std::vector<Pose2d> pts;
+	try {
+		pts = path->Interpolate(ratios);
+	} catch (const std::out_of_range&) { // start already satisfies the goal: the composite path has no segment and
+		return 0; // the reference's SearchPath throws here (path_composite.h:45-46); reported as "no samples"
+	}
+	long n = (long)pts.size();
+	for (long i = 0; i < n && i < cap; i++) {
+		poses[3 * i] = pts[i].x();
+		poses[3 * i + 1] = pts[i].y();
+		poses[3 * i + 2] = pts[i].theta;
+		cusp[i] = cuspIndices.count((int)i) ? 1 : 0;
+	}
+	return n;
+}
+
 // Full reference SearchPath (wavefront + GVD + A* + resampling + smoothing): timing only.
 int ref_hybrid_search_full(void* hh, const double* start, const double* goal, uint64_t seed, double* seconds, long* path_len)
 {

@@ -15,6 +15,7 @@
 #include "ppx_device.cuh"
 #include "ppx_fastlane.cuh"
 #include "ppx_hybrid_host.h"
+#include "ppx_resample.cuh"
 
 using namespace ppx;
 
@@ -355,6 +356,25 @@ void twin_hybrid_search(void* hh, const float* wfCost, const double* start, cons
 		}
 	}
 	*result = r;
+}
+
+// k_hybrid_resample for one query, sequentially (hybrid_a_star.cpp:260-291).
+long twin_hybrid_resample(void* hh, const double* goal, const ppx_hybrid_path_state* path, int pathLen, float pathInterpolation,
+	long cap, double* poses, uint8_t* cusp, double* pathLength)
+{
+	auto* h = (TwinHybrid*)hh;
+	const HybridDev& P = h->dev;
+	std::vector<double> finalLength(pathLen > 0 ? pathLen : 1);
+	ResamplePath rp;
+	Pose gl = { goal[0], goal[1], goal[2] };
+	int n = resample_plan(P, path, pathLen, gl, pathInterpolation, finalLength.data(), rp, poses, cusp, (int)cap);
+	for (int i = 0; i < n; i++) {
+		Pose p = resample_pose(P, rp, poses[3 * i]);
+		poses[3 * i] = p.x; poses[3 * i + 1] = p.y; poses[3 * i + 2] = p.th;
+	}
+	if (pathLength)
+		*pathLength = rp.length;
+	return n;
 }
 
 void twin_mt64_uniform(uint64_t seed, long n, double* out)

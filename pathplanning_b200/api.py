@@ -414,3 +414,20 @@ class HybridAStar:
         self.ctx._check(ppx.ppx_hybrid_search(self._h, nq, _ptr(starts), _ptr(goals), _ptr(seeds), C.byref(lim), _ptr(res),
                                               _ptr(paths), _ptr(log)))
         return dict(results=res, paths=paths, log=log)
+
+    def resample(self, goals, results, paths, path_interpolation=0.1, max_points=4096):
+        """The pose array HybridAStar::SearchPath hands to the smoother (hybrid_a_star.cpp:260-291) for the chains of
+        search(): -> dict(poses (nq,max_points,3), cusp (nq,max_points) bool, count (nq,), length (nq,))"""
+        goals = _f64(goals)
+        results = np.ascontiguousarray(results, HYBRID_RESULT)
+        paths = np.ascontiguousarray(paths, HYBRID_PATH_STATE)
+        nq = len(goals)
+        assert paths.ndim == 2 and len(paths) == nq and len(results) == nq
+        poses = np.zeros((nq, max_points, 3), np.float64)
+        cusp = np.zeros((nq, max_points), np.uint8)
+        count = np.zeros(nq, np.int32)
+        length = np.zeros(nq, np.float64)
+        self.ctx._check(ppx.ppx_hybrid_resample(self._h, nq, _ptr(goals), _ptr(results), _ptr(paths), paths.shape[1],
+                                                C.c_float(path_interpolation), max_points, _ptr(poses), _ptr(cusp), _ptr(count),
+                                                _ptr(length)))
+        return dict(poses=poses, cusp=cusp.astype(bool), count=count, length=length)

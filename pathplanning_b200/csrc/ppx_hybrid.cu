@@ -31,6 +31,7 @@ __device__ __noinline__ double ppx_sin_ool(double x);
 #include <cstdlib>
 #include "ppx_ctx.h"
 #include "ppx_hybrid_host.h"
+#include "ppx_resample.cuh"
 
 using namespace ppx;
 
@@ -222,6 +223,48 @@ struct SearchConsts {
 	MapDev map;
 	FastMap fm; // FP32 cell filter of the primitives' collision checks (ppx_fastlane.cuh)
 };
+
+// N3: hybrid_a_star.cpp:260-291 for a batch of solved queries, one warp per query: lane 0 plans (composite
+// length, cusp ratios, sample ratios -- a sequential double accumulation), the 32 lanes interpolate.
+constexpr int kResampleWarps = 4;
+__global__ void __launch_bounds__(kResampleWarps * 32) k_hybrid_resample(const SearchConsts* __restrict__ consts, int64_t nq,
+	const double* __restrict__ goals, const ppx_hybrid_result* __restrict__ results, const ppx_hybrid_path_state* __restrict__ paths,
+	int maxPath, float pathInterpolation, int maxPoints, double* __restrict__ finalLength, double* __restrict__ poses,
+	uint8_t* __restrict__ cusp, int32_t* __restrict__ count, double* __restrict__ lengths)
+{
+	__shared__ ResamplePath s_rp[kResampleWarps];
+	const HybridDev& P = consts->P;
+	const unsigned lane = threadIdx.x & 31;
+	const int wib = threadIdx.x >> 5;
+	for (int64_t q = (int64_t)blockIdx.x * kResampleWarps + wib; q < nq; q += (int64_t)gridDim.x * kResampleWarps) {
+		double* out = poses + (size_t)q * maxPoints * 3;
+		uint8_t* cq = cusp + (size_t)q * maxPoints;
+		int n = 0;
+		if (lane == 0) {
+			const ppx_hybrid_result& r = results[q];
+			s_rp[wib].length = 0.0;
+			if (r.status == 0 && r.path_len > maxPath)
+				n = -1; // the chain was cut by max_path
+			else if (r.status == 0 && r.path_len >= 2) {
+				const Pose goal = { goals[3 * q], goals[3 * q + 1], goals[3 * q + 2] };
+				n = resample_plan(P, paths + (size_t)q * maxPath, r.path_len, goal, pathInterpolation,
+					finalLength + (size_t)q * maxPath, s_rp[wib], out, cq, maxPoints);
+			}
+			count[q] = n;
+			if (lengths)
+				lengths[q] = s_rp[wib].length;
+		}
+		__syncwarp();
+		n = __shfl_sync(0xffffffffu, n, 0);
+		for (int i = (int)lane; i < n; i += 32) {
+			Pose p = resample_pose(P, s_rp[wib], out[3 * i]);
+			out[3 * i] = p.x;
+			out[3 * i + 1] = p.y;
+			out[3 * i + 2] = p.th;
+		}
+		__syncwarp();
+	}
+}
 
 // Schedule of a batch: queries are independent, and the batch ends when its longest query does.  A
 // query whose start cell the goal's wavefront never reached exhausts its whole reachable state set
@@ -741,6 +784,52 @@ int ppx_hybrid_expand(ppx_hybrid* h, const double* goal, int64_t n, const double
 	PPX_CUDA(ctx, cudaMemcpyAsync(children, base + oChildren, n * PPX_MAX_CHILDREN * sizeof(ppx_hybrid_child), cudaMemcpyDeviceToHost, ctx->stream));
 	if (parent_heuristic)
 		PPX_CUDA(ctx, cudaMemcpyAsync(parent_heuristic, base + oHeur, n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_hybrid_resample(ppx_hybrid* h, int64_t nq, const double* goals, const ppx_hybrid_result* results,
+	const ppx_hybrid_path_state* paths, int32_t max_path, float path_interpolation, int32_t max_points, double* poses,
+	uint8_t* cusp, int32_t* count, double* lengths)
+{
+	PPX_CHECK(check_handle(h));
+	ppx_ctx* ctx = h->ctx;
+	PPX_REQUIRE(ctx, nq >= 0 && max_path >= 2 && max_points > 0 && path_interpolation > 0.0f, "bad arguments");
+	PPX_REQUIRE(ctx, nq == 0 || (goals && results && paths && poses && cusp && count), "bad arguments");
+	if (nq == 0)
+		return PPX_OK;
+	size_t off = 0;
+	auto carve = [&](size_t bytes) {
+		size_t o = off;
+		off += (bytes + 255) & ~(size_t)255;
+		return o;
+	};
+	const size_t bGoals = (size_t)nq * 24, bRes = (size_t)nq * sizeof(ppx_hybrid_result);
+	const size_t bPaths = (size_t)nq * max_path * sizeof(ppx_hybrid_path_state), bFinal = (size_t)nq * max_path * 8;
+	const size_t bPoses = (size_t)nq * max_points * 24, bCusp = (size_t)nq * max_points, bCount = (size_t)nq * 4, bLen = (size_t)nq * 8;
+	size_t oGoals = carve(bGoals), oRes = carve(bRes), oPaths = carve(bPaths), oFinal = carve(bFinal), oPoses = carve(bPoses);
+	size_t oCusp = carve(bCusp), oCount = carve(bCount), oLen = carve(bLen);
+	char* base;
+	PPX_CHECK(ppx_scratch(ctx, 5, off, (void**)&base));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oGoals, goals, bGoals, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oRes, results, bRes, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oPaths, paths, bPaths, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(base + oCusp, 0, bCusp, ctx->stream));
+	SearchConsts consts { h->dev, ctx->map_dev(), fast_map_derive(ctx->desc) };
+	if (!h->d_consts)
+		PPX_CUDA(ctx, cudaMalloc(&h->d_consts, sizeof(SearchConsts)));
+	PPX_CUDA(ctx, cudaMemcpyAsync(h->d_consts, &consts, sizeof(SearchConsts), cudaMemcpyHostToDevice, ctx->stream));
+	int ctas = (int)std::min<int64_t>((nq + kResampleWarps - 1) / kResampleWarps, (int64_t)ctx->num_sms * 8);
+	k_hybrid_resample<<<ctas, kResampleWarps * 32, 0, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, (const double*)(base + oGoals),
+		(const ppx_hybrid_result*)(base + oRes), (const ppx_hybrid_path_state*)(base + oPaths), max_path, path_interpolation,
+		max_points, (double*)(base + oFinal), (double*)(base + oPoses), (uint8_t*)(base + oCusp), (int32_t*)(base + oCount),
+		(double*)(base + oLen));
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaMemcpyAsync(poses, base + oPoses, bPoses, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(cusp, base + oCusp, bCusp, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(count, base + oCount, bCount, cudaMemcpyDeviceToHost, ctx->stream));
+	if (lengths)
+		PPX_CUDA(ctx, cudaMemcpyAsync(lengths, base + oLen, bLen, cudaMemcpyDeviceToHost, ctx->stream));
 	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	return PPX_OK;
 }

@@ -89,6 +89,7 @@ _SIGS = {
     "ppx_hybrid_heuristic": (C.c_int, [_p, _p, _i64, _p, _p, _p, _p]),
     "ppx_hybrid_expand": (C.c_int, [_p, _p, _i64, _p, _p, _p, _p, _p]),
     "ppx_hybrid_search": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
+    "ppx_hybrid_resample": (C.c_int, [_p, _i64, _p, _p, _p, C.c_int32, C.c_float, C.c_int32, _p, _p, _p, _p]),
     "ppx_hybrid_search_dev": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
 }
 

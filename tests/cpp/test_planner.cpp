@@ -43,6 +43,11 @@ void TestHybridAStar(const Ref<Device>& dev)
 	CHECK(std::hypot(path.back().x() - goal.x(), path.back().y() - goal.y()) < spatialTolerance);
 	CHECK(std::fabs(path.back().theta - goal.theta) < angularTolerance);
 	CHECK(hybridAStar.GetGraphSearchOptimalCost() >= std::hypot(8.0, 8.0) - 1e-9);
+	// the pose array is sampled every pathInterpolation along the solution, cusp points snapped in (hybrid_a_star.cpp:260-291)
+	for (size_t i = 1; i < path.size(); i++)
+		CHECK(std::hypot(path[i].x() - path[i - 1].x(), path[i].y() - path[i - 1].y()) <= 0.15 + 1e-9);
+	CHECK(!hybridAStar.GetCuspIndices().empty() && hybridAStar.GetCuspIndices().front() == 0);
+	CHECK(hybridAStar.GetGraphSearchStates().size() >= 2 && hybridAStar.GetGraphSearchStates().size() < path.size());
 	std::printf("hybrid A*: %zu states, cost %.4f, %d expansions\n", path.size(), hybridAStar.GetGraphSearchOptimalCost(),
 		hybridAStar.GetStats().numExpandedNodes);
 

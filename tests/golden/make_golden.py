@@ -260,6 +260,28 @@ def main_hybrid():
     print("hybrid_c2.npz", os.path.getsize(os.path.join(HERE, "hybrid_c2.npz")))
 
 
+def main_resample():
+    """N3: the resampled pose arrays (hybrid_a_star.cpp:260-291) of the hybrid_c2 queries, at two step sizes."""
+    w = c2_world()
+    w.set_validator_params(1.0, 0.1)
+    H = refapi.Hybrid(w)
+    qs = hybrid_queries(w)
+    out = {}
+    for i, (s, g, seed) in enumerate(qs):
+        r = H.search(s, g, seed)
+        if r["status"] != 0:
+            continue
+        for tag, interp in (("a", 0.1), ("b", 0.25)):
+            poses, cusp, length = H.resampled(interp)
+            out[f"q{i}{tag}_poses"] = poses
+            out[f"q{i}{tag}_cusp"] = np.flatnonzero(cusp).astype(np.int32)
+            out[f"q{i}{tag}_length"] = np.array(length)
+        print("query", i, "samples", len(poses), "cusps", int(cusp.sum()))
+    out["interp"] = np.array([0.1, 0.25], np.float32)
+    np.savez_compressed(os.path.join(HERE, "hybrid_resample_c2.npz"), **out)
+    print("hybrid_resample_c2.npz", os.path.getsize(os.path.join(HERE, "hybrid_resample_c2.npz")))
+
+
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
     if which in ("all", "base"):
@@ -268,3 +290,5 @@ if __name__ == "__main__":
         main_wavefront()
     if which in ("all", "hybrid"):
         main_hybrid()
+    if which in ("all", "resample"):
+        main_resample()

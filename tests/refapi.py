@@ -25,6 +25,7 @@ def lib():
             getattr(_lib, name).restype = C.c_double
         _lib.ref_hybrid_expansions.restype = C.c_long
         _lib.ref_hybrid_solution.restype = C.c_long
+        _lib.ref_hybrid_resampled.restype = C.c_long
     return _lib
 
 
@@ -294,6 +295,14 @@ class Hybrid:
         return dict(status=st, cost=cost.value, n_expanded=n, n_children=nchild.value, n_samples=nsamp.value,
                     times=list(times), exp_keys=keys[:n], exp_poses=poses[:n], path=sp[:m].copy(), kinds=kinds[:m].copy(),
                     lengths=lens[:m].copy())
+
+    def resampled(self, path_interpolation=0.1, cap=8192):
+        """hybrid_a_star.cpp:260-291 on the last search: resampled graph-search path + cusp flags + composite length."""
+        poses = np.empty((cap, 3), np.float64)
+        cusp = np.zeros(cap, np.uint8)
+        length = C.c_double()
+        n = lib().ref_hybrid_resampled(self.h, C.c_float(path_interpolation), C.c_long(cap), _p(poses), _p(cusp), C.byref(length))
+        return poses[:n].copy(), cusp[:n].astype(bool), length.value
 
     def search_full(self, start, goal, seed):
         sec = C.c_double()

@@ -112,3 +112,36 @@ def test_twin_search(twin, fx, ref):
             assert np.array_equal(r["path"]["kind"][1:], fx[f"q{i}_kinds"][1:])
             assert np.array_equal(r["path"]["length"][1:], fx[f"q{i}_lengths"][1:])
     w.close()
+
+
+def test_twin_resample(twin, fx, ref):
+    """N3 (hybrid_a_star.cpp:260-291): the resampled pose array of the solution chain -- sample count, cusp
+    indices and composite length identical to the reference, poses within 1e-9 (host libm on both sides)."""
+    w = _c2_ref_world(ref)
+    H = ref.Hybrid(w)
+    gold = load_npz("hybrid_resample_c2.npz")
+    solved = 0
+    for i in range(len(fx["q_seed"])):
+        if fx["q_status"][i] != 0:
+            continue
+        wf, _, _ = w.wavefront(fx["q_goal"][i])
+        r = twin.search(wf, fx["q_start"][i], fx["q_goal"][i], int(fx["q_seed"][i]))
+        rr = H.search(fx["q_start"][i], fx["q_goal"][i], int(fx["q_seed"][i]))
+        assert rr["status"] == 0
+        for interp in (0.1, 0.25):
+            ref_poses, ref_cusp, ref_len = H.resampled(interp)
+            poses, cusp, length = twin.resample(fx["q_goal"][i], r["path"], interp)
+            tag = "a" if interp == 0.1 else "b"  # the committed fixture holds the same arrays
+            assert np.array_equal(ref_poses, gold[f"q{i}{tag}_poses"]) and np.array_equal(np.flatnonzero(ref_cusp), gold[f"q{i}{tag}_cusp"])
+            assert length == ref_len, i
+            assert len(poses) == len(ref_poses), i
+            assert np.array_equal(cusp, ref_cusp), i
+            if len(r["path"]) < 2:  # start already satisfies the goal: no segment, no samples (the reference throws)
+                assert len(poses) == 0
+                continue
+            assert cusp[0]  # ratio 0 is always snapped; ratio 1 only when the last sample falls within half a step of the end
+            assert np.abs(poses - ref_poses).max() < 1e-9, (i, np.abs(poses - ref_poses).max())
+        solved += 1
+    assert solved >= 5
+    H.close()
+    w.close()

@@ -148,3 +148,81 @@ def test_search_live_reference(ctx, ref, planner):
     H.close()
     w.close()
     assert not differing, f"queries with a different expansion sequence: {differing}"
+
+
+def test_resample_golden(planner, fx):
+    """N3 (hybrid_a_star.cpp:260-291): solution chains resampled on the device vs the arrays the reference built
+    (tests/golden/hybrid_resample_c2.npz): sample counts and cusp indices identical, poses within 1e-6."""
+    gold = load_npz("hybrid_resample_c2.npz")
+    out = planner.search(fx["q_start"], fx["q_goal"], fx["q_seed"], max_path=256)
+    checked = 0
+    for tag, interp in (("a", 0.1), ("b", 0.25)):
+        rs = planner.resample(fx["q_goal"], out["results"], out["paths"], interp, max_points=1024)
+        for i in range(len(fx["q_seed"])):
+            n = int(rs["count"][i])
+            if fx["q_status"][i] != 0:
+                assert n == 0
+                continue
+            ref_poses = gold[f"q{i}{tag}_poses"]
+            assert n == len(ref_poses), (i, tag, n, len(ref_poses))
+            assert np.array_equal(np.flatnonzero(rs["cusp"][i, :n]), gold[f"q{i}{tag}_cusp"]), (i, tag)
+            assert not rs["cusp"][i, n:].any()
+            if n:
+                assert_close_rel([rs["length"][i]], [float(gold[f"q{i}{tag}_length"])], REL, "composite length")
+                d = np.abs(rs["poses"][i, :n] - ref_poses)
+                d[:, 2] = np.minimum(d[:, 2], 2 * np.pi - d[:, 2])
+                assert d.max() < 1e-6 * max(1.0, np.abs(ref_poses).max()), (i, tag, d.max())
+                checked += 1
+    assert checked >= 20
+
+
+def test_resample_limits(planner, fx):
+    out = planner.search(fx["q_start"][:1], fx["q_goal"][:1], fx["q_seed"][:1], max_path=256)
+    rs = planner.resample(fx["q_goal"][:1], out["results"], out["paths"], 0.1, max_points=16)
+    assert int(rs["count"][0]) == -1  # 232 samples do not fit
+    out = planner.search(fx["q_start"][:1], fx["q_goal"][:1], fx["q_seed"][:1], max_path=4)
+    rs = planner.resample(fx["q_goal"][:1], out["results"], out["paths"], 0.1, max_points=1024)
+    assert int(rs["count"][0]) == -1  # the chain itself was cut by max_path
+
+
+def test_resample_live_reference(ref, planner):
+    """100 fresh queries: device search + device resampling vs the reference running here."""
+    g = load_npz("edges_c2.npz")
+    w = ref.World(g["lb"], g["ub"], float(g["resolution"]))
+    for r in g["rects"]:
+        w.add_rectangle(*r)
+    w.update()
+    w.set_validator_params(1.0, 0.1)
+    H = ref.Hybrid(w)
+    rng = np.random.default_rng(314)
+    starts, goals = [], []
+    while len(starts) < 100:
+        p = np.stack([rng.uniform(-18.5, 18.5, 2), rng.uniform(-18.5, 18.5, 2), rng.uniform(-np.pi, np.pi, 2)], 1)
+        if w.is_state_valid(p).all():
+            starts.append(p[0])
+            goals.append(p[1])
+    starts, goals = np.array(starts), np.array(goals)
+    seeds = np.arange(100, dtype=np.uint64) + 9000
+    out = planner.search(starts, goals, seeds, max_path=256, max_log=12000)
+    rs = planner.resample(goals, out["results"], out["paths"], 0.1, max_points=2048)
+    solved = 0
+    for i in range(100):
+        r = H.search(starts[i], goals[i], int(seeds[i]))
+        n = r["n_expanded"]
+        if not (int(out["results"][i]["status"]) == r["status"] and int(out["results"][i]["n_expanded"]) == n
+                and np.array_equal(out["log"][i]["key"][:n], r["exp_keys"][:, :3])):
+            continue  # expansion sequence differs (covered by test_search_live_reference)
+        if r["status"] != 0:
+            assert int(rs["count"][i]) == 0
+            continue
+        ref_poses, ref_cusp, ref_len = H.resampled(0.1)
+        m = int(rs["count"][i])
+        assert m == len(ref_poses), (i, m, len(ref_poses))
+        assert np.array_equal(rs["cusp"][i, :m], ref_cusp), i
+        d = np.abs(rs["poses"][i, :m] - ref_poses)
+        d[:, 2] = np.minimum(d[:, 2], 2 * np.pi - d[:, 2])
+        assert d.max() < 1e-6 * max(1.0, np.abs(ref_poses).max()), (i, d.max())
+        solved += 1
+    H.close()
+    w.close()
+    assert solved >= 60

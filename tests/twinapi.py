@@ -119,6 +119,21 @@ class Hybrid:
         return dict(result=r, path=path[:int(r["path_len"])], log=log[:n], gf=gf[:n])
 
 
+    def resample(self, goal, path, path_interpolation=0.1, cap=8192):
+        """-> (poses (n,3), cusp (n,) bool, composite length)"""
+        path = np.ascontiguousarray(path)
+        g = np.ascontiguousarray(goal, np.float64)
+        poses = np.zeros((cap, 3), np.float64)
+        cusp = np.zeros(cap, np.uint8)
+        length = np.zeros(1, np.float64)
+        fn = lib().twin_hybrid_resample
+        fn.restype = C.c_long
+        n = fn(self.h, _p(g), _p(path), C.c_int(len(path)), C.c_float(path_interpolation), C.c_long(cap), _p(poses), _p(cusp),
+               _p(length))
+        assert n >= 0, n
+        return poses[:n].copy(), cusp[:n].astype(bool), float(length[0])
+
+
 def mt64_uniform(seed, n):
     out = np.empty(n, np.float64)
     lib().twin_mt64_uniform(C.c_uint64(seed), C.c_long(n), _p(out))
