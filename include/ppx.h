@@ -415,6 +415,46 @@ int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_
 	const double* starts, const double* goals, const uint64_t* seeds, ppx_rrt_result* results, int64_t node_capacity,
 	double* nodes, int32_t* parents, double* costs);
 
+/* ---------------------------------------------------------------------------------------------
+ * N2: Smoother (algo/smoother.h:17-92, algo/smoother.cpp:33-224) for a batch of pose arrays.
+ *
+ * Replaces Smoother::Initialize + Smoother::Smooth(path, cuspIndices) + GetPath(), the step that follows the
+ * graph search in HybridAStar::SearchPath (hybrid_a_star.cpp:293-303).  The gradient descent runs on the
+ * device, one CTA per path; the two GVD lookups it makes (GVD::GetNearestObstacleCell /
+ * GetNearestVoronoiEdgeCell, gvd.h:36,76 -- smoother.cpp:110,118) read cell grids the caller uploads with
+ * ppx_smoother_set_gvd after GVD::Update() (the Voronoi half of N1 stays on the host).
+ */
+typedef struct ppx_smoother ppx_smoother;
+
+typedef struct ppx_smoother_params { /* Smoother::Parameters (smoother.h:29-62), same defaults on the reference side */
+	float step_tolerance; /* 1e-3 */
+	int32_t max_iterations; /* 2000 */
+	float learning_rate; /* 0.01 */
+	float path_weight; /* 0 */
+	float smooth_weight; /* 0.4 */
+	float voronoi_weight; /* 0.02 */
+	float collision_weight; /* 0.2 */
+	float curvature_weight; /* 0.4 */
+	float collision_ratio; /* 0.2 */
+	float max_curvature; /* Initialize(.., maxCurvature): 1 / minTurningRadius (hybrid_a_star.cpp:218) */
+	float alpha, d_max; /* GVD::alpha = 20, GVD::dMax = 30 (gvd.h:181) */
+	float min_safe_radius; /* StateValidatorOccupancyMap::minSafeRadius */
+} ppx_smoother_params;
+
+int ppx_smoother_create(ppx_ctx* ctx, const ppx_smoother_params* params, ppx_smoother** out);
+int ppx_smoother_destroy(ppx_smoother* s);
+/* nearest_obstacle / nearest_edge: rows * cols (row, col) int32 pairs, row-major like the map grids */
+int ppx_smoother_set_gvd(ppx_smoother* s, const int32_t* nearest_obstacle, const int32_t* nearest_edge);
+/*
+ * poses / cusp / count: the arrays ppx_hybrid_resample returns (max_points entries per path; count[q] <= 0
+ * = no path).  out_poses[q] receives Smoother::GetPath() (x, y moved; theta unchanged, smoother.cpp:152),
+ * status[q] Smoother::Status: 0 MaxIteration, 1 StepTolerance, 2 PathSize, -1 Failure (unsafe result or no
+ * path; the caller then keeps the unsmoothed path, hybrid_a_star.cpp:295-298).  iterations (may be NULL):
+ * gradient steps taken.
+ */
+int ppx_smoother_smooth(ppx_smoother* s, int64_t nq, const double* poses, const uint8_t* cusp, const int32_t* count,
+	int32_t max_points, double* out_poses, int32_t* status, int32_t* iterations);
+
 #ifdef __cplusplus
 }
 #endif

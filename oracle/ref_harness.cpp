@@ -763,6 +763,65 @@ long ref_hybrid_resampled(void* hh, float pathInterpolation, long cap, double* p
 	return n;
 }
 
+// N2: the nearest-obstacle / nearest-Voronoi-edge cell grids of the planner's GVD (after its last Update), (row, col)
+// pairs, rows*cols*2 ints each -- the lookups Smoother::Smooth makes (smoother.cpp:110,118).
+void ref_hybrid_gvd_cells(void* hh, int32_t* nearestObstacle, int32_t* nearestEdge)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& gvd = *h->planner->m_gvd;
+	const int rows = h->world->map->Rows(), cols = h->world->map->Columns();
+	for (int r = 0; r < rows; r++)
+		for (int c = 0; c < cols; c++) {
+			const auto& o = gvd.GetNearestObstacleCell(r, c);
+			const auto& e = gvd.GetNearestVoronoiEdgeCell(r, c);
+			size_t i = ((size_t)r * cols + c) * 2;
+			nearestObstacle[i] = o.row; nearestObstacle[i + 1] = o.col;
+			nearestEdge[i] = e.row; nearestEdge[i + 1] = e.col;
+		}
+}
+
+// N2: Smoother::SetParameters of the planner's smoother; p = the 10 leading fields of ppx_smoother_params as doubles
+// (step_tolerance, max_iterations, learning_rate, path/smooth/voronoi/collision/curvature weights, collision_ratio,
+// max_curvature).
+void ref_hybrid_smoother_set(void* hh, const double* p)
+{
+	auto* h = (RefHybrid*)hh;
+	Smoother::Parameters q((float)p[9]);
+	q.stepTolerance = (float)p[0];
+	q.maxIterations = (int)p[1];
+	q.learningRate = (float)p[2];
+	q.pathWeight = (float)p[3];
+	q.smoothWeight = (float)p[4];
+	q.voronoiWeight = (float)p[5];
+	q.collisionWeight = (float)p[6];
+	q.curvatureWeight = (float)p[7];
+	q.collisionRatio = (float)p[8];
+	h->planner->m_smoother.SetParameters(q);
+}
+
+// N2: Smoother::Smooth (smoother.cpp:33-158) of the planner's own smoother on a given pose array + cusp flags.
+// Returns Smoother::Status; out receives Smoother::GetPath().
+int ref_hybrid_smooth(void* hh, long n, const double* poses, const uint8_t* cusp, double* out)
+{
+	auto* h = (RefHybrid*)hh;
+	auto& sm = h->planner->m_smoother;
+	std::vector<Pose2d> path;
+	std::unordered_set<int> cuspIndices;
+	for (long i = 0; i < n; i++) {
+		Pose2d pose(poses[3 * i], poses[3 * i + 1], 0.0);
+		pose.theta = poses[3 * i + 2]; // as SearchPath hands it over: no re-wrap of the interpolated heading
+		path.push_back(pose);
+		if (cusp[i])
+			cuspIndices.insert((int)i);
+	}
+	int st = (int)sm.Smooth(path, cuspIndices);
+	const auto& res = sm.GetPath();
+	for (size_t i = 0; i < res.size() && (long)i < n; i++) {
+		out[3 * i] = res[i].x(); out[3 * i + 1] = res[i].y(); out[3 * i + 2] = res[i].theta;
+	}
+	return st;
+}
+
 // Full reference SearchPath (wavefront + GVD + A* + resampling + smoothing): timing only.
 int ref_hybrid_search_full(void* hh, const double* start, const double* goal, uint64_t seed, double* seconds, long* path_len)
 {

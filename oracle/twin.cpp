@@ -16,6 +16,7 @@
 #include "ppx_fastlane.cuh"
 #include "ppx_hybrid_host.h"
 #include "ppx_resample.cuh"
+#include "ppx_smooth.cuh"
 
 using namespace ppx;
 
@@ -375,6 +376,66 @@ long twin_hybrid_resample(void* hh, const double* goal, const ppx_hybrid_path_st
 	if (pathLength)
 		*pathLength = rp.length;
 	return n;
+}
+
+// k_smooth for one path, sequentially: phase A / phase B of ppx_smooth.cuh (smoother.cpp:33-158).
+int twin_smooth(void* hw, const ppx_smoother_params* p, const int32_t* nearObstacle, const int32_t* nearEdge, long n,
+	const double* poses, const uint8_t* cusp, double* out, int* iterations)
+{
+	auto* w = (TwinWorld*)hw;
+	MapDev map = w->dev();
+	SmoothDev P;
+	P.stepTolerance = p->step_tolerance; P.maxIterations = p->max_iterations; P.learningRate = p->learning_rate;
+	P.pathWeight = p->path_weight; P.smoothWeight = p->smooth_weight; P.voronoiWeight = p->voronoi_weight;
+	P.collisionWeight = p->collision_weight; P.curvatureWeight = p->curvature_weight; P.collisionRatio = p->collision_ratio;
+	P.maxCurvature = p->max_curvature; P.alpha = p->alpha; P.dMax = p->d_max; P.minSafeRadius = p->min_safe_radius;
+	P.nearObstacle = nearObstacle; P.nearEdge = nearEdge;
+	const float unsafeRadius = P.minSafeRadius * (1 + P.collisionRatio);
+	std::vector<V2> pos(n), nxt(n), cm1(n), cc(n), cp1(n);
+	std::vector<uint8_t> flags(n, 0);
+	for (long i = 0; i < n; i++) {
+		pos[i] = v2(poses[3 * i], poses[3 * i + 1]);
+		flags[i] = smooth_is_index(cusp, (int)n, (int)i) ? 1 : 0;
+	}
+	int st, it = -1;
+	if (n < 5) {
+		st = 2;
+	} else {
+		float step = P.stepTolerance;
+		while (true) {
+			it++;
+			if (it >= P.maxIterations) { st = 0; break; }
+			if (step < P.stepTolerance) { st = 1; break; }
+			for (long i = 0; i < n; i++) {
+				if (!(flags[i] & 1)) continue;
+				bool on = smooth_curvature(P, pos[i - 1], pos[i], pos[i + 1], cm1[i], cc[i], cp1[i]);
+				flags[i] = on ? 3 : 1;
+			}
+			float mx = 0.0f;
+			for (long i = 0; i < n; i++) {
+				V2 g = v2(0.0, 0.0);
+				if (i > 0 && flags[i - 1] == 3) g = g + cp1[i - 1];
+				if (flags[i] & 1) {
+					g = smooth_own_terms(P, map, g, v2(poses[3 * i], poses[3 * i + 1]), pos[i - 2], pos[i - 1], pos[i], pos[i + 1],
+						pos[i + 2], unsafeRadius);
+					if (flags[i] == 3) g = g + cc[i];
+				}
+				if (i + 1 < n && flags[i + 1] == 3) g = g + cm1[i + 1];
+				nxt[i] = pos[i] - (double)P.learningRate * g;
+				mx = fmaxf(mx, (float)v2_norm(g));
+			}
+			step = mx;
+			pos.swap(nxt);
+		}
+	}
+	bool bad = false;
+	for (long i = 0; i < n; i++) {
+		float d;
+		if (!is_state_valid(map, pos[i].x, pos[i].y, poses[3 * i + 2], P.minSafeRadius, &d)) bad = true;
+		out[3 * i] = pos[i].x; out[3 * i + 1] = pos[i].y; out[3 * i + 2] = poses[3 * i + 2];
+	}
+	if (iterations) *iterations = it;
+	return bad ? -1 : st;
 }
 
 void twin_mt64_uniform(uint64_t seed, long n, double* out)

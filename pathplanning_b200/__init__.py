@@ -11,4 +11,5 @@ from . import lib  # noqa: F401  (raises ImportError loudly when libppx.so is no
 from .api import (  # noqa: F401
     Context, MapDesc, ValidatorParams, RSCostParams, PPXError,
     RS_EDGE, CSTEER_EDGE, LINE_EDGE, make_rs_edges, make_csteer_edges, HybridParams, HybridAStar,
+    SmootherParams, Smoother,
 )

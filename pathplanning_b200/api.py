@@ -11,7 +11,7 @@ from dataclasses import dataclass, field
 
 import numpy as np
 
-from .lib import ppx, MapDescC, ValidatorParamsC, RSCostParamsC, HybridParamsC, HybridLimitsC, RRTParamsC
+from .lib import ppx, MapDescC, ValidatorParamsC, RSCostParamsC, HybridParamsC, HybridLimitsC, RRTParamsC, SmootherParamsC
 
 RS_EDGE = np.dtype([("start", "<f8", (3,)), ("len", "<f8", (5,)), ("code", "<u8")], align=True)
 CSTEER_EDGE = np.dtype([("start", "<f8", (3,)), ("length", "<f8"), ("beta", "<f8"), ("cos_beta", "<f8"),
@@ -431,3 +431,64 @@ class HybridAStar:
                                                 C.c_float(path_interpolation), max_points, _ptr(poses), _ptr(cusp), _ptr(count),
                                                 _ptr(length)))
         return dict(poses=poses, cusp=cusp.astype(bool), count=count, length=length)
+
+
+@dataclass
+class SmootherParams:
+    """Smoother::Parameters (algo/smoother.h:29-62) + the GVD constants and validator radius Smooth reads."""
+    step_tolerance: float = 1e-3
+    max_iterations: int = 2000
+    learning_rate: float = 0.01
+    path_weight: float = 0.0
+    smooth_weight: float = 0.4
+    voronoi_weight: float = 0.02
+    collision_weight: float = 0.2
+    curvature_weight: float = 0.4
+    collision_ratio: float = 0.2
+    max_curvature: float = 0.5  # 1 / minTurningRadius (hybrid_a_star.cpp:218)
+    alpha: float = 20.0
+    d_max: float = 30.0
+    min_safe_radius: float = 1.0
+
+    def to_c(self):
+        return SmootherParamsC(self.step_tolerance, self.max_iterations, self.learning_rate, self.path_weight,
+                               self.smooth_weight, self.voronoi_weight, self.collision_weight, self.curvature_weight,
+                               self.collision_ratio, self.max_curvature, self.alpha, self.d_max, self.min_safe_radius)
+
+
+class Smoother:
+    """ppx_smoother: Smoother::Initialize / Smooth / GetPath (algo/smoother.cpp:18-158) for batches of pose arrays."""
+
+    def __init__(self, ctx: Context, params: SmootherParams = None):
+        self.ctx = ctx
+        self.params = params or SmootherParams()
+        h = C.c_void_p()
+        p = self.params.to_c()
+        ctx._check(ppx.ppx_smoother_create(ctx.handle, C.byref(p), C.byref(h)))
+        self._h = h
+
+    def close(self):
+        if getattr(self, "_h", None):
+            ppx.ppx_smoother_destroy(self._h)
+            self._h = None
+
+    def set_gvd(self, nearest_obstacle, nearest_edge):
+        """(rows, cols, 2) int32 grids of GVD::GetNearestObstacleCell / GetNearestVoronoiEdgeCell"""
+        a = np.ascontiguousarray(nearest_obstacle, np.int32)
+        b = np.ascontiguousarray(nearest_edge, np.int32)
+        self.ctx._check(ppx.ppx_smoother_set_gvd(self._h, _ptr(a), _ptr(b)))
+
+    def smooth(self, poses, cusp, count):
+        """poses (nq, max_points, 3), cusp (nq, max_points), count (nq,) as returned by HybridAStar.resample
+        -> dict(poses, status (nq,), iterations (nq,))"""
+        poses = np.ascontiguousarray(poses, np.float64)
+        cusp = np.ascontiguousarray(cusp, np.uint8)
+        count = np.ascontiguousarray(count, np.int32)
+        nq, max_points = poses.shape[0], poses.shape[1]
+        assert poses.shape == (nq, max_points, 3) and cusp.shape == (nq, max_points) and count.shape == (nq,)
+        out = np.zeros_like(poses)
+        status = np.zeros(nq, np.int32)
+        iters = np.zeros(nq, np.int32)
+        self.ctx._check(ppx.ppx_smoother_smooth(self._h, nq, _ptr(poses), _ptr(cusp), _ptr(count), max_points, _ptr(out),
+                                                _ptr(status), _ptr(iters)))
+        return dict(poses=out, status=status, iterations=iters)

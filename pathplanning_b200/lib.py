@@ -46,6 +46,13 @@ class HybridLimitsC(C.Structure):
     _fields_ = [("max_nodes", C.c_int32), ("max_expansions", C.c_int32), ("max_path", C.c_int32), ("max_log", C.c_int32)]
 
 
+class SmootherParamsC(C.Structure):
+    _fields_ = [("step_tolerance", C.c_float), ("max_iterations", C.c_int32), ("learning_rate", C.c_float),
+                ("path_weight", C.c_float), ("smooth_weight", C.c_float), ("voronoi_weight", C.c_float),
+                ("collision_weight", C.c_float), ("curvature_weight", C.c_float), ("collision_ratio", C.c_float),
+                ("max_curvature", C.c_float), ("alpha", C.c_float), ("d_max", C.c_float), ("min_safe_radius", C.c_float)]
+
+
 _p = C.c_void_p
 _i64 = C.c_int64
 _SIGS = {
@@ -90,6 +97,10 @@ _SIGS = {
     "ppx_hybrid_expand": (C.c_int, [_p, _p, _i64, _p, _p, _p, _p, _p]),
     "ppx_hybrid_search": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
     "ppx_hybrid_resample": (C.c_int, [_p, _i64, _p, _p, _p, C.c_int32, C.c_float, C.c_int32, _p, _p, _p, _p]),
+    "ppx_smoother_create": (C.c_int, [_p, C.POINTER(SmootherParamsC), C.POINTER(_p)]),
+    "ppx_smoother_destroy": (C.c_int, [_p]),
+    "ppx_smoother_set_gvd": (C.c_int, [_p, _p, _p]),
+    "ppx_smoother_smooth": (C.c_int, [_p, _i64, _p, _p, _p, C.c_int32, _p, _p, _p]),
     "ppx_hybrid_search_dev": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
 }
 

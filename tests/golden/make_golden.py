@@ -282,6 +282,78 @@ def main_resample():
     print("hybrid_resample_c2.npz", os.path.getsize(os.path.join(HERE, "hybrid_resample_c2.npz")))
 
 
+OPEN_WORLD = dict(lb=(-10.0, -10.0, -np.pi), ub=(10.0, 10.0, np.pi), resolution=0.1,
+                  rects=[(2.0, 2.0, 0.0, 5.0, 0.0), (3.0, 1.0, 4.0, -4.0, 0.5), (1.0, 4.0, -5.0, 0.0, 0.0)])
+OPEN_QUERIES = [((-8.0, -8.0, 0.0), (8.0, 8.0, 0.78), 11), ((-8.0, 6.0, -1.0), (7.0, -7.0, 0.0), 12),
+                ((0.0, 0.0, 0.0), (0.0, -8.0, 3.0), 13), ((8.0, 2.0, 3.1), (-8.0, 3.0, 3.1), 14),
+                ((-2.0, -6.0, 1.57), (-2.0, 8.0, 1.57), 15), ((6.0, 6.0, -2.0), (-7.0, -7.0, 2.0), 16)]
+
+
+def _smooth_configs():
+    import pathplanning_b200 as pp
+    mc = float(np.float32(1.0 / 2.0))
+    return {"d": pp.SmootherParams(max_curvature=mc),  # the defaults HybridAStar::Initialize sets: the descent diverges
+            "s": pp.SmootherParams(max_curvature=mc, max_iterations=1),  # its first step: every gradient term once
+            "c": pp.SmootherParams(max_curvature=mc, curvature_weight=0.0),  # without the curvature term: converges
+            "p": pp.SmootherParams(max_curvature=mc, curvature_weight=0.0, path_weight=0.1, max_iterations=200)}
+
+
+SMOOTH_CONFIGS = _smooth_configs()
+
+
+def open_world():
+    w = refapi.World(OPEN_WORLD["lb"], OPEN_WORLD["ub"], OPEN_WORLD["resolution"])
+    for r in OPEN_WORLD["rects"]:
+        w.add_rectangle(*r)
+    w.update()
+    return w
+
+
+def main_smooth():
+    """N2: Smoother::Smooth (smoother.cpp:33-158) on the resampled solutions of (a) the hybrid_c2 queries and (b) six
+    queries on an open 20 m x 20 m lot, with the GVD cell grids the smoother reads."""
+    out = {}
+    for tag, w, qs in (("c2", c2_world(), None), ("open", open_world(), OPEN_QUERIES)):
+        w.set_validator_params(1.0, 0.1)
+        H = refapi.Hybrid(w)
+        if qs is None:
+            qs = hybrid_queries(w)
+        k = 0
+        for i, (s, g, seed) in enumerate(qs):
+            r = H.search(s, g, seed)
+            if r["status"] != 0:
+                continue
+            poses, cusp, length = H.resampled(0.1)
+            if len(poses) == 0:
+                continue
+            if k == 0:
+                a, b = H.gvd_cells()
+                out[f"{tag}_near_obstacle"] = a.astype(np.int16)
+                out[f"{tag}_near_edge"] = b.astype(np.int16)
+                if tag == "open":
+                    occ, sq = w.grids()
+                    pc, _ = w.gvd_update()
+                    info = w.info()
+                    out.update(open_occupancy=occ.astype(np.int8), open_sqdist=sq, open_pathcost=pc,
+                               open_world_origin=np.array(info["world_origin"]), open_resolution=np.float32(info["resolution"]),
+                               open_lb=np.array(OPEN_WORLD["lb"]), open_ub=np.array(OPEN_WORLD["ub"]))
+            out[f"{tag}{k}_in"] = poses
+            out[f"{tag}{k}_cusp"] = np.flatnonzero(cusp).astype(np.int32)
+            for cfg, sp in SMOOTH_CONFIGS.items():
+                H.set_smoother(sp)
+                st, sm = H.smooth(poses, cusp)
+                out[f"{tag}{k}{cfg}_out"] = sm[:, :2]
+                out[f"{tag}{k}{cfg}_status"] = np.array(st)
+                print(tag, "query", i, "cfg", cfg, "points", len(poses), "status", st, "nan", bool(np.isnan(sm).any()),
+                      "moved", float(np.nanmax(np.abs(sm[:, :2] - poses[:, :2]))))
+            k += 1
+        out[f"{tag}_n"] = np.array(k)
+        H.close()
+        w.close()
+    np.savez_compressed(os.path.join(HERE, "smooth.npz"), **out)
+    print("smooth.npz", os.path.getsize(os.path.join(HERE, "smooth.npz")))
+
+
 if __name__ == "__main__":
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
     if which in ("all", "base"):
@@ -292,3 +364,5 @@ if __name__ == "__main__":
         main_hybrid()
     if which in ("all", "resample"):
         main_resample()
+    if which in ("all", "smooth"):
+        main_smooth()

@@ -304,6 +304,29 @@ class Hybrid:
         n = lib().ref_hybrid_resampled(self.h, C.c_float(path_interpolation), C.c_long(cap), _p(poses), _p(cusp), C.byref(length))
         return poses[:n].copy(), cusp[:n].astype(bool), length.value
 
+    def gvd_cells(self):
+        """(rows, cols, 2) nearest-obstacle and nearest-Voronoi-edge cells of the planner's GVD (after a search)"""
+        i = self.world.info()
+        rows, cols = i["rows"], i["cols"]
+        a = np.zeros((rows, cols, 2), np.int32)
+        b = np.zeros((rows, cols, 2), np.int32)
+        lib().ref_hybrid_gvd_cells(self.h, _p(a), _p(b))
+        return a, b
+
+    def set_smoother(self, sp):
+        """Smoother::SetParameters from a pathplanning_b200.SmootherParams"""
+        v = np.array([sp.step_tolerance, sp.max_iterations, sp.learning_rate, sp.path_weight, sp.smooth_weight, sp.voronoi_weight,
+                      sp.collision_weight, sp.curvature_weight, sp.collision_ratio, sp.max_curvature], np.float64)
+        lib().ref_hybrid_smoother_set(self.h, _p(v))
+
+    def smooth(self, poses, cusp):
+        """Smoother::Smooth of the planner's smoother -> (Smoother::Status, GetPath())"""
+        poses = np.ascontiguousarray(poses, np.float64)
+        cusp = np.ascontiguousarray(cusp, np.uint8)
+        out = np.zeros_like(poses)
+        st = lib().ref_hybrid_smooth(self.h, C.c_long(len(poses)), _p(poses), _p(cusp), _p(out))
+        return int(st), out
+
     def search_full(self, start, goal, seed):
         sec = C.c_double()
         plen = C.c_long()

@@ -16,6 +16,14 @@ from common import load_npz, c2_world_desc
 twinapi = pytest.importorskip("twinapi")
 
 
+def sys_path_golden():
+    import os
+    import sys
+    d = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    if d not in sys.path:
+        sys.path.insert(0, d)
+
+
 @pytest.fixture(scope="module")
 def fx():
     return load_npz("hybrid_c2.npz")
@@ -143,5 +151,44 @@ def test_twin_resample(twin, fx, ref):
             assert np.abs(poses - ref_poses).max() < 1e-9, (i, np.abs(poses - ref_poses).max())
         solved += 1
     assert solved >= 5
+    H.close()
+    w.close()
+
+
+def test_twin_smooth(twin, fx, ref):
+    """N2 (smoother.cpp:33-224): the per-point phase A / phase B restatement run sequentially on the host gives the
+    reference's smoothed path bit for bit (same libm on both sides; NaNs of the diverging default descent
+    included), with the same status -- live reference on the C2 fixture queries, four parameter sets."""
+    sys_path_golden()
+    from make_golden import SMOOTH_CONFIGS
+    w = _c2_ref_world(ref)
+    H = ref.Hybrid(w)
+    gold = load_npz("smooth.npz")
+    checked = moved = k = 0
+    for i in range(len(fx["q_seed"])):
+        if fx["q_status"][i] != 0:
+            continue
+        H.search(fx["q_start"][i], fx["q_goal"][i], int(fx["q_seed"][i]))
+        poses, cusp, _ = H.resampled(0.1)
+        if len(poses) == 0:
+            continue
+        assert np.array_equal(poses, gold[f"c2{k}_in"])
+        near_obs, near_edge = H.gvd_cells()
+        assert np.array_equal(near_obs, gold["c2_near_obstacle"]) and np.array_equal(near_edge, gold["c2_near_edge"])
+        for cfg, sp in SMOOTH_CONFIGS.items():
+            H.set_smoother(sp)
+            st_ref, out_ref = H.smooth(poses, cusp)
+            assert st_ref == int(gold[f"c2{k}{cfg}_status"]) and np.array_equal(out_ref[:, :2], gold[f"c2{k}{cfg}_out"], equal_nan=True)
+            st, out, iters = twin.world.smooth(sp.to_c(), near_obs, near_edge, poses, cusp)
+            assert st == st_ref, (i, cfg, st, st_ref)
+            assert np.array_equal(out, out_ref, equal_nan=True), (i, cfg, np.nanmax(np.abs(out - out_ref)))
+            checked += 1
+            moved += int(cfg in "cp" and 1e-3 < np.nanmax(np.abs(out[:, :2] - poses[:, :2])) < 1.0)
+        # a short path is returned as is with Status::PathSize
+        st_ref, out_ref = H.smooth(poses[:4], cusp[:4])
+        st, out, _ = twin.world.smooth(sp.to_c(), near_obs, near_edge, poses[:4], cusp[:4])
+        assert st == st_ref == 2 and np.array_equal(out, out_ref)
+        k += 1
+    assert checked >= 40 and moved >= 20
     H.close()
     w.close()

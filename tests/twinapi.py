@@ -41,6 +41,18 @@ class World:
             lib().twin_world_destroy(self.h)
             self.h = None
 
+    def smooth(self, params_c, near_obstacle, near_edge, poses, cusp):
+        """-> (status, smoothed poses (n,3), iterations)"""
+        poses = np.ascontiguousarray(poses, np.float64)
+        cusp = np.ascontiguousarray(cusp, np.uint8)
+        a = np.ascontiguousarray(near_obstacle, np.int32)
+        b = np.ascontiguousarray(near_edge, np.int32)
+        out = np.zeros_like(poses)
+        it = C.c_int()
+        st = lib().twin_smooth(self.h, C.byref(params_c), _p(a), _p(b), C.c_long(len(poses)), _p(poses), _p(cusp), _p(out),
+                               C.byref(it))
+        return int(st), out, it.value
+
     def check_rs(self, edges, rmin, radius, min_step, impl=1):
         n = len(edges)
         edges = np.ascontiguousarray(edges)
