@@ -22,6 +22,7 @@
 #include <stdexcept>
 #include <string>
 #include <vector>
+#include <unordered_set>
 #include "ppx.h"
 
 namespace Planner {
@@ -458,6 +459,125 @@ private:
 	std::vector<int> m_cuspIndices;
 	double m_cost = std::numeric_limits<double>::infinity();
 	Stats m_stats;
+};
+
+// Smoother (algo/smoother.h:17-92): gradient-descent smoothing of pose arrays on the device (ppx_smoother_*).
+// The GVD lookups Smooth makes are cell grids the caller provides (SetGVD) -- the Voronoi half of the GVD is not
+// built on the device; with the reference tree they are GVD::GetNearestObstacleCell / GetNearestVoronoiEdgeCell.
+class Smoother {
+public:
+	enum Status { MaxIteration = 0, StepTolerance, PathSize, Failure = -1, Collision = -2 }; // smoother.h:19-25
+	struct Parameters { // smoother.h:29-62, same defaults
+		float stepTolerance = 1e-3f;
+		int maxIterations = 2000;
+		float learningRate = 0.01f;
+		float pathWeight = 0.0f, smoothWeight = 0.4f, voronoiWeight = 0.02f, collisionWeight = 0.2f, curvatureWeight = 0.4f;
+		float collisionRatio = 0.2f;
+		float maxCurvature;
+		explicit Parameters(float maxCurvature_) : maxCurvature(maxCurvature_) { }
+	};
+	float alpha = 20.0f, dMax = 30.0f; // GVD::alpha, GVD::dMax (gvd.h:181)
+
+	Smoother() : m_param(1.0f) { }
+	~Smoother()
+	{
+		if (m_gpu)
+			ppx_smoother_destroy(m_gpu);
+	}
+	bool Initialize(const Ref<StateValidatorOccupancyMap>& validator, float maxCurvature)
+	{
+		if (!validator) {
+			isInitialized = false;
+			return false;
+		}
+		m_param = Parameters(maxCurvature);
+		m_validator = validator;
+		m_dirty = true;
+		isInitialized = true;
+		return true;
+	}
+	Parameters GetParameters() const { return m_param; }
+	void SetParameters(const Parameters& p)
+	{
+		m_param = p;
+		m_dirty = true;
+	}
+	/// rows * cols (row, col) pairs each, after GVD::Update()
+	void SetGVD(const std::vector<int32_t>& nearestObstacleCell, const std::vector<int32_t>& nearestVoronoiEdgeCell)
+	{
+		m_nearObstacle = nearestObstacleCell;
+		m_nearEdge = nearestVoronoiEdgeCell;
+		m_dirty = true;
+	}
+	Status Smooth(const std::vector<Pose2d>& path, const std::unordered_set<int>& cuspIndices = {})
+	{
+		if (!isInitialized)
+			return Status::Failure; // smoother.cpp:39-42
+		std::vector<Status> st;
+		std::vector<std::vector<Pose2d>> out;
+		SmoothBatch({ path }, { cuspIndices }, st, out);
+		m_currentPath = out[0];
+		return st[0];
+	}
+	/// n paths in one device call
+	void SmoothBatch(const std::vector<std::vector<Pose2d>>& paths, const std::vector<std::unordered_set<int>>& cuspIndices,
+		std::vector<Status>& status, std::vector<std::vector<Pose2d>>& out)
+	{
+		if (!isInitialized)
+			throw std::runtime_error("Smoother: not initialized");
+		const size_t n = paths.size();
+		if (cuspIndices.size() != n)
+			throw std::invalid_argument("SmoothBatch: sizes differ");
+		auto& dev = m_validator->GetMap()->GetDevice();
+		if (m_dirty) {
+			if (m_gpu)
+				ppx_smoother_destroy(m_gpu);
+			m_gpu = nullptr;
+			ppx_smoother_params p { m_param.stepTolerance, m_param.maxIterations, m_param.learningRate, m_param.pathWeight,
+				m_param.smoothWeight, m_param.voronoiWeight, m_param.collisionWeight, m_param.curvatureWeight, m_param.collisionRatio,
+				m_param.maxCurvature, alpha, dMax, m_validator->minSafeRadius };
+			dev->Check(ppx_smoother_create(dev->Context(), &p, &m_gpu));
+			dev->Check(ppx_smoother_set_gvd(m_gpu, m_nearObstacle.data(), m_nearEdge.data()));
+			m_dirty = false;
+		}
+		size_t maxPoints = 1;
+		for (auto& p : paths)
+			maxPoints = std::max(maxPoints, p.size());
+		std::vector<double> poses(n * maxPoints * 3), res(n * maxPoints * 3);
+		std::vector<uint8_t> cusp(n * maxPoints);
+		std::vector<int32_t> count(n), st(n);
+		for (size_t i = 0; i < n; i++) {
+			count[i] = (int32_t)paths[i].size();
+			for (size_t k = 0; k < paths[i].size(); k++) {
+				double* q = &poses[(i * maxPoints + k) * 3];
+				q[0] = paths[i][k].x(); q[1] = paths[i][k].y(); q[2] = paths[i][k].theta;
+				cusp[i * maxPoints + k] = cuspIndices[i].count((int)k) ? 1 : 0;
+			}
+		}
+		dev->Check(ppx_smoother_smooth(m_gpu, (int64_t)n, poses.data(), cusp.data(), count.data(), (int32_t)maxPoints, res.data(),
+			st.data(), nullptr));
+		status.resize(n);
+		out.assign(n, {});
+		for (size_t i = 0; i < n; i++) {
+			status[i] = (Status)st[i];
+			for (int k = 0; k < count[i]; k++) {
+				const double* q = &res[(i * maxPoints + k) * 3];
+				Pose2d p;
+				p.px = q[0]; p.py = q[1]; p.theta = q[2];
+				out[i].push_back(p);
+			}
+		}
+	}
+	const std::vector<Pose2d>& GetPath() const { return m_currentPath; }
+	bool isInitialized = false;
+
+private:
+	Parameters m_param;
+	Ref<StateValidatorOccupancyMap> m_validator;
+	ppx_smoother* m_gpu = nullptr;
+	bool m_dirty = true;
+	std::vector<int32_t> m_nearObstacle, m_nearEdge;
+	std::vector<Pose2d> m_currentPath;
 };
 
 } // namespace Planner

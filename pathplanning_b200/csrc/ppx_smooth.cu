@@ -14,7 +14,7 @@ using namespace ppx;
 
 namespace {
 
-constexpr int kSmoothThreads = 128;
+constexpr int kSmoothThreads = 256;
 constexpr int kBytesPerPoint = 5 * (int)sizeof(V2) + 2; // pos, pos', 3 curvature parts, cusp flag, state flags
 
 struct SmoothConsts {
@@ -23,19 +23,19 @@ struct SmoothConsts {
 };
 
 __global__ void __launch_bounds__(kSmoothThreads) k_smooth(const SmoothConsts* __restrict__ consts, int64_t nq,
-	const double* __restrict__ poses, const uint8_t* __restrict__ cusp, const int32_t* __restrict__ count, int maxPoints,
+	const double* __restrict__ poses, const uint8_t* __restrict__ cusp, const int32_t* __restrict__ count, int maxPoints, int capPoints,
 	double* __restrict__ out, int32_t* __restrict__ status, int32_t* __restrict__ iterations)
 {
 	extern __shared__ double s_raw[];
 	__shared__ float s_red[2][kSmoothThreads / 32];
 	__shared__ int s_unsafe;
 	V2* pos = (V2*)s_raw;
-	V2* nxt = pos + maxPoints;
-	V2* cm1 = nxt + maxPoints;
-	V2* cc = cm1 + maxPoints;
-	V2* cp1 = cc + maxPoints;
-	uint8_t* s_cusp = (uint8_t*)(cp1 + maxPoints);
-	uint8_t* flags = s_cusp + maxPoints; // bit 0: optimised index, bit 1: curvature term active this iteration
+	V2* nxt = pos + capPoints; // capPoints: the longest path of the batch
+	V2* cm1 = nxt + capPoints;
+	V2* cc = cm1 + capPoints;
+	V2* cp1 = cc + capPoints;
+	uint8_t* s_cusp = (uint8_t*)(cp1 + capPoints);
+	uint8_t* flags = s_cusp + capPoints; // bit 0: optimised index, bit 1: curvature term active this iteration
 	const SmoothDev& P = consts->P;
 	const MapDev& map = consts->map;
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -46,6 +46,8 @@ __global__ void __launch_bounds__(kSmoothThreads) k_smooth(const SmoothConsts* _
 		const double* in = poses + (size_t)q * maxPoints * 3;
 		double* o = out + (size_t)q * maxPoints * 3;
 		__syncthreads();
+		pos = (V2*)s_raw;
+		nxt = pos + capPoints;
 		if (n <= 0) { // no path to smooth
 			if (tid == 0) {
 				status[q] = -1;
@@ -210,10 +212,16 @@ extern "C" int ppx_smoother_smooth(ppx_smoother* s, int64_t nq, const double* po
 	PPX_REQUIRE(ctx, s->has_maps, "ppx_smoother_set_gvd has not been called");
 	PPX_REQUIRE(ctx, nq >= 0 && max_points > 0, "bad arguments");
 	PPX_REQUIRE(ctx, nq == 0 || (poses && cusp && count && out_poses && status), "bad arguments");
-	const size_t smem = (size_t)max_points * kBytesPerPoint + 16;
-	PPX_REQUIRE(ctx, smem <= 200 * 1024, "max_points too large for the smoother (<= 2400)");
 	if (nq == 0)
 		return PPX_OK;
+	int cap = 8;
+	for (int64_t q = 0; q < nq; q++) {
+		PPX_REQUIRE(ctx, count[q] <= max_points, "count[q] exceeds max_points");
+		cap = std::max(cap, (int)count[q]);
+	}
+	cap = (cap + 7) & ~7;
+	const size_t smem = (size_t)cap * kBytesPerPoint + 16;
+	PPX_REQUIRE(ctx, smem <= 200 * 1024, "path too long for the smoother (<= 2400 points)");
 	size_t off = 0;
 	auto carve = [&](size_t bytes) {
 		size_t o = off;
@@ -228,6 +236,7 @@ extern "C" int ppx_smoother_smooth(ppx_smoother* s, int64_t nq, const double* po
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oIn, poses, bPoses, cudaMemcpyHostToDevice, ctx->stream));
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oCusp, cusp, bCusp, cudaMemcpyHostToDevice, ctx->stream));
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oCount, count, bCount, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(base + oOut, 0, bPoses, ctx->stream));
 	SmoothConsts c;
 	const ppx_smoother_params& p = s->params;
 	c.P.stepTolerance = p.step_tolerance;
@@ -253,7 +262,7 @@ extern "C" int ppx_smoother_smooth(ppx_smoother* s, int64_t nq, const double* po
 	int perSm = (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / smem));
 	int ctas = (int)std::min<int64_t>(nq, (int64_t)ctx->num_sms * perSm);
 	k_smooth<<<ctas, kSmoothThreads, smem, ctx->stream>>>(s->d_consts, nq, (const double*)(base + oIn), (const uint8_t*)(base + oCusp),
-		(const int32_t*)(base + oCount), max_points, (double*)(base + oOut), (int32_t*)(base + oStatus), (int32_t*)(base + oIter));
+		(const int32_t*)(base + oCount), max_points, cap, (double*)(base + oOut), (int32_t*)(base + oStatus), (int32_t*)(base + oIter));
 	PPX_LAUNCHED(ctx);
 	PPX_CUDA(ctx, cudaMemcpyAsync(out_poses, base + oOut, bPoses, cudaMemcpyDeviceToHost, ctx->stream));
 	PPX_CUDA(ctx, cudaMemcpyAsync(status, base + oStatus, bCount, cudaMemcpyDeviceToHost, ctx->stream));

@@ -51,6 +51,30 @@ void TestHybridAStar(const Ref<Device>& dev)
 	std::printf("hybrid A*: %zu states, cost %.4f, %d expansions\n", path.size(), hybridAStar.GetGraphSearchOptimalCost(),
 		hybridAStar.GetStats().numExpandedNodes);
 
+	// Smoother on that pose array (smoother.cpp:33-158) without the curvature term: the descent converges, the end
+	// points stay, interior points move by centimetres, the result is collision free
+	{
+		Smoother smoother;
+		CHECK(smoother.Initialize(stateValidator, 1.0f / 2.0f));
+		auto sp = smoother.GetParameters();
+		sp.curvatureWeight = 0.0f;
+		smoother.SetParameters(sp);
+		std::vector<int32_t> none(2 * (size_t)map->Rows() * map->Columns(), -1); // no obstacle, no Voronoi edge
+		smoother.SetGVD(none, none);
+		std::unordered_set<int> cusps(hybridAStar.GetCuspIndices().begin(), hybridAStar.GetCuspIndices().end());
+		Smoother::Status st = smoother.Smooth(path, cusps);
+		CHECK(st == Smoother::MaxIteration || st == Smoother::StepTolerance);
+		const auto& sm = smoother.GetPath();
+		CHECK(sm.size() == path.size());
+		CHECK(sm.front().x() == path.front().x() && sm.back().y() == path.back().y());
+		double moved = 0.0;
+		for (size_t i = 0; i < sm.size(); i++)
+			moved = std::max(moved, std::hypot(sm[i].x() - path[i].x(), sm[i].y() - path[i].y()));
+		CHECK(moved > 1e-6 && moved < 1.0);
+		CHECK(smoother.Smooth({ path[0], path[1], path[2] }) == Smoother::PathSize);
+		std::printf("smoother: status %d, max displacement %.4f m\n", (int)st, moved);
+	}
+
 	// a wall across the map with no gap: the goal becomes unreachable -> Status::Failure
 	int r0, c0;
 	for (double y = -10.0; y < 10.0; y += 0.05) {
