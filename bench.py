@@ -202,7 +202,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._stop = threading.Event()
+        self._halt = threading.Event()
         self.active = threading.Event()
         try:
             import pynvml
@@ -223,7 +223,7 @@ class ClockSampler(threading.Thread):
             nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
             nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
         }
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             if self.active.is_set():
                 try:
                     self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
@@ -236,7 +236,7 @@ class ClockSampler(threading.Thread):
             time.sleep(0.002)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
 
     def summary(self):
         return {"sm_mhz": float(np.median(self.samples)) if self.samples else None, "sm_max_mhz": self.max_mhz,

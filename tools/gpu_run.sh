@@ -1,6 +1,6 @@
 #!/bin/bash
 # usage: tools/gpu_run.sh TAG   (run on the GPU box via gpurun; outputs under gpurun_out/)
-TAG=${1:-r1x}
+TAG=${1:-r1l}
 set -x
 nvidia-smi -L
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_$TAG.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_$TAG.log
