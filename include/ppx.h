@@ -103,6 +103,19 @@ int ppx_map_upload(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* sqdist
 int ppx_map_build(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* occupancy, const float* pathcost,
 	int32_t* sqdist_out);
 
+/*
+ * N4: outline rasterisation of polygon obstacles into the occupancy grid -- Shape::RasterizeLine
+ * (state_validator/obstacle.cpp:7-61) over PolygonShape::GetGridCellsPosition (:77-85) with the occupancy write
+ * of ObstacleListOccupancyMap::AddObstacle (obstacle_list_occupancy_map.cpp:29-45), for n_polygons obstacles
+ * added in order.  vertices: world coordinates (x, y) of every outline vertex as
+ * Obstacle::GetBoundaryWorldPosition returns them (the rotation by the pose stays on the host: its libm decides the
+ * cell of a vertex on a cell border); offsets[p] .. offsets[p+1] are polygon p's vertices.  occupancy (host, rows *
+ * cols, in/out): cells of polygon p receive id first_id + p, a later polygon overwrites an earlier one like the
+ * reference's sequential adds; first_id must exceed every id already in the grid.  Follow with ppx_map_build.
+ */
+int ppx_map_rasterize(ppx_ctx* ctx, const ppx_map_desc* desc, int32_t n_polygons, const int32_t* offsets,
+	const double* vertices, int32_t first_id, int32_t* occupancy);
+
 /* StateValidatorOccupancyMap public fields (state_validator_occupancy_map.h:27-28). */
 typedef struct ppx_validator_params {
 	float min_safe_radius;

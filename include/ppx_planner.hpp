@@ -34,6 +34,10 @@ enum class Status { Success = 0, Failure = -1 }; // algo/path_planner.h:9-12
 enum class Steer { Left = 0, Straight = 1, Right = 2 }; // paths/path.h:9-13
 enum class Direction { Forward = 0, Backward = 1, NoMotion = 2 }; // paths/path.h:15-19
 
+struct Point2d { // Eigen::Vector2d of geometry/2dplane.h:14
+	double x = 0, y = 0;
+};
+
 struct Pose2d { // geometry/2dplane.h:17-34; the constructor wraps theta to (-pi, pi] like WrapTheta (:36-45)
 	double px = 0, py = 0, theta = 0;
 	Pose2d() = default;
@@ -107,6 +111,23 @@ public:
 	void SetOccupied(int row, int col, int obstacleId = 0) { m_occupancy[(size_t)row * m_desc.cols + col] = obstacleId; m_dirty = true; }
 	void SetFree(int row, int col) { m_occupancy[(size_t)row * m_desc.cols + col] = -1; m_dirty = true; }
 	bool IsOccupied(int row, int col) const { return m_occupancy[(size_t)row * m_desc.cols + col] >= 0; }
+	int GetOccupancyValue(int row, int col) const { return m_occupancy[(size_t)row * m_desc.cols + col]; }
+	/// ObstacleListOccupancyMap::AddObstacle (obstacle_list_occupancy_map.cpp:29-45) for a polygon outline given by its
+	/// world-frame vertices (Obstacle::GetBoundaryWorldPosition): rasterised on the device (ppx_map_rasterize); the
+	/// obstacle receives the next id.  Returns the id.
+	int AddObstacle(const std::vector<Point2d>& boundaryWorldPosition)
+	{
+		std::vector<double> v;
+		for (auto& p : boundaryWorldPosition) {
+			v.push_back(p.x);
+			v.push_back(p.y);
+		}
+		const int32_t offsets[2] = { 0, (int32_t)boundaryWorldPosition.size() };
+		const int id = m_nextId++;
+		m_dev->Check(ppx_map_rasterize(m_dev->Context(), &m_desc, 1, offsets, v.data(), id, m_occupancy.data()));
+		m_dirty = true;
+		return id;
+	}
 	/// OccupancyMap::Update() + GVD::Update() (occupancy_map.cpp:16-19): upload + distance map build.
 	void Update()
 	{
@@ -128,6 +149,7 @@ private:
 	ppx_map_desc m_desc {};
 	std::vector<int32_t> m_occupancy, m_sqdist;
 	bool m_dirty = true;
+	int m_nextId = 0;
 };
 
 // PathReedsShepp (paths/path_reeds_shepp.h:8-37): a solved segment anchored at its start pose.

@@ -763,6 +763,51 @@ long ref_hybrid_resampled(void* hh, float pathInterpolation, long cap, double* p
 	return n;
 }
 
+// N4: Obstacle::GetBoundaryWorldPosition of a RectangleShape / RegularPolygonShape / CircleShape at a pose
+// (obstacle.cpp:87-127): kind 0 rectangle (a = dx, b = dy), 1 regular polygon (a = radius, b = count), 2 circle
+// (a = radius, b = count).  Returns the number of vertices written to out (x, y pairs).
+int ref_shape_vertices(int kind, double a, double b, double x, double y, double theta, double* out, int cap)
+{
+	Ref<Shape> shape;
+	if (kind == 0)
+		shape = makeRef<RectangleShape>(a, b);
+	else if (kind == 1)
+		shape = makeRef<RegularPolygonShape>(a, (int)b);
+	else
+		shape = makeRef<CircleShape>(a, (int)b);
+	Obstacle o;
+	o.SetShape(shape);
+	o.SetPose(Pose2d(x, y, theta));
+	auto pts = o.GetBoundaryWorldPosition();
+	int n = 0;
+	for (auto& p : pts) {
+		if (n >= cap)
+			break;
+		out[2 * n] = p.x();
+		out[2 * n + 1] = p.y();
+		n++;
+	}
+	return n;
+}
+
+// N4: AddObstacle of such a shape into the world's map (obstacle_list_occupancy_map.cpp:29-45)
+int ref_world_add_shape(void* h, int kind, double a, double b, double x, double y, double theta)
+{
+	auto* w = (RefWorld*)h;
+	Ref<Shape> shape;
+	if (kind == 0)
+		shape = makeRef<RectangleShape>(a, b);
+	else if (kind == 1)
+		shape = makeRef<RegularPolygonShape>(a, (int)b);
+	else
+		shape = makeRef<CircleShape>(a, (int)b);
+	auto o = makeRef<Obstacle>();
+	o->SetShape(shape);
+	o->SetPose(Pose2d(x, y, theta));
+	w->obstacles.push_back(o);
+	return w->map->AddObstacle(o) ? 1 : 0;
+}
+
 // N2: the nearest-obstacle / nearest-Voronoi-edge cell grids of the planner's GVD (after its last Update), (row, col)
 // pairs, rows*cols*2 ints each -- the lookups Smoother::Smooth makes (smoother.cpp:110,118).
 void ref_hybrid_gvd_cells(void* hh, int32_t* nearestObstacle, int32_t* nearestEdge)

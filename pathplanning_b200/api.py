@@ -182,6 +182,21 @@ class Context:
         self._check(ppx.ppx_map_upload(self._h, C.byref(d), _ptr(keep[0]), _ptr(keep[1]), _ptr(keep[2])))
         self.map = desc
 
+    def rasterize(self, desc: "MapDesc", polygons, occupancy=None, first_id=0):
+        """Shape::RasterizeLine + ObstacleListOccupancyMap::AddObstacle (obstacle.cpp:7-85,
+        obstacle_list_occupancy_map.cpp:29-45) for a list of polygons given by their world-frame vertices ((k, 2)
+        arrays, as Obstacle::GetBoundaryWorldPosition returns them) -> occupancy (rows, cols) int32, -1 = free."""
+        occ = (np.full((desc.rows, desc.cols), -1, np.int32) if occupancy is None
+               else np.ascontiguousarray(occupancy, np.int32).copy())
+        polys = [np.ascontiguousarray(p, np.float64).reshape(-1, 2) for p in polygons]
+        offsets = np.zeros(len(polys) + 1, np.int32)
+        offsets[1:] = np.cumsum([len(p) for p in polys])
+        verts = np.concatenate(polys) if polys else np.zeros((0, 2))
+        assert occ.max(initial=-1) < first_id or not polys, "first_id must exceed the ids already in the grid"
+        d = desc.to_c()
+        self._check(ppx.ppx_map_rasterize(self.handle, C.byref(d), len(polys), _ptr(offsets), _ptr(verts), first_id, _ptr(occ)))
+        return occ
+
     def build_map(self, desc: MapDesc, occupancy, pathcost=None, want_sqdist=True):
         """ppx_map_build: occupancy grid in, obstacle squared-distance map computed on the device (N1)."""
         cells = desc.rows * desc.cols

@@ -75,6 +75,20 @@ void TestHybridAStar(const Ref<Device>& dev)
 		std::printf("smoother: status %d, max displacement %.4f m\n", (int)st, moved);
 	}
 
+	// an obstacle outline rasterised on the device (ObstacleListOccupancyMap::AddObstacle): a 2 m x 1 m rectangle
+	{
+		auto m2 = std::make_shared<OccupancyMap>(dev, 0.1f, 20.0f, 20.0f, lb, ub);
+		int id0 = m2->AddObstacle({ { 1.0, 0.5 }, { -1.0, 0.5 }, { -1.0, -0.5 }, { 1.0, -0.5 } });
+		int id1 = m2->AddObstacle({ { 5.0, 5.0 }, { 6.0, 5.0 }, { 5.5, 6.0 } });
+		CHECK(id0 == 0 && id1 == 1);
+		int r, c;
+		CHECK(m2->WorldPositionToGridCell(1.0, 0.0, r, c) && m2->GetOccupancyValue(r, c) == 0); // on the right side
+		CHECK(m2->WorldPositionToGridCell(0.0, 0.0, r, c) && !m2->IsOccupied(r, c)); // outlines only: the inside stays free
+		CHECK(m2->WorldPositionToGridCell(5.5, 5.0, r, c) && m2->GetOccupancyValue(r, c) == 1);
+		m2->Update();
+		CHECK(m2->WorldPositionToGridCell(0.0, 0.0, r, c) && std::fabs(m2->GetDistanceToNearestObstacle(r, c) - 0.5f) < 0.11f);
+	}
+
 	// a wall across the map with no gap: the goal becomes unreachable -> Status::Failure
 	int r0, c0;
 	for (double y = -10.0; y < 10.0; y += 0.05) {

@@ -116,6 +116,11 @@ class World:
         return lib().ref_world_add_rectangle(self.h, C.c_double(dx), C.c_double(dy), C.c_double(x), C.c_double(y),
                                              C.c_double(theta))
 
+    def add_shape(self, kind, a, b, x, y, theta):
+        """kind 0 RectangleShape(a, b), 1 RegularPolygonShape(a, int(b)), 2 CircleShape(a, int(b)) at Pose2d(x, y, theta)"""
+        return lib().ref_world_add_shape(self.h, C.c_int(kind), C.c_double(a), C.c_double(b), C.c_double(x), C.c_double(y),
+                                         C.c_double(theta))
+
     def set_cells(self, rows, cols, obstacle_id=0):
         rows = np.ascontiguousarray(rows, np.int32)
         cols = np.ascontiguousarray(cols, np.int32)
@@ -244,6 +249,14 @@ def nonholo_build(lb, ub, spatial_res=1.0, ang_res=0.0872, rmin=2.0, rev=1.0, fw
 DEFAULT_HYBRID = dict(min_turning_radius=2.0, direction_switching_cost=0.0, reverse_cost_multiplier=1.0,
                       forward_cost_multiplier=1.0, voronoi_cost_multiplier=1.0, num_generated_motion=5,
                       spatial_resolution=1.0, angular_resolution=0.0872)
+
+
+def shape_vertices(kind, a, b, x, y, theta, cap=256):
+    """Obstacle::GetBoundaryWorldPosition of the shape at the pose -> (k, 2) world coordinates"""
+    out = np.zeros((cap, 2), np.float64)
+    n = lib().ref_shape_vertices(C.c_int(kind), C.c_double(a), C.c_double(b), C.c_double(x), C.c_double(y), C.c_double(theta),
+                                 _p(out), C.c_int(cap))
+    return out[:n].copy()
 
 
 class Hybrid:

@@ -63,3 +63,55 @@ def test_distance_map_empty_and_single(ctx):
     rr, cc = np.indices(occ.shape)
     assert np.array_equal(sq, (rr - 5) ** 2 + (cc - 50) ** 2)
     assert np.array_equal(sq, synth.exact_sqdist(occ))
+
+
+# ---- N4: obstacle outlines rasterised on the device (ppx_map_rasterize) ---------------------------------------
+@pytest.mark.parametrize("name", ["C2", "C3"])
+def test_rasterize_parking_lot(ctx, ref, name):
+    """The bench maps: every rectangle outline through Shape::RasterizeLine on the device, ids as AddObstacle assigns
+    them -> occupancy identical to the reference's; then the distance map built from it is the reference's too."""
+    cfg = getattr(synth, name)
+    rects = synth.config_rects(cfg)
+    w = _ref_world(ref, cfg, rects)
+    occ_ref, sq_ref = w.grids()
+    polys = [ref.shape_vertices(0, dx, dy, x, y, th) for (dx, dy, x, y, th) in rects]
+    occ = ctx.rasterize(w.map_desc(), polys)
+    assert np.array_equal(occ, occ_ref), f"{(occ != occ_ref).sum()} cells differ"
+    assert np.array_equal(ctx.build_map(w.map_desc(), occ), sq_ref)
+    w.close()
+
+
+def test_rasterize_mixed_shapes(ctx, ref):
+    """Rectangles, regular polygons and circles at random poses, overlapping each other and the map border: a cell
+    shared by several outlines keeps the id of the obstacle added last; cells outside the map are dropped."""
+    cfg = dict(lb=(-20.0, -15.0, -np.pi), ub=(20.0, 15.0, np.pi), resolution=0.1)
+    w = ref.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    rng = np.random.default_rng(5)
+    polys = []
+    for i in range(300):
+        kind = int(rng.integers(0, 3))
+        a = float(rng.uniform(0.3, 6.0))
+        b = float(rng.uniform(0.3, 6.0)) if kind == 0 else float(rng.integers(3, 25))
+        x, y, th = float(rng.uniform(-22, 22)), float(rng.uniform(-17, 17)), float(rng.uniform(-np.pi, np.pi))
+        assert w.add_shape(kind, a, b, x, y, th) == 1
+        polys.append(ref.shape_vertices(kind, a, b, x, y, th))
+    w.update()
+    occ_ref, sq_ref = w.grids()
+    occ = ctx.rasterize(w.map_desc(), polys)
+    assert np.array_equal(occ, occ_ref), f"{(occ != occ_ref).sum()} cells differ"
+    assert len(np.unique(occ)) > 200  # ids survive
+    # incremental use: the second half added onto the grid of the first half
+    half = ctx.rasterize(w.map_desc(), polys[:150])
+    full = ctx.rasterize(w.map_desc(), polys[150:], occupancy=half, first_id=150)
+    assert np.array_equal(full, occ_ref)
+    assert np.array_equal(ctx.build_map(w.map_desc(), occ), sq_ref)
+    w.close()
+
+
+def test_rasterize_degenerate(ctx):
+    desc = pp.MapDesc(rows=40, cols=60, resolution=0.25, world_origin=(-5.0, -7.5), lb=(-5, -7.5, -np.pi), ub=(5, 7.5, np.pi))
+    assert (ctx.rasterize(desc, []) == -1).all()
+    one = ctx.rasterize(desc, [np.array([[0.1, 0.1]])])  # a single vertex: the edge v -> v is its own cell
+    assert (one >= 0).sum() == 1 and one[int((0.1 + 5.0) / 0.25), int((0.1 + 7.5) / 0.25)] == 0
+    out = ctx.rasterize(desc, [np.array([[100.0, 100.0], [120.0, 130.0], [90.0, 140.0]])])  # entirely outside
+    assert (out == -1).all()
