@@ -815,6 +815,7 @@ int ppx_hybrid_resample(ppx_hybrid* h, int64_t nq, const double* goals, const pp
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oRes, results, bRes, cudaMemcpyHostToDevice, ctx->stream));
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oPaths, paths, bPaths, cudaMemcpyHostToDevice, ctx->stream));
 	PPX_CUDA(ctx, cudaMemsetAsync(base + oCusp, 0, bCusp, ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(base + oPoses, 0, bPoses, ctx->stream)); // entries past count[q] read as zero
 	SearchConsts consts { h->dev, ctx->map_dev(), fast_map_derive(ctx->desc) };
 	if (!h->d_consts)
 		PPX_CUDA(ctx, cudaMalloc(&h->d_consts, sizeof(SearchConsts)));
