@@ -468,6 +468,25 @@ int ppx_smoother_set_gvd(ppx_smoother* s, const int32_t* nearest_obstacle, const
 int ppx_smoother_smooth(ppx_smoother* s, int64_t nq, const double* poses, const uint8_t* cusp, const int32_t* count,
 	int32_t max_points, double* out_poses, int32_t* status, int32_t* iterations);
 
+/* ---------------------------------------------------------------------------------------------
+ * N4 / BASELINE config C1: grid A* -- AStarN2 (algo/a_star_n2.h:29-34 over algo/a_star.h:326-434) with
+ * AStarStatePropagatorFcnN2::GetNeighborStates (algo/a_star_n2.cpp:12-28), for a batch of (start, goal) cells on
+ * the context's occupancy grid.  The reference's step-cost and heuristic callbacks (std::function) are fixed to
+ * the Euclidean cell distance (interfaces/python/scripts/example_a_star_grid.py:46-52).
+ */
+typedef struct ppx_astar_result {
+	int32_t status; /* 0 Success, -1 Failure (frontier exhausted, or an end point outside the grid), PPX_ERR_CAPACITY */
+	int32_t n_explored; /* GetExploredStates().size() */
+	int32_t n_nodes; /* search-tree nodes created */
+	int32_t path_len; /* cells on GetPath(), start and goal included */
+	double cost; /* GetOptimalCost() */
+} ppx_astar_result;
+
+/* starts / goals: nq (row, col) pairs; paths (may be NULL with max_path 0): max_path (row, col) pairs per query,
+ * -1 past path_len; max_nodes 0 = 4 * cells. */
+int ppx_astar_n2(ppx_ctx* ctx, int64_t nq, const int32_t* starts, const int32_t* goals, int32_t max_nodes, int32_t max_path,
+	ppx_astar_result* results, int32_t* paths);
+
 #ifdef __cplusplus
 }
 #endif

@@ -33,6 +33,10 @@ RRT_RESULT = np.dtype([("status", "<i4"), ("iterations", "<i4"), ("n_nodes", "<i
 assert RRT_RESULT.itemsize == 32
 
 
+ASTAR_RESULT = np.dtype([("status", np.int32), ("n_explored", np.int32), ("n_nodes", np.int32), ("path_len", np.int32),
+                         ("cost", np.float64)])
+
+
 class PPXError(RuntimeError):
     pass
 
@@ -196,6 +200,17 @@ class Context:
         d = desc.to_c()
         self._check(ppx.ppx_map_rasterize(self.handle, C.byref(d), len(polys), _ptr(offsets), _ptr(verts), first_id, _ptr(occ)))
         return occ
+
+    def astar_n2(self, starts, goals, max_path=0, max_nodes=0):
+        """AStarN2 with Euclidean step cost and heuristic (a_star_n2.cpp:12-28, a_star.h:326-434) for (row, col) cell
+        pairs on the uploaded occupancy grid -> dict(results (nq,) ASTAR_RESULT, paths (nq, max_path, 2) or None)"""
+        s = np.ascontiguousarray(starts, np.int32).reshape(-1, 2)
+        g = np.ascontiguousarray(goals, np.int32).reshape(-1, 2)
+        nq = len(s)
+        res = np.zeros(nq, ASTAR_RESULT)
+        paths = np.zeros((nq, max_path, 2), np.int32) if max_path else None
+        self._check(ppx.ppx_astar_n2(self.handle, nq, _ptr(s), _ptr(g), max_nodes, max_path, _ptr(res), _ptr(paths)))
+        return dict(results=res, paths=paths)
 
     def build_map(self, desc: MapDesc, occupancy, pathcost=None, want_sqdist=True):
         """ppx_map_build: occupancy grid in, obstacle squared-distance map computed on the device (N1)."""

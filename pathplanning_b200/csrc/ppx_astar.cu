@@ -1,0 +1,336 @@
+// libppx.so: grid A* (SURVEY N4 / BASELINE config C1) -- AStarN2 = AStar<GridCellPosition, NullAction, ..., GraphSearch>
+// (algo/a_star_n2.h:29-34, algo/a_star.h:326-434) with AStarStatePropagatorFcnN2 (algo/a_star_n2.cpp:12-28) for a batch
+// of (start, goal) cell pairs on the context's occupancy grid, one warp per query.
+//
+// The reference takes the step cost and the heuristic as std::function callbacks, which cannot cross a C ABI; this
+// entry point fixes both to the Euclidean cell distance, the pair interfaces/python/scripts/example_a_star_grid.py
+// passes (config C1).  Everything else is the reference's: neighbour order of GridCellPosition::GetNeighbors
+// (utils/grid.cpp:16-50), occupied neighbours and corner-cutting diagonals dropped, the Frontier's pop order
+// ("smallest totalCost, most recently pushed among equals", utils/frontier.h) as a binary heap on (totalCost, -push
+// sequence), Find / Contains on the cell as a dense table (0 absent, 1 explored, n+2 in the frontier as node n),
+// ProcessPossibleShortcut as a dead flag on the replaced node.  Lanes 0..7 evaluate the neighbours of the popped cell,
+// lane 0 commits them in order.
+#include <algorithm>
+#include "ppx_ctx.h"
+
+namespace {
+
+constexpr int kAstarWarps = 4;
+
+struct AstarWs {
+	uint32_t* table; // [cells]
+	int* cell; // [maxNodes] row * cols + col
+	int* parent;
+	double* g;
+	double* f;
+	uint8_t* dead;
+	double* heapF;
+	uint32_t* heapSeq;
+	uint32_t* heapNode;
+};
+
+struct AstarLayout {
+	size_t oTable, oCell, oParent, oG, oF, oDead, oHeapF, oHeapSeq, oHeapNode, bytes;
+	int maxNodes;
+	size_t cells;
+};
+
+AstarLayout astar_layout(size_t cells, int maxNodes)
+{
+	AstarLayout L;
+	size_t off = 0;
+	auto carve = [&](size_t b) {
+		size_t o = off;
+		off += (b + 255) & ~(size_t)255;
+		return o;
+	};
+	L.oTable = carve(cells * 4);
+	L.oCell = carve((size_t)maxNodes * 4);
+	L.oParent = carve((size_t)maxNodes * 4);
+	L.oG = carve((size_t)maxNodes * 8);
+	L.oF = carve((size_t)maxNodes * 8);
+	L.oDead = carve((size_t)maxNodes);
+	L.oHeapF = carve((size_t)maxNodes * 8);
+	L.oHeapSeq = carve((size_t)maxNodes * 4);
+	L.oHeapNode = carve((size_t)maxNodes * 4);
+	L.bytes = off;
+	L.maxNodes = maxNodes;
+	L.cells = cells;
+	return L;
+}
+
+__device__ __forceinline__ bool before(double fa, uint32_t sa, double fb, uint32_t sb) { return fa < fb || (fa == fb && sa > sb); }
+
+__device__ void heap_push(const AstarWs& W, int& heapSize, uint32_t& seqCounter, double f, int node)
+{
+	uint32_t seq = seqCounter++;
+	int i = heapSize++;
+	while (i > 0) {
+		int p = (i - 1) >> 1;
+		double pf = W.heapF[p];
+		uint32_t ps = W.heapSeq[p];
+		if (!before(f, seq, pf, ps))
+			break;
+		W.heapF[i] = pf;
+		W.heapSeq[i] = ps;
+		W.heapNode[i] = W.heapNode[p];
+		i = p;
+	}
+	W.heapF[i] = f;
+	W.heapSeq[i] = seq;
+	W.heapNode[i] = (uint32_t)node;
+}
+
+__device__ int heap_pop(const AstarWs& W, int& heapSize)
+{
+	int top = (int)W.heapNode[0];
+	int n = --heapSize;
+	if (n > 0) {
+		double f = W.heapF[n];
+		uint32_t seq = W.heapSeq[n], node = W.heapNode[n];
+		int i = 0;
+		while (true) {
+			int l = 2 * i + 1, r = l + 1;
+			if (l >= n)
+				break;
+			int c = l;
+			double cf = W.heapF[l];
+			uint32_t cs = W.heapSeq[l];
+			if (r < n) {
+				double rf = W.heapF[r];
+				uint32_t rs = W.heapSeq[r];
+				if (before(rf, rs, cf, cs)) {
+					c = r;
+					cf = rf;
+					cs = rs;
+				}
+			}
+			if (!before(cf, cs, f, seq))
+				break;
+			W.heapF[i] = cf;
+			W.heapSeq[i] = cs;
+			W.heapNode[i] = W.heapNode[c];
+			i = c;
+		}
+		W.heapF[i] = f;
+		W.heapSeq[i] = seq;
+		W.heapNode[i] = node;
+	}
+	return top;
+}
+
+__device__ __forceinline__ double euclid(int r0, int c0, int r1, int c1)
+{
+	double dr = (double)(r0 - r1), dc = (double)(c0 - c1);
+	return sqrt(dr * dr + dc * dc);
+}
+
+__global__ void __launch_bounds__(kAstarWarps * 32) k_astar_n2(const uint8_t* __restrict__ occ8, int rows, int cols, int64_t nq,
+	const int32_t* __restrict__ starts, const int32_t* __restrict__ goals, AstarLayout L, char* __restrict__ slabs, int maxPath,
+	ppx_astar_result* __restrict__ results, int32_t* __restrict__ paths, unsigned long long* __restrict__ queue)
+{
+	const unsigned lane = threadIdx.x & 31;
+	const size_t gwarp = (size_t)blockIdx.x * kAstarWarps + (threadIdx.x >> 5);
+	char* slab = slabs + gwarp * L.bytes;
+	AstarWs W;
+	W.table = (uint32_t*)(slab + L.oTable);
+	W.cell = (int*)(slab + L.oCell);
+	W.parent = (int*)(slab + L.oParent);
+	W.g = (double*)(slab + L.oG);
+	W.f = (double*)(slab + L.oF);
+	W.dead = (uint8_t*)(slab + L.oDead);
+	W.heapF = (double*)(slab + L.oHeapF);
+	W.heapSeq = (uint32_t*)(slab + L.oHeapSeq);
+	W.heapNode = (uint32_t*)(slab + L.oHeapNode);
+
+	while (true) {
+		long long q = 0;
+		if (lane == 0)
+			q = (long long)atomicAdd(queue, 1ull);
+		q = __shfl_sync(0xffffffffu, q, 0);
+		if (q >= nq)
+			break;
+		for (size_t i = lane; i < L.cells; i += 32)
+			W.table[i] = 0u;
+		__syncwarp();
+		const int sr = starts[2 * q], sc = starts[2 * q + 1], gr = goals[2 * q], gc = goals[2 * q + 1];
+		int heapSize = 0, numNodes = 0, nExplored = 0, status = 1, solution = -1; // lane 0's copies are the state
+		uint32_t seqCounter = 0;
+		const bool okEnds = sr >= 0 && sr < rows && sc >= 0 && sc < cols && gr >= 0 && gr < rows && gc >= 0 && gc < cols;
+		if (!okEnds)
+			status = PPX_ERR_INVALID;
+		if (lane == 0 && okEnds) { // InitializeSearch, a_star.h:350-364: root in the frontier AND in the explored set
+			W.cell[0] = sr * cols + sc;
+			W.parent[0] = -1;
+			W.g[0] = 0.0;
+			W.f[0] = 0.0;
+			W.dead[0] = 0;
+			numNodes = 1;
+			heap_push(W, heapSize, seqCounter, 0.0, 0);
+			W.table[sr * cols + sc] = 2u; // node 0 in the frontier
+			nExplored = 1;
+		}
+		__syncwarp();
+		while (status == 1) {
+			int n = -1;
+			if (lane == 0) {
+				while (heapSize > 0) {
+					int m = heap_pop(W, heapSize);
+					if (W.dead[m])
+						continue; // m_frontier.Remove
+					n = m;
+					break;
+				}
+				if (n < 0)
+					status = -1; // Status::Failure: frontier exhausted
+				else if (W.cell[n] == gr * cols + gc) { // IsSolution
+					solution = n;
+					status = 0;
+					n = -1;
+				} else {
+					if (n != 0)
+						nExplored++; // the root was inserted by InitializeSearch already
+					W.table[W.cell[n]] = 1u; // explored, no longer in the frontier
+				}
+			}
+			n = __shfl_sync(0xffffffffu, n, 0);
+			status = __shfl_sync(0xffffffffu, status, 0);
+			if (n < 0)
+				break;
+			const int cell = W.cell[n];
+			const int r = cell / cols, c = cell % cols;
+			// GetNeighbors order (utils/grid.cpp:16-50): left column (same, bottom, top), right column, bottom, top
+			int nr = r, nc = c;
+			bool exists = false;
+			if (lane < 8) {
+				const int dr[8] = { 0, -1, 1, 0, -1, 1, -1, 1 };
+				const int dc[8] = { -1, -1, -1, 1, 1, 1, 0, 0 };
+				nr = r + dr[lane];
+				nc = c + dc[lane];
+				exists = nr >= 0 && nr < rows && nc >= 0 && nc < cols;
+				if (exists && occ8[(size_t)nr * cols + nc])
+					exists = false; // IsOccupied(n)
+				if (exists && nr != r && nc != c && occ8[(size_t)nr * cols + c] && occ8[(size_t)r * cols + nc])
+					exists = false; // diagonal between two occupied cells
+			}
+			double step = 0.0, h = 0.0;
+			uint32_t entry = 0;
+			if (exists) {
+				step = euclid(r, c, nr, nc);
+				h = euclid(nr, nc, gr, gc);
+				entry = W.table[(size_t)nr * cols + nc];
+			}
+			const double parentG = W.g[n];
+			for (int j = 0; j < 8; j++) { // commit in order (lane 0 holds the search state)
+				const bool ex = __shfl_sync(0xffffffffu, (int)exists, j) != 0;
+				const double st = __shfl_sync(0xffffffffu, step, j), hj = __shfl_sync(0xffffffffu, h, j);
+				const int cr = __shfl_sync(0xffffffffu, nr, j), cc = __shfl_sync(0xffffffffu, nc, j);
+				if (!ex || lane != 0 || status != 1)
+					continue;
+				const int ci = cr * cols + cc;
+				const uint32_t e = W.table[ci]; // re-read: an earlier neighbour cannot alias it, but keep it simple
+				const double g = parentG + st, f = g + hj;
+				bool push = false;
+				if (e == 0u)
+					push = true;
+				else if (e >= 2u) { // ProcessPossibleShortcut, a_star.h:412-421
+					const int fn = (int)(e - 2u);
+					if (W.f[fn] > f) {
+						W.dead[fn] = 1;
+						push = true;
+					}
+				}
+				if (push) {
+					if (numNodes >= L.maxNodes) {
+						status = PPX_ERR_CAPACITY;
+						continue;
+					}
+					const int m = numNodes++;
+					W.cell[m] = ci;
+					W.parent[m] = n;
+					W.g[m] = g;
+					W.f[m] = f;
+					W.dead[m] = 0;
+					heap_push(W, heapSize, seqCounter, f, m);
+					W.table[ci] = (uint32_t)m + 2u;
+				}
+			}
+			(void)entry;
+			__syncwarp();
+			status = __shfl_sync(0xffffffffu, status, 0);
+		}
+		if (lane == 0) {
+			ppx_astar_result res;
+			res.status = status == 1 ? -1 : status;
+			res.n_explored = nExplored;
+			res.n_nodes = numNodes;
+			res.path_len = 0;
+			res.cost = PPX_INF;
+			if (status == 0 && solution >= 0) {
+				res.cost = W.g[solution]; // GetOptimalCost
+				int depth = 0;
+				for (int m = solution; m >= 0; m = W.parent[m])
+					depth++;
+				res.path_len = depth;
+				if (paths && maxPath > 0) {
+					int32_t* out = paths + (size_t)q * maxPath * 2;
+					int pos = depth - 1;
+					for (int m = solution; m >= 0; m = W.parent[m], pos--) {
+						if (pos >= maxPath)
+							continue;
+						out[2 * pos] = W.cell[m] / cols;
+						out[2 * pos + 1] = W.cell[m] % cols;
+					}
+				}
+			}
+			results[q] = res;
+		}
+		__syncwarp();
+	}
+}
+
+}
+
+extern "C" int ppx_astar_n2(ppx_ctx* ctx, int64_t nq, const int32_t* starts, const int32_t* goals, int32_t max_nodes,
+	int32_t max_path, ppx_astar_result* results, int32_t* paths)
+{
+	if (!ctx)
+		return PPX_ERR_INVALID;
+	PPX_REQUIRE(ctx, ctx->has_map && ctx->d_occ8, "ppx_astar_n2 needs a map with an occupancy grid");
+	PPX_REQUIRE(ctx, nq >= 0 && max_path >= 0 && max_nodes >= 0, "bad arguments");
+	PPX_REQUIRE(ctx, nq == 0 || (starts && goals && results), "bad arguments");
+	PPX_REQUIRE(ctx, max_path == 0 || paths, "max_path > 0 needs the paths array");
+	if (nq == 0)
+		return PPX_OK;
+	const size_t cells = ctx->cells;
+	const int maxNodes = max_nodes > 0 ? max_nodes : (int)std::min<size_t>(4 * cells + 16, (size_t)1 << 28);
+	AstarLayout L = astar_layout(cells, maxNodes);
+	const int warps = (int)std::min<int64_t>(nq, (int64_t)ctx->num_sms * kAstarWarps * 2);
+	const int ctas = (warps + kAstarWarps - 1) / kAstarWarps;
+	char* slabs;
+	PPX_CHECK(ppx_scratch(ctx, 7, (size_t)ctas * kAstarWarps * L.bytes, (void**)&slabs));
+	size_t off = 0;
+	auto carve = [&](size_t b) {
+		size_t o = off;
+		off += (b + 255) & ~(size_t)255;
+		return o;
+	};
+	const size_t bEnds = (size_t)nq * 8, bRes = (size_t)nq * sizeof(ppx_astar_result), bPaths = (size_t)nq * max_path * 8;
+	const size_t oS = carve(bEnds), oG = carve(bEnds), oR = carve(bRes), oP = carve(bPaths);
+	char* base;
+	PPX_CHECK(ppx_scratch(ctx, 5, off, (void**)&base));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oS, starts, bEnds, cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(base + oG, goals, bEnds, cudaMemcpyHostToDevice, ctx->stream));
+	if (bPaths)
+		PPX_CUDA(ctx, cudaMemsetAsync(base + oP, 0xff, bPaths, ctx->stream)); // -1 past path_len
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
+	k_astar_n2<<<ctas, kAstarWarps * 32, 0, ctx->stream>>>(ctx->d_occ8, ctx->desc.rows, ctx->desc.cols, nq, (const int32_t*)(base + oS),
+		(const int32_t*)(base + oG), L, slabs, max_path, (ppx_astar_result*)(base + oR), max_path ? (int32_t*)(base + oP) : nullptr,
+		ctx->d_queue);
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaMemcpyAsync(results, base + oR, bRes, cudaMemcpyDeviceToHost, ctx->stream));
+	if (bPaths)
+		PPX_CUDA(ctx, cudaMemcpyAsync(paths, base + oP, bPaths, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}

@@ -121,6 +121,16 @@ class World:
         return lib().ref_world_add_shape(self.h, C.c_int(kind), C.c_double(a), C.c_double(b), C.c_double(x), C.c_double(y),
                                          C.c_double(theta))
 
+    def astar_n2(self, start, goal, cap=4096):
+        """AStarN2 with Euclidean cost / heuristic functors -> dict(status, cost, explored, seconds, path (k,2))"""
+        cost, sec = C.c_double(), C.c_double()
+        explored, plen = C.c_long(), C.c_long()
+        path = np.zeros((cap, 2), np.int32)
+        st = lib().ref_astar_n2(self.h, C.c_int(int(start[0])), C.c_int(int(start[1])), C.c_int(int(goal[0])), C.c_int(int(goal[1])),
+                                C.byref(cost), C.byref(explored), C.byref(sec), C.c_long(cap), _p(path), C.byref(plen))
+        return dict(status=int(st), cost=cost.value, explored=explored.value, seconds=sec.value, path=path[:min(plen.value, cap)].copy(),
+                    path_len=plen.value)
+
     def set_cells(self, rows, cols, obstacle_id=0):
         rows = np.ascontiguousarray(rows, np.int32)
         cols = np.ascontiguousarray(cols, np.int32)
