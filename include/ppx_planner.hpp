@@ -15,6 +15,7 @@
 // scalar methods keep the reference's signatures and run a batch of one.
 // There is NO CPU fallback: constructing a Device without a CUDA device throws.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <limits>
@@ -600,6 +601,84 @@ private:
 	bool m_dirty = true;
 	std::vector<int32_t> m_nearObstacle, m_nearEdge;
 	std::vector<Pose2d> m_currentPath;
+};
+
+// AStarN2 (algo/a_star_n2.h:29-34) over AStarStatePropagatorFcnN2 (a_star_n2.cpp:12-28) with the Euclidean step cost and
+// heuristic of example_a_star_grid.py -- the reference takes both as std::function callbacks, which cannot cross the C ABI.
+struct GridCellPosition { // utils/grid.h:8-21
+	int row = -1, col = -1;
+	bool operator==(const GridCellPosition& o) const { return row == o.row && col == o.col; }
+};
+
+class AStarN2 {
+public:
+	bool Initialize(const Ref<OccupancyMap>& map)
+	{
+		m_map = map;
+		isInitialized = (bool)map;
+		return isInitialized;
+	}
+	void SetInitState(const GridCellPosition& c) { m_init = c; }
+	void SetGoalState(const GridCellPosition& c) { m_goal = c; }
+	Status SearchPath()
+	{
+		if (!isInitialized)
+			return Status::Failure; // a_star.h:330-333
+		if (m_map->Dirty())
+			m_map->Update();
+		std::vector<Status> st;
+		std::vector<std::vector<GridCellPosition>> paths;
+		std::vector<double> costs;
+		std::vector<int> explored;
+		SearchPathBatch({ m_init }, { m_goal }, st, paths, costs, &explored);
+		m_path = paths[0];
+		m_cost = costs[0];
+		m_numExplored = explored[0];
+		return st[0];
+	}
+	/// n independent queries in one device call
+	void SearchPathBatch(const std::vector<GridCellPosition>& inits, const std::vector<GridCellPosition>& goals, std::vector<Status>& status,
+		std::vector<std::vector<GridCellPosition>>& paths, std::vector<double>& costs, std::vector<int>* numExplored = nullptr,
+		int maxPath = 4096)
+	{
+		if (!isInitialized)
+			throw std::runtime_error("AStarN2: not initialized");
+		const size_t n = inits.size();
+		if (goals.size() != n)
+			throw std::invalid_argument("SearchPathBatch: sizes differ");
+		std::vector<int32_t> s(2 * n), g(2 * n), cells(n * (size_t)maxPath * 2);
+		for (size_t i = 0; i < n; i++) {
+			s[2 * i] = inits[i].row; s[2 * i + 1] = inits[i].col;
+			g[2 * i] = goals[i].row; g[2 * i + 1] = goals[i].col;
+		}
+		std::vector<ppx_astar_result> res(n);
+		auto& dev = m_map->GetDevice();
+		dev->Check(ppx_astar_n2(dev->Context(), (int64_t)n, s.data(), g.data(), 0, maxPath, res.data(), cells.data()));
+		status.resize(n);
+		paths.assign(n, {});
+		costs.resize(n);
+		if (numExplored)
+			numExplored->resize(n);
+		for (size_t i = 0; i < n; i++) {
+			status[i] = res[i].status == 0 ? Status::Success : Status::Failure;
+			costs[i] = res[i].cost;
+			if (numExplored)
+				(*numExplored)[i] = res[i].n_explored;
+			for (int k = 0; k < std::min(res[i].path_len, maxPath); k++)
+				paths[i].push_back({ cells[(i * (size_t)maxPath + k) * 2], cells[(i * (size_t)maxPath + k) * 2 + 1] });
+		}
+	}
+	std::vector<GridCellPosition> GetPath() const { return m_path; }
+	double GetOptimalCost() const { return m_cost; }
+	int GetNumExploredStates() const { return m_numExplored; } // GetExploredStates().size()
+	bool isInitialized = false;
+
+private:
+	Ref<OccupancyMap> m_map;
+	GridCellPosition m_init, m_goal;
+	std::vector<GridCellPosition> m_path;
+	double m_cost = std::numeric_limits<double>::infinity();
+	int m_numExplored = 0;
 };
 
 } // namespace Planner

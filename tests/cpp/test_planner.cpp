@@ -89,6 +89,21 @@ void TestHybridAStar(const Ref<Device>& dev)
 		CHECK(m2->WorldPositionToGridCell(0.0, 0.0, r, c) && std::fabs(m2->GetDistanceToNearestObstacle(r, c) - 0.5f) < 0.11f);
 	}
 
+	// test_a_star.cpp:17-35 on the occupancy grid: AStarN2 from (0,0)... here (10,10) to (100,60) on the empty map
+	{
+		AStarN2 aStar;
+		CHECK(aStar.Initialize(map));
+		GridCellPosition s0 { 10, 10 }, g0 { 100, 60 };
+		aStar.SetInitState(s0);
+		aStar.SetGoalState(g0);
+		CHECK(aStar.SearchPath() == Status::Success);
+		auto cells = aStar.GetPath();
+		CHECK(!cells.empty() && cells.front() == s0 && cells.back() == g0);
+		// 50 diagonal + 40 straight steps
+		CHECK(std::fabs(aStar.GetOptimalCost() - (50 * std::sqrt(2.0) + 40)) < 1e-9 && cells.size() == 91);
+		std::printf("grid A*: %zu cells, cost %.4f, %d explored\n", cells.size(), aStar.GetOptimalCost(), aStar.GetNumExploredStates());
+	}
+
 	// a wall across the map with no gap: the goal becomes unreachable -> Status::Failure
 	int r0, c0;
 	for (double y = -10.0; y < 10.0; y += 0.05) {
