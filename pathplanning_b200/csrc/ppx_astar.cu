@@ -305,7 +305,13 @@ extern "C" int ppx_astar_n2(ppx_ctx* ctx, int64_t nq, const int32_t* starts, con
 	const size_t cells = ctx->cells;
 	const int maxNodes = max_nodes > 0 ? max_nodes : (int)std::min<size_t>(4 * cells + 16, (size_t)1 << 28);
 	AstarLayout L = astar_layout(cells, maxNodes);
-	const int warps = (int)std::min<int64_t>(nq, (int64_t)ctx->num_sms * kAstarWarps * 2);
+	int warps = (int)std::min<int64_t>(nq, (int64_t)ctx->num_sms * kAstarWarps * 2);
+	{ // one workspace per resident warp: keep the total under a quarter of the free device memory
+		size_t freeB = 0, totalB = 0;
+		PPX_CUDA(ctx, cudaMemGetInfo(&freeB, &totalB));
+		const size_t budget = std::max<size_t>(freeB / 4, L.bytes);
+		warps = (int)std::max<size_t>(1, std::min<size_t>((size_t)warps, budget / L.bytes));
+	}
 	const int ctas = (warps + kAstarWarps - 1) / kAstarWarps;
 	char* slabs;
 	PPX_CHECK(ppx_scratch(ctx, 7, (size_t)ctas * kAstarWarps * L.bytes, (void**)&slabs));
