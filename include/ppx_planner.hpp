@@ -316,7 +316,7 @@ private:
 };
 
 // HybridAStar (algo/hybrid_a_star.h:215-263, hybrid_a_star.cpp:206-304): graph search on the device.
-// Path smoothing (Smoother) is not part of the device path; GetPath() returns the pose array
+// HybridAStar does not run the smoother itself (class Smoother below does, given the GVD cell grids); GetPath() returns the pose array
 // SearchPath builds for the smoother (hybrid_a_star.cpp:260-291, resampled on the device every
 // pathInterpolation with the cusp points snapped in) -- what the reference's GetPath() returns when
 // smoothing does not succeed (:294-297); GetGraphSearchStates() returns the node states of the solution.
