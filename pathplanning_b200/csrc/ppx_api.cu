@@ -145,6 +145,8 @@ int ppx_ctx_create(int device, ppx_ctx** out)
 	ctx->stream = ctx->own_stream;
 	PPX_CUDA(ctx, cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device));
 	PPX_CUDA(ctx, cudaMalloc(&ctx->d_queue, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_rsq, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
+	PPX_CUDA(ctx, cudaMemset(ctx->d_rsq, 0, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
 	*out = ctx;
 	return PPX_OK;
 }
@@ -161,6 +163,7 @@ int ppx_ctx_destroy(ppx_ctx* ctx)
 	cudaFree(ctx->d_clearance);
 	cudaFree(ctx->d_occ8);
 	cudaFree(ctx->d_queue);
+	cudaFree(ctx->d_rsq);
 	cudaFree(ctx->d_nonholo);
 	cudaFree(ctx->d_wf_cost);
 	cudaFree(ctx->d_wf_explored);
@@ -203,6 +206,13 @@ int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value)
 		return PPX_ERR_INVALID;
 	if (!strcmp(name, "rs_filter")) {
 		ctx->rs_filter = value != 0;
+		return PPX_OK;
+	}
+	if (!strcmp(name, "rs_overlap")) {
+		PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+		PPX_CUDA(ctx, cudaMemset(ctx->d_rsq, 0, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
+		ctx->rs_slot = 0;
+		ctx->rs_overlap = value != 0;
 		return PPX_OK;
 	}
 	return ppx_fail(ctx, PPX_ERR_INVALID, "unknown option %s", name);

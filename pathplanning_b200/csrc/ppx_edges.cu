@@ -115,9 +115,18 @@ __device__ __noinline__ void audit_sample(const RSFastLane<SmemLen>& lane, const
 template <bool kAudit, int kCtas>
 __global__ void __launch_bounds__(kThreads, kCtas) k_check_rs(MapDev map, FastMap fm, int64_t n,
 	const ppx_rs_edge* __restrict__ edges, double r, float minSafeRadius, float minStep, uint8_t* __restrict__ valid,
-	float* __restrict__ last, uint32_t* __restrict__ samples, unsigned long long* __restrict__ queue, AuditOut* audit)
+	float* __restrict__ last, uint32_t* __restrict__ samples, unsigned long long* __restrict__ queue, AuditOut* audit,
+	unsigned long long* nextQueue)
 {
 	__shared__ double s_len[5][kThreads];
+	if (nextQueue) { // overlapped launches ("rs_overlap"): zero the successor's cursor, then let the successor in
+		if (blockIdx.x == 0 && threadIdx.x == 0) {
+			atomicExch(nextQueue, 0ull);
+			__threadfence();
+		}
+		__syncthreads();
+		asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+	}
 	const unsigned lane_id = threadIdx.x & 31;
 	const unsigned lt_mask = (1u << lane_id) - 1;
 	double* mycol = &s_len[0][threadIdx.x];
@@ -211,6 +220,8 @@ __global__ void __launch_bounds__(kThreads, kCtas) k_check_rs(MapDev map, FastMa
 			}
 		}
 	}
+	if (nextQueue) // this launch must not complete before its predecessor has (stream order for whatever follows)
+		asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 __global__ void __launch_bounds__(kThreads) k_check_csteer(MapDev map, int64_t n, const ppx_csteer_edge* __restrict__ edges,
@@ -356,14 +367,33 @@ int ppx_is_state_valid(ppx_ctx* ctx, int64_t n, const double* poses, const ppx_v
 }
 
 static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, double min_turning_radius,
-	const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, uint32_t* d_samples, int queueSlot)
+	const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, uint32_t* d_samples, int queueSlot, bool overlap = false)
 {
 	FastMap fm = fast_map_derive(ctx->desc);
 	if (!ctx->rs_filter)
 		fm.enabled = 0;
+	if (overlap) {
+		// programmatic dependent launch: this kernel may start while the previous one on the stream still drains
+		cudaLaunchConfig_t cfg = {};
+		cfg.gridDim = dim3((unsigned)grid_for(ctx, n, kThreads, kCheckCtasPerSm));
+		cfg.blockDim = dim3(kThreads);
+		cfg.dynamicSmemBytes = 0;
+		cfg.stream = ctx->stream;
+		cudaLaunchAttribute attr[1];
+		attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		attr[0].val.programmaticStreamSerializationAllowed = 1;
+		cfg.attrs = attr;
+		cfg.numAttrs = 1;
+		unsigned long long* q = ctx->d_rsq + queueSlot;
+		unsigned long long* next = ctx->d_rsq + (queueSlot + 1) % ppx_ctx::kMaxChunks;
+		PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_check_rs<false, kCheckCtasPerSm>, ctx->map_dev(), fm, n, d_edges, min_turning_radius,
+			vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, q, (AuditOut*)nullptr, next));
+		ctx->launches++;
+		return PPX_OK;
+	}
 	k_check_rs<false, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
 		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples,
-		ctx->d_queue + queueSlot, nullptr);
+		ctx->d_queue + queueSlot, nullptr, nullptr);
 	PPX_LAUNCHED(ctx);
 	return PPX_OK;
 }
@@ -375,6 +405,11 @@ int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (d_edges && d_valid && d_last)), "bad arguments");
 	if (n == 0)
 		return PPX_OK;
+	if (ctx->rs_overlap) { // no memset between the kernels: each launch zeroes the cursor of the next one
+		const int slot = ctx->rs_slot;
+		ctx->rs_slot = (slot + 1) % ppx_ctx::kMaxChunks;
+		return launch_check_rs(ctx, n, d_edges, min_turning_radius, vp, d_valid, d_last, d_samples, slot, true);
+	}
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
 	return launch_check_rs(ctx, n, d_edges, min_turning_radius, vp, d_valid, d_last, d_samples, 0);
 }
@@ -400,7 +435,7 @@ int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, 
 	FastMap fm = fast_map_derive(ctx->desc);
 	k_check_rs<true, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
 		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
-		d_audit);
+		d_audit, nullptr);
 	PPX_LAUNCHED(ctx);
 	AuditOut h {};
 	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));

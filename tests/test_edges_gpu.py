@@ -217,3 +217,48 @@ def test_rs_filter_odd_edges(ctx, c3_edges):
         ctx.set_option("rs_filter", 1)
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2])
     assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
+
+
+def test_rs_overlap_option(ctx, c3_edges):
+    """"rs_overlap": consecutive device-pointer launches may overlap (programmatic dependent launch).  Twelve launches
+    over three different edge sets with own output arrays, then stream-ordered copies back: every result equals the
+    serial one, also for the last launches (a launch must not complete before its predecessor)."""
+    import ctypes as C
+    from pathplanning_b200.lib import ppx
+    edges, _ = c3_edges
+    n = 60000
+    vp = pp.ValidatorParams(1.0, 0.1)
+    sets = [np.ascontiguousarray(edges[i * n:(i + 1) * n]) for i in range(3)]
+    want = [ctx.check_edges_rs(e, 2.0, vp) for e in sets]
+    vpc = vp.to_c()
+
+    def dalloc(nbytes):
+        p = C.c_void_p()
+        ctx._check(ppx.ppx_dev_alloc(ctx.handle, nbytes, C.byref(p)))
+        return p
+
+    d_edges = [dalloc(e.nbytes) for e in sets]
+    for d, e in zip(d_edges, sets):
+        ctx._check(ppx.ppx_memcpy_h2d(ctx.handle, d, e.ctypes.data_as(C.c_void_p), e.nbytes))
+    launches = 12
+    d_valid = [dalloc(n) for _ in range(launches)]
+    d_last = [dalloc(4 * n) for _ in range(launches)]
+    ctx.set_option("rs_overlap", 1)
+    try:
+        for rep in range(2):
+            for k in range(launches):
+                ctx._check(ppx.ppx_check_edges_rs_dev(ctx.handle, n, d_edges[k % 3], 2.0, C.byref(vpc), d_valid[k], d_last[k], None))
+            for k in reversed(range(launches)):
+                v = np.zeros(n, np.uint8)
+                l = np.zeros(n, np.float32)
+                ctx._check(ppx.ppx_memcpy_d2h(ctx.handle, v.ctypes.data_as(C.c_void_p), d_valid[k], n))
+                ctx._check(ppx.ppx_memcpy_d2h(ctx.handle, l.ctypes.data_as(C.c_void_p), d_last[k], 4 * n))
+                assert np.array_equal(v.astype(bool), want[k % 3][0]), (rep, k)
+                assert np.array_equal(l.view(np.uint32), want[k % 3][1].view(np.uint32)), (rep, k)
+    finally:
+        ctx.set_option("rs_overlap", 0)
+    # back to serial launches on the same context
+    again = ctx.check_edges_rs(sets[0], 2.0, vp)
+    assert np.array_equal(again[0], want[0][0]) and np.array_equal(again[1].view(np.uint32), want[0][1].view(np.uint32))
+    for p in d_edges + d_valid + d_last:
+        ppx.ppx_dev_free(ctx.handle, p)

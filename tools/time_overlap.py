@@ -78,8 +78,12 @@ def main():
 
     for rep in range(2):
         a, b = timed(False), timed(True)
+        ctxs[0].set_option("rs_overlap", 1)
+        c = timed(False)
+        ctxs[0].set_option("rs_overlap", 0)
         print(f"one context: {a * 1e3:.1f} us per 1M-edge launch = {N / a / 1e6:.2f} G edges/s; two contexts alternating: "
-              f"{b * 1e3:.1f} us per launch = {N / b / 1e6:.2f} G edges/s (results identical)", flush=True)
+              f"{b * 1e3:.1f} us per launch = {N / b / 1e6:.2f} G edges/s; one context with rs_overlap (programmatic dependent "
+              f"launch): {c * 1e3:.1f} us = {N / c / 1e6:.2f} G edges/s (results identical)", flush=True)
 
 
 if __name__ == "__main__":
