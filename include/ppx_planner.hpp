@@ -68,6 +68,8 @@ public:
 	Device(const Device&) = delete;
 	Device& operator=(const Device&) = delete;
 	ppx_ctx* Context() const { return m_ctx; }
+	/// ppx_ctx_set_option: "rs_filter", "rs_overlap" (include/ppx.h)
+	void SetOption(const char* name, long long value) { Check(ppx_ctx_set_option(m_ctx, name, value)); }
 	void Check(int rc) const
 	{
 		if (rc != PPX_OK)
