@@ -440,15 +440,16 @@ def ours_main(args):
                                   e.data_ptr(), None, None, None)
         assert rc == 0, ppx.ppx_last_error(ctx.handle)
         d_edges.append(e)
-    d_valid = torch.empty(n, dtype=torch.uint8, device=dev)
-    d_last = torch.empty(n, dtype=torch.float32, device=dev)
+    # every batch has its own output arrays (what the overlapped launches of "rs_overlap" require)
+    outs = [(torch.empty(n, dtype=torch.uint8, device=dev), torch.empty(n, dtype=torch.float32, device=dev)) for _ in range(N_BATCHES)]
+    d_valid, d_last = outs[0]
     d_samples = torch.empty(n, dtype=torch.int32, device=dev)
     d_word = torch.empty(n, dtype=torch.int32, device=dev)
 
     def step(b, samples=False):
         if args.mode == "check":
-            rc = ppx.ppx_check_edges_rs_dev(ctx.handle, n, d_edges[b].data_ptr(), RMIN, ctypes.byref(vp), d_valid.data_ptr(),
-                                            d_last.data_ptr(), d_samples.data_ptr() if samples else None)
+            rc = ppx.ppx_check_edges_rs_dev(ctx.handle, n, d_edges[b].data_ptr(), RMIN, ctypes.byref(vp), outs[b][0].data_ptr(),
+                                            outs[b][1].data_ptr(), d_samples.data_ptr() if samples else None)
         else:
             rc = ppx.ppx_connect_check_rs_dev(ctx.handle, n, d_starts[b].data_ptr(), d_goals[b].data_ptr(), ctypes.byref(cp),
                                               ctypes.byref(vp), d_valid.data_ptr(), d_last.data_ptr(), d_word.data_ptr(), None, None)
@@ -467,6 +468,29 @@ def ours_main(args):
     valid_frac = float(d_valid.float().mean().item())
     in_bytes = 72 if args.mode == "check" else 48
     bytes_per_edge = in_bytes + 8 + 4.0 * mean_samples
+
+    # Launch mode of the timed loop.  "rs_overlap": consecutive launches on the stream overlap by programmatic dependent
+    # launch, so that the drain of one batch (a few long sample chains) is filled by the next batch.
+    # Used only after it has reproduced the serial results of every batch here; the serial figure is reported as well.
+    overlap_ok, want = False, None
+    if args.mode == "check" and not args.serial_only:
+        for b in range(N_BATCHES):
+            step(b)
+        torch.cuda.synchronize()
+        want = [(v.clone(), l.clone()) for v, l in outs]
+        for v, l in outs:
+            v.zero_()
+            l.zero_()
+        try:
+            ctx.set_option("rs_overlap", 1)
+            for i in range(3 * N_BATCHES):
+                step(i % N_BATCHES)
+            torch.cuda.synchronize()
+            overlap_ok = all(torch.equal(outs[b][0], want[b][0]) and torch.equal(outs[b][1], want[b][1]) for b in range(N_BATCHES))
+        except Exception:  # pragma: no cover
+            overlap_ok = False
+        if not overlap_ok:
+            ctx.set_option("rs_overlap", 0)
 
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -501,6 +525,29 @@ def ours_main(args):
     ms_total = float(t.item())
     ms_per_step = ms_total / args.steps
     value = world * n / (ms_per_step * 1e-3)
+
+    serial = None
+    if overlap_ok:
+        # the overlapped loop must have left every batch's serial results behind; then the same loop, strictly serial
+        if not all(torch.equal(outs[b][0], want[b][0]) and torch.equal(outs[b][1], want[b][1]) for b in range(N_BATCHES)):
+            raise RuntimeError("overlapped launches gave different results")
+        ctx.set_option("rs_overlap", 0)
+        for i in range(3):
+            step(i % N_BATCHES)
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        for i in range(args.steps):
+            step(i % N_BATCHES)
+        s1.record(stream)
+        barrier()
+        ts = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        serial_ms = float(ts.item()) / args.steps
+        serial = {"value": world * n / (serial_ms * 1e-3), "unit": "edges/s", "ms_per_step": serial_ms,
+                  "what": "the same loop with strictly serial launches (option off): every launch waits for the last sample "
+                          "chain of the previous one"}
 
     # e2e: the host-buffer C-ABI call a reference-side caller makes (pinned host memory)
     if args.mode == "check":
@@ -539,16 +586,6 @@ def ours_main(args):
     e2e_value = world * n * e2e_steps / float(te.item())
     sampler.stop()
 
-    # extra, reported beside `value` (which stays strictly serial launches): the same launches with the "rs_overlap"
-    # option, so that the drain tail of one batch (a few long sample chains) is overlapped by the next
-    # batch.  Own output arrays per batch, results compared with the serial ones.
-    pipelined = None
-    if args.mode == "check" and world == 1 and not args.no_pipelined:
-        try:
-            pipelined = pipelined_section(args, pp, ppx, synth, desc, occ, dev, n, d_edges, vp, stream, ctx)
-        except Exception as e:  # pragma: no cover
-            pipelined = {"error": f"{type(e).__name__}: {e}"}
-
     hybrid = None
     if not args.no_hybrid:
         try:
@@ -563,6 +600,8 @@ def ours_main(args):
         else:
             peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
         achieved = bytes_per_edge * n / (ms_per_step * 1e-3) / 1e9
+        if serial:
+            serial["roofline_frac"] = bytes_per_edge * n / (serial["ms_per_step"] * 1e-3) / 1e9 / peak
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
@@ -572,6 +611,9 @@ def ours_main(args):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "mode": args.mode, "edges_per_gpu_per_step": n,
+                       "launches": ("overlapped: ppx_ctx_set_option(rs_overlap) = programmatic dependent launch on one stream, own "
+                                    "output arrays per batch, results verified against serial launches; see \"serial\"")
+                       if overlap_ok else "serial",
                        "mean_samples_per_edge": mean_samples, "valid_fraction": valid_frac,
                        "l2": f"{N_BATCHES} rotating edge batches ({N_BATCHES * n * in_bytes / 1e6:.0f} MB) > 126 MB L2; the 16 MB clearance grid is meant to stay L2-resident"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -584,55 +626,13 @@ def ours_main(args):
                     "steps": e2e_steps},
             "gpu_launches": launches,
             "clocks": sampler.summary(),
-            "overlapped": pipelined,
+            "serial": serial,
             "hybrid": hybrid,
         }
         _emit(line)
     if world > 1:
         dist.destroy_process_group()
     ctx.close()
-
-
-def pipelined_section(args, pp, ppx, synth, desc, occ, dev, n, d_edges, vp, stream, ctx):
-    """The same launches on the same context and stream with the "rs_overlap" option: consecutive launches overlap by
-    programmatic dependent launch, every batch has its own output arrays, results compared with the serial ones."""
-    import torch
-    nb = len(d_edges)
-    outs = [(torch.empty(n, dtype=torch.uint8, device=dev), torch.empty(n, dtype=torch.float32, device=dev)) for _ in range(nb)]
-
-    def launch(b):
-        rc = ppx.ppx_check_edges_rs_dev(ctx.handle, n, d_edges[b].data_ptr(), RMIN, ctypes.byref(vp), outs[b][0].data_ptr(),
-                                        outs[b][1].data_ptr(), None)
-        assert rc == 0, ppx.ppx_last_error(ctx.handle)
-
-    for b in range(nb):
-        launch(b)
-    torch.cuda.synchronize()
-    want = [(v.clone(), l.clone()) for v, l in outs]
-    for v, l in outs:
-        v.zero_()
-        l.zero_()
-    ctx.set_option("rs_overlap", 1)
-    try:
-        for i in range(8):
-            launch(i % nb)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for i in range(args.steps):
-            launch(i % nb)
-        e1.record(stream)
-        torch.cuda.synchronize()
-    finally:
-        ctx.set_option("rs_overlap", 0)
-    ms = e0.elapsed_time(e1) / args.steps
-    same = all(torch.equal(outs[b][0], want[b][0]) and torch.equal(outs[b][1], want[b][1]) for b in range(nb))
-    if not same:
-        raise RuntimeError("overlapped launches gave different results")
-    return {"value": n / (ms * 1e-3), "unit": "edges/s", "ms_per_step": ms, "steps": args.steps,
-            "what": "the same launches on the same stream with ppx_ctx_set_option(\"rs_overlap\", 1): consecutive launches "
-                    "overlap by programmatic dependent launch (the drain of one batch is filled by the next), own output "
-                    "arrays per batch; results identical to the serial run"}
 
 
 def main():
@@ -644,7 +644,7 @@ def main():
     ap.add_argument("--mode", default="check", choices=["check", "solve_check"])
     ap.add_argument("--cpu-edges-per-core", type=int, default=250_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-pipelined", action="store_true", help="skip the rs_overlap measurement")
+    ap.add_argument("--serial-only", action="store_true", help="time strictly serial launches (no rs_overlap)")
     ap.add_argument("--no-hybrid", action="store_true", help="skip the Hybrid A* (config C4) section of the JSON line")
     ap.add_argument("--hybrid-queries", type=int, default=4096)
     ap.add_argument("--cpu-plans-per-core", type=int, default=16)
