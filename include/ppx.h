@@ -115,7 +115,9 @@ int ppx_map_build(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* occupan
  * Obstacle::GetBoundaryWorldPosition returns them (the rotation by the pose stays on the host: its libm decides the
  * cell of a vertex on a cell border); offsets[p] .. offsets[p+1] are polygon p's vertices.  occupancy (host, rows *
  * cols, in/out): cells of polygon p receive id first_id + p, a later polygon overwrites an earlier one like the
- * reference's sequential adds; first_id must exceed every id already in the grid.  Follow with ppx_map_build.
+ * reference's sequential adds; first_id must exceed every id already in the grid.  first_id = -1 removes instead:
+ * the outline cells of the given polygons are set free whoever owns them, as ObstacleListOccupancyMap::RemoveObstacle
+ * does (obstacle_list_occupancy_map.cpp:47-61).  Follow with ppx_map_build.
  */
 int ppx_map_rasterize(ppx_ctx* ctx, const ppx_map_desc* desc, int32_t n_polygons, const int32_t* offsets,
 	const double* vertices, int32_t first_id, int32_t* occupancy);

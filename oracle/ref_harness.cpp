@@ -808,6 +808,15 @@ int ref_world_add_shape(void* h, int kind, double a, double b, double x, double 
 	return w->map->AddObstacle(o) ? 1 : 0;
 }
 
+// N4: RemoveObstacle of the index-th obstacle added to the world (obstacle_list_occupancy_map.cpp:47-61)
+int ref_world_remove_obstacle(void* h, int index)
+{
+	auto* w = (RefWorld*)h;
+	if (index < 0 || index >= (int)w->obstacles.size())
+		return 0;
+	return w->map->RemoveObstacle(w->obstacles[index]) ? 1 : 0;
+}
+
 // N2: the nearest-obstacle / nearest-Voronoi-edge cell grids of the planner's GVD (after its last Update), (row, col)
 // pairs, rows*cols*2 ints each -- the lookups Smoother::Smooth makes (smoother.cpp:110,118).
 void ref_hybrid_gvd_cells(void* hh, int32_t* nearestObstacle, int32_t* nearestEdge)

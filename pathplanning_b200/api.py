@@ -189,14 +189,15 @@ class Context:
     def rasterize(self, desc: "MapDesc", polygons, occupancy=None, first_id=0):
         """Shape::RasterizeLine + ObstacleListOccupancyMap::AddObstacle (obstacle.cpp:7-85,
         obstacle_list_occupancy_map.cpp:29-45) for a list of polygons given by their world-frame vertices ((k, 2)
-        arrays, as Obstacle::GetBoundaryWorldPosition returns them) -> occupancy (rows, cols) int32, -1 = free."""
+        arrays, as Obstacle::GetBoundaryWorldPosition returns them) -> occupancy (rows, cols) int32, -1 = free.
+        first_id = -1 removes the outlines instead (RemoveObstacle, :47-61)."""
         occ = (np.full((desc.rows, desc.cols), -1, np.int32) if occupancy is None
                else np.ascontiguousarray(occupancy, np.int32).copy())
         polys = [np.ascontiguousarray(p, np.float64).reshape(-1, 2) for p in polygons]
         offsets = np.zeros(len(polys) + 1, np.int32)
         offsets[1:] = np.cumsum([len(p) for p in polys])
         verts = np.concatenate(polys) if polys else np.zeros((0, 2))
-        assert occ.max(initial=-1) < first_id or not polys, "first_id must exceed the ids already in the grid"
+        assert first_id == -1 or occ.max(initial=-1) < first_id or not polys, "first_id must exceed the ids already in the grid"
         d = desc.to_c()
         self._check(ppx.ppx_map_rasterize(self.handle, C.byref(d), len(polys), _ptr(offsets), _ptr(verts), first_id, _ptr(occ)))
         return occ

@@ -116,8 +116,12 @@ __global__ void __launch_bounds__(128) k_rasterize(int rows, int cols, double ox
 	const int id = firstId + p;
 	for (int x = x0; x <= x1; x++) {
 		const int r = steep ? y : x, c = steep ? x : y;
-		if (r >= 0 && r < rows && c >= 0 && c < cols)
-			atomicMax(&occupancy[(size_t)r * cols + c], id);
+		if (r >= 0 && r < rows && c >= 0 && c < cols) {
+			if (firstId >= 0)
+				atomicMax(&occupancy[(size_t)r * cols + c], id);
+			else
+				occupancy[(size_t)r * cols + c] = -1; // RemoveObstacle (obstacle_list_occupancy_map.cpp:47-61): cleared whoever owns it
+		}
 		err -= dy;
 		if (err < 0) {
 			y += ystep;
@@ -133,7 +137,7 @@ extern "C" int ppx_map_rasterize(ppx_ctx* ctx, const ppx_map_desc* desc, int32_t
 {
 	if (!ctx || !desc)
 		return PPX_ERR_INVALID;
-	PPX_REQUIRE(ctx, n_polygons >= 0 && offsets && occupancy && first_id >= 0, "bad arguments");
+	PPX_REQUIRE(ctx, n_polygons >= 0 && offsets && occupancy && first_id >= -1, "bad arguments");
 	PPX_REQUIRE(ctx, desc->rows > 0 && desc->cols > 0 && desc->resolution > 0.0f, "bad map description");
 	if (n_polygons == 0)
 		return PPX_OK;

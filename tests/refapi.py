@@ -131,6 +131,10 @@ class World:
         return dict(status=int(st), cost=cost.value, explored=explored.value, seconds=sec.value, path=path[:min(plen.value, cap)].copy(),
                     path_len=plen.value)
 
+    def remove_obstacle(self, index):
+        """RemoveObstacle of the index-th obstacle added to this world"""
+        return lib().ref_world_remove_obstacle(self.h, C.c_int(index))
+
     def set_cells(self, rows, cols, obstacle_id=0):
         rows = np.ascontiguousarray(rows, np.int32)
         cols = np.ascontiguousarray(cols, np.int32)

@@ -105,6 +105,15 @@ def test_rasterize_mixed_shapes(ctx, ref):
     full = ctx.rasterize(w.map_desc(), polys[150:], occupancy=half, first_id=150)
     assert np.array_equal(full, occ_ref)
     assert np.array_equal(ctx.build_map(w.map_desc(), occ), sq_ref)
+    # RemoveObstacle: the outline cells of the removed obstacles become free even where another outline crosses them
+    gone = [7, 42, 150, 299]
+    for i in gone:
+        assert w.remove_obstacle(i) == 1
+    w.update()
+    occ_ref2, sq_ref2 = w.grids()
+    occ2 = ctx.rasterize(w.map_desc(), [polys[i] for i in gone], occupancy=occ, first_id=-1)
+    assert np.array_equal(occ2, occ_ref2) and (occ2 != occ).any()
+    assert np.array_equal(ctx.build_map(w.map_desc(), occ2), sq_ref2)
     w.close()
 
 
