@@ -131,6 +131,18 @@ public:
 		m_dirty = true;
 		return id;
 	}
+	/// ObstacleListOccupancyMap::RemoveObstacle (obstacle_list_occupancy_map.cpp:47-61): the outline cells become free
+	void RemoveObstacle(const std::vector<Point2d>& boundaryWorldPosition)
+	{
+		std::vector<double> v;
+		for (auto& p : boundaryWorldPosition) {
+			v.push_back(p.x);
+			v.push_back(p.y);
+		}
+		const int32_t offsets[2] = { 0, (int32_t)boundaryWorldPosition.size() };
+		m_dev->Check(ppx_map_rasterize(m_dev->Context(), &m_desc, 1, offsets, v.data(), -1, m_occupancy.data()));
+		m_dirty = true;
+	}
 	/// OccupancyMap::Update() + GVD::Update() (occupancy_map.cpp:16-19): upload + distance map build.
 	void Update()
 	{

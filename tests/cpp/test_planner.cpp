@@ -87,6 +87,10 @@ void TestHybridAStar(const Ref<Device>& dev)
 		CHECK(m2->WorldPositionToGridCell(5.5, 5.0, r, c) && m2->GetOccupancyValue(r, c) == 1);
 		m2->Update();
 		CHECK(m2->WorldPositionToGridCell(0.0, 0.0, r, c) && std::fabs(m2->GetDistanceToNearestObstacle(r, c) - 0.5f) < 0.11f);
+		m2->RemoveObstacle({ { 1.0, 0.5 }, { -1.0, 0.5 }, { -1.0, -0.5 }, { 1.0, -0.5 } });
+		m2->Update();
+		CHECK(m2->WorldPositionToGridCell(1.0, 0.0, r, c) && !m2->IsOccupied(r, c));
+		CHECK(m2->WorldPositionToGridCell(0.0, 0.0, r, c) && m2->GetDistanceToNearestObstacle(r, c) > 5.0f); // only the triangle is left
 	}
 
 	// test_a_star.cpp:17-35 on the occupancy grid: AStarN2 from (0,0)... here (10,10) to (100,60) on the empty map
