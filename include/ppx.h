@@ -90,8 +90,10 @@ typedef struct ppx_map_desc {
 } ppx_map_desc;
 
 /*
- * Upload (or refresh after OccupancyMap::Update / GVD::Update) the grids.  Any pointer may be
- * NULL to keep the previous device copy.
+ * Upload (or refresh after OccupancyMap::Update / GVD::Update) the grids.  sqdist / occupancy may be
+ * NULL to keep the previous device copy.  pathcost == NULL keeps the previous potential only when
+ * neither of the other grids changes in this call; with a new sqdist or occupancy the potential is
+ * reset to zero (it belongs to the map it was computed for).
  *   sqdist    GVD::ObstacleDistanceMap::m_distance, squared cell distance, int32 (gvd.h:38-39)
  *   occupancy OccupancyMap::m_occupancyMatrix, >=0 means occupied (occupancy_map.h:129-130,
  *             obstacle_list_occupancy_map.cpp:63-69)
@@ -106,6 +108,29 @@ int ppx_map_upload(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* sqdist
  * proceeds like ppx_map_upload.  sqdist_out (rows*cols, may be NULL) receives the distance grid. */
 int ppx_map_build(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* occupancy, const float* pathcost,
 	int32_t* sqdist_out);
+
+/* N1, all of it: the GVD of the occupancy grid on the device -- GVD::ObstacleDistanceMap (m_distance, m_obstacle;
+ * state_validator/gvd.cpp:30-89), the Voronoi-edge set CheckVoro leaves behind (:105-131), GVD::VoronoiDistanceMap
+ * (m_distance, m_edge; :200-264) and GVD::PathCostMap (:266-283, alpha 20, dMax 30 as gvd.h:180) -- then proceeds like
+ * ppx_map_upload with the grids it built (the context's sqdist, occupancy and pathcost).  Incremental
+ * SetObstacle / UnsetObstacle (:74-89) are a rebuild here: ppx_map_rasterize the change, call this again (3 ms on
+ * 2000 x 2000).
+ *   flags  PPX_GVD_VORONOI: Voronoi edges as the reference marks them when the GVD (and with it the Voronoi map) exists
+ *          while the obstacle brushfire runs -- `GVD gvd(map); gvd.Update();` before or instead of `map.Update()`
+ *          (interfaces/python/scripts/example.py:47-48).  Without the flag: the Voronoi map the reference has when
+ *          OccupancyMap::Update() ran BEFORE the GVD was created (HybridAStar::Initialize after map->Update()): no edge
+ *          cell, Voronoi distance INT_MAX everywhere, and a potential that is a function of the obstacle distance only.
+ * Outputs (host, each may be NULL): sqdist / voro_sqdist rows*cols int32, pathcost rows*cols float,
+ * nearest_obstacle / nearest_edge rows*cols*2 int32 (row, col) pairs, (-1, -1) where there is none.
+ * Parity: the reference computes the two distance maps by a priority-queue brushfire through
+ * 8-neighbours, whose result depends on how std::priority_queue orders equal keys; it equals the exact transform used
+ * here on axis-aligned maps (C2: every grid identical) and differs in a few cells per thousand on arbitrarily rotated
+ * obstacles, where the brushfire itself is not exact.  The Voronoi rule is order-free: applied to the reference's own
+ * final grids it reproduces the reference's edge set cell for cell.  ppx_map_upload with reference-built grids stays
+ * the strict-parity path. */
+#define PPX_GVD_VORONOI 1
+int ppx_gvd_build(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* occupancy, int32_t flags, int32_t* sqdist_out,
+	int32_t* voro_sqdist_out, float* pathcost_out, int32_t* nearest_obstacle_out, int32_t* nearest_edge_out);
 
 /*
  * N4: outline rasterisation of polygon obstacles into the occupancy grid -- Shape::RasterizeLine
@@ -441,7 +466,8 @@ int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_
  * graph search in HybridAStar::SearchPath (hybrid_a_star.cpp:293-303).  The gradient descent runs on the
  * device, one CTA per path; the two GVD lookups it makes (GVD::GetNearestObstacleCell /
  * GetNearestVoronoiEdgeCell, gvd.h:36,76 -- smoother.cpp:110,118) read cell grids the caller uploads with
- * ppx_smoother_set_gvd after GVD::Update() (the Voronoi half of N1 stays on the host).
+ * ppx_smoother_set_gvd after GVD::Update(), or takes from the context's device-built GVD (ppx_gvd_build) with
+ * ppx_smoother_use_gvd.
  */
 typedef struct ppx_smoother ppx_smoother;
 
@@ -464,6 +490,8 @@ int ppx_smoother_create(ppx_ctx* ctx, const ppx_smoother_params* params, ppx_smo
 int ppx_smoother_destroy(ppx_smoother* s);
 /* nearest_obstacle / nearest_edge: rows * cols (row, col) int32 pairs, row-major like the map grids */
 int ppx_smoother_set_gvd(ppx_smoother* s, const int32_t* nearest_obstacle, const int32_t* nearest_edge);
+/* the same two grids from the GVD ppx_gvd_build left on the device (PPX_ERR_STATE without one) */
+int ppx_smoother_use_gvd(ppx_smoother* s);
 /*
  * poses / cusp / count: the arrays ppx_hybrid_resample returns (max_points entries per path; count[q] <= 0
  * = no path).  out_poses[q] receives Smoother::GetPath() (x, y moved; theta unchanged, smoother.cpp:152),

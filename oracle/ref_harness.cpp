@@ -338,6 +338,23 @@ void ref_world_gvd_update(void* h, float* pathcost, int* voro_sqdist)
 		memcpy(voro_sqdist, w->gvd->m_voronoiMap->m_distance.m_data, n * sizeof(int));
 }
 
+// The nearest-obstacle / nearest-Voronoi-edge cells of the world's own GVD (after ref_world_gvd_update), (row, col) pairs.
+void ref_world_gvd_cells(void* h, int32_t* nearestObstacle, int32_t* nearestEdge)
+{
+	auto* w = (RefWorld*)h;
+	if (!w->gvd)
+		return;
+	const int rows = w->map->Rows(), cols = w->map->Columns();
+	for (int r = 0; r < rows; r++)
+		for (int c = 0; c < cols; c++) {
+			const auto& o = w->gvd->GetNearestObstacleCell(r, c);
+			const auto& e = w->gvd->GetNearestVoronoiEdgeCell(r, c);
+			size_t i = ((size_t)r * cols + c) * 2;
+			nearestObstacle[i] = o.row; nearestObstacle[i + 1] = o.col;
+			nearestEdge[i] = e.row; nearestEdge[i + 1] = e.col;
+		}
+}
+
 int ref_is_state_valid(void* h, const double* pose)
 {
 	auto* w = (RefWorld*)h;

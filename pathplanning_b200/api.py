@@ -226,6 +226,33 @@ class Context:
         self.map = desc
         return None if sq is None else sq.reshape(desc.rows, desc.cols)
 
+    def build_gvd(self, desc: MapDesc, occupancy, voronoi=True, want=("sqdist", "voro_sqdist", "pathcost")):
+        """ppx_gvd_build: the whole GVD of the occupancy grid on the device (N1) -- obstacle distance map, Voronoi
+        edges, Voronoi distance map, path-cost map; installed as the context's map.  Returns the grids named in
+        `want` (also "nearest_obstacle", "nearest_edge": rows x cols x 2)."""
+        cells = desc.rows * desc.cols
+        occ = np.ascontiguousarray(occupancy, dtype=np.int32).reshape(-1)
+        if occ.size != cells:
+            raise ValueError(f"occupancy has {occ.size} cells, expected {cells}")
+        shape = (desc.rows, desc.cols)
+        out = {}
+        if "sqdist" in want:
+            out["sqdist"] = np.empty(shape, np.int32)
+        if "voro_sqdist" in want:
+            out["voro_sqdist"] = np.empty(shape, np.int32)
+        if "pathcost" in want:
+            out["pathcost"] = np.empty(shape, np.float32)
+        if "nearest_obstacle" in want:
+            out["nearest_obstacle"] = np.empty(shape + (2,), np.int32)
+        if "nearest_edge" in want:
+            out["nearest_edge"] = np.empty(shape + (2,), np.int32)
+        d = desc.to_c()
+        self._check(ppx.ppx_gvd_build(self._h, C.byref(d), _ptr(occ), 1 if voronoi else 0, _ptr(out.get("sqdist")),
+                                      _ptr(out.get("voro_sqdist")), _ptr(out.get("pathcost")), _ptr(out.get("nearest_obstacle")),
+                                      _ptr(out.get("nearest_edge"))))
+        self.map = desc
+        return out
+
     # ---- A7 -----------------------------------------------------------------------------------
     def is_state_valid(self, poses, vp: ValidatorParams):
         poses = _f64(poses)
@@ -508,6 +535,10 @@ class Smoother:
         a = np.ascontiguousarray(nearest_obstacle, np.int32)
         b = np.ascontiguousarray(nearest_edge, np.int32)
         self.ctx._check(ppx.ppx_smoother_set_gvd(self._h, _ptr(a), _ptr(b)))
+
+    def use_gvd(self):
+        """take the two cell grids from the GVD the context built on the device (Context.build_gvd)"""
+        self.ctx._check(ppx.ppx_smoother_use_gvd(self._h))
 
     def smooth(self, poses, cusp, count):
         """poses (nq, max_points, 3), cusp (nq, max_points), count (nq,) as returned by HybridAStar.resample

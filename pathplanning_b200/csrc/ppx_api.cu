@@ -76,7 +76,6 @@ __global__ void k_occupied(const int* __restrict__ occupancy, uint8_t* __restric
 // map: free cells (-1), zero potential.
 int ppx_map_alloc(ppx_ctx* ctx, const ppx_map_desc* desc)
 {
-	PPX_CUDA(ctx, cudaSetDevice(ctx->device));
 	size_t cells = (size_t)desc->rows * desc->cols;
 	if (cells == ctx->cells)
 		return PPX_OK;
@@ -140,7 +139,7 @@ int ppx_ctx_create(int device, ppx_ctx** out)
 		return ppx_fail(nullptr, PPX_ERR_INVALID, "device %d out of range (%d devices)", device, count);
 	auto* ctx = new ppx_ctx();
 	ctx->device = device;
-	PPX_CUDA(ctx, cudaSetDevice(device));
+	PPX_GUARD(ctx); // the caller's current device is restored on return
 	PPX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
 	ctx->stream = ctx->own_stream;
 	PPX_CUDA(ctx, cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device));
@@ -155,13 +154,16 @@ int ppx_ctx_destroy(ppx_ctx* ctx)
 {
 	if (!ctx)
 		return PPX_ERR_INVALID;
-	cudaSetDevice(ctx->device);
+	PPX_GUARD(ctx);
 	cudaStreamSynchronize(ctx->stream);
 	cudaFree(ctx->d_sqdist);
 	cudaFree(ctx->d_occupancy);
 	cudaFree(ctx->d_pathcost);
 	cudaFree(ctx->d_clearance);
 	cudaFree(ctx->d_occ8);
+	cudaFree(ctx->d_voro_sq);
+	cudaFree(ctx->d_near_obst);
+	cudaFree(ctx->d_near_edge);
 	cudaFree(ctx->d_queue);
 	cudaFree(ctx->d_rsq);
 	cudaFree(ctx->d_nonholo);
@@ -186,6 +188,7 @@ int ppx_ctx_destroy(ppx_ctx* ctx)
 
 int ppx_ctx_set_stream(ppx_ctx* ctx, void* cuda_stream)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
@@ -194,6 +197,7 @@ int ppx_ctx_set_stream(ppx_ctx* ctx, void* cuda_stream)
 
 int ppx_ctx_synchronize(ppx_ctx* ctx)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -202,6 +206,7 @@ int ppx_ctx_synchronize(ppx_ctx* ctx)
 
 int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value)
 {
+	PPX_GUARD(ctx);
 	if (!ctx || !name)
 		return PPX_ERR_INVALID;
 	if (!strcmp(name, "rs_filter")) {
@@ -224,15 +229,16 @@ int64_t ppx_ctx_launch_count(const ppx_ctx* ctx) { return ctx ? ctx->launches : 
 
 int ppx_dev_alloc(ppx_ctx* ctx, uint64_t bytes, void** dptr)
 {
+	PPX_GUARD(ctx);
 	if (!ctx || !dptr)
 		return PPX_ERR_INVALID;
-	PPX_CUDA(ctx, cudaSetDevice(ctx->device));
 	PPX_CUDA(ctx, cudaMalloc(dptr, bytes ? bytes : 1));
 	return PPX_OK;
 }
 
 int ppx_dev_free(ppx_ctx* ctx, void* dptr)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_CUDA(ctx, cudaFree(dptr));
@@ -241,6 +247,7 @@ int ppx_dev_free(ppx_ctx* ctx, void* dptr)
 
 int ppx_host_alloc(ppx_ctx* ctx, uint64_t bytes, void** hptr)
 {
+	PPX_GUARD(ctx);
 	if (!ctx || !hptr)
 		return PPX_ERR_INVALID;
 	PPX_CUDA(ctx, cudaHostAlloc(hptr, bytes ? bytes : 1, cudaHostAllocDefault));
@@ -249,6 +256,7 @@ int ppx_host_alloc(ppx_ctx* ctx, uint64_t bytes, void** hptr)
 
 int ppx_host_free(ppx_ctx* ctx, void* hptr)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_CUDA(ctx, cudaFreeHost(hptr));
@@ -257,6 +265,7 @@ int ppx_host_free(ppx_ctx* ctx, void* hptr)
 
 int ppx_memcpy_h2d(ppx_ctx* ctx, void* dst, const void* src, uint64_t bytes)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
@@ -266,6 +275,7 @@ int ppx_memcpy_h2d(ppx_ctx* ctx, void* dst, const void* src, uint64_t bytes)
 
 int ppx_memcpy_d2h(ppx_ctx* ctx, void* dst, const void* src, uint64_t bytes)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
@@ -276,6 +286,7 @@ int ppx_memcpy_d2h(ppx_ctx* ctx, void* dst, const void* src, uint64_t bytes)
 int ppx_map_upload(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* sqdist, const int32_t* occupancy,
 	const float* pathcost)
 {
+	PPX_GUARD(ctx);
 	if (!ctx || !desc)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, desc->rows > 0 && desc->cols > 0, "map size must be positive");
@@ -284,12 +295,16 @@ int ppx_map_upload(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* sqdist
 	if (cells != ctx->cells && !sqdist)
 		return ppx_fail(ctx, PPX_ERR_INVALID, "first upload of a map of this size needs sqdist");
 	PPX_CHECK(ppx_map_alloc(ctx, desc));
+	if (sqdist || occupancy)
+		ctx->has_gvd = false; // the device-built Voronoi grids describe the previous map
 	if (sqdist)
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_sqdist, sqdist, cells * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
 	if (occupancy)
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_occupancy, occupancy, cells * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
 	if (pathcost)
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_pathcost, pathcost, cells * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	else if (sqdist || occupancy) // a potential belongs to the map it was computed for: a new map without one searches with zero
+		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_pathcost, 0, cells * sizeof(float), ctx->stream));
 	return ppx_map_derive(ctx, desc, sqdist != nullptr, occupancy != nullptr);
 }
 

@@ -294,6 +294,7 @@ __global__ void __launch_bounds__(kAstarWarps * 32) k_astar_n2(const uint8_t* __
 extern "C" int ppx_astar_n2(ppx_ctx* ctx, int64_t nq, const int32_t* starts, const int32_t* goals, int32_t max_nodes,
 	int32_t max_path, ppx_astar_result* results, int32_t* paths)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, ctx->has_map && ctx->d_occ8, "ppx_astar_n2 needs a map with an occupancy grid");

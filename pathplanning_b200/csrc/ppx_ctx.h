@@ -29,6 +29,13 @@ struct ppx_ctx {
 	float* d_clearance = nullptr;
 	uint8_t* d_occ8 = nullptr; // occupancy >= 0 (IsOccupied), one byte per cell
 	size_t cells = 0;
+	// the rest of the GVD when it was built on the device (ppx_gvd_build): squared distance to the nearest Voronoi
+	// edge cell, nearest obstacle / edge cells packed row << 16 | col (-1 none)
+	bool has_gvd = false;
+	size_t gvd_cells = 0;
+	int* d_voro_sq = nullptr;
+	int* d_near_obst = nullptr;
+	int* d_near_edge = nullptr;
 
 	// grow-only device scratch for the host-buffer entry points
 	struct Scratch {
@@ -74,11 +81,33 @@ struct ppx_ctx {
 	}
 };
 
+// Every extern "C" entry point runs on its context's device whatever device is current in the calling
+// thread (a process may hold one context per GPU, and torch changes the current device freely), and
+// leaves the caller's current device as it found it.
+struct ppx_device_guard {
+	int prev = -1;
+	bool changed = false;
+	explicit ppx_device_guard(const ppx_ctx* ctx)
+	{
+		if (ctx && cudaGetDevice(&prev) == cudaSuccess && prev != ctx->device)
+			changed = cudaSetDevice(ctx->device) == cudaSuccess;
+	}
+	~ppx_device_guard()
+	{
+		if (changed)
+			cudaSetDevice(prev);
+	}
+	ppx_device_guard(const ppx_device_guard&) = delete;
+	ppx_device_guard& operator=(const ppx_device_guard&) = delete;
+};
+#define PPX_GUARD(ctx) ppx_device_guard ppx_guard_(ctx)
+
 int ppx_fail(ppx_ctx* ctx, int code, const char* fmt, ...);
 int ppx_scratch(ppx_ctx* ctx, int slot, size_t bytes, void** out);
 int ppx_pipeline_init(ppx_ctx* ctx);
 int ppx_map_alloc(ppx_ctx* ctx, const ppx_map_desc* desc);
 int ppx_map_derive(ppx_ctx* ctx, const ppx_map_desc* desc, bool newSqdist, bool newOccupancy);
+int ppx_gvd_unpack_cells(ppx_ctx* ctx, int* d_nearObstacle, int* d_nearEdge);
 
 #define PPX_CUDA(ctx, call)                                                                           \
 	do {                                                                                              \

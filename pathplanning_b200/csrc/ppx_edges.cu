@@ -349,6 +349,7 @@ extern "C" {
 
 int ppx_is_state_valid(ppx_ctx* ctx, int64_t n, const double* poses, const ppx_validator_params* vp, uint8_t* valid)
 {
+	PPX_GUARD(ctx);
 	PPX_CHECK(require_map(ctx));
 	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (poses && valid)), "bad arguments");
 	if (n == 0)
@@ -401,6 +402,7 @@ static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, double min_turning_radius,
 	const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, uint32_t* d_samples)
 {
+	PPX_GUARD(ctx);
 	PPX_CHECK(require_map(ctx));
 	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (d_edges && d_valid && d_last)), "bad arguments");
 	if (n == 0)
@@ -417,6 +419,7 @@ int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
 	const ppx_validator_params* vp, uint8_t* valid, float* last, uint32_t* samples, uint64_t* counters, float* max_dev_cells)
 {
+	PPX_GUARD(ctx);
 	PPX_CHECK(require_map(ctx));
 	PPX_REQUIRE(ctx, n > 0 && vp && edges && valid && last && samples && counters && max_dev_cells, "bad arguments");
 	ppx_rs_edge* d_edges;
@@ -456,6 +459,7 @@ int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, 
 int ppx_check_edges_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
 	const ppx_validator_params* vp, uint8_t* valid, float* last, uint32_t* samples)
 {
+	PPX_GUARD(ctx);
 	PPX_CHECK(require_map(ctx));
 	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (edges && valid && last)), "bad arguments");
 	if (n == 0)
@@ -501,6 +505,7 @@ int ppx_check_edges_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double
 int ppx_check_edges_csteer(ppx_ctx* ctx, int64_t n, const ppx_csteer_edge* edges, const ppx_validator_params* vp,
 	uint8_t* valid, float* last, double* final_pose)
 {
+	PPX_GUARD(ctx);
 	PPX_CHECK(require_map(ctx));
 	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (edges && valid && last)), "bad arguments");
 	if (n == 0)
@@ -529,6 +534,7 @@ int ppx_check_edges_csteer(ppx_ctx* ctx, int64_t n, const ppx_csteer_edge* edges
 int ppx_check_edges_line(ppx_ctx* ctx, int64_t n, const ppx_line_edge* edges, const ppx_validator_params* vp,
 	uint8_t* valid, float* last)
 {
+	PPX_GUARD(ctx);
 	PPX_CHECK(require_map(ctx));
 	PPX_REQUIRE(ctx, n >= 0 && vp && (n == 0 || (edges && valid && last)), "bad arguments");
 	if (n == 0)
@@ -552,6 +558,7 @@ int ppx_check_edges_line(ppx_ctx* ctx, int64_t n, const ppx_line_edge* edges, co
 int ppx_rs_solve_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, const double* d_goals,
 	const ppx_rs_cost_params* cp, ppx_rs_edge* d_edges, int32_t* d_word, double* d_length, float* d_cost)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, n >= 0 && cp && (n == 0 || (d_starts && d_goals)), "bad arguments");
@@ -568,6 +575,7 @@ int ppx_connect_check_rs_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, co
 	const ppx_rs_cost_params* cp, const ppx_validator_params* vp, uint8_t* d_valid, float* d_last, int32_t* d_word,
 	double* d_length, float* d_cost)
 {
+	PPX_GUARD(ctx);
 	PPX_CHECK(require_map(ctx));
 	PPX_REQUIRE(ctx, n >= 0 && cp && vp && (n == 0 || (d_starts && d_goals && d_valid && d_last)), "bad arguments");
 	if (n == 0)
@@ -631,6 +639,7 @@ static int solve_host(ppx_ctx* ctx, int64_t n, const double* starts, const doubl
 int ppx_rs_solve(ppx_ctx* ctx, int64_t n, const double* starts, const double* goals, const ppx_rs_cost_params* cp,
 	ppx_rs_edge* edges, int32_t* word, double* length, float* cost)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, n >= 0 && cp && (n == 0 || (starts && goals)), "bad arguments");
@@ -643,6 +652,7 @@ int ppx_connect_check_rs(ppx_ctx* ctx, int64_t n, const double* starts, const do
 	const ppx_rs_cost_params* cp, const ppx_validator_params* vp, uint8_t* valid, float* last, int32_t* word,
 	double* length, float* cost)
 {
+	PPX_GUARD(ctx);
 	PPX_CHECK(require_map(ctx));
 	PPX_REQUIRE(ctx, n >= 0 && cp && vp && (n == 0 || (starts && goals && valid && last)), "bad arguments");
 	if (n == 0)
@@ -653,6 +663,7 @@ int ppx_connect_check_rs(ppx_ctx* ctx, int64_t n, const double* starts, const do
 int ppx_rs_interpolate(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius, int32_t nratios,
 	const double* ratios, double* poses)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, n >= 0 && nratios >= 0 && (n * nratios == 0 || (edges && ratios && poses)), "bad arguments");

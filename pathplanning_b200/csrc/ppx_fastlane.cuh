@@ -46,9 +46,20 @@ inline FastMap fast_map_derive(const ppx_map_desc& d)
 	double uUx = (d.ub[0] + d.local_origin[0] - d.world_origin[0]) / res;
 	double uLy = (d.lb[1] + d.local_origin[1] - d.world_origin[1]) / res;
 	double uUy = (d.ub[1] + d.local_origin[1] - d.world_origin[1]) / res;
+	// ... while the step of IsPathValid measures the distance to the border on the WORLD position
+	// (`state.x() - bounds[0].x()`, state_validator_occupancy_map.cpp:54-59): the margin `ib` the filter
+	// certifies a step against must be a lower bound in that frame too.  The two frames differ by
+	// local_origin (OccupancyMap::SetPosition); the certified rows/cols are those inside both.
+	double wLx = (d.lb[0] - d.world_origin[0]) / res, wUx = (d.ub[0] - d.world_origin[0]) / res;
+	double wLy = (d.lb[1] - d.world_origin[1]) / res, wUy = (d.ub[1] - d.world_origin[1]) / res;
+	bool finite = std::isfinite(uLx) && std::isfinite(uUx) && std::isfinite(uLy) && std::isfinite(uUy)
+		&& std::isfinite(wLx) && std::isfinite(wUx) && std::isfinite(wLy) && std::isfinite(wUy);
+	uLx = uLx > wLx ? uLx : wLx;
+	uUx = uUx < wUx ? uUx : wUx;
+	uLy = uLy > wLy ? uLy : wLy;
+	uUy = uUy < wUy ? uUy : wUy;
 	auto lo = [](double u) { double c = ceil(u) + 1; return c < 0 ? 0.0 : c; };
 	auto hi = [](double u, int n) { double c = floor(u) - 2; return c > n - 1 ? (double)(n - 1) : c; };
-	bool finite = std::isfinite(uLx) && std::isfinite(uUx) && std::isfinite(uLy) && std::isfinite(uUy);
 	f.enabled = finite && d.lb[2] <= -PPX_PI && d.ub[2] >= PPX_PI && d.rows < (1 << 20) && d.cols < (1 << 20);
 	if (f.enabled) {
 		double a = lo(uLx), b = hi(uUx, d.rows), c = lo(uLy), e = hi(uUy, d.cols);

@@ -19,39 +19,60 @@ namespace {
 
 constexpr int kNone = 1 << 29; // "no occupied cell in this column"
 
-__global__ void __launch_bounds__(128) k_edt_columns(const int* __restrict__ occupancy, int rows, int cols, int* __restrict__ g)
+// `nearRow` (optional): row of that nearest seed cell of the column (-1: none; the smaller row on a tie).
+__global__ void __launch_bounds__(128) k_edt_columns(const int* __restrict__ seed, int rows, int cols, int* __restrict__ g,
+	int* __restrict__ nearRow)
 {
 	int c = blockIdx.x * blockDim.x + threadIdx.x;
 	if (c >= cols)
 		return;
-	int d = kNone;
-	for (int r = 0; r < rows; r++) { // nearest occupied cell above (smaller row)
-		bool occ = occupancy[(size_t)r * cols + c] >= 0; // IsOccupied, obstacle_list_occupancy_map.cpp:63-69
+	int d = kNone, src = -1;
+	for (int r = 0; r < rows; r++) { // nearest seed cell above (smaller row)
+		bool occ = seed[(size_t)r * cols + c] >= 0; // IsOccupied, obstacle_list_occupancy_map.cpp:63-69
 		d = occ ? 0 : (d >= kNone ? kNone : d + 1);
+		src = occ ? r : src;
 		g[(size_t)r * cols + c] = d;
+		if (nearRow)
+			nearRow[(size_t)r * cols + c] = src;
 	}
 	d = kNone;
+	src = -1;
 	for (int r = rows - 1; r >= 0; r--) { // ... and below
 		size_t i = (size_t)r * cols + c;
 		int up = g[i];
 		d = up == 0 ? 0 : (d >= kNone ? kNone : d + 1);
-		g[i] = min(up, d);
+		src = up == 0 ? r : src;
+		if (d < up) {
+			g[i] = d;
+			if (nearRow)
+				nearRow[i] = src;
+		}
 	}
 }
 
-__global__ void __launch_bounds__(256) k_edt_rows(const int* __restrict__ g, int rows, int cols, int* __restrict__ sqdist)
+// nearest (optional): the seed cell that realises the minimum, packed row << 16 | col (-1: none).  Among equidistant
+// seed cells the first one met by the outward search wins (own column, then c - d before c + d, growing d).
+__global__ void __launch_bounds__(256) k_edt_rows(const int* __restrict__ g, const int* __restrict__ nearRow, int rows, int cols,
+	int* __restrict__ sqdist, int* __restrict__ nearest)
 {
 	extern __shared__ int s_g[];
+	int* s_nr = s_g + cols;
 	for (int r = blockIdx.x; r < rows; r += gridDim.x) {
 		__syncthreads();
-		for (int c = threadIdx.x; c < cols; c += blockDim.x)
+		for (int c = threadIdx.x; c < cols; c += blockDim.x) {
 			s_g[c] = g[(size_t)r * cols + c];
+			if (nearest)
+				s_nr[c] = nearRow[(size_t)r * cols + c];
+		}
 		__syncthreads();
 		for (int c = threadIdx.x; c < cols; c += blockDim.x) {
 			long long best = 0x7fffffffLL; // INT_MAX: no obstacle anywhere (gvd.cpp:22)
+			int bestCol = -1;
 			int gc = s_g[c];
-			if (gc < kNone)
+			if (gc < kNone) {
 				best = (long long)gc * gc;
+				bestCol = c;
+			}
 			for (int d = 1; d < cols; d++) {
 				long long dd = (long long)d * d;
 				if (dd >= best)
@@ -61,17 +82,105 @@ __global__ void __launch_bounds__(256) k_edt_rows(const int* __restrict__ g, int
 					break;
 				if (lo >= 0) {
 					int v = s_g[lo];
-					if (v < kNone)
-						best = min(best, dd + (long long)v * v);
+					if (v < kNone && dd + (long long)v * v < best) {
+						best = dd + (long long)v * v;
+						bestCol = lo;
+					}
 				}
 				if (hi < cols) {
 					int v = s_g[hi];
-					if (v < kNone)
-						best = min(best, dd + (long long)v * v);
+					if (v < kNone && dd + (long long)v * v < best) {
+						best = dd + (long long)v * v;
+						bestCol = hi;
+					}
 				}
 			}
 			sqdist[(size_t)r * cols + c] = (int)min(best, 0x7fffffffLL);
+			if (nearest)
+				nearest[(size_t)r * cols + c] = bestCol >= 0 ? (s_nr[bestCol] << 16 | bestCol) : -1;
 		}
+	}
+}
+
+// Voronoi-edge cells.  The reference marks them while the obstacle brushfire runs (CheckVoro, gvd.cpp:105-131, called
+// for a popped cell s and a neighbour n it does not lower, :57-69) and unmarks a cell whenever it is popped again
+// (:53-55).  What is left when the queue is empty is a function of the FINAL distance / nearest-obstacle grids: cell s
+// is an edge cell iff some 8-neighbour n has a nearest obstacle of another obstacle id that is neither equal nor
+// adjacent to s's, one of the two distances exceeds 1, both "stabilities" d2(s, obst[n]) - dist[s] and
+// d2(n, obst[s]) - dist[n] are >= 0 and s's is not the larger one.  (Checked against the compiled reference: applied to
+// the reference's own final grids the rule gives the reference's edge set cell for cell on every test map.)
+__global__ void __launch_bounds__(256) k_voronoi_edges(const int* __restrict__ occupancy, const int* __restrict__ sqdist,
+	const int* __restrict__ nearest, int rows, int cols, int* __restrict__ edge /* 0 edge, -1 not */)
+{
+	const size_t cells = (size_t)rows * cols;
+	for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < cells; i += (size_t)gridDim.x * blockDim.x) {
+		const int r = (int)(i / cols), c = (int)(i % cols);
+		const int os = nearest[i];
+		int isEdge = -1;
+		if (os >= 0) {
+			const int osr = os >> 16, osc = os & 0xffff;
+			const int ids = occupancy[(size_t)osr * cols + osc];
+			const long long ds = sqdist[i];
+			for (int k = 0; k < 8 && isEdge < 0; k++) {
+				const int nr = r + (k < 3 ? -1 : (k < 5 ? 0 : 1));
+				const int nc = c + (k == 0 || k == 3 || k == 5 ? -1 : (k == 1 || k == 6 ? 0 : 1));
+				if (nr < 0 || nr >= rows || nc < 0 || nc >= cols)
+					continue;
+				const size_t j = (size_t)nr * cols + nc;
+				const int on = nearest[j];
+				if (on < 0)
+					continue;
+				const int onr = on >> 16, onc = on & 0xffff;
+				if (occupancy[(size_t)onr * cols + onc] == ids)
+					continue; // same obstacle id, gvd.cpp:110-111
+				const long long dn = sqdist[j];
+				if (!(ds > 1 || dn > 1))
+					continue;
+				if (!(abs(osr - onr) > 1 || abs(osc - onc) > 1))
+					continue;
+				const long long sStab = (long long)(r - onr) * (r - onr) + (long long)(c - onc) * (c - onc) - ds;
+				const long long nStab = (long long)(nr - osr) * (nr - osr) + (long long)(nc - osc) * (nc - osc) - dn;
+				if (sStab < 0 || nStab < 0)
+					continue;
+				if (sStab <= nStab)
+					isEdge = 0;
+			}
+		}
+		edge[i] = isEdge;
+	}
+}
+
+// GVD::PathCostMap::Update, gvd.cpp:266-283, with the float / double mixing of the original expression:
+// (alpha / (alpha + obstDist)) and (voroDist / (obstDist + voroDist)) are float, std::pow(float, int) is double.
+__global__ void __launch_bounds__(256) k_pathcost(const int* __restrict__ sqdist, const int* __restrict__ voroSq, size_t cells,
+	float res, float alpha, float dMax, float* __restrict__ pathcost)
+{
+	for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < cells; i += (size_t)gridDim.x * blockDim.x) {
+		const float obstDist = (float)(sqrt((double)sqdist[i]) * (double)res); // gvd.h:38
+		const float voroDist = (float)(sqrt((double)voroSq[i]) * (double)res); // gvd.h:82
+		float out = 0.0f;
+		if (!(obstDist >= dMax || voroDist == __int_as_float(0x7f800000))) {
+			const float a = (alpha / (alpha + obstDist)) * (voroDist / (obstDist + voroDist));
+			const double t = (double)(obstDist - dMax);
+			const double q = (t * t) / ((double)dMax * (double)dMax); // pow(x, 2) is exactly x * x for float-valued x
+			out = (float)((double)a * q);
+		}
+		pathcost[i] = out;
+	}
+}
+
+__global__ void __launch_bounds__(256) k_fill_int(int* __restrict__ p, size_t n, int v)
+{
+	for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+		p[i] = v;
+}
+
+__global__ void __launch_bounds__(256) k_unpack_cells(const int* __restrict__ packed, size_t n, int* __restrict__ out)
+{
+	for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+		int v = packed[i];
+		out[2 * i] = v < 0 ? -1 : v >> 16; // GridCellPosition(-1, -1) when there is none
+		out[2 * i + 1] = v < 0 ? -1 : v & 0xffff;
 	}
 }
 
@@ -135,6 +244,7 @@ __global__ void __launch_bounds__(128) k_rasterize(int rows, int cols, double ox
 extern "C" int ppx_map_rasterize(ppx_ctx* ctx, const ppx_map_desc* desc, int32_t n_polygons, const int32_t* offsets,
 	const double* vertices, int32_t first_id, int32_t* occupancy)
 {
+	PPX_GUARD(ctx);
 	if (!ctx || !desc)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, n_polygons >= 0 && offsets && occupancy && first_id >= -1, "bad arguments");
@@ -165,29 +275,127 @@ extern "C" int ppx_map_rasterize(ppx_ctx* ctx, const ppx_map_desc* desc, int32_t
 	return PPX_OK;
 }
 
+namespace {
+
+// Exact squared distance transform of the seed grid (>= 0 seeds) with the nearest seed cell, into sq / nearest.
+int edt_with_source(ppx_ctx* ctx, const ppx_map_desc* desc, const int* d_seed, int* d_g, int* d_nr, int* d_sq, int* d_nearest)
+{
+	k_edt_columns<<<(desc->cols + 127) / 128, 128, 0, ctx->stream>>>(d_seed, desc->rows, desc->cols, d_g, d_nr);
+	PPX_LAUNCHED(ctx);
+	const size_t smem = (size_t)desc->cols * sizeof(int) * 2;
+	PPX_CUDA(ctx, cudaFuncSetAttribute(k_edt_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+	int blocks = std::min(desc->rows, ctx->num_sms * 4);
+	k_edt_rows<<<blocks, 256, smem, ctx->stream>>>(d_g, d_nr, desc->rows, desc->cols, d_sq, d_nearest);
+	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
+}
+
+extern "C" int ppx_gvd_build(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* occupancy, int32_t flags, int32_t* sqdist_out,
+	int32_t* voro_sqdist_out, float* pathcost_out, int32_t* nearest_obstacle_out, int32_t* nearest_edge_out)
+{
+	PPX_GUARD(ctx);
+	if (!ctx || !desc)
+		return PPX_ERR_INVALID;
+	PPX_REQUIRE(ctx, occupancy, "ppx_gvd_build needs the occupancy grid");
+	PPX_REQUIRE(ctx, desc->rows > 0 && desc->cols > 0 && desc->rows < 32768 && desc->cols < 32768, "map size out of range");
+	PPX_REQUIRE(ctx, desc->resolution > 0.0f, "resolution must be positive");
+	PPX_REQUIRE(ctx, (size_t)desc->cols * sizeof(int) * 2 <= 160 * 1024, "map too wide for the row pass (cols <= 20480)");
+	PPX_CHECK(ppx_map_alloc(ctx, desc));
+	const size_t cells = (size_t)desc->rows * desc->cols;
+	if (ctx->gvd_cells != cells) {
+		PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+		cudaFree(ctx->d_voro_sq);
+		cudaFree(ctx->d_near_obst);
+		cudaFree(ctx->d_near_edge);
+		ctx->d_voro_sq = ctx->d_near_obst = ctx->d_near_edge = nullptr;
+		ctx->gvd_cells = 0;
+		PPX_CUDA(ctx, cudaMalloc(&ctx->d_voro_sq, cells * sizeof(int)));
+		PPX_CUDA(ctx, cudaMalloc(&ctx->d_near_obst, cells * sizeof(int)));
+		PPX_CUDA(ctx, cudaMalloc(&ctx->d_near_edge, cells * sizeof(int)));
+		ctx->gvd_cells = cells;
+	}
+	ctx->has_gvd = false;
+	int* d_g;
+	PPX_CHECK(ppx_scratch(ctx, 6, cells * sizeof(int) * 5, (void**)&d_g));
+	int* d_nr = d_g + cells;
+	int* d_edge = d_nr + cells;
+	int* d_unpack = d_edge + cells; // 2 * cells
+	const int blocks = (int)std::min<size_t>((cells + 255) / 256, (size_t)ctx->num_sms * 8);
+	PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_occupancy, occupancy, cells * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+	// GVD::ObstacleDistanceMap (gvd.cpp:30-89): m_distance and m_obstacle
+	PPX_CHECK(edt_with_source(ctx, desc, ctx->d_occupancy, d_g, d_nr, ctx->d_sqdist, ctx->d_near_obst));
+	if (flags & PPX_GVD_VORONOI) {
+		// CheckVoro (gvd.cpp:105-131) -> VoronoiDistanceMap (gvd.cpp:200-264): m_distance and m_edge
+		k_voronoi_edges<<<blocks, 256, 0, ctx->stream>>>(ctx->d_occupancy, ctx->d_sqdist, ctx->d_near_obst, desc->rows, desc->cols, d_edge);
+		PPX_LAUNCHED(ctx);
+		PPX_CHECK(edt_with_source(ctx, desc, d_edge, d_g, d_nr, ctx->d_voro_sq, ctx->d_near_edge));
+	} else {
+		// the obstacle brushfire ran before a Voronoi map existed (OccupancyMap::Update before the GVD was created):
+		// no edge is ever set, the Voronoi distance stays INT_MAX (gvd.cpp:190-192)
+		k_fill_int<<<blocks, 256, 0, ctx->stream>>>(ctx->d_voro_sq, cells, 0x7fffffff);
+		PPX_LAUNCHED(ctx);
+		k_fill_int<<<blocks, 256, 0, ctx->stream>>>(ctx->d_near_edge, cells, -1);
+		PPX_LAUNCHED(ctx);
+	}
+	k_pathcost<<<blocks, 256, 0, ctx->stream>>>(ctx->d_sqdist, ctx->d_voro_sq, cells, desc->resolution, 20.0f, 30.0f, ctx->d_pathcost);
+	PPX_LAUNCHED(ctx);
+	if (sqdist_out)
+		PPX_CUDA(ctx, cudaMemcpyAsync(sqdist_out, ctx->d_sqdist, cells * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	if (voro_sqdist_out)
+		PPX_CUDA(ctx, cudaMemcpyAsync(voro_sqdist_out, ctx->d_voro_sq, cells * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	if (pathcost_out)
+		PPX_CUDA(ctx, cudaMemcpyAsync(pathcost_out, ctx->d_pathcost, cells * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	if (nearest_obstacle_out) {
+		k_unpack_cells<<<blocks, 256, 0, ctx->stream>>>(ctx->d_near_obst, cells, d_unpack);
+		PPX_LAUNCHED(ctx);
+		PPX_CUDA(ctx, cudaMemcpyAsync(nearest_obstacle_out, d_unpack, cells * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	}
+	if (nearest_edge_out) {
+		k_unpack_cells<<<blocks, 256, 0, ctx->stream>>>(ctx->d_near_edge, cells, d_unpack);
+		PPX_LAUNCHED(ctx);
+		PPX_CUDA(ctx, cudaMemcpyAsync(nearest_edge_out, d_unpack, cells * 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	}
+	PPX_CHECK(ppx_map_derive(ctx, desc, true, true));
+	ctx->has_gvd = true;
+	return PPX_OK;
+}
+
+// The (row, col) pairs of the context's GVD as ppx_smoother_set_gvd takes them, device to device.
+int ppx_gvd_unpack_cells(ppx_ctx* ctx, int* d_nearObstacle, int* d_nearEdge)
+{
+	if (!ctx->has_gvd)
+		return ppx_fail(ctx, PPX_ERR_STATE, "no GVD on the device (ppx_gvd_build)");
+	const int blocks = (int)std::min<size_t>((ctx->gvd_cells + 255) / 256, (size_t)ctx->num_sms * 8);
+	k_unpack_cells<<<blocks, 256, 0, ctx->stream>>>(ctx->d_near_obst, ctx->gvd_cells, d_nearObstacle);
+	PPX_LAUNCHED(ctx);
+	k_unpack_cells<<<blocks, 256, 0, ctx->stream>>>(ctx->d_near_edge, ctx->gvd_cells, d_nearEdge);
+	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
 extern "C" int ppx_map_build(ppx_ctx* ctx, const ppx_map_desc* desc, const int32_t* occupancy, const float* pathcost,
 	int32_t* sqdist_out)
 {
+	PPX_GUARD(ctx);
 	if (!ctx || !desc)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, occupancy, "ppx_map_build needs the occupancy grid");
 	PPX_REQUIRE(ctx, desc->rows > 0 && desc->cols > 0 && desc->rows < 32768 && desc->cols < 32768, "map size out of range");
 	PPX_REQUIRE(ctx, desc->resolution > 0.0f, "resolution must be positive");
-	PPX_REQUIRE(ctx, (size_t)desc->cols * sizeof(int) <= 160 * 1024, "map too wide for the row pass (cols <= 40960)");
+	PPX_REQUIRE(ctx, (size_t)desc->cols * sizeof(int) * 2 <= 160 * 1024, "map too wide for the row pass (cols <= 20480)");
 	PPX_CHECK(ppx_map_alloc(ctx, desc));
 	const size_t cells = (size_t)desc->rows * desc->cols;
 	int* d_g;
 	PPX_CHECK(ppx_scratch(ctx, 6, cells * sizeof(int), (void**)&d_g));
+	ctx->has_gvd = false;
 	PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_occupancy, occupancy, cells * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
-	k_edt_columns<<<(desc->cols + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_occupancy, desc->rows, desc->cols, d_g);
-	PPX_LAUNCHED(ctx);
-	const size_t smem = (size_t)desc->cols * sizeof(int);
-	PPX_CUDA(ctx, cudaFuncSetAttribute(k_edt_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-	int blocks = std::min(desc->rows, ctx->num_sms * 4);
-	k_edt_rows<<<blocks, 256, smem, ctx->stream>>>(d_g, desc->rows, desc->cols, ctx->d_sqdist);
-	PPX_LAUNCHED(ctx);
+	PPX_CHECK(edt_with_source(ctx, desc, ctx->d_occupancy, d_g, nullptr, ctx->d_sqdist, nullptr));
 	if (pathcost)
 		PPX_CUDA(ctx, cudaMemcpyAsync(ctx->d_pathcost, pathcost, cells * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	else
+		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_pathcost, 0, cells * sizeof(float), ctx->stream));
 	if (sqdist_out)
 		PPX_CUDA(ctx, cudaMemcpyAsync(sqdist_out, ctx->d_sqdist, cells * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
 	return ppx_map_derive(ctx, desc, true, true);

@@ -654,6 +654,7 @@ extern "C" {
 
 int ppx_hybrid_create(ppx_ctx* ctx, const ppx_hybrid_params* params, const ppx_validator_params* vp, ppx_hybrid** out)
 {
+	PPX_GUARD(ctx);
 	if (!ctx || !out)
 		return PPX_ERR_INVALID;
 	*out = nullptr;
@@ -688,6 +689,7 @@ int ppx_hybrid_create(ppx_ctx* ctx, const ppx_hybrid_params* params, const ppx_v
 
 int ppx_hybrid_destroy(ppx_hybrid* h)
 {
+	PPX_GUARD(h ? h->ctx : nullptr);
 	if (!h)
 		return PPX_ERR_INVALID;
 	cudaStreamSynchronize(h->ctx->stream);
@@ -702,6 +704,7 @@ int ppx_hybrid_destroy(ppx_hybrid* h)
 
 int ppx_hybrid_table(ppx_hybrid* h, int32_t* dims, double* offsets, double* values)
 {
+	PPX_GUARD(h ? h->ctx : nullptr);
 	if (!h)
 		return PPX_ERR_INVALID;
 	if (dims) {
@@ -724,6 +727,7 @@ int ppx_hybrid_table(ppx_hybrid* h, int32_t* dims, double* offsets, double* valu
 int ppx_hybrid_heuristic(ppx_hybrid* h, const double* goal, int64_t n, const double* poses, double* combined,
 	double* nonholo, double* obstacles)
 {
+	PPX_GUARD(h ? h->ctx : nullptr);
 	PPX_CHECK(check_handle(h));
 	ppx_ctx* ctx = h->ctx;
 	PPX_REQUIRE(ctx, goal && n >= 0 && (n == 0 || poses), "bad arguments");
@@ -753,6 +757,7 @@ int ppx_hybrid_heuristic(ppx_hybrid* h, const double* goal, int64_t n, const dou
 int ppx_hybrid_expand(ppx_hybrid* h, const double* goal, int64_t n, const double* parents, const uint64_t* seeds,
 	int32_t* n_children, ppx_hybrid_child* children, double* parent_heuristic)
 {
+	PPX_GUARD(h ? h->ctx : nullptr);
 	PPX_CHECK(check_handle(h));
 	ppx_ctx* ctx = h->ctx;
 	PPX_REQUIRE(ctx, goal && n >= 0 && (n == 0 || (parents && seeds && n_children && children)), "bad arguments");
@@ -792,6 +797,7 @@ int ppx_hybrid_resample(ppx_hybrid* h, int64_t nq, const double* goals, const pp
 	const ppx_hybrid_path_state* paths, int32_t max_path, float path_interpolation, int32_t max_points, double* poses,
 	uint8_t* cusp, int32_t* count, double* lengths)
 {
+	PPX_GUARD(h ? h->ctx : nullptr);
 	PPX_CHECK(check_handle(h));
 	ppx_ctx* ctx = h->ctx;
 	PPX_REQUIRE(ctx, nq >= 0 && max_path >= 2 && max_points > 0 && path_interpolation > 0.0f, "bad arguments");
@@ -839,6 +845,7 @@ int ppx_hybrid_search_dev(ppx_hybrid* h, int64_t nq, const double* d_starts, con
 	const uint64_t* d_seeds, const ppx_hybrid_limits* limits, ppx_hybrid_result* d_results,
 	ppx_hybrid_path_state* d_paths, ppx_hybrid_log_entry* d_log)
 {
+	PPX_GUARD(h ? h->ctx : nullptr);
 	PPX_CHECK(check_handle(h));
 	ppx_ctx* ctx = h->ctx;
 	PPX_REQUIRE(ctx, nq >= 0 && limits && (nq == 0 || (d_starts && d_goals && d_results)), "bad arguments");
@@ -861,6 +868,7 @@ int ppx_hybrid_search_dev(ppx_hybrid* h, int64_t nq, const double* d_starts, con
 int ppx_hybrid_search(ppx_hybrid* h, int64_t nq, const double* starts, const double* goals, const uint64_t* seeds,
 	const ppx_hybrid_limits* limits, ppx_hybrid_result* results, ppx_hybrid_path_state* paths, ppx_hybrid_log_entry* log)
 {
+	PPX_GUARD(h ? h->ctx : nullptr);
 	PPX_CHECK(check_handle(h));
 	ppx_ctx* ctx = h->ctx;
 	PPX_REQUIRE(ctx, nq >= 0 && limits && (nq == 0 || (starts && goals && results)), "bad arguments");

@@ -168,6 +168,7 @@ extern "C" {
 int ppx_knn_dev(ppx_ctx* ctx, int32_t dim, int64_t npoints, const double* d_points, int64_t nqueries, const double* d_queries,
 	int32_t k, int32_t* d_indices, double* d_dist2)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, (dim == 2 || dim == 3) && npoints >= 0 && nqueries >= 0 && k >= 1 && k <= kMaxK, "knn: dim must be 2 or 3, 1 <= k <= 32");
@@ -195,6 +196,7 @@ int ppx_knn_dev(ppx_ctx* ctx, int32_t dim, int64_t npoints, const double* d_poin
 int ppx_knn(ppx_ctx* ctx, int32_t dim, int64_t npoints, const double* points, int64_t nqueries, const double* queries, int32_t k,
 	int32_t* indices, double* dist2)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, (dim == 2 || dim == 3) && npoints >= 0 && nqueries >= 0 && k >= 1 && k <= kMaxK, "knn: dim must be 2 or 3, 1 <= k <= 32");

@@ -328,7 +328,7 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 	__shared__ int s_candValid[kRrtMaxK];
 	__shared__ double s_wd[8];
 	__shared__ int s_wi[8], s_wo[8];
-	__shared__ int s_winner, s_ctl, s_n, s_nn;
+	__shared__ int s_winner, s_ctlbuf[2], s_n, s_nn;
 	__shared__ long long s_tree;
 
 	RrtWs W;
@@ -375,7 +375,12 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 		}
 		__syncthreads();
 
+		// The control word is double-buffered by iteration parity: thread 0 may already be writing the next
+		// iteration's word (after its last barrier of this iteration) while a late warp still reads this one.
+		unsigned it = 0;
 		while (true) {
+			it++;
+			volatile int& s_ctl = s_ctlbuf[it & 1];
 			if (threadIdx.x == 0) {
 				count++;
 				if (count > (long long)P.maxIteration || (unsigned)n > P.maxNodes) { // rrt.h:64-69
@@ -550,6 +555,7 @@ int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_
 	const double* starts, const double* goals, const uint64_t* seeds, ppx_rrt_result* results, int64_t node_capacity,
 	double* nodes, int32_t* parents, double* costs)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, params && ntrees >= 0 && (ntrees == 0 || (starts && goals && seeds && results)), "bad arguments");

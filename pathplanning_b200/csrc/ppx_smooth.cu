@@ -162,6 +162,7 @@ struct ppx_smoother {
 
 extern "C" int ppx_smoother_create(ppx_ctx* ctx, const ppx_smoother_params* params, ppx_smoother** out)
 {
+	PPX_GUARD(ctx);
 	if (!ctx || !out)
 		return PPX_ERR_INVALID;
 	PPX_REQUIRE(ctx, params, "ppx_smoother_create needs parameters");
@@ -176,6 +177,7 @@ extern "C" int ppx_smoother_create(ppx_ctx* ctx, const ppx_smoother_params* para
 
 extern "C" int ppx_smoother_destroy(ppx_smoother* s)
 {
+	PPX_GUARD(s ? s->ctx : nullptr);
 	if (!s)
 		return PPX_ERR_INVALID;
 	cudaFree(s->d_near_obstacle);
@@ -187,6 +189,7 @@ extern "C" int ppx_smoother_destroy(ppx_smoother* s)
 
 extern "C" int ppx_smoother_set_gvd(ppx_smoother* s, const int32_t* nearest_obstacle, const int32_t* nearest_edge)
 {
+	PPX_GUARD(s ? s->ctx : nullptr);
 	if (!s)
 		return PPX_ERR_INVALID;
 	ppx_ctx* ctx = s->ctx;
@@ -203,9 +206,27 @@ extern "C" int ppx_smoother_set_gvd(ppx_smoother* s, const int32_t* nearest_obst
 	return PPX_OK;
 }
 
+extern "C" int ppx_smoother_use_gvd(ppx_smoother* s)
+{
+	PPX_GUARD(s ? s->ctx : nullptr);
+	if (!s)
+		return PPX_ERR_INVALID;
+	ppx_ctx* ctx = s->ctx;
+	const size_t bytes = (size_t)ctx->desc.rows * ctx->desc.cols * 2 * sizeof(int32_t);
+	if (!s->d_near_obstacle) {
+		PPX_CUDA(ctx, cudaMalloc(&s->d_near_obstacle, bytes));
+		PPX_CUDA(ctx, cudaMalloc(&s->d_near_edge, bytes));
+	}
+	PPX_CHECK(ppx_gvd_unpack_cells(ctx, s->d_near_obstacle, s->d_near_edge));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	s->has_maps = true;
+	return PPX_OK;
+}
+
 extern "C" int ppx_smoother_smooth(ppx_smoother* s, int64_t nq, const double* poses, const uint8_t* cusp, const int32_t* count,
 	int32_t max_points, double* out_poses, int32_t* status, int32_t* iterations)
 {
+	PPX_GUARD(s ? s->ctx : nullptr);
 	if (!s)
 		return PPX_ERR_INVALID;
 	ppx_ctx* ctx = s->ctx;

@@ -378,6 +378,7 @@ extern "C" {
 
 int ppx_wavefront_dev(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	if (!ctx->has_map)
@@ -390,6 +391,7 @@ int ppx_wavefront_dev(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_c
 
 int ppx_wavefront(ppx_ctx* ctx, int64_t n, const double* goals, float* cost, uint8_t* explored)
 {
+	PPX_GUARD(ctx);
 	if (!ctx)
 		return PPX_ERR_INVALID;
 	if (!ctx->has_map)

@@ -72,6 +72,7 @@ _SIGS = {
     "ppx_memcpy_d2h": (C.c_int, [_p, _p, _p, C.c_uint64]),
     "ppx_map_upload": (C.c_int, [_p, C.POINTER(MapDescC), _p, _p, _p]),
     "ppx_map_build": (C.c_int, [_p, C.POINTER(MapDescC), _p, _p, _p]),
+    "ppx_gvd_build": (C.c_int, [_p, C.POINTER(MapDescC), _p, C.c_int32, _p, _p, _p, _p, _p]),
     "ppx_is_state_valid": (C.c_int, [_p, _i64, _p, C.POINTER(ValidatorParamsC), _p]),
     "ppx_check_edges_rs": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p]),
     "ppx_check_edges_rs_audit": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(ValidatorParamsC), _p, _p, _p, _p, _p]),
@@ -100,6 +101,7 @@ _SIGS = {
     "ppx_smoother_create": (C.c_int, [_p, C.POINTER(SmootherParamsC), C.POINTER(_p)]),
     "ppx_smoother_destroy": (C.c_int, [_p]),
     "ppx_smoother_set_gvd": (C.c_int, [_p, _p, _p]),
+    "ppx_smoother_use_gvd": (C.c_int, [_p]),
     "ppx_smoother_smooth": (C.c_int, [_p, _i64, _p, _p, _p, C.c_int32, _p, _p, _p]),
     "ppx_map_rasterize": (C.c_int, [_p, C.POINTER(MapDescC), C.c_int32, _p, _p, C.c_int32, _p]),
     "ppx_astar_n2": (C.c_int, [_p, _i64, _p, _p, C.c_int32, C.c_int32, _p, _p]),

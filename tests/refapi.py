@@ -164,6 +164,14 @@ class World:
         lib().ref_world_gvd_update(self.h, _p(pc), _p(vd))
         return pc, vd
 
+    def gvd_cells(self):
+        """(rows, cols, 2) nearest-obstacle and nearest-Voronoi-edge cells of the world's GVD (after gvd_update)"""
+        i = self.info()
+        a = np.zeros((i["rows"], i["cols"], 2), np.int32)
+        b = np.zeros((i["rows"], i["cols"], 2), np.int32)
+        lib().ref_world_gvd_cells(self.h, _p(a), _p(b))
+        return a, b
+
     def set_validator_params(self, min_safe_radius, min_step):
         self.min_safe_radius, self.min_step = float(min_safe_radius), float(min_step)
         lib().ref_world_set_validator_params(self.h, C.c_float(min_safe_radius), C.c_float(min_step))

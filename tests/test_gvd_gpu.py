@@ -124,3 +124,127 @@ def test_rasterize_degenerate(ctx):
     assert (one >= 0).sum() == 1 and one[int((0.1 + 5.0) / 0.25), int((0.1 + 7.5) / 0.25)] == 0
     out = ctx.rasterize(desc, [np.array([[100.0, 100.0], [120.0, 130.0], [90.0, 140.0]])])  # entirely outside
     assert (out == -1).all()
+
+
+# ---- N1, Voronoi half: ppx_gvd_build ------------------------------------------------------------------------------
+def _oracle_rule():
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+    import gvd_rule
+    return gvd_rule
+
+
+def _gvd_world(ref, cfg, rects=None, shapes=None):
+    """Reference GVD attached before the obstacle brushfire (example.py:47-48): CheckVoro active."""
+    w = ref.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    for r in (rects or []):
+        w.add_rectangle(*r)
+    for s in (shapes or []):
+        w.add_shape(*s)
+    pc, vd = w.gvd_update()
+    occ, sq = w.grids()
+    return w, occ, sq, vd, pc
+
+
+def _check_against_port(g, occ, res):
+    """Device grids vs the numpy restatement (exact transforms + the order-free Voronoi rule): everything identical;
+    the nearest-cell grids name a seed cell at exactly the stored distance (their tie choice is the device's own)."""
+    rule = _oracle_rule()
+    sq, _ = rule.exact_edt(occ >= 0)
+    assert np.array_equal(g["sqdist"], sq)
+    no = g["nearest_obstacle"]
+    edges = rule.voronoi_edges(occ, g["sqdist"], no)
+    assert np.array_equal(g["voro_sqdist"] == 0, edges)
+    vsq, _ = rule.exact_edt(edges)
+    assert np.array_equal(g["voro_sqdist"], vsq)
+    assert np.array_equal(g["pathcost"].view(np.uint32), rule.path_cost(sq, vsq, res).view(np.uint32))
+    rr, cc = np.indices(occ.shape)
+    for near, seed, dist in ((no, occ >= 0, g["sqdist"]), (g["nearest_edge"], edges, g["voro_sqdist"])):
+        if not seed.any():
+            assert (near == -1).all()
+            continue
+        assert seed[near[..., 0], near[..., 1]].all()
+        assert np.array_equal((near[..., 0] - rr) ** 2 + (near[..., 1] - cc) ** 2, dist)
+
+
+ALL = ("sqdist", "voro_sqdist", "pathcost", "nearest_obstacle", "nearest_edge")
+
+
+@pytest.mark.parametrize("name", ["C2", "C3"])
+def test_gvd_build_parking_lot(ctx, ref, name):
+    """The whole GVD on the device vs the compiled reference on the bench maps: obstacle distance map and Voronoi-edge
+    set identical on C2; the Voronoi distance map differs only where the reference's 8-neighbour brushfire
+    overestimates (device = exact transform <= reference), in < 0.05 % of the cells, and the potential is
+    bit-identical wherever the two distance maps are."""
+    cfg = getattr(synth, name)
+    w, occ, sq_ref, vd_ref, pc_ref = _gvd_world(ref, cfg, rects=synth.config_rects(cfg))
+    g = ctx.build_gvd(w.map_desc(), occ, voronoi=True, want=ALL)
+    assert np.array_equal(g["sqdist"], sq_ref)
+    e_dev, e_ref = g["voro_sqdist"] == 0, vd_ref == 0
+    if name == "C2":
+        assert np.array_equal(e_dev, e_ref) and e_ref.sum() > 4000
+    else:
+        assert (e_dev != e_ref).sum() <= 2e-3 * e_ref.sum(), (e_dev != e_ref).sum()
+    dv = g["voro_sqdist"] != vd_ref
+    assert dv.mean() < 5e-4, dv.sum()
+    if name == "C2":
+        assert (g["voro_sqdist"][dv] < vd_ref[dv]).all()
+    same = ~dv
+    assert np.array_equal(g["pathcost"].view(np.uint32)[same], pc_ref.view(np.uint32)[same])
+    if name == "C2":
+        assert np.abs(g["pathcost"] - pc_ref).max() < 1e-2
+    _check_against_port(g, occ, w.resolution)
+    w.close()
+
+
+def test_gvd_build_without_voronoi_is_the_fixture_potential(ctx):
+    """flags = 0: the Voronoi map of a GVD created after OccupancyMap::Update() -- no edge, distance INT_MAX -- gives
+    the potential of tests/golden/edges_c2.npz (generated through that call order) bit for bit."""
+    from common import load_npz, c2_world_desc
+    gold = load_npz("edges_c2.npz")
+    desc, occ, sq, pc = c2_world_desc(gold)
+    g = ctx.build_gvd(desc, occ, voronoi=False, want=ALL)
+    assert np.array_equal(g["sqdist"], sq)
+    assert (g["voro_sqdist"] == INT_MAX).all() and (g["nearest_edge"] == -1).all()
+    assert np.array_equal(g["pathcost"].view(np.uint32), pc.view(np.uint32))
+
+
+def test_gvd_build_random_clutter_and_updates(ctx, ref):
+    """Arbitrarily rotated shapes: here the reference's brushfire is itself not an exact transform (its m_distance
+    overestimates in a few cells per map), so the bar is the measured deviation: obstacle distances
+    < 0.05 % of the cells (device smaller), Voronoi-edge cells < 4 % of the edge set.  The device is checked exactly
+    against the restated rule.  Then RemoveObstacle + AddObstacle: the reference updates incrementally
+    (gvd.cpp:74-89), the device rebuilds; same bars."""
+    from test_oracle_cpu import random_shapes
+    rng = np.random.default_rng(1)
+    cfg = dict(lb=(-20.0, -20.0, -np.pi), ub=(20.0, 20.0, np.pi), resolution=0.1)
+    shapes = random_shapes(rng, 58)
+    w, occ, sq_ref, vd_ref, pc_ref = _gvd_world(ref, cfg, shapes=shapes)
+
+    def check(occ, sq_ref, vd_ref):
+        g = ctx.build_gvd(w.map_desc(), occ, voronoi=True, want=ALL)
+        d = g["sqdist"] != sq_ref
+        assert d.mean() < 5e-4 and (g["sqdist"][d] < sq_ref[d]).all()
+        e_dev, e_ref = g["voro_sqdist"] == 0, vd_ref == 0
+        assert (e_dev != e_ref).sum() < 0.04 * e_ref.sum(), ((e_dev != e_ref).sum(), e_ref.sum())
+        _check_against_port(g, occ, w.resolution)
+
+    check(occ, sq_ref, vd_ref)
+    for i in (3, 17, 40):
+        assert w.remove_obstacle(i) == 1
+    extra = random_shapes(rng, 5)
+    for s in extra:
+        assert w.add_shape(*s) == 1
+    pc2, vd2 = w.gvd_update()
+    occ2, sq2 = w.grids()
+    assert (occ2 != occ).any()
+    check(occ2, sq2, vd2)
+    w.close()
+
+
+def test_gvd_build_empty_map(ctx):
+    desc = pp.MapDesc(rows=37, cols=53, resolution=0.5, world_origin=(0.0, 0.0), lb=(0, 0, -np.pi), ub=(18.5, 26.5, np.pi))
+    g = ctx.build_gvd(desc, np.full((37, 53), -1, np.int32), voronoi=True, want=ALL)
+    assert (g["sqdist"] == INT_MAX).all() and (g["voro_sqdist"] == INT_MAX).all() and (g["pathcost"] == 0).all()
+    assert (g["nearest_obstacle"] == -1).all() and (g["nearest_edge"] == -1).all()
