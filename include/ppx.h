@@ -389,6 +389,11 @@ int ppx_hybrid_search_dev(ppx_hybrid* h, int64_t nq, const double* d_starts, con
 	const uint64_t* d_seeds, const ppx_hybrid_limits* limits, ppx_hybrid_result* d_results,
 	ppx_hybrid_path_state* d_paths, ppx_hybrid_log_entry* d_log);
 
+/* Device time of the two phases of the last ppx_hybrid_search[_dev] call on this handle -- the wavefronts
+ * (ObstaclesHeuristic::Update per distinct goal cell) and the graph searches -- in milliseconds, from CUDA events
+ * on the context's stream.  Waits for that call to finish.  PPX_ERR_STATE when the call was split into chunks. */
+int ppx_hybrid_timing(ppx_hybrid* h, double* wavefront_ms, double* search_ms);
+
 /*
  * N3: the "Process graph search path" step of HybridAStar::SearchPath (algo/hybrid_a_star.cpp:260-291) for
  * the solution chains a search returned: the composite path (paths/path_composite.h:43-100) is resampled

@@ -460,6 +460,12 @@ class HybridAStar:
         self.ctx._check(ppx.ppx_hybrid_expand(self._h, _ptr(goal), n, _ptr(parents), _ptr(seeds), _ptr(count), _ptr(children), _ptr(ph)))
         return count, children, ph
 
+    def timing(self):
+        """(wavefront_ms, search_ms) of the last search call on this planner, device time"""
+        a, b = C.c_double(), C.c_double()
+        self.ctx._check(ppx.ppx_hybrid_timing(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def search(self, starts, goals, seeds, max_path=0, max_log=0, max_expansions=0, max_nodes=0):
         """-> dict(results (nq,) HYBRID_RESULT, paths (nq,max_path) or None, log (nq,max_log) or None)"""
         starts, goals = _f64(starts), _f64(goals)

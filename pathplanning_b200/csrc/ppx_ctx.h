@@ -18,6 +18,7 @@ struct ppx_ctx {
 	int rs_filter = 1; // 0: k_check_rs evaluates every sample with the exact FP64 path (A/B tests)
 	int rs_overlap = 0; // 1: consecutive ppx_check_edges_rs_dev launches overlap (programmatic dependent launch)
 	int rs_slot = 0; // cursor slot of the next overlapped launch
+	int search_engine = 1; // Hybrid A* graph search: 1 = one CTA per query (master + worker warps), 0 = one warp per query
 	unsigned long long* d_rsq = nullptr; // kMaxChunks cursors of the overlapped launches (each launch zeroes its successor's)
 
 	// world model

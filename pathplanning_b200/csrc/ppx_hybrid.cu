@@ -59,12 +59,15 @@ struct ppx_hybrid {
 	void* d_io = nullptr;
 	size_t ioBytes = 0;
 	void* d_consts = nullptr;
+	cudaEvent_t ev[3] {}; // start / wavefronts done / search done of the last ppx_hybrid_search[_dev] call
+	bool timed = false;
 };
 
 namespace {
 
 constexpr int kGenSlots = 3; // children sets per warp in shared memory (see k_hybrid_search)
-constexpr int kSearchWarps = 4; // warps (queries) per CTA
+constexpr int kSearchWarps = 4; // warps (queries) per CTA of the one-warp-per-query engine
+constexpr int kCtaWarps = 4; // warps per CTA of the CTA-per-query engine: 1 master + 3 workers
 
 // NonHolonomicHeuristic::Build, heuristics.cpp:62-73: one Reeds-Shepp solve per table entry
 __global__ void __launch_bounds__(128) k_nonholo_build(HybridDev P, double* __restrict__ values)
@@ -320,7 +323,10 @@ __global__ void __launch_bounds__(1024) k_query_order(MapDev map, int64_t nq, co
 	}
 }
 
-// The graph search of one query per warp.
+#include "ppx_hybrid_cta.cuh"
+
+// The graph search of one query per warp (ppx_ctx_set_option "search_engine" = 0; the default engine is the
+// CTA-per-query kernel above, same results).
 __global__ void __launch_bounds__(kSearchWarps * 32) k_hybrid_search(const SearchConsts* __restrict__ consts, int64_t nq,
 	const double* __restrict__ starts, const double* __restrict__ goals, const unsigned long long* __restrict__ seeds,
 	const int* __restrict__ wfSlot, const float* __restrict__ wfCost, WsLayout L, char* __restrict__ slabs,
@@ -608,31 +614,57 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 	L.tableSize = h->tx * h->ty * 7;
 	L.maxNodes = limits.max_nodes > 0 ? limits.max_nodes : 2 * L.tableSize;
 	L.bytes = (ws_bytes(L.maxNodes, L.tableSize) + 255) & ~(size_t)255;
-	// as many queries in flight as are resident (255 registers -> 8 warps per SM), at most 12 GB of slabs
-	static const int wps = getenv("PPX_SEARCH_WPS") ? atoi(getenv("PPX_SEARCH_WPS")) : 8;
-	int64_t warps = std::min<int64_t>(nq, (int64_t)ctx->num_sms * wps);
 	const size_t budget = (size_t)12 << 30;
-	warps = std::max<int64_t>(1, std::min<int64_t>(warps, (int64_t)(budget / L.bytes)));
-	int ctas = (int)((warps + kSearchWarps - 1) / kSearchWarps);
-	PPX_CHECK(grow(ctx, &h->d_slabs, &h->slabBytes, (size_t)ctas * kSearchWarps * L.bytes));
-	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
 	SearchConsts consts { h->dev, ctx->map_dev(), fast_map_derive(ctx->desc) };
 	if (!ctx->rs_filter)
 		consts.fm.enabled = 0;
 	if (!h->d_consts)
 		PPX_CUDA(ctx, cudaMalloc(&h->d_consts, sizeof(SearchConsts)));
 	PPX_CUDA(ctx, cudaMemcpyAsync(h->d_consts, &consts, sizeof(SearchConsts), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
+	int64_t resident; // queries in flight
+	int ctas;
+	size_t slab;
+	if (ctx->search_engine == 1) {
+		// one CTA per query: master warp + worker warps (ppx_hybrid_cta.cuh)
+		const int nCs = 2 * h->dev.numDeltas;
+		slab = (cta_ws_bytes(L.maxNodes, L.tableSize, nCs) + 255) & ~(size_t)255;
+		static int perSm = 0;
+		if (!perSm) {
+			PPX_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_hybrid_search_cta<kCtaWarps>, kCtaWarps * 32, 0));
+			if (getenv("PPX_SEARCH_CTAS"))
+				perSm = std::min(perSm, atoi(getenv("PPX_SEARCH_CTAS")));
+			perSm = std::max(perSm, 1);
+		}
+		resident = std::min<int64_t>(nq, (int64_t)ctx->num_sms * perSm);
+		resident = std::max<int64_t>(1, std::min<int64_t>(resident, (int64_t)(budget / slab)));
+		ctas = (int)resident;
+	} else {
+		// as many queries in flight as are resident (168 registers -> 8 warps per SM), at most 12 GB of slabs
+		static const int wps = getenv("PPX_SEARCH_WPS") ? atoi(getenv("PPX_SEARCH_WPS")) : 8;
+		slab = L.bytes;
+		resident = std::min<int64_t>(nq, (int64_t)ctx->num_sms * wps);
+		resident = std::max<int64_t>(1, std::min<int64_t>(resident, (int64_t)(budget / slab)));
+		ctas = (int)((resident + kSearchWarps - 1) / kSearchWarps);
+		resident = (int64_t)ctas * kSearchWarps;
+	}
+	PPX_CHECK(grow(ctx, &h->d_slabs, &h->slabBytes, (size_t)resident * slab));
 	int* d_order = nullptr;
-	if (nq > warps && nq < (int64_t)1 << 31) { // more queries than resident warps: schedule the long ones first
+	if (nq > resident && nq < (int64_t)1 << 31) { // more queries than slots: schedule the long ones first
 		float* d_keys;
 		PPX_CHECK(ppx_scratch(ctx, 6, (size_t)nq * 8, (void**)&d_keys));
 		d_order = (int*)(d_keys + nq);
 		k_query_order<<<1, 1024, 0, ctx->stream>>>(ctx->map_dev(), nq, d_starts, d_wfSlot, d_wf, d_keys, d_order);
 		PPX_LAUNCHED(ctx);
 	}
-	k_hybrid_search<<<ctas, kSearchWarps * 32, 0, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, d_starts, d_goals,
-		(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, (char*)h->d_slabs, limits, d_results, d_paths, d_log, ctx->d_queue,
-		d_order);
+	if (ctx->search_engine == 1)
+		k_hybrid_search_cta<kCtaWarps><<<ctas, kCtaWarps * 32, 0, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, d_starts, d_goals,
+			(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, slab, (char*)h->d_slabs, limits, d_results, d_paths, d_log,
+			ctx->d_queue, d_order);
+	else
+		k_hybrid_search<<<ctas, kSearchWarps * 32, 0, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, d_starts, d_goals,
+			(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, (char*)h->d_slabs, limits, d_results, d_paths, d_log, ctx->d_queue,
+			d_order);
 	PPX_LAUNCHED(ctx);
 #ifdef PPX_SEARCH_STATS
 	{
@@ -679,6 +711,8 @@ int ppx_hybrid_create(ppx_ctx* ctx, const ppx_hybrid_params* params, const ppx_v
 		return ppx_fail(ctx, PPX_ERR_CUDA, "cudaMalloc(heuristic table): %s", cudaGetErrorString(e));
 	}
 	h->dev.nh = h->d_table;
+	for (auto& e : h->ev)
+		cudaEventCreate(&e);
 	int blocks = (int)std::min<size_t>((total + 127) / 128, (size_t)ctx->num_sms * 16);
 	k_nonholo_build<<<blocks, 128, 0, ctx->stream>>>(h->dev, h->d_table);
 	PPX_LAUNCHED(ctx);
@@ -698,6 +732,9 @@ int ppx_hybrid_destroy(ppx_hybrid* h)
 	cudaFree(h->d_wf);
 	cudaFree(h->d_io);
 	cudaFree(h->d_consts);
+	for (auto& e : h->ev)
+		if (e)
+			cudaEventDestroy(e);
 	delete h;
 	return PPX_OK;
 }
@@ -855,13 +892,38 @@ int ppx_hybrid_search_dev(ppx_hybrid* h, int64_t nq, const double* d_starts, con
 	const size_t grid = ctx->cells * sizeof(float);
 	const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(((size_t)8 << 30) / grid)));
 	PPX_CHECK(grow(ctx, (void**)&h->d_wf, &h->wfBytes, (size_t)chunk * grid));
+	h->timed = chunk >= nq;
 	for (int64_t q0 = 0; q0 < nq; q0 += chunk) {
 		const int64_t m = std::min(chunk, nq - q0);
+		if (h->timed)
+			cudaEventRecord(h->ev[0], ctx->stream);
 		PPX_CHECK(ppx_wavefront_launch(ctx, m, d_goals + 3 * q0, h->d_wf, nullptr));
+		if (h->timed)
+			cudaEventRecord(h->ev[1], ctx->stream);
 		PPX_CHECK(launch_search(h, m, d_starts + 3 * q0, d_goals + 3 * q0, d_seeds ? d_seeds + q0 : nullptr, nullptr, h->d_wf, *limits,
 			d_results + q0, d_paths ? d_paths + (size_t)q0 * limits->max_path : nullptr,
 			d_log ? d_log + (size_t)q0 * limits->max_log : nullptr));
+		if (h->timed)
+			cudaEventRecord(h->ev[2], ctx->stream);
 	}
+	return PPX_OK;
+}
+
+int ppx_hybrid_timing(ppx_hybrid* h, double* wavefront_ms, double* search_ms)
+{
+	PPX_GUARD(h ? h->ctx : nullptr);
+	if (!h || !h->ctx)
+		return PPX_ERR_INVALID;
+	if (!h->timed)
+		return ppx_fail(h->ctx, PPX_ERR_STATE, "no timed search (the last call was split into chunks, or there was none)");
+	PPX_CUDA(h->ctx, cudaEventSynchronize(h->ev[2]));
+	float a = 0, b = 0;
+	PPX_CUDA(h->ctx, cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));
+	PPX_CUDA(h->ctx, cudaEventElapsedTime(&b, h->ev[1], h->ev[2]));
+	if (wavefront_ms)
+		*wavefront_ms = a;
+	if (search_ms)
+		*search_ms = b;
 	return PPX_OK;
 }
 
@@ -922,7 +984,10 @@ int ppx_hybrid_search(ppx_hybrid* h, int64_t nq, const double* starts, const dou
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oSeeds, seeds, nq * 8, cudaMemcpyHostToDevice, ctx->stream));
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oSlot, wfSlot.data(), nq * 4, cudaMemcpyHostToDevice, ctx->stream));
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oUGoals, uniqueGoals.data(), nGoals * 24, cudaMemcpyHostToDevice, ctx->stream));
+	h->timed = true;
+	cudaEventRecord(h->ev[0], ctx->stream);
 	PPX_CHECK(ppx_wavefront_launch(ctx, nGoals, (const double*)(base + oUGoals), h->d_wf, nullptr));
+	cudaEventRecord(h->ev[1], ctx->stream);
 	ppx_hybrid_path_state* d_paths = paths ? (ppx_hybrid_path_state*)(base + oPaths) : nullptr;
 	ppx_hybrid_log_entry* d_log = log ? (ppx_hybrid_log_entry*)(base + oLog) : nullptr;
 	if (d_paths)
@@ -931,6 +996,7 @@ int ppx_hybrid_search(ppx_hybrid* h, int64_t nq, const double* starts, const dou
 		PPX_CUDA(ctx, cudaMemsetAsync(d_log, 0, (size_t)nq * limits->max_log * sizeof(ppx_hybrid_log_entry), ctx->stream));
 	PPX_CHECK(launch_search(h, nq, (const double*)(base + oStarts), (const double*)(base + oGoals), (const uint64_t*)(base + oSeeds),
 		(const int*)(base + oSlot), h->d_wf, *limits, (ppx_hybrid_result*)(base + oRes), d_paths, d_log));
+	cudaEventRecord(h->ev[2], ctx->stream);
 	PPX_CUDA(ctx, cudaMemcpyAsync(results, base + oRes, nq * sizeof(ppx_hybrid_result), cudaMemcpyDeviceToHost, ctx->stream));
 	if (paths)
 		PPX_CUDA(ctx, cudaMemcpyAsync(paths, d_paths, (size_t)nq * limits->max_path * sizeof(ppx_hybrid_path_state), cudaMemcpyDeviceToHost, ctx->stream));

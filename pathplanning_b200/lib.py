@@ -106,6 +106,7 @@ _SIGS = {
     "ppx_map_rasterize": (C.c_int, [_p, C.POINTER(MapDescC), C.c_int32, _p, _p, C.c_int32, _p]),
     "ppx_astar_n2": (C.c_int, [_p, _i64, _p, _p, C.c_int32, C.c_int32, _p, _p]),
     "ppx_hybrid_search_dev": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
+    "ppx_hybrid_timing": (C.c_int, [_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
 
 for _name, (_res, _args) in _SIGS.items():

@@ -140,6 +140,10 @@ class World:
         cols = np.ascontiguousarray(cols, np.int32)
         lib().ref_world_set_cells(self.h, C.c_long(len(rows)), _p(rows), _p(cols), C.c_int(obstacle_id))
 
+    def set_position(self, x, y):
+        """OccupancyMap::SetPosition: the local frame's origin in world coordinates (occupancy_map.h:60-61)"""
+        lib().ref_world_set_position(self.h, C.c_double(x), C.c_double(y))
+
     def update(self):
         lib().ref_world_update(self.h)
 

@@ -262,3 +262,71 @@ def test_rs_overlap_option(ctx, c3_edges):
     assert np.array_equal(again[0], want[0][0]) and np.array_equal(again[1].view(np.uint32), want[0][1].view(np.uint32))
     for p in d_edges + d_valid + d_last:
         ppx.ppx_dev_free(ctx.handle, p)
+
+
+def test_local_origin_nonzero(ctx, ref):
+    """OccupancyMap::SetPosition != 0: ValidateBounds sees the LOCAL position, the step's distance to the border the
+    WORLD position (state_validator_occupancy_map.cpp:18-20 vs :54-59).  The FP32 cell filter must certify against
+    both frames: filter on / off bit-identical, and both equal to the live reference, near every border."""
+    g = load_npz("edges_c2.npz")
+    for pos in ((-6.0, 3.5), (7.25, -9.0)):
+        w = ref.World(g["lb"], g["ub"], float(g["resolution"]))
+        for r in g["rects"][::3]:
+            w.add_rectangle(*r)
+        w.set_position(*pos)
+        w.update()
+        occ, sq = w.grids()
+        desc = w.map_desc()
+        assert tuple(desc.local_origin) == pos
+        ctx.upload_map(desc, sq, occ, None)
+        rng = np.random.default_rng(17)
+        n = 40000
+        starts = np.stack([rng.uniform(-21, 21, n), rng.uniform(-21, 21, n), rng.uniform(-np.pi, np.pi, n)], 1)
+        d, a = rng.uniform(0.1, 15, n), rng.uniform(-np.pi, np.pi, n)
+        goals = np.stack([starts[:, 0] + d * np.cos(a), starts[:, 1] + d * np.sin(a), rng.uniform(-np.pi, np.pi, n)], 1)
+        rr = w.check_rs_edges(starts, goals, 2.0)
+        assert 0.02 < rr["valid"].mean() < 0.98
+        edges = pp.make_rs_edges(starts, rr["steer"], rr["dir"], rr["len"])
+        vp = pp.ValidatorParams(1.0, 0.1)
+        on = ctx.check_edges_rs(edges, 2.0, vp, want_samples=True)
+        ctx.set_option("rs_filter", 0)
+        try:
+            off = ctx.check_edges_rs(edges, 2.0, vp, want_samples=True)
+        finally:
+            ctx.set_option("rs_filter", 1)
+        for got in (on, off):
+            assert np.array_equal(got[0], rr["valid"])
+            assert np.array_equal(got[2].astype(np.int64), rr["samples"].astype(np.int64))
+            assert_close_rel(got[1], rr["last"], REL, "last")
+        assert np.array_equal(on[1].view(np.uint32), off[1].view(np.uint32))
+        w.close()
+
+
+def test_two_contexts_one_process(ctx, c2):
+    """One context per GPU may live in one process, and the caller (or torch) may change the current device between
+    calls: every entry point runs on its context's device and restores the caller's.  With a single GPU both contexts
+    sit on device 0; the second one must not disturb the first one's scratch buffers or map."""
+    import torch
+    g = c2
+    desc, occ, sq, pc = c2_world_desc(g)
+    ctx.upload_map(desc, sq, occ, pc)  # earlier tests of this module left other maps on the shared context
+    vp = pp.ValidatorParams(1.0, 0.1)
+    edges = pp.make_rs_edges(g["starts"], g["steer"], g["dir"], g["len"])
+    want = ctx.check_edges_rs(edges, 2.0, vp)
+    ndev = torch.cuda.device_count()
+    other = pp.Context(ndev - 1)
+    try:
+        other.upload_map(desc, sq, occ, pc)
+        if ndev > 1:
+            torch.cuda.set_device(0)
+        got = other.check_edges_rs(edges, 2.0, vp)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1].view(np.uint32), want[1].view(np.uint32))
+        if ndev > 1:
+            assert torch.cuda.current_device() == 0
+            torch.cuda.set_device(ndev - 1)
+        again = ctx.check_edges_rs(edges, 2.0, vp)
+        assert np.array_equal(again[0], want[0])
+    finally:
+        other.close()
+        if ndev > 1:
+            torch.cuda.set_device(0)

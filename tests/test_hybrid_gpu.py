@@ -226,3 +226,31 @@ def test_resample_live_reference(ref, planner):
     H.close()
     w.close()
     assert solved >= 60
+
+
+def test_search_engines_identical(ctx, planner, fx):
+    """The CTA-per-query engine (master warp + worker warps, the default) against the one-warp-per-query engine:
+    result records (status, counts, node numbering, cost bits, expansion hash), solution chains and expansion logs
+    are byte-identical, on the fixture queries and on 600 random ones -- more than there are resident CTAs on a
+    small grid, so slots are reused."""
+    rng = np.random.default_rng(2024)
+    vp = pp.ValidatorParams(1.0, 0.1)
+    pts = np.empty((0, 3))
+    while len(pts) < 1200:
+        p = np.stack([rng.uniform(-18.5, 18.5, 4000), rng.uniform(-18.5, 18.5, 4000), rng.uniform(-np.pi, np.pi, 4000)], 1)
+        pts = np.concatenate([pts, p[ctx.is_state_valid(p, vp)]])
+    starts = np.concatenate([fx["q_start"], pts[:600]])
+    goals = np.concatenate([fx["q_goal"], pts[600:1200]])
+    seeds = np.concatenate([fx["q_seed"].astype(np.uint64), np.arange(600, dtype=np.uint64) + 77])
+    outs = []
+    for engine in (0, 1):
+        ctx.set_option("search_engine", engine)
+        try:
+            outs.append(planner.search(starts, goals, seeds, max_path=256, max_log=3000))
+        finally:
+            ctx.set_option("search_engine", 1)
+    a, b = outs
+    assert a["results"].tobytes() == b["results"].tobytes(), np.flatnonzero(a["results"] != b["results"])[:10]
+    assert a["paths"].tobytes() == b["paths"].tobytes()
+    assert a["log"].tobytes() == b["log"].tobytes()
+    assert (a["results"]["status"] == 0).sum() > 300
