@@ -67,7 +67,6 @@ namespace {
 
 constexpr int kGenSlots = 3; // children sets per warp in shared memory (see k_hybrid_search)
 constexpr int kSearchWarps = 4; // warps (queries) per CTA of the one-warp-per-query engine
-constexpr int kCtaWarps = 4; // warps per CTA of the CTA-per-query engine: 1 master + 3 workers
 
 // NonHolonomicHeuristic::Build, heuristics.cpp:62-73: one Reeds-Shepp solve per table entry
 __global__ void __launch_bounds__(128) k_nonholo_build(HybridDev P, double* __restrict__ values)
@@ -614,7 +613,7 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 	L.tableSize = h->tx * h->ty * 7;
 	L.maxNodes = limits.max_nodes > 0 ? limits.max_nodes : 2 * L.tableSize;
 	L.bytes = (ws_bytes(L.maxNodes, L.tableSize) + 255) & ~(size_t)255;
-	const size_t budget = (size_t)12 << 30;
+	const size_t budget = (size_t)32 << 30; // of slabs (180 GB of HBM; the wavefront grids of 4096 goals take 2.6 GB)
 	SearchConsts consts { h->dev, ctx->map_dev(), fast_map_derive(ctx->desc) };
 	if (!ctx->rs_filter)
 		consts.fm.enabled = 0;
@@ -625,18 +624,45 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 	int64_t resident; // queries in flight
 	int ctas;
 	size_t slab;
+	using CtaKernel = void (*)(const SearchConsts*, int64_t, const double*, const double*, const unsigned long long*, const int*,
+		const float*, WsLayout, size_t, char*, ppx_hybrid_limits, ppx_hybrid_result*, ppx_hybrid_path_state*, ppx_hybrid_log_entry*,
+		unsigned long long*, const int*, unsigned long long*);
+	CtaKernel ctaKernel = nullptr;
+	int ctaWarps = 4;
+	size_t ctaSmem = 0;
 	if (ctx->search_engine == 1) {
-		// one CTA per query: master warp + worker warps (ppx_hybrid_cta.cuh)
+		// one CTA per query: master warp + worker warps (ppx_hybrid_cta.cuh).  The key table lives in shared memory
+		// (16-bit entries) when it fits; a batch much larger than the GPU holds runs with one worker per master and
+		// twice the CTAs, a batch the GPU can hold at once with three workers per master (shortest critical path).
 		const int nCs = 2 * h->dev.numDeltas;
 		slab = (cta_ws_bytes(L.maxNodes, L.tableSize, nCs) + 255) & ~(size_t)255;
-		static int perSm = 0;
-		if (!perSm) {
-			PPX_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_hybrid_search_cta<kCtaWarps>, kCtaWarps * 32, 0));
+		const bool smemTable = (size_t)L.tableSize * 2 <= 28 * 1024 && L.maxNodes + 2 <= 65535
+			&& !(getenv("PPX_SEARCH_SMEMTAB") && atoi(getenv("PPX_SEARCH_SMEMTAB")) == 0);
+		// key table (16-bit entries, padded to 16 bytes) + ready bitmap (2 bits per node)
+		ctaSmem = smemTable ? (size_t)((L.tableSize + 7) & ~7) * 2 + (size_t)((L.maxNodes + 15) / 16) * 4 : 0;
+		auto pick = [&](int warps) -> CtaKernel {
+			if (warps == 2) // throughput mode: small shared-memory footprint, 8 CTAs per SM
+				return k_hybrid_search_cta<2, false, kCtaHeapSmemSmall>;
+			return smemTable ? k_hybrid_search_cta<4, true, kCtaHeapSmemBig> : k_hybrid_search_cta<4, false, kCtaHeapSmemBig>;
+		};
+		auto perSmOf = [&](int warps, int* out) -> int {
+			PPX_CUDA(ctx, cudaFuncSetAttribute(pick(warps), cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+			PPX_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(out, pick(warps), warps * 32, warps == 2 ? 0 : ctaSmem));
 			if (getenv("PPX_SEARCH_CTAS"))
-				perSm = std::min(perSm, atoi(getenv("PPX_SEARCH_CTAS")));
-			perSm = std::max(perSm, 1);
-		}
-		resident = std::min<int64_t>(nq, (int64_t)ctx->num_sms * perSm);
+				*out = std::min(*out, atoi(getenv("PPX_SEARCH_CTAS")));
+			*out = std::max(*out, 1);
+			return PPX_OK;
+		};
+		int perSm4 = 1, perSm2 = 1;
+		PPX_CHECK(perSmOf(4, &perSm4));
+		PPX_CHECK(perSmOf(2, &perSm2));
+		ctaWarps = nq >= 2 * (int64_t)ctx->num_sms * perSm4 ? 2 : 4;
+		if (getenv("PPX_SEARCH_WARPS"))
+			ctaWarps = atoi(getenv("PPX_SEARCH_WARPS")) == 2 ? 2 : 4;
+		ctaKernel = pick(ctaWarps);
+		if (ctaWarps == 2)
+			ctaSmem = 0;
+		resident = std::min<int64_t>(nq, (int64_t)ctx->num_sms * (ctaWarps == 2 ? perSm2 : perSm4));
 		resident = std::max<int64_t>(1, std::min<int64_t>(resident, (int64_t)(budget / slab)));
 		ctas = (int)resident;
 	} else {
@@ -657,11 +683,30 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 		k_query_order<<<1, 1024, 0, ctx->stream>>>(ctx->map_dev(), nq, d_starts, d_wfSlot, d_wf, d_keys, d_order);
 		PPX_LAUNCHED(ctx);
 	}
-	if (ctx->search_engine == 1)
-		k_hybrid_search_cta<kCtaWarps><<<ctas, kCtaWarps * 32, 0, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, d_starts, d_goals,
+	static const bool statsOn = getenv("PPX_SEARCH_STATS") != nullptr; // phase cycles of the CTA engine to stderr (tools/time_search.py)
+	static unsigned long long* d_stats = nullptr;
+	if (statsOn && !d_stats)
+		PPX_CUDA(ctx, cudaMalloc(&d_stats, 32 * sizeof(unsigned long long)));
+	if (statsOn)
+		PPX_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 32 * sizeof(unsigned long long), ctx->stream));
+	if (ctx->search_engine == 1) {
+		ctaKernel<<<ctas, ctaWarps * 32, ctaSmem, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, d_starts, d_goals,
 			(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, slab, (char*)h->d_slabs, limits, d_results, d_paths, d_log,
-			ctx->d_queue, d_order);
-	else
+			ctx->d_queue, d_order, statsOn ? d_stats : nullptr);
+		if (statsOn) {
+			unsigned long long st[32];
+			cudaStreamSynchronize(ctx->stream);
+			cudaMemcpy(st, d_stats, sizeof(st), cudaMemcpyDeviceToHost);
+			const double ne = (double)std::max<unsigned long long>(1, st[11]);
+			fprintf(stderr, "cta search stats (%lld queries, %d ctas x %d warps, smem table %zu B, %llu expansions): cycles/expansion pop %.0f, "
+				"rng+log %.0f, own gen %.0f, rs %.0f, wait %.0f, commit-load %.0f, commit-decide %.0f, commit-write %.0f | kids ready %.1f%%, claimed %.1f%%, "
+				"own %.1f%% | rs shots ready %llu, claimed %llu, own %llu | workers: %llu passes, %.2f nodes/pass, %.0f cycles/pass, %llu rs "
+				"tasks, %llu idle, nodes generated / expanded %.2f\n",
+				(long long)nq, ctas, ctaWarps, ctaSmem, st[11], st[0] / ne, st[1] / ne, st[2] / ne, st[3] / ne, st[4] / ne, st[5] / ne,
+				st[7] / ne, st[6] / ne, 100.0 * st[8] / ne, 100.0 * st[9] / ne, 100.0 * st[10] / ne, st[12], st[13], st[14], st[16],
+				st[16] ? (double)st[17] / st[16] : 0.0, st[16] ? (double)st[18] / st[16] : 0.0, st[20], st[19], (st[17] + st[10]) / ne);
+		}
+	} else
 		k_hybrid_search<<<ctas, kSearchWarps * 32, 0, ctx->stream>>>((const SearchConsts*)h->d_consts, nq, d_starts, d_goals,
 			(const unsigned long long*)d_seeds, d_wfSlot, d_wf, L, (char*)h->d_slabs, limits, d_results, d_paths, d_log, ctx->d_queue,
 			d_order);
