@@ -36,6 +36,12 @@ N_BATCHES = 4  # rotating batches: 4 x 72 MB of edge records > 126 MB L2
 RMIN = 2.0
 RADIUS, MIN_STEP = 1.0, 0.1
 WORKLOAD = "C3: 1M Reeds-Shepp edges x disc footprint r=1.0m on 2000x2000 grid @0.1m (parking lot, p=0.5)"
+L2_NOTE = "GPU arm: 4 rotating edge batches per rank (288 MB of records in mode check) > 126 MB L2, no flush needed"
+
+
+def bench_config(mode):
+    """The `config` object, identical on both arms."""
+    return {"workload": WORKLOAD, "mode": mode, "l2": L2_NOTE}
 
 
 _REAL_STDOUT = None
@@ -58,6 +64,19 @@ def _emit(line):
     os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
 
 
+def _synth():
+    """pathplanning_b200/synth.py loaded by path: importing the package would dlopen libppx.so, which the reference arm
+    must not do (its record has to show no product code loaded)."""
+    import importlib.util
+    if "ppx_synth" in sys.modules:
+        return sys.modules["ppx_synth"]
+    spec = importlib.util.spec_from_file_location("ppx_synth", os.path.join(ROOT, "pathplanning_b200", "synth.py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["ppx_synth"] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -69,7 +88,7 @@ def host_cores():
 # Reference arm: the compiled reference on the host cores (test infrastructure, see oracle/)
 def _ref_world():
     import refapi
-    from pathplanning_b200 import synth
+    synth = _synth()
     cfg = synth.C3
     w = refapi.World(cfg["lb"], cfg["ub"], cfg["resolution"])
     for r in synth.config_rects(cfg):
@@ -98,7 +117,7 @@ def run_reference(args, per_core):
     """Times the reference's own CPU implementation with one process per host core.
     Returns (edges_per_s, ms_per_step, cores, sample description)."""
     import multiprocessing as mp
-    from pathplanning_b200 import synth
+    synth = _synth()
     cores = host_cores()
     w = _ref_world()  # built once, inherited by fork (process-global Random<> statics stay per process)
     n = per_core * cores
@@ -126,30 +145,38 @@ def run_reference(args, per_core):
     return n / sec, sec * 1e3, cores, sample
 
 
-def _ref_hybrid_worker(queries, conn):
-    """Child process: the reference's wavefront + GVD update + graph search (hybrid_a_star.cpp:248-257) per query."""
+def _ref_hybrid_worker(queries, field, conn):
+    """Child process: the reference's wavefront + GVD update + graph search (hybrid_a_star.cpp:248-257) per query.
+    The GVD is attached before the obstacle brushfire runs (example.py:47-48), so the potential is the Voronoi field;
+    `field` = (sqdist, voro_sqdist) built by the device (ppx_gvd_build) replaces the reference's two distance grids, so
+    that both arms search the same potential (the reference recomputes it from those grids at every GVD::Update)."""
+    import zlib
     import refapi
-    from pathplanning_b200 import synth
+    synth = _synth()
     try:
         cfg = synth.C2
         w = refapi.World(cfg["lb"], cfg["ub"], cfg["resolution"])
         for r in synth.config_rects(cfg):
             w.add_rectangle(*r)
-        w.update()
+        w.gvd_update()
+        diff = w.set_gvd_distances(*field) if field is not None else (0, 0)
         w.set_validator_params(RADIUS, MIN_STEP)
         H = refapi.Hybrid(w)
         t0 = time.perf_counter()
-        ok = 0
-        for s, g, seed in queries:
-            ok += H.search(s, g, seed)["status"] == 0
-        conn.send((time.perf_counter() - t0, ok))
+        recs = []
+        for qi, s, g, seed in queries:
+            r = H.search(s, g, seed)
+            recs.append((qi, int(r["status"]), int(r["n_expanded"]), zlib.crc32(np.ascontiguousarray(r["exp_keys"][:, :3], np.int32).tobytes()),
+                         float(r["cost"])))
+        conn.send((time.perf_counter() - t0, recs, diff))
     except Exception as e:  # pragma: no cover
         conn.send(e)
     conn.close()
 
 
-def run_reference_hybrid(starts, goals, seeds, per_core):
-    """plans/s of the reference on all host cores (one process per core) over the first per_core*cores queries."""
+def run_reference_hybrid(starts, goals, seeds, per_core, field=None):
+    """plans/s of the reference on all host cores (one process per core) over the first per_core*cores queries, and the
+    per-query records (status, expansions, CRC of the expansion sequence, cost) the GPU run is checked against."""
     import multiprocessing as mp
     cores = host_cores()
     n = min(len(starts), per_core * cores)
@@ -157,9 +184,9 @@ def run_reference_hybrid(starts, goals, seeds, per_core):
     procs, pipes = [], []
     for c in range(cores):
         idx = range(c, n, cores)
-        qs = [(tuple(starts[i]), tuple(goals[i]), int(seeds[i])) for i in idx]
+        qs = [(i, tuple(starts[i]), tuple(goals[i]), int(seeds[i])) for i in idx]
         a, b = ctxmp.Pipe(duplex=False)
-        p = ctxmp.Process(target=_ref_hybrid_worker, args=(qs, b))
+        p = ctxmp.Process(target=_ref_hybrid_worker, args=(qs, field, b))
         p.start()
         procs.append(p)
         pipes.append(a)
@@ -170,8 +197,10 @@ def run_reference_hybrid(starts, goals, seeds, per_core):
         if isinstance(r, Exception):
             raise r
     sec = max(r[0] for r in results)
-    return {"value": n / sec, "unit": "plans/s", "cores": cores, "kind": "reference",
-            "sample": f"first {n} of the 4096 queries, wavefront + GVD update + graph search each, one process per core"}
+    recs = sorted(rec for r in results for rec in r[1])
+    base = {"value": n / sec, "unit": "plans/s", "cores": cores, "kind": "reference",
+            "sample": f"first {n} of the queries, wavefront + GVD update + graph search each, one process per core"}
+    return base, recs, results[0][2]
 
 
 def reference_main(args):
@@ -183,11 +212,13 @@ def reference_main(args):
         _emit({"impl": "reference", "unavailable": "oracle/_ref/libpp_ref.so not built"})
         return
     value, ms, cores, sample = run_reference(args, per_core=args.cpu_edges_per_core)
+    per_step_edges = args.cpu_edges_per_core * cores
     line = {
         "impl": "reference", "metric": "collision-checked RS edges/s", "value": value, "unit": "edges/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "mode": args.mode},
+        "config": bench_config(args.mode),
+        "config_detail": {"edges_per_step": per_step_edges, "note": "bounded sample of the workload per step, all host cores"},
         "cpu_baseline": {"value": value, "unit": "edges/s", "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "edges/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -256,32 +287,38 @@ def c4_queries(ctx, pp, n, seed=12345):
 
 
 def hybrid_section(args, rank, world, local_rank, stream):
-    """Config C4: 4096 Hybrid A* queries on the C2 map, sharded by query over the ranks (strong scaling), results
-    gathered with one NCCL all_gather of the fixed-size result records."""
+    """Config C4: Hybrid A* queries on the C2 map, sharded by query over the ranks (strong scaling, interleaved shards,
+    no data-path collective), results gathered with one NCCL all_gather of the fixed-size result records.
+
+    The potential both arms search is the Voronoi field the DEVICE builds (ppx_gvd_build); the CPU arm gets the
+    device-built distance grids injected into the reference's GVD, and a sample of the timed batch is compared with the
+    reference inside the run: status, expansion count, CRC of the expansion sequence, cost."""
+    import zlib
     import torch
     import torch.distributed as dist
     import pathplanning_b200 as pp
     from pathplanning_b200 import synth
     from pathplanning_b200.lib import ppx, HybridLimitsC
     from pathplanning_b200.api import HYBRID_RESULT
+    from pathplanning_b200.shard import shard_indices, gather_records
     dev = torch.device("cuda", local_rank)
     ctx = pp.Context(local_rank)
     ctx.set_stream(stream.cuda_stream)
     cfg = synth.C2
     occ = synth.rasterize_rectangles(synth.config_rects(cfg), cfg["lb"], cfg["ub"], cfg["resolution"])
-    sq = synth.exact_sqdist(occ)
     rows, cols, origin = synth.map_geometry(cfg["lb"], cfg["ub"], cfg["resolution"])
-    ctx.upload_map(pp.MapDesc(rows=rows, cols=cols, resolution=cfg["resolution"], world_origin=origin, lb=cfg["lb"], ub=cfg["ub"]),
-                   sq, occ, None)
+    desc = pp.MapDesc(rows=rows, cols=cols, resolution=cfg["resolution"], world_origin=origin, lb=cfg["lb"], ub=cfg["ub"])
+    t0 = time.perf_counter()
+    field = ctx.build_gvd(desc, occ, voronoi=True)
+    gvd_ms = (time.perf_counter() - t0) * 1e3
     planner = pp.HybridAStar(ctx, pp.HybridParams(), pp.ValidatorParams(RADIUS, MIN_STEP))
     nq = args.hybrid_queries
     starts, goals, seeds = c4_queries(ctx, pp, nq)
-    from pathplanning_b200.shard import shard_range, gather_records
-    lo, hi = shard_range(nq, rank, world)
-    m = hi - lo
-    d_s = torch.from_numpy(starts[lo:hi].copy()).to(dev)
-    d_g = torch.from_numpy(goals[lo:hi].copy()).to(dev)
-    d_seed = torch.from_numpy(seeds[lo:hi].astype(np.int64)).to(dev)
+    mine = shard_indices(nq, rank, world, layout="strided")
+    m = len(mine)
+    d_s = torch.from_numpy(starts[mine].copy()).to(dev)
+    d_g = torch.from_numpy(goals[mine].copy()).to(dev)
+    d_seed = torch.from_numpy(seeds[mine].astype(np.int64)).to(dev)
     d_res = torch.zeros(m * HYBRID_RESULT.itemsize, dtype=torch.uint8, device=dev)
     lim = HybridLimitsC(0, 0, 0, 0)
     launches0 = ctx.launch_count
@@ -297,6 +334,8 @@ def hybrid_section(args, rank, world, local_rank, stream):
         torch.cuda.synchronize()
 
     run_dev()  # warm-up (allocates the workspaces)
+    run_dev()
+    run_dev()
     barrier()
     reps = 3
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -309,43 +348,62 @@ def hybrid_section(args, rank, world, local_rank, stream):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_dev = float(t.item())
-    launches = (ctx.launch_count - launches0) // (reps + 1)
+    wf_ms, search_ms = planner.timing()  # this rank's last repetition
+    launches = (ctx.launch_count - launches0) // (reps + 3)
+    local = d_res.cpu().numpy().view(HYBRID_RESULT).copy()  # the device-timed run's records of this shard
     # through the host-buffer call (goal de-duplication, H2D, wavefronts, search, D2H of results + paths)
-    planner.search(starts[lo:hi], goals[lo:hi], seeds[lo:hi], max_path=128)
+    planner.search(starts[mine], goals[mine], seeds[mine], max_path=128)
     barrier()
     t0 = time.perf_counter()
-    out = planner.search(starts[lo:hi], goals[lo:hi], seeds[lo:hi], max_path=128)
+    out = planner.search(starts[mine], goals[mine], seeds[mine], max_path=128)
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    res = out["results"]
+    same_as_timed = bool(out["results"].tobytes() == local.tobytes())
     # gather of the fixed-size records: the only collective of the path
     gather_ms = 0.0
-    solved = int((res["status"] == 0).sum())
-    expanded = int(res["n_expanded"].sum())
+    allres = local if world == 1 else None
     if world > 1:
-        local = d_res.cpu().numpy().view(HYBRID_RESULT)  # the device-timed run's records of this shard
         torch.cuda.synchronize()
-        gather_records(local, nq, device=dev)  # warm-up of the collective
+        gather_records(local, nq, device=dev, indices=mine)  # warm-up of the collective
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         g0.record()
-        allres = gather_records(local, nq, device=dev)
+        allres = gather_records(local, nq, device=dev, indices=mine)
         g1.record()
         torch.cuda.synchronize()
         gather_ms = g0.elapsed_time(g1)
-        solved, expanded = int((allres["status"] == 0).sum()), int(allres["n_expanded"].sum())
+    solved, expanded = int((allres["status"] == 0).sum()), int(allres["n_expanded"].sum())
     section = {
         "metric": "batched Hybrid A* plans/s", "workload": f"C4: {nq} independent start/goal queries on the C2 parking lot (400x400 @0.1m), "
-        "wavefront + graph search per query, sharded by query", "scaling": "strong", "queries_per_gpu": m,
-        "value": nq / (ms_dev * 1e-3), "unit": "plans/s", "ms": ms_dev,
-        "e2e": {"value": nq / float(te.item()), "unit": "plans/s", "h2d_bytes": int(m * 56), "d2h_bytes": int(m * (40 + 128 * 40))},
-        "solved": solved, "expansions": expanded, "gather_ms": gather_ms, "gpu_launches": int(launches),
+        "wavefront + graph search per query, sharded by query (interleaved)", "scaling": "strong", "queries_per_gpu": m,
+        "value": nq / (ms_dev * 1e-3), "unit": "plans/s", "ms": ms_dev, "wavefront_ms": wf_ms, "search_ms": search_ms,
+        "e2e": {"value": nq / float(te.item()), "unit": "plans/s", "h2d_bytes": int(m * 56), "d2h_bytes": int(m * (40 + 128 * 40)),
+                "records_equal_device_timed_run": same_as_timed},
+        "solved": solved, "expansions": expanded, "longest_query_expansions": int(allres["n_expanded"].max()),
+        "gather_ms": gather_ms, "gpu_launches": int(launches),
+        "field": {"what": "Voronoi potential built on the device (ppx_gvd_build: distance map, Voronoi edges, Voronoi distance "
+                          "map, PathCostMap); the CPU arm searches the same field", "build_ms_host_call": gvd_ms,
+                  "voronoi_edge_cells": int((field["voro_sqdist"] == 0).sum())},
         "note": "smoothing (SURVEY N2) is not part of this figure, neither here nor in the CPU figure",
     }
+    # roofline of k_hybrid_search_cta: it is bound by instruction issue on dependent chains, not by HBM.  Warp-instructions
+    # per expansion come from the committed ncu capture of this workload; the peak is 4 schedulers x SMs x clock.
+    ipath = os.path.join(ROOT, "profiles", "hybrid_issue.json")
+    if os.path.exists(ipath):
+        ij = json.load(open(ipath))
+        sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
+        clock_ghz = ij.get("sm_clock_ghz", 1.965)
+        achieved = expanded / (search_ms * 1e-3) * ij["warp_instructions_per_expansion"] / 1e9 / max(1, world) if world == 1 else None
+        if achieved is not None:
+            peak = 4 * sms * clock_ghz
+            section["roofline"] = {"bound": "issue", "kernel": "k_hybrid_search_cta", "achieved": achieved, "peak": peak,
+                                   "unit": "G warp-instructions/s", "frac": achieved / peak,
+                                   "warp_instructions_per_expansion": ij["warp_instructions_per_expansion"],
+                                   "source": ij.get("source"), "note": "search phase only (search_ms); HBM is not its bound"}
     if world > 1:
-        # weak-scaling companion: every rank searches all nq queries (4096 per GPU); a strong-scaled shard of
-        # 4096/N queries is bounded below by its longest single query (a chain of ~7000 dependent expansions)
+        # weak-scaling companion: every rank searches all nq queries; a strong-scaled shard of nq/N queries is bounded
+        # below by its longest single query (a chain of ~7000 dependent expansions)
         d_sw = torch.from_numpy(starts.copy()).to(dev)
         d_gw = torch.from_numpy(goals.copy()).to(dev)
         d_seedw = torch.from_numpy(seeds.astype(np.int64)).to(dev)
@@ -369,7 +427,32 @@ def hybrid_section(args, rank, world, local_rank, stream):
                            "ms": float(tw.item())}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            section["cpu_baseline"] = run_reference_hybrid(starts, goals, seeds, args.cpu_plans_per_core)
+            base, recs, diff = run_reference_hybrid(starts, goals, seeds, args.cpu_plans_per_core,
+                                                    field=(field["sqdist"], field["voro_sqdist"]))
+            section["cpu_baseline"] = base
+            # the same queries on the device with expansion logs, tied to the timed batch through the result records
+            k = len(recs)
+            chk = planner.search(starts[:k], goals[:k], seeds[:k], max_log=12000)
+            mismatched, untied = [], 0
+            for qi, st, nexp, crc, cost in recs:
+                r = chk["results"][qi]
+                tr = allres[qi]
+                if not (int(tr["status"]) == int(r["status"]) and int(tr["n_expanded"]) == int(r["n_expanded"])
+                        and int(tr["expanded_hash"]) == int(r["expanded_hash"])):
+                    untied += 1
+                good = int(r["status"]) == st and int(r["n_expanded"]) == nexp and nexp <= 12000
+                if good:
+                    good = zlib.crc32(np.ascontiguousarray(chk["log"][qi]["key"][:nexp], np.int32).tobytes()) == crc
+                if good and st == 0:
+                    good = abs(float(r["cost"]) - cost) <= 1e-6 * max(1.0, abs(cost))
+                if not good:
+                    mismatched.append(int(qi))
+            section["checked_vs_reference"] = {
+                "queries": k, "matching": k - len(mismatched), "mismatched": mismatched[:16], "not_tied_to_timed_batch": untied,
+                "compared": "status, expansion count, CRC32 of the expansion sequence (discrete keys), cost within 1e-6; the logged "
+                            "run equals the timed batch in status / expansion count / expansion hash",
+                "reference_field_cells_replaced": {"obstacle_distance": diff[0], "voronoi_distance": diff[1],
+                                                   "of": int(rows * cols)}}
         except Exception as e:  # pragma: no cover
             section["cpu_baseline"] = {"unavailable": f"{type(e).__name__}: {e}"}
     planner.close()
@@ -610,14 +693,16 @@ def ours_main(args):
             "metric": "collision-checked RS edges/s", "value": value, "unit": "edges/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "mode": args.mode, "edges_per_gpu_per_step": n,
+            "config": bench_config(args.mode),  # identical on the reference arm
+            "config_detail": {"edges_per_gpu_per_step": n,
                        "launches": ("overlapped: ppx_ctx_set_option(rs_overlap) = programmatic dependent launch on one stream, own "
                                     "output arrays per batch, results verified against serial launches; see \"serial\"")
                        if overlap_ok else "serial",
                        "mean_samples_per_edge": mean_samples, "valid_fraction": valid_frac,
                        "l2": f"{N_BATCHES} rotating edge batches ({N_BATCHES * n * in_bytes / 1e6:.0f} MB) > 126 MB L2; the 16 MB clearance grid is meant to stay L2-resident"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "bytes_per_edge": bytes_per_edge,
+                         "traffic": traffic, "traffic_source": "profiles/traffic.json (ncu --set full capture of one launch, not measured in "
+                         "this run)" if traffic is not None else None, "peak_source": peak_src, "bytes_per_edge": bytes_per_edge,
                          "note": "FP64-issue / dependent-L2-latency bound, not HBM bound (DESIGN.md)"},
             "cpu_baseline": cpu_baseline,
             "map_build": {"ms": map_build_ms, "cells": int(rows * cols),

@@ -338,6 +338,30 @@ void ref_world_gvd_update(void* h, float* pathcost, int* voro_sqdist)
 		memcpy(voro_sqdist, w->gvd->m_voronoiMap->m_distance.m_data, n * sizeof(int));
 }
 
+// bench.py, C4: the reference searches the SAME potential the device built.  Overwrites the two distance grids of the
+// world's GVD (GVD::PathCostMap::Update recomputes the potential from them at every GVD::Update, gvd.cpp:266-283,
+// hybrid_a_star.cpp:250) with the caller's; returns the number of cells that differed (obstacle, Voronoi).
+void ref_world_set_gvd_distances(void* h, const int* sqdist, const int* voro_sqdist, long* diff)
+{
+	auto* w = (RefWorld*)h;
+	if (!w->gvd)
+		w->gvd = makeRef<GVD>(w->map);
+	long n = (long)w->map->Rows() * w->map->Columns();
+	int* a = w->map->m_obstacleDistanceMap->m_distance.m_data;
+	int* b = w->gvd->m_voronoiMap->m_distance.m_data;
+	long da = 0, db = 0;
+	for (long i = 0; i < n; i++) {
+		da += a[i] != sqdist[i];
+		db += b[i] != voro_sqdist[i];
+		a[i] = sqdist[i];
+		b[i] = voro_sqdist[i];
+	}
+	if (diff) {
+		diff[0] = da;
+		diff[1] = db;
+	}
+}
+
 // The nearest-obstacle / nearest-Voronoi-edge cells of the world's own GVD (after ref_world_gvd_update), (row, col) pairs.
 void ref_world_gvd_cells(void* h, int32_t* nearestObstacle, int32_t* nearestEdge)
 {

@@ -168,6 +168,15 @@ class World:
         lib().ref_world_gvd_update(self.h, _p(pc), _p(vd))
         return pc, vd
 
+    def set_gvd_distances(self, sqdist, voro_sqdist):
+        """overwrite the GVD's two distance grids (the potential is recomputed from them at every GVD::Update);
+        returns how many (obstacle, Voronoi) cells differed from the reference's own"""
+        a = np.ascontiguousarray(sqdist, np.int32)
+        b = np.ascontiguousarray(voro_sqdist, np.int32)
+        diff = (C.c_long * 2)()
+        lib().ref_world_set_gvd_distances(self.h, _p(a), _p(b), diff)
+        return int(diff[0]), int(diff[1])
+
     def gvd_cells(self):
         """(rows, cols, 2) nearest-obstacle and nearest-Voronoi-edge cells of the world's GVD (after gvd_update)"""
         i = self.info()

@@ -13,6 +13,10 @@ import pathplanning_b200 as pp  # noqa: E402
 from pathplanning_b200 import synth  # noqa: E402
 
 
+ENGINES = [int(e) for e in os.environ.get("PPX_ENGINES", "0,1").split(",")]
+REPS = int(os.environ.get("PPX_REPS", "2"))
+
+
 def main():
     ctx = pp.Context(0)
     cfg = synth.C2
@@ -34,9 +38,9 @@ def main():
     ref = None
     for n in sizes:
         outs = {}
-        for engine in (0, 1):
+        for engine in ENGINES:
             ctx.set_option("search_engine", engine)
-            for rep in range(2):
+            for rep in range(REPS):
                 t0 = time.perf_counter()
                 out = planner.search(S[:n], G[:n], seeds[:n], max_path=128)
                 dt = time.perf_counter() - t0
@@ -46,12 +50,15 @@ def main():
             print(f"engine {engine} n={n}: host {dt * 1e3:.1f} ms, wavefront {wf:.2f} ms, search {se:.2f} ms -> "
                   f"{n / ((wf + se) * 1e-3):.0f} plans/s; solved {int((r['status'] == 0).sum())}, expansions {int(r['n_expanded'].sum())}, "
                   f"max {int(r['n_expanded'].max())}", flush=True)
-        same = outs[0]["results"].tobytes() == outs[1]["results"].tobytes() and outs[0]["paths"].tobytes() == outs[1]["paths"].tobytes()
-        print(f"  engines identical: {same}", flush=True)
+        if len(ENGINES) == 2:
+            same = outs[0]["results"].tobytes() == outs[1]["results"].tobytes() and outs[0]["paths"].tobytes() == outs[1]["paths"].tobytes()
+            print(f"  engines identical: {same}", flush=True)
+    if os.environ.get("PPX_NO_LONGEST"):
+        return
     # the longest single query alone (critical path)
-    r = outs[1]["results"]
+    r = outs[ENGINES[-1]]["results"]
     worst = int(np.argmax(r["n_expanded"]))
-    for engine in (0, 1):
+    for engine in ENGINES:
         ctx.set_option("search_engine", engine)
         for rep in range(2):
             planner.search(S[worst:worst + 1], G[worst:worst + 1], seeds[worst:worst + 1])
