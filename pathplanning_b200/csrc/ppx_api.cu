@@ -220,6 +220,12 @@ int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value)
 		ctx->rs_overlap = value != 0;
 		return PPX_OK;
 	}
+	if (!strcmp(name, "rs_engine")) {
+		if (value != 0 && value != 1)
+			return ppx_fail(ctx, PPX_ERR_INVALID, "rs_engine must be 0 (k_check_rs) or 1 (k_check_rs2)");
+		ctx->rs_engine = (int)value;
+		return PPX_OK;
+	}
 	if (!strcmp(name, "search_engine")) {
 		if (value != 0 && value != 1)
 			return ppx_fail(ctx, PPX_ERR_INVALID, "search_engine must be 0 (warp per query) or 1 (CTA per query)");

@@ -15,6 +15,7 @@ struct ppx_ctx {
 	int num_sms = 0;
 	std::string error;
 	int64_t launches = 0;
+	int rs_engine = 1; // batched Reeds-Shepp edge check: 1 = k_check_rs2 (knot records, bulk-copy staging), 0 = k_check_rs
 	int rs_filter = 1; // 0: k_check_rs evaluates every sample with the exact FP64 path (A/B tests)
 	int rs_overlap = 0; // 1: consecutive ppx_check_edges_rs_dev launches overlap (programmatic dependent launch)
 	int rs_slot = 0; // cursor slot of the next overlapped launch

@@ -848,6 +848,89 @@ PPX_HD void rs_solve(const Pose& start, const Pose& goal, double r, float rev, f
 
 
 #ifdef __CUDACC__
+// Solver::GetOptimalPath / GetShortestPath for EIGHT pairs per warp: the four lanes of a quad take the four mirrored goals
+// of one pair (goal, timeflip, reflect, both: reeds_shepp.cpp:518-535), every lane walks the 12 base formulas in enum
+// order -- the same formula on all 32 lanes at the same time, so the warp does not diverge on the formula switch -- and the
+// quad takes the lexicographic minimum of (float cost, word), which is the reference's "first strict minimum in enum
+// order" (word = base * 4 + mirror).  All four lanes of a quad return the pair's solution.  Must be called converged.
+__device__ __forceinline__ void rs_solve_quad(const Pose& start, const Pose& goal, double r, float rev, float fwd, float sw,
+	int shortest, int& outWord, double& ot, double& ou, double& ov)
+{
+	const int q = (int)(threadIdx.x & 3);
+	double dx = goal.x - start.x, dy = goal.y - start.y;
+	double sN, cN;
+	PPX_SINCOS(-start.th, &sN, &cN);
+	double gx = cN * dx + (-sN) * dy;
+	double gy = sN * dx + cN * dy;
+	double gth = wrap_theta(wrap_theta(goal.th - start.th));
+	gx = gx / r;
+	gy = gy / r;
+	double sG, cG;
+	PPX_SINCOS(gth, &sG, &cG);
+	const double x = (q & 1) ? -gx : gx;
+	const double y = (q & 2) ? -gy : gy;
+	const bool flipTh = (q == 1 || q == 2);
+	const double th = wrap_theta(flipTh ? -gth : gth);
+	const double sq = flipTh ? -sG : sG;
+	RSGoalTerms a, b;
+	a.gth = b.gth = th;
+	a.xi = x - sq;
+	a.eta = y - 1 + cG;
+	b.xi = x + sq;
+	b.eta = y - 1 - cG;
+	a.u1sq = a.xi * a.xi + a.eta * a.eta;
+	b.u1sq = b.xi * b.xi + b.eta * b.eta;
+	a.u1 = sqrt(a.u1sq);
+	b.u1 = sqrt(b.u1sq);
+	a.phi = PPX_ATAN2(a.eta, a.xi);
+	b.phi = PPX_ATAN2(b.eta, b.xi);
+	const float INF = __int_as_float(0x7f800000);
+	float bestCost = INF; // GetOptimalPath: float cost; GetShortestPath: the double length (kept in bestLen)
+	double bestLen = PPX_INF;
+	int bestWord = 64;
+	double bt = 0, bu = 0, bv = 0;
+	#pragma unroll 1
+	for (int base = 0; base < 12; base++) {
+		double t = 0, u = 0, v = 0;
+		const double length = rs_motion_lengths(base, a, b, t, u, v);
+		const int word = base * 4 + q;
+		if (shortest) {
+			if (length < bestLen) { // words of one lane come in increasing order: strict < keeps the first
+				bestLen = length;
+				bestWord = word;
+				bt = t; bu = u; bv = v;
+			}
+		} else if (length != PPX_INF) {
+			RSSeg seg;
+			const double mLength = rs_build_segment(word, t, u, v, seg);
+			const float cost = rs_compute_cost(seg, mLength, r, rev, fwd, sw);
+			if (cost < bestCost) {
+				bestCost = cost;
+				bestWord = word;
+				bt = t; bu = u; bv = v;
+			}
+		}
+	}
+	#pragma unroll
+	for (int off = 1; off <= 2; off <<= 1) {
+		const float oc = __shfl_xor_sync(0xffffffffu, bestCost, off);
+		const double ol = __shfl_xor_sync(0xffffffffu, bestLen, off);
+		const int ow = __shfl_xor_sync(0xffffffffu, bestWord, off);
+		const double t2 = __shfl_xor_sync(0xffffffffu, bt, off);
+		const double u2 = __shfl_xor_sync(0xffffffffu, bu, off);
+		const double v2 = __shfl_xor_sync(0xffffffffu, bv, off);
+		const bool take = shortest ? (ol < bestLen || (ol == bestLen && ow < bestWord)) : (oc < bestCost || (oc == bestCost && ow < bestWord));
+		if (take) {
+			bestCost = oc;
+			bestLen = ol;
+			bestWord = ow;
+			bt = t2; bu = u2; bv = v2;
+		}
+	}
+	outWord = bestWord < 48 ? bestWord : -1;
+	ot = bt; ou = bu; ov = bv;
+}
+
 // Solver::GetOptimalPath evaluated by a whole warp: the 48 words are independent, lane L takes word
 // L and (lanes 0..15) word 32 + L.  The reference's scan in enum order with a strict `<` keeps the
 // first word of minimal float cost, i.e. the minimum of (cost, word) in lexicographic order over

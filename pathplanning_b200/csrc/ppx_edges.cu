@@ -1,12 +1,12 @@
 // libppx.so: batched StateValidatorOccupancyMap::IsStateValid / IsPathValid (A7) over
 // Reeds-Shepp, constant-steer and straight edges, and the batched Reeds-Shepp solver (A3).
 //
-// Mapping: one edge per thread, persistent grid sized to the SM count.  The reference's
-// adaptive sphere-tracing makes sample k+1 depend on the clearance read at sample k, so the
-// samples of one edge are inherently sequential (3-5 dependent L2 round trips per edge); the
-// parallelism is across edges, and the latency is hidden by resident warps.  Edge records are
-// staged through shared memory with one bulk (TMA) copy per CTA tile so that the 72-byte AoS
-// records are read from HBM fully coalesced.
+// Mapping.  k_check_rs2 (ppx_check_rs2.cuh, the default) / k_check_rs: every lane of a warp runs the sphere-tracing loop of
+// one edge at a time in FP32 with certified cells (ppx_fastlane.cuh) and picks up a new edge when it finishes, so a warp
+// stays on one instruction stream although edges need 1 to ~200 dependent samples; uncertified samples are evaluated by
+// the exact FP64 restatement of the reference.  k_check_rs2 stages the 72-byte records of 32 edges per warp with one
+// bulk async copy (cp.async.bulk + mbarrier) and turns them into FP32 knot records with all lanes active.
+// k_check_csteer / k_check_line / k_rs_solve / k_rs_interpolate: one item per thread, persistent grid.
 #include <algorithm>
 #include <cstring>
 #include "ppx_ctx.h"
@@ -55,7 +55,7 @@ struct SmemLen {
 // lanes of the warp are parked (or nothing else is runnable) the warp evaluates those samples with
 // the exact FP64 restatement of the reference (rs_exact_sample) in one divergent pass.
 constexpr int kGrab = 128;
-constexpr int kCheckCtasPerSm = 6; // 80 registers, no spills; 24 warps/SM measured best (r1g sweep)
+constexpr int kCheckCtasPerSm = 6; // 80 registers (k_check_rs<0,6>: 32 B of spill stores, ppx_edges.ptxas.log); 24 warps/SM measured best (r1g sweep)
 constexpr int kParkBatch = 8;
 constexpr int kRefillBatch = 8;
 
@@ -224,6 +224,8 @@ __global__ void __launch_bounds__(kThreads, kCtas) k_check_rs(MapDev map, FastMa
 		asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
+#include "ppx_check_rs2.cuh"
+
 __global__ void __launch_bounds__(kThreads) k_check_csteer(MapDev map, int64_t n, const ppx_csteer_edge* __restrict__ edges,
 	float minSafeRadius, float minStep, uint8_t* __restrict__ valid, float* __restrict__ last, double* __restrict__ finalPose)
 {
@@ -327,6 +329,52 @@ __global__ void __launch_bounds__(kThreads) k_rs_interpolate(int64_t n, const pp
 	}
 }
 
+// Batched Solver::GetOptimalPath / GetShortestPath, eight pairs per warp (rs_solve_quad): quad k of a warp solves pair
+// 8 * w + k, its first lane writes the results.
+__global__ void __launch_bounds__(kThreads) k_rs_solve_quad(int64_t n, const double* __restrict__ starts, const double* __restrict__ goals,
+	ppx_rs_cost_params cp, ppx_rs_edge* __restrict__ edges, int32_t* __restrict__ word, double* __restrict__ length,
+	float* __restrict__ cost)
+{
+	const int64_t quad = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 2;
+	const int64_t nquads = ((int64_t)gridDim.x * blockDim.x) >> 2;
+	const int64_t rounds = (n + nquads - 1) / nquads; // all lanes of a warp take part in the quad shuffles
+	for (int64_t k = 0; k < rounds; k++) {
+		const int64_t i = k * nquads + quad;
+		const bool have = i < n;
+		Pose s = { 0, 0, 0 }, g = { 0, 0, 0 };
+		if (have) {
+			s = { starts[3 * i], starts[3 * i + 1], starts[3 * i + 2] };
+			g = { goals[3 * i], goals[3 * i + 1], goals[3 * i + 2] };
+		}
+		int w;
+		double t, u, v;
+		rs_solve_quad(s, g, cp.min_turning_radius, cp.reverse_cost_multiplier, cp.forward_cost_multiplier, cp.direction_switching_cost,
+			cp.shortest, w, t, u, v);
+		if (!have || (threadIdx.x & 3) != 0)
+			continue;
+		RSSeg seg;
+		double mLength = 0.0;
+		float c = __int_as_float(0x7f800000);
+		if (w >= 0) {
+			mLength = rs_build_segment(w, t, u, v, seg);
+			c = rs_compute_cost(seg, mLength, cp.min_turning_radius, cp.reverse_cost_multiplier, cp.forward_cost_multiplier,
+				cp.direction_switching_cost);
+		} else { // PathSegment(): all motions invalid, m_length 0
+			for (int m = 0; m < 5; m++)
+				seg.len[m] = PPX_INF;
+			seg.code = 0xAAAAA;
+		}
+		if (edges)
+			store_rs_edge(edges + i, s, seg);
+		if (word)
+			word[i] = w;
+		if (length)
+			length[i] = mLength * cp.min_turning_radius;
+		if (cost)
+			cost[i] = c;
+	}
+}
+
 int grid_for(const ppx_ctx* ctx, int64_t n, int threads, int blocksPerSm)
 {
 	int64_t need = (n + threads - 1) / threads;
@@ -387,14 +435,23 @@ static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 		cfg.numAttrs = 1;
 		unsigned long long* q = ctx->d_rsq + queueSlot;
 		unsigned long long* next = ctx->d_rsq + (queueSlot + 1) % ppx_ctx::kMaxChunks;
-		PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_check_rs<false, kCheckCtasPerSm>, ctx->map_dev(), fm, n, d_edges, min_turning_radius,
-			vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, q, (AuditOut*)nullptr, next));
+		if (ctx->rs_engine == 1)
+			PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_check_rs2<false, false>, ctx->map_dev(), fm, n, d_edges, min_turning_radius,
+				vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, q, (AuditOut*)nullptr, next, SolveArgs {}));
+		else
+			PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_check_rs<false, kCheckCtasPerSm>, ctx->map_dev(), fm, n, d_edges, min_turning_radius,
+				vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, q, (AuditOut*)nullptr, next));
 		ctx->launches++;
 		return PPX_OK;
 	}
-	k_check_rs<false, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
-		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples,
-		ctx->d_queue + queueSlot, nullptr, nullptr);
+	if (ctx->rs_engine == 1)
+		k_check_rs2<false, false><<<grid_for(ctx, n, kThreads, kCheck2Ctas), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+			min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples,
+			ctx->d_queue + queueSlot, nullptr, nullptr, SolveArgs {});
+	else
+		k_check_rs<false, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+			min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples,
+			ctx->d_queue + queueSlot, nullptr, nullptr);
 	PPX_LAUNCHED(ctx);
 	return PPX_OK;
 }
@@ -436,9 +493,14 @@ int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, 
 	PPX_CUDA(ctx, cudaMemsetAsync(d_audit, 0, sizeof(AuditOut), ctx->stream));
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
 	FastMap fm = fast_map_derive(ctx->desc);
-	k_check_rs<true, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
-		min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
-		d_audit, nullptr);
+	if (ctx->rs_engine == 1)
+		k_check_rs2<true, false><<<grid_for(ctx, n, kThreads, kCheck2Ctas), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+			min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
+			d_audit, nullptr, SolveArgs {});
+	else
+		k_check_rs<true, kCheckCtasPerSm><<<grid_for(ctx, n, kThreads, kCheckCtasPerSm), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
+			min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
+			d_audit, nullptr);
 	PPX_LAUNCHED(ctx);
 	AuditOut h {};
 	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
@@ -476,7 +538,7 @@ int ppx_check_edges_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double
 	PPX_CHECK(ppx_pipeline_init(ctx));
 	const int64_t minChunk = 250000; // a launch has a fixed tail of ~0.1 ms (its longest sample chains): few, large chunks
 	int nchunks = (int)std::min<int64_t>(ppx_ctx::kMaxChunks, std::max<int64_t>(1, n / minChunk));
-	int64_t chunk = (n + nchunks - 1) / nchunks;
+	int64_t chunk = ((n + nchunks - 1) / nchunks + 1) & ~(int64_t)1; // even: every chunk starts on a 16-byte boundary (bulk copy)
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, ppx_ctx::kMaxChunks * sizeof(unsigned long long), ctx->stream));
 	PPX_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
 	PPX_CUDA(ctx, cudaStreamWaitEvent(ctx->s_h2d, ctx->ev_start, 0));
@@ -564,9 +626,14 @@ int ppx_rs_solve_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, const doub
 	PPX_REQUIRE(ctx, n >= 0 && cp && (n == 0 || (d_starts && d_goals)), "bad arguments");
 	if (n == 0)
 		return PPX_OK;
-	MapDev none {};
-	k_rs_solve<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(none, n, d_starts, d_goals, *cp, 0, 0.0f, 0.0f,
-		d_edges, d_word, d_length, d_cost, nullptr, nullptr);
+	if (ctx->rs_engine == 1) {
+		k_rs_solve_quad<<<grid_for(ctx, 4 * n, kThreads, 8), kThreads, 0, ctx->stream>>>(n, d_starts, d_goals, *cp, d_edges, d_word, d_length,
+			d_cost);
+	} else {
+		MapDev none {};
+		k_rs_solve<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(none, n, d_starts, d_goals, *cp, 0, 0.0f, 0.0f,
+			d_edges, d_word, d_length, d_cost, nullptr, nullptr);
+	}
 	PPX_LAUNCHED(ctx);
 	return PPX_OK;
 }
@@ -580,8 +647,24 @@ int ppx_connect_check_rs_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, co
 	PPX_REQUIRE(ctx, n >= 0 && cp && vp && (n == 0 || (d_starts && d_goals && d_valid && d_last)), "bad arguments");
 	if (n == 0)
 		return PPX_OK;
-	k_rs_solve<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_starts, d_goals, *cp, 1,
-		vp->min_safe_radius, vp->min_path_interpolation_distance, nullptr, d_word, d_length, d_cost, d_valid, d_last);
+	if (ctx->rs_engine == 1) {
+		// Connect + IsPathValid in one kernel: quad solver feeding the lane machine (ppx_check_rs2.cuh); the solved segments
+		// pass through a scratch array the exact path re-reads
+		ppx_rs_edge* d_solved;
+		PPX_CHECK(ppx_scratch(ctx, 7, (size_t)n * sizeof(ppx_rs_edge), (void**)&d_solved));
+		FastMap fm = fast_map_derive(ctx->desc);
+		if (!ctx->rs_filter)
+			fm.enabled = 0;
+		SolveArgs sa { d_starts, d_goals, d_solved, d_word, d_length, d_cost, cp->reverse_cost_multiplier, cp->forward_cost_multiplier,
+			cp->direction_switching_cost, cp->shortest };
+		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
+		k_check_rs2<false, true><<<grid_for(ctx, n, kThreads, 3), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, nullptr,
+			cp->min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, nullptr, ctx->d_queue,
+			nullptr, nullptr, sa);
+	} else {
+		k_rs_solve<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_starts, d_goals, *cp, 1,
+			vp->min_safe_radius, vp->min_path_interpolation_distance, nullptr, d_word, d_length, d_cost, d_valid, d_last);
+	}
 	PPX_LAUNCHED(ctx);
 	return PPX_OK;
 }

@@ -330,3 +330,46 @@ def test_two_contexts_one_process(ctx, c2):
         other.close()
         if ndev > 1:
             torch.cuda.set_device(0)
+
+
+def test_rs_engines_identical(ctx, c3_edges):
+    """k_check_rs2 (knot records in shared memory, bulk-copy staging, a sample per iteration; the default) against
+    k_check_rs (round-1 micro-step machine): verdicts, `last` bits and sample counts identical -- for a batch that is
+    not a multiple of the 32-edge grab, for a tiny batch, and for a device pointer that is NOT 16-byte aligned (the
+    bulk copy needs an aligned source; the kernel then loads the records directly)."""
+    import ctypes as C
+    from pathplanning_b200.lib import ppx
+    edges, rr = c3_edges
+    vp = pp.ValidatorParams(1.0, 0.1)
+    for n in (200000, 60001, 33, 5):
+        e = np.ascontiguousarray(edges[:n])
+        outs = []
+        for engine in (0, 1):
+            ctx.set_option("rs_engine", engine)
+            try:
+                outs.append(ctx.check_edges_rs(e, 2.0, vp, want_samples=True))
+            finally:
+                ctx.set_option("rs_engine", 1)
+        a, b = outs
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[2], b[2]), n
+        assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32)), n
+        assert np.array_equal(b[0], rr["valid"][:n])
+    # misaligned device pointer: records start 72 bytes into the allocation
+    n = 4097
+    e = np.ascontiguousarray(edges[:n + 1])
+    d = C.c_void_p()
+    ctx._check(ppx.ppx_dev_alloc(ctx.handle, e.nbytes, C.byref(d)))
+    d_valid, d_last = C.c_void_p(), C.c_void_p()
+    ctx._check(ppx.ppx_dev_alloc(ctx.handle, n, C.byref(d_valid)))
+    ctx._check(ppx.ppx_dev_alloc(ctx.handle, 4 * n, C.byref(d_last)))
+    ctx._check(ppx.ppx_memcpy_h2d(ctx.handle, d, e.ctypes.data_as(C.c_void_p), e.nbytes))
+    vpc = vp.to_c()
+    ctx._check(ppx.ppx_check_edges_rs_dev(ctx.handle, n, C.c_void_p(d.value + 72), 2.0, C.byref(vpc), d_valid, d_last, None))
+    v = np.zeros(n, np.uint8)
+    l = np.zeros(n, np.float32)
+    ctx._check(ppx.ppx_memcpy_d2h(ctx.handle, v.ctypes.data_as(C.c_void_p), d_valid, n))
+    ctx._check(ppx.ppx_memcpy_d2h(ctx.handle, l.ctypes.data_as(C.c_void_p), d_last, 4 * n))
+    assert np.array_equal(v.astype(bool), rr["valid"][1:n + 1])
+    assert_close_rel(l, rr["last"][1:n + 1], REL, "last")
+    for p in (d, d_valid, d_last):
+        ppx.ppx_dev_free(ctx.handle, p)
