@@ -221,8 +221,8 @@ int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value)
 		return PPX_OK;
 	}
 	if (!strcmp(name, "rs_engine")) {
-		if (value != 0 && value != 1)
-			return ppx_fail(ctx, PPX_ERR_INVALID, "rs_engine must be 0 (k_check_rs) or 1 (k_check_rs2)");
+		if (value < 0 || value > 2)
+			return ppx_fail(ctx, PPX_ERR_INVALID, "rs_engine must be 0 (k_check_rs), 1 (k_check_rs2) or 2 (1 + quad solver for ppx_rs_solve)");
 		ctx->rs_engine = (int)value;
 		return PPX_OK;
 	}

@@ -435,7 +435,7 @@ static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 		cfg.numAttrs = 1;
 		unsigned long long* q = ctx->d_rsq + queueSlot;
 		unsigned long long* next = ctx->d_rsq + (queueSlot + 1) % ppx_ctx::kMaxChunks;
-		if (ctx->rs_engine == 1)
+		if (ctx->rs_engine >= 1)
 			PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_check_rs2<false, false>, ctx->map_dev(), fm, n, d_edges, min_turning_radius,
 				vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, q, (AuditOut*)nullptr, next, SolveArgs {}));
 		else
@@ -444,7 +444,7 @@ static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 		ctx->launches++;
 		return PPX_OK;
 	}
-	if (ctx->rs_engine == 1)
+	if (ctx->rs_engine >= 1)
 		k_check_rs2<false, false><<<grid_for(ctx, n, kThreads, kCheck2Ctas), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
 			min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples,
 			ctx->d_queue + queueSlot, nullptr, nullptr, SolveArgs {});
@@ -493,7 +493,7 @@ int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, 
 	PPX_CUDA(ctx, cudaMemsetAsync(d_audit, 0, sizeof(AuditOut), ctx->stream));
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
 	FastMap fm = fast_map_derive(ctx->desc);
-	if (ctx->rs_engine == 1)
+	if (ctx->rs_engine >= 1)
 		k_check_rs2<true, false><<<grid_for(ctx, n, kThreads, kCheck2Ctas), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, d_edges,
 			min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, ctx->d_queue,
 			d_audit, nullptr, SolveArgs {});
@@ -626,7 +626,10 @@ int ppx_rs_solve_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, const doub
 	PPX_REQUIRE(ctx, n >= 0 && cp && (n == 0 || (d_starts && d_goals)), "bad arguments");
 	if (n == 0)
 		return PPX_OK;
-	if (ctx->rs_engine == 1) {
+	if (ctx->rs_engine == 2) {
+		// quad form (8 pairs per warp, no formula divergence): 1.96 ms per 1M pairs on B200 against 1.62 ms for one pair per
+		// thread -- the per-thread loop over the 48 words does not diverge either and needs no cross-lane reduction; kept for
+		// A/B (tools/time_check.py), the fused Connect + IsPathValid kernel uses the quad solver because it runs at 168 registers
 		k_rs_solve_quad<<<grid_for(ctx, 4 * n, kThreads, 8), kThreads, 0, ctx->stream>>>(n, d_starts, d_goals, *cp, d_edges, d_word, d_length,
 			d_cost);
 	} else {
@@ -647,7 +650,7 @@ int ppx_connect_check_rs_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, co
 	PPX_REQUIRE(ctx, n >= 0 && cp && vp && (n == 0 || (d_starts && d_goals && d_valid && d_last)), "bad arguments");
 	if (n == 0)
 		return PPX_OK;
-	if (ctx->rs_engine == 1) {
+	if (ctx->rs_engine >= 1) {
 		// Connect + IsPathValid in one kernel: quad solver feeding the lane machine (ppx_check_rs2.cuh); the solved segments
 		// pass through a scratch array the exact path re-reads
 		ppx_rs_edge* d_solved;

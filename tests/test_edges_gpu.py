@@ -158,6 +158,7 @@ def c3_edges(ctx, ref):
     ctx.upload_map(w.map_desc(), sq, occ, None)
     s, g = synth.random_rs_queries(200000, seed=4242)
     rr = w.check_rs_edges(s, g, 2.0)
+    rr["map"] = (w.map_desc(), sq, occ)  # tests that run after another map was uploaded to the shared context restore it
     w.close()
     return pp.make_rs_edges(s, rr["steer"], rr["dir"], rr["len"]), rr
 
@@ -340,6 +341,7 @@ def test_rs_engines_identical(ctx, c3_edges):
     import ctypes as C
     from pathplanning_b200.lib import ppx
     edges, rr = c3_edges
+    ctx.upload_map(*rr["map"], None)
     vp = pp.ValidatorParams(1.0, 0.1)
     for n in (200000, 60001, 33, 5):
         e = np.ascontiguousarray(edges[:n])
