@@ -526,6 +526,36 @@ typedef struct ppx_astar_result {
 int ppx_astar_n2(ppx_ctx* ctx, int64_t nq, const int32_t* starts, const int32_t* goals, int32_t max_nodes, int32_t max_path,
 	ppx_astar_result* results, int32_t* paths);
 
+/* ---------------------------------------------------------------------------------------------
+ * Multi-GPU.  The path shards by independent units -- edge batches, start/goal queries -- with the world model
+ * replicated; one context per GPU, one process (or thread) per context.  The reference has no counterpart (it is
+ * single-threaded, no communication backend); these are the two collectives a sharded caller needs, over NCCL / NVLink:
+ *   ppx_comm_broadcast_map     the grids of the root's context (what ppx_map_upload / ppx_gvd_build installed: description,
+ *                              sqdist, occupancy, pathcost) into every rank's context, once per map update;
+ *   ppx_comm_gather_results    fixed-size records of every rank (e.g. ppx_hybrid_result of its shard), uneven shards
+ *                              allowed, concatenated in rank order on every rank;
+ *   ppx_comm_gather_paths      variable-length pose arrays (ppx_hybrid_resample's count / poses) by counts -> offsets:
+ *                              every rank receives offsets[total_queries + 1] and the packed poses of all queries, rank
+ *                              order, query order within a rank.
+ * All device pointers; collectives are enqueued on the context's stream, the calls return after the host-side
+ * bookkeeping they need (counts) -- ppx_ctx_synchronize before reading the outputs.  NCCL is loaded at run time
+ * (libnccl.so.2); PPX_ERR_STATE when it is not there.
+ * Bootstrap: rank 0 calls ppx_comm_unique_id and hands the 128 bytes to the other ranks by any means (MPI, a file,
+ * torch.distributed's store); every rank then calls ppx_comm_init. */
+#define PPX_COMM_ID_BYTES 128
+int ppx_comm_unique_id(void* id_out /* PPX_COMM_ID_BYTES */);
+int ppx_comm_init(ppx_ctx* ctx, const void* id, int32_t rank, int32_t world);
+int ppx_comm_destroy(ppx_ctx* ctx);
+int ppx_comm_broadcast_map(ppx_ctx* ctx, int32_t root);
+/* d_all: room for `capacity` records; counts (host, world entries, may be NULL): records per rank */
+int ppx_comm_gather_results(ppx_ctx* ctx, const void* d_local, int64_t n_local, int32_t record_bytes, void* d_all, int64_t capacity,
+	int64_t* counts);
+/* d_count[n_local], d_poses[n_local][max_points][3] as ppx_hybrid_resample lays them out (on the device);
+ * query_counts (host, world entries, may be NULL); d_offsets_all: total_queries + 1 int64; d_poses_all: total poses x 3 */
+int ppx_comm_gather_paths(ppx_ctx* ctx, int64_t n_local, const int32_t* d_count, const double* d_poses, int32_t max_points,
+	int64_t* query_counts, int64_t* d_offsets_all, int64_t offsets_capacity, double* d_poses_all, int64_t poses_capacity,
+	int64_t* total_poses);
+
 #ifdef __cplusplus
 }
 #endif

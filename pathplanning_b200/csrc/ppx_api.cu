@@ -156,6 +156,8 @@ int ppx_ctx_destroy(ppx_ctx* ctx)
 		return PPX_ERR_INVALID;
 	PPX_GUARD(ctx);
 	cudaStreamSynchronize(ctx->stream);
+	if (ctx->comm)
+		ppx_comm_destroy(ctx);
 	cudaFree(ctx->d_sqdist);
 	cudaFree(ctx->d_occupancy);
 	cudaFree(ctx->d_pathcost);

@@ -22,6 +22,10 @@ struct ppx_ctx {
 	int search_engine = 1; // Hybrid A* graph search: 1 = one CTA per query (master + worker warps), 0 = one warp per query
 	unsigned long long* d_rsq = nullptr; // kMaxChunks cursors of the overlapped launches (each launch zeroes its successor's)
 
+	// multi-GPU (ppx_comm.cu): ncclComm_t of this rank, NULL without ppx_comm_init
+	void* comm = nullptr;
+	int comm_rank = 0, comm_world = 1;
+
 	// world model
 	bool has_map = false;
 	ppx_map_desc desc {};

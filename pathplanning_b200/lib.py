@@ -107,6 +107,12 @@ _SIGS = {
     "ppx_astar_n2": (C.c_int, [_p, _i64, _p, _p, C.c_int32, C.c_int32, _p, _p]),
     "ppx_hybrid_search_dev": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
     "ppx_hybrid_timing": (C.c_int, [_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "ppx_comm_unique_id": (C.c_int, [_p]),
+    "ppx_comm_init": (C.c_int, [_p, _p, C.c_int32, C.c_int32]),
+    "ppx_comm_destroy": (C.c_int, [_p]),
+    "ppx_comm_broadcast_map": (C.c_int, [_p, C.c_int32]),
+    "ppx_comm_gather_results": (C.c_int, [_p, _p, _i64, C.c_int32, _p, _i64, _p]),
+    "ppx_comm_gather_paths": (C.c_int, [_p, _i64, _p, _p, C.c_int32, _p, _p, _i64, _p, _i64, _p]),
 }
 
 for _name, (_res, _args) in _SIGS.items():
