@@ -170,6 +170,23 @@ typedef struct ppx_rs_edge {
 
 #define PPX_RS_CODE(steer, dir, i) ((uint64_t)(((steer) & 3) | (((dir) & 3) << 2)) << (4 * (i)))
 
+/* Rectangular car footprint (BASELINE config 3 "rectangular car footprint").  NOT a reference behaviour: the reference
+ * checks one disc of radius minSafeRadius at the pose (two `// TODO add offset`, state_validator_occupancy_map.cpp:23,60).
+ * Defined here: the length x width rectangle, its centre rear_to_center ahead of the pose along the heading, is covered by
+ * n_discs discs of one radius rho = sqrt((length / n_discs)^2 + width^2) / 2 centred on the slices' centres; a pose is
+ * valid iff every disc centre passes IsStateValid with minSafeRadius = rho.  Along a path: the reference's sphere tracing
+ * (state_validator_occupancy_map.cpp:42-66) with step = max(min(slack, border) / gamma, min_step), slack = the smallest
+ * (clearance - rho) over the discs, border = the smallest distance of a disc centre to the bounds,
+ * gamma = sqrt(1 + (o_max / min_turning_radius)^2), o_max the largest disc offset (a disc centre travels up to gamma times
+ * as far as the pose).  Its checker is a restatement over the reference's own Interpolate and distance map
+ * (oracle/ref_harness.cpp, kind "port", parity unpinned by definition); results are reported apart from the disc check. */
+typedef struct ppx_footprint_params {
+	double length, width; /* e.g. 4.5 x 2.0 m */
+	double rear_to_center; /* offset of the rectangle's centre from the pose along the heading (m) */
+	int32_t n_discs; /* 1..16 */
+	float min_step; /* minPathInterpolationDistance */
+} ppx_footprint_params;
+
 /* A constant-steer primitive = PathConstantSteer (paths/path_constant_steer.cpp:5-25) over
  * KinematicBicycleModel::ConstantSteer (models/kinematic_bicycle_model.cpp:5-32).  The three
  * model constants are evaluated on the host by the KinematicBicycleModel mirror so that they
@@ -214,6 +231,12 @@ int ppx_check_edges_rs_audit(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, 
 	const ppx_validator_params* vp, uint8_t* valid, float* last, uint32_t* samples, uint64_t* counters,
 	float* max_dev_cells);
 
+/* The rectangular-footprint variant of ppx_is_state_valid / ppx_check_edges_rs[_dev] (see ppx_footprint_params). */
+int ppx_is_state_valid_rect(ppx_ctx* ctx, int64_t n, const double* poses, const ppx_footprint_params* fp, uint8_t* valid);
+int ppx_check_edges_rs_rect(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
+	const ppx_footprint_params* fp, uint8_t* valid, float* last, uint32_t* samples);
+int ppx_check_edges_rs_rect_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, double min_turning_radius,
+	const ppx_footprint_params* fp, uint8_t* d_valid, float* d_last, uint32_t* d_samples);
 int ppx_check_edges_csteer(ppx_ctx* ctx, int64_t n, const ppx_csteer_edge* edges, const ppx_validator_params* vp,
 	uint8_t* valid, float* last, double* final_pose /* 3n, after Truncate(last) when invalid; may be NULL */);
 int ppx_check_edges_line(ppx_ctx* ctx, int64_t n, const ppx_line_edge* edges, const ppx_validator_params* vp,

@@ -448,6 +448,90 @@ double ref_check_rs_segments(void* h, long n, const double* starts, const int* s
 	return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
+// Rectangular footprint variant (BASELINE config 3; NOT a reference behaviour -- "port", parity unpinned by definition): the
+// definition of include/ppx.h (ppx_footprint_params) restated over the reference's own pieces -- PathReedsShepp::Interpolate for
+// the poses, StateValidatorOccupancyMap::IsStateValid with minSafeRadius = rho for every covering disc, the map's distance grid.
+// fp = { length, width, rear_to_center, n_discs, min_step }.
+double ref_check_rs_segments_rect(void* h, long n, const double* starts, const int* steer, const int* dir, const double* len,
+	double rmin, const double* fp, uint8_t* valid, float* last, int* samples)
+{
+	auto* w = (RefWorld*)h;
+	const int nd = (int)fp[3];
+	const double seg = fp[0] / nd, first = fp[2] - fp[0] / 2.0 + seg / 2.0;
+	const float rho = (float)std::sqrt(seg * seg / 4.0 + fp[1] * fp[1] / 4.0);
+	double omax = 0.0;
+	for (int i = 0; i < nd; i++)
+		omax = std::fmax(omax, std::fabs(first + i * seg));
+	const float gamma = (float)std::sqrt(1.0 + (omax / rmin) * (omax / rmin));
+	const float minStep = (float)fp[4];
+	const auto& bounds = w->space->bounds;
+	const float savedRadius = w->validator->minSafeRadius;
+	w->validator->minSafeRadius = rho;
+	auto poseState = [&](const Pose2d& p, float& slack, float& border) {
+		const double s = std::sin(p.theta), c = std::cos(p.theta);
+		bool ok = true;
+		slack = border = std::numeric_limits<float>::infinity();
+		for (int i = 0; i < nd; i++) {
+			const double o = first + i * seg;
+			Pose2d d;
+			d.position = Point2d(p.x() + o * c, p.y() + o * s);
+			d.theta = p.theta;
+			float dist = 0.0f;
+			if (!w->validator->IsStateValid(d))
+				ok = false;
+			auto cell = w->map->WorldPositionToGridCell(d.position);
+			if (w->map->IsInsideMap(cell)) {
+				bool inb = !(d.x() - w->map->GetPosition().x() < bounds[0].x() || d.x() - w->map->GetPosition().x() > bounds[1].x()
+					|| d.y() - w->map->GetPosition().y() < bounds[0].y() || d.y() - w->map->GetPosition().y() > bounds[1].y());
+				double th = d.theta;
+				while (th > M_PI) th -= 2 * M_PI;
+				while (th < -M_PI) th += 2 * M_PI;
+				inb = inb && !(th < bounds[0].theta || th > bounds[1].theta);
+				if (inb)
+					dist = w->map->GetObstacleDistanceMap()->GetDistanceToNearestObstacle(cell);
+			}
+			slack = std::min(slack, dist - rho);
+			double b = std::min({ d.x() - bounds[0].x(), bounds[1].x() - d.x(), d.y() - bounds[0].y(), bounds[1].y() - d.y() });
+			border = std::min(border, (float)b);
+		}
+		return ok;
+	};
+	auto t0 = std::chrono::steady_clock::now();
+	for (long i = 0; i < n; i++) {
+		Pose2d s;
+		s.position = Point2d(starts[3 * i], starts[3 * i + 1]);
+		s.theta = starts[3 * i + 2];
+		PathReedsShepp path(s, MakeSegment(steer + 5 * i, dir + 5 * i, len + 5 * i), rmin);
+		const double pathLength = path.GetLength();
+		float slack, border, l = 1.0f;
+		int ns = 0;
+		bool ok = true;
+		if (pathLength == 0.0) {
+			ns = 1;
+			ok = poseState(path.GetInitialState(), slack, border);
+		} else {
+			double lastValidLength = 0.0, length = 0.0;
+			while (length < pathLength) {
+				Pose2d state = path.Interpolate(length / pathLength);
+				ns++;
+				if (!poseState(state, slack, border)) {
+					l = lastValidLength / pathLength;
+					ok = false;
+					break;
+				}
+				lastValidLength = length;
+				float delta = std::min(slack, border) / gamma;
+				length += std::max(delta, minStep);
+			}
+		}
+		valid[i] = ok;
+		last[i] = l;
+		if (samples) samples[i] = ns;
+	}
+	w->validator->minSafeRadius = savedRadius;
+	return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
 // Constant-steer primitives (A2): validity, last ratio, final pose (after truncation when invalid,
 // exactly as GetConstantSteerChild does, hybrid_a_star.cpp:117-123).
 void ref_check_csteer(void* h, long n, const double* starts, const double* steering, const double* length,

@@ -261,6 +261,28 @@ class Context:
         self._check(ppx.ppx_is_state_valid(self._h, len(poses), _ptr(poses), C.byref(v), _ptr(out)))
         return out.astype(bool)
 
+    def is_state_valid_rect(self, poses, footprint):
+        """rectangular-footprint variant (ppx_footprint_params: length, width, rear_to_center, n_discs, min_step)"""
+        from .lib import FootprintParamsC
+        poses = _f64(poses)
+        out = np.empty(len(poses), dtype=np.uint8)
+        fp = FootprintParamsC(*footprint)
+        self._check(ppx.ppx_is_state_valid_rect(self._h, len(poses), _ptr(poses), C.byref(fp), _ptr(out)))
+        return out.astype(bool)
+
+    def check_edges_rs_rect(self, edges, min_turning_radius, footprint):
+        """-> (valid, last, samples) for the rectangular-footprint variant; not a reference behaviour (see ppx.h)"""
+        from .lib import FootprintParamsC
+        edges = np.ascontiguousarray(edges, dtype=RS_EDGE)
+        n = len(edges)
+        valid = np.empty(n, dtype=np.uint8)
+        last = np.empty(n, dtype=np.float32)
+        samples = np.empty(n, dtype=np.uint32)
+        fp = FootprintParamsC(*footprint)
+        self._check(ppx.ppx_check_edges_rs_rect(self._h, n, _ptr(edges), float(min_turning_radius), C.byref(fp), _ptr(valid), _ptr(last),
+                                                _ptr(samples)))
+        return valid.astype(bool), last, samples
+
     def check_edges_rs(self, edges, min_turning_radius, vp: ValidatorParams, want_samples=False):
         edges = np.ascontiguousarray(edges, dtype=RS_EDGE)
         n = len(edges)

@@ -267,6 +267,79 @@ PPX_HD bool rs_is_path_valid(const MapDev& map, const Pose& start, const RSSeg& 
 }
 
 // ---------------------------------------------------------------------------------------------
+// Rectangular car footprint (BASELINE config 3).  The reference checks ONE disc (two `// TODO add offset`,
+// state_validator_occupancy_map.cpp:23,60); this variant has no reference semantics and is defined here (ppx.h,
+// ppx_footprint_params): the length x width rectangle, centred `rear_to_center` ahead of the pose, is covered by n discs
+// of one radius rho along the heading; a pose is valid iff every disc centre passes IsStateValid with minSafeRadius = rho
+// (bounds, map, clearance of its cell).  Along a path the sampling is the reference's sphere tracing on the tightest disc,
+// de-rated by gamma = the largest ratio between the travel of a disc centre and the travel of the pose.
+struct RectDev {
+	int n; // discs
+	double first, pitch; // offset of disc 0 along the heading, distance between disc centres (m)
+	float rho; // common radius
+	float gamma; // >= 1
+	float minStep;
+};
+
+// validity of the pose and the smallest slack (clearance - rho) over the discs, the smallest distance to the bounds
+PPX_HD bool rect_state_valid(const MapDev& m, const RectDev& R, double x, double y, double th, float* slack, float* border)
+{
+	double s, c;
+	PPX_SINCOS(th, &s, &c);
+	float minSlack = __int_as_float(0x7f800000), minBorder = __int_as_float(0x7f800000);
+	bool ok = true;
+	for (int i = 0; i < R.n; i++) {
+		const double o = R.first + i * R.pitch;
+		const double dx = x + o * c, dy = y + o * s;
+		float d = 0.0f;
+		if (!is_state_valid(m, dx, dy, th, R.rho, &d))
+			ok = false;
+		minSlack = std_minf(minSlack, d - R.rho);
+		double b = dx - m.lbx;
+		if (m.ubx - dx < b) b = m.ubx - dx;
+		if (dy - m.lby < b) b = dy - m.lby;
+		if (m.uby - dy < b) b = m.uby - dy;
+		minBorder = std_minf(minBorder, (float)b);
+	}
+	*slack = minSlack;
+	*border = minBorder;
+	return ok;
+}
+
+PPX_HD bool rs_is_path_valid_rect(const MapDev& map, const RectDev& R, const Pose& start, const RSSeg& seg, double r, float* last,
+	unsigned* samples)
+{
+	const double pathLength = rs_total_length(seg) * r;
+	unsigned ns = 0;
+	float slack = 0.0f, border = 0.0f;
+	if (pathLength == 0.0) {
+		*last = 1.0f;
+		if (samples) *samples = 1;
+		return rect_state_valid(map, R, start.x, start.y, start.th, &slack, &border);
+	}
+	RSWalker w;
+	w.init(start);
+	double lastValidLength = 0.0, length = 0.0;
+	bool ok = true;
+	while (length < pathLength) {
+		Pose p = w.at(seg, r, (length / pathLength) * pathLength);
+		ns++;
+		if (!rect_state_valid(map, R, p.x, p.y, p.th, &slack, &border)) {
+			*last = (float)(lastValidLength / pathLength);
+			ok = false;
+			break;
+		}
+		lastValidLength = length;
+		float delta = std_minf(slack, border) / R.gamma;
+		length += (double)std_maxf(delta, R.minStep);
+	}
+	if (ok)
+		*last = 1.0f;
+	if (samples) *samples = ns;
+	return ok;
+}
+
+// ---------------------------------------------------------------------------------------------
 // Lane state machine of the re-converging Reeds-Shepp edge checker ("lane refill").
 //
 // IsPathValid on an RS path is a chain of data-dependent samples, each of which walks a

@@ -375,6 +375,55 @@ __global__ void __launch_bounds__(kThreads) k_rs_solve_quad(int64_t n, const dou
 	}
 }
 
+// rectangular footprint variant (ppx_device.cuh, RectDev): one edge / pose per thread, exact FP64 positions
+__global__ void __launch_bounds__(kThreads) k_check_rs_rect(MapDev map, RectDev R, int64_t n, const ppx_rs_edge* __restrict__ edges,
+	double r, uint8_t* __restrict__ valid, float* __restrict__ last, uint32_t* __restrict__ samples)
+{
+	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride) {
+		Pose start;
+		RSSeg seg;
+		load_rs_edge(edges + i, start, seg);
+		float l;
+		unsigned ns;
+		bool ok = rs_is_path_valid_rect(map, R, start, seg, r, &l, &ns);
+		valid[i] = ok ? 1 : 0;
+		last[i] = l;
+		if (samples)
+			samples[i] = ns;
+	}
+}
+
+__global__ void __launch_bounds__(kThreads) k_is_state_valid_rect(MapDev map, RectDev R, int64_t n, const double* __restrict__ poses,
+	uint8_t* __restrict__ valid)
+{
+	int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+	const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+	for (; i < n; i += stride) {
+		float slack, border;
+		valid[i] = rect_state_valid(map, R, poses[3 * i], poses[3 * i + 1], poses[3 * i + 2], &slack, &border) ? 1 : 0;
+	}
+}
+
+// ppx_footprint_params -> device constants; false when the parameters make no sense
+bool rect_derive(const ppx_footprint_params* fp, double rmin, RectDev& R)
+{
+	if (!fp || !(fp->length > 0.0) || !(fp->width > 0.0) || fp->n_discs < 1 || fp->n_discs > 16 || !(fp->min_step > 0.0f) || !(rmin > 0.0))
+		return false;
+	R.n = fp->n_discs;
+	const double seg = fp->length / fp->n_discs; // every disc covers a length / n by width slice of the rectangle
+	R.pitch = seg;
+	R.first = fp->rear_to_center - fp->length / 2.0 + seg / 2.0;
+	R.rho = (float)sqrt(seg * seg / 4.0 + fp->width * fp->width / 4.0);
+	double omax = 0.0;
+	for (int i = 0; i < R.n; i++)
+		omax = fmax(omax, fabs(R.first + i * R.pitch));
+	R.gamma = (float)sqrt(1.0 + (omax / rmin) * (omax / rmin)); // a disc centre at offset o moves ds * sqrt(1 + (o * kappa)^2), kappa <= 1 / rmin
+	R.minStep = fp->min_step;
+	return true;
+}
+
 int grid_for(const ppx_ctx* ctx, int64_t n, int threads, int blocksPerSm)
 {
 	int64_t need = (n + threads - 1) / threads;
@@ -560,6 +609,70 @@ int ppx_check_edges_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double
 			PPX_CUDA(ctx, cudaMemcpyAsync(samples + off, d_samples + off, m * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->s_d2h));
 	}
 	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->s_d2h));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_check_edges_rs_rect_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, double min_turning_radius,
+	const ppx_footprint_params* fp, uint8_t* d_valid, float* d_last, uint32_t* d_samples)
+{
+	PPX_GUARD(ctx);
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && (n == 0 || (d_edges && d_valid && d_last)), "bad arguments");
+	RectDev R;
+	PPX_REQUIRE(ctx, rect_derive(fp, min_turning_radius, R), "bad footprint parameters");
+	if (n == 0)
+		return PPX_OK;
+	k_check_rs_rect<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), R, n, d_edges, min_turning_radius, d_valid,
+		d_last, d_samples);
+	PPX_LAUNCHED(ctx);
+	return PPX_OK;
+}
+
+int ppx_check_edges_rs_rect(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double min_turning_radius,
+	const ppx_footprint_params* fp, uint8_t* valid, float* last, uint32_t* samples)
+{
+	PPX_GUARD(ctx);
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && (n == 0 || (edges && valid && last)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	ppx_rs_edge* d_edges;
+	uint8_t* d_valid;
+	float* d_last;
+	uint32_t* d_samples = nullptr;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * sizeof(ppx_rs_edge), (void**)&d_edges));
+	PPX_CHECK(ppx_scratch(ctx, 1, n, (void**)&d_valid));
+	PPX_CHECK(ppx_scratch(ctx, 2, n * sizeof(float), (void**)&d_last));
+	if (samples)
+		PPX_CHECK(ppx_scratch(ctx, 3, n * sizeof(uint32_t), (void**)&d_samples));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_edges, edges, n * sizeof(ppx_rs_edge), cudaMemcpyHostToDevice, ctx->stream));
+	PPX_CHECK(ppx_check_edges_rs_rect_dev(ctx, n, d_edges, min_turning_radius, fp, d_valid, d_last, d_samples));
+	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaMemcpyAsync(last, d_last, n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+	if (samples)
+		PPX_CUDA(ctx, cudaMemcpyAsync(samples, d_samples, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+	return PPX_OK;
+}
+
+int ppx_is_state_valid_rect(ppx_ctx* ctx, int64_t n, const double* poses, const ppx_footprint_params* fp, uint8_t* valid)
+{
+	PPX_GUARD(ctx);
+	PPX_CHECK(require_map(ctx));
+	PPX_REQUIRE(ctx, n >= 0 && (n == 0 || (poses && valid)), "bad arguments");
+	RectDev R;
+	PPX_REQUIRE(ctx, rect_derive(fp, 1.0, R), "bad footprint parameters");
+	if (n == 0)
+		return PPX_OK;
+	double* d_poses;
+	uint8_t* d_valid;
+	PPX_CHECK(ppx_scratch(ctx, 0, n * 3 * sizeof(double), (void**)&d_poses));
+	PPX_CHECK(ppx_scratch(ctx, 1, n, (void**)&d_valid));
+	PPX_CUDA(ctx, cudaMemcpyAsync(d_poses, poses, n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+	k_is_state_valid_rect<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), R, n, d_poses, d_valid);
+	PPX_LAUNCHED(ctx);
+	PPX_CUDA(ctx, cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, ctx->stream));
 	PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
 	return PPX_OK;
 }

@@ -23,6 +23,11 @@ class ValidatorParamsC(C.Structure):
     _fields_ = [("min_safe_radius", C.c_float), ("min_path_interpolation_distance", C.c_float)]
 
 
+class FootprintParamsC(C.Structure):
+    _fields_ = [("length", C.c_double), ("width", C.c_double), ("rear_to_center", C.c_double), ("n_discs", C.c_int32),
+                ("min_step", C.c_float)]
+
+
 class RSCostParamsC(C.Structure):
     _fields_ = [("min_turning_radius", C.c_double), ("reverse_cost_multiplier", C.c_float),
                 ("forward_cost_multiplier", C.c_float), ("direction_switching_cost", C.c_float),
@@ -107,6 +112,9 @@ _SIGS = {
     "ppx_astar_n2": (C.c_int, [_p, _i64, _p, _p, C.c_int32, C.c_int32, _p, _p]),
     "ppx_hybrid_search_dev": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
     "ppx_hybrid_timing": (C.c_int, [_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "ppx_is_state_valid_rect": (C.c_int, [_p, _i64, _p, C.POINTER(FootprintParamsC), _p]),
+    "ppx_check_edges_rs_rect": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(FootprintParamsC), _p, _p, _p]),
+    "ppx_check_edges_rs_rect_dev": (C.c_int, [_p, _i64, _p, C.c_double, C.POINTER(FootprintParamsC), _p, _p, _p]),
     "ppx_comm_unique_id": (C.c_int, [_p]),
     "ppx_comm_init": (C.c_int, [_p, _p, C.c_int32, C.c_int32]),
     "ppx_comm_destroy": (C.c_int, [_p]),

@@ -238,6 +238,24 @@ class World:
                                           C.c_double(rmin), _p(valid), _p(last), _p(samples))
         return dict(valid=valid.astype(bool), last=last, samples=samples, seconds=sec)
 
+    def check_rs_segments_rect(self, starts, steer, direction, length, rmin, footprint):
+        """rectangular-footprint variant restated over the reference's Interpolate / IsStateValid / distance map ("port");
+        footprint = (length, width, rear_to_center, n_discs, min_step)"""
+        starts = np.ascontiguousarray(starts, np.float64)
+        steer = np.ascontiguousarray(steer, np.int32)
+        direction = np.ascontiguousarray(direction, np.int32)
+        length = np.ascontiguousarray(length, np.float64)
+        n = len(starts)
+        valid = np.empty(n, np.uint8)
+        last = np.empty(n, np.float32)
+        samples = np.empty(n, np.int32)
+        fp = np.array(footprint, np.float64)
+        f = lib().ref_check_rs_segments_rect
+        f.restype = C.c_double
+        sec = f(self.h, C.c_long(n), _p(starts), _p(steer), _p(direction), _p(length), C.c_double(rmin), _p(fp), _p(valid), _p(last),
+                _p(samples))
+        return dict(valid=valid.astype(bool), last=last, samples=samples, seconds=sec)
+
     def check_csteer(self, starts, steering, length, direction, wheelbase=2.6):
         starts = np.ascontiguousarray(starts, np.float64)
         steering = np.ascontiguousarray(steering, np.float64)

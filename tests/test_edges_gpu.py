@@ -375,3 +375,35 @@ def test_rs_engines_identical(ctx, c3_edges):
     assert_close_rel(l, rr["last"][1:n + 1], REL, "last")
     for p in (d, d_valid, d_last):
         ppx.ppx_dev_free(ctx.handle, p)
+
+
+@pytest.mark.parametrize("footprint", [(4.5, 2.0, 1.3, 3, 0.1), (4.5, 2.0, 0.0, 1, 0.1), (3.0, 1.6, 1.0, 5, 0.05)])
+def test_rect_footprint_variant(ctx, ref, c3_edges, footprint):
+    """BASELINE config 3's "rectangular car footprint".  The reference has none (one disc, two `TODO add offset`); the
+    variant is DEFINED in include/ppx.h (covering discs along the heading, de-rated sphere tracing) and its checker is
+    that definition restated over the reference's own Interpolate / IsStateValid / distance map -- "port", parity
+    unpinned by definition, reported apart from the disc results.  Verdicts and sample counts identical, `last` 1e-6."""
+    from pathplanning_b200 import synth
+    edges, rr = c3_edges
+    ctx.upload_map(*rr["map"], None)
+    n = 60000
+    cfg = synth.C3
+    w = ref.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+    for r in synth.config_rects(cfg):
+        w.add_rectangle(*r)
+    w.update()
+    want = w.check_rs_segments_rect(edges["start"][:n], rr["steer"][:n], rr["dir"][:n], rr["len"][:n], 2.0, footprint)
+    w.close()
+    v, l, s = ctx.check_edges_rs_rect(np.ascontiguousarray(edges[:n]), 2.0, footprint)
+    assert 0.01 < want["valid"].mean() < 0.9
+    diff = np.flatnonzero((v != want["valid"]) | (s.astype(np.int64) != want["samples"].astype(np.int64)))
+    assert len(diff) <= 2, (len(diff), diff[:5])  # a disc centre within an ulp of a cell border may flip with the libm
+    same = np.setdiff1d(np.arange(n), diff)
+    assert_close_rel(l[same], want["last"][same], REL, "last")
+    # the rectangle is stricter than the reference's single disc of the same half-width placed at the pose... only when the
+    # pose disc lies inside the cover: with the centre at the pose and one disc (second case) rho >= width / 2
+    if footprint[2] == 0.0 and footprint[3] == 1:
+        vd, _ = ctx.check_edges_rs(np.ascontiguousarray(edges[:n]), 2.0, pp.ValidatorParams(footprint[1] / 2.0, footprint[4]))
+        assert not (v & ~vd).any()
+    poses = edges["start"][:5000]
+    assert np.array_equal(ctx.is_state_valid_rect(poses, footprint), v[:5000] | (l[:5000] > 0) | (s[:5000] > 1))
