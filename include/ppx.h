@@ -549,6 +549,26 @@ typedef struct ppx_astar_result {
 int ppx_astar_n2(ppx_ctx* ctx, int64_t nq, const int32_t* starts, const int32_t* goals, int32_t max_nodes, int32_t max_path,
 	ppx_astar_result* results, int32_t* paths);
 
+/* The same with a choice of functors, and BidirectionalAStarN2 (algo/bidirectional_a_star.h:41-204, a_star_n2.h:36-42).
+ * The reference's callbacks are std::function objects (Python lambdas through pyplanning.cpp:140-154); a callback cannot
+ * cross a C ABI into a kernel, so the device offers the table of functors those callbacks are in practice:
+ *   cost_kind       0 Euclidean cell distance, 1 Manhattan, 2 octile (max + (sqrt 2 - 1) min), 3 Euclidean x cell_cost[neighbour]
+ *   heuristic_kind  0 Euclidean, 1 Manhattan, 2 octile to the search's goal; 3 zero
+ * bidirectional != 0: forward and reverse searches advance in turn (pop + Expand + FindIntersection each) until the two
+ * frontier tops prove the best meeting point optimal; the forward search's heuristic aims at the goal, the reverse one at
+ * the start.  (The reference's AverageHeuristic pair never sets the goal of the heuristics it averages -- built from one
+ * heuristic object, as example_a_star_grid.py:97 does, it is the constant zero: that is heuristic_kind 3.)
+ * Results: n_explored / n_nodes are the sums over both searches, cost = GetOptimalCost(), the path is GetPath(): the forward
+ * path followed by the reverse search's path reversed, the meeting cell twice (bidirectional_a_star.h:66-72). */
+typedef struct ppx_astar_params {
+	int32_t cost_kind, heuristic_kind;
+	const float* cell_cost; /* host, rows * cols, cost_kind 3 only */
+	int32_t bidirectional;
+	int32_t _pad;
+} ppx_astar_params;
+int ppx_astar_n2_ex(ppx_ctx* ctx, int64_t nq, const int32_t* starts, const int32_t* goals, const ppx_astar_params* params,
+	int32_t max_nodes, int32_t max_path, ppx_astar_result* results, int32_t* paths);
+
 /* ---------------------------------------------------------------------------------------------
  * Multi-GPU.  The path shards by independent units -- edge batches, start/goal queries -- with the world model
  * replicated; one context per GPU, one process (or thread) per context.  The reference has no counterpart (it is

@@ -1116,6 +1116,62 @@ int ref_astar_n2(void* hw, int r0, int c0, int r1, int c1, double* cost, long* e
 	return (int)st;
 }
 
+// Grid A* with the functor table of ppx_astar_params (same formulas as the device's grid_metric), unidirectional (AStarN2) or
+// BidirectionalAStarN2 with one heuristic object per direction.  cellcost: rows*cols floats for cost kind 3.
+int ref_astar_n2_ex(void* hw, int r0, int c0, int r1, int c1, int costKind, int heurKind, const float* cellcost, int bidirectional,
+	double* cost, long* explored, long cap, int* path_cells, long* path_len)
+{
+	auto* w = (RefWorld*)hw;
+	const int cols = w->map->Columns();
+	auto metric = [](int kind, const GridCellPosition& a, const GridCellPosition& b) {
+		const double dr = std::fabs((double)(a.row - b.row)), dc = std::fabs((double)(a.col - b.col));
+		if (kind == 1)
+			return dr + dc;
+		if (kind == 2)
+			return std::fmax(dr, dc) + (std::sqrt(2.0) - 1.0) * std::fmin(dr, dc);
+		return std::sqrt(dr * dr + dc * dc);
+	};
+	std::function<double(const GridCellPosition&, const GridCellPosition&)> costFcn = [=](const GridCellPosition& a, const GridCellPosition& b) {
+		if (costKind == 3)
+			return metric(0, a, b) * (double)cellcost[(size_t)b.row * cols + b.col];
+		return metric(costKind, a, b);
+	};
+	std::function<double(const GridCellPosition&, const GridCellPosition&)> heurFcn = [=](const GridCellPosition& s, const GridCellPosition& g) {
+		return heurKind == 3 ? 0.0 : metric(heurKind, s, g);
+	};
+	Ref<OccupancyMap> map = w->map;
+	std::vector<GridCellPosition> path;
+	Status st;
+	if (!bidirectional) {
+		AStarN2 astar;
+		astar.Initialize(makeRef<AStarStatePropagatorFcnN2>(map, costFcn), makeRef<AStarHeuristicFcnN2>(heurFcn));
+		astar.SetInitState(GridCellPosition(r0, c0));
+		astar.SetGoalState(GridCellPosition(r1, c1));
+		st = astar.SearchPath();
+		*cost = astar.GetOptimalCost();
+		*explored = (long)astar.GetExploredStates().size();
+		path = astar.GetPath();
+	} else {
+		BidirectionalAStarN2 astar;
+		astar.Initialize(makeRef<AStarStatePropagatorFcnN2>(map, costFcn), makeRef<AStarStatePropagatorFcnN2>(map, costFcn),
+			makeRef<AStarHeuristicFcnN2>(heurFcn), makeRef<AStarHeuristicFcnN2>(heurFcn));
+		astar.SetInitState(GridCellPosition(r0, c0));
+		astar.SetGoalState(GridCellPosition(r1, c1));
+		st = astar.SearchPath();
+		*cost = st == Status::Success ? astar.GetOptimalCost() : std::numeric_limits<double>::infinity();
+		auto [fe, re] = astar.GetExploredStates();
+		*explored = (long)(fe.size() + re.size());
+		if (st == Status::Success)
+			path = astar.GetPath();
+	}
+	*path_len = (long)path.size();
+	for (long i = 0; i < (long)path.size() && i < cap; i++) {
+		path_cells[2 * i] = path[i].row;
+		path_cells[2 * i + 1] = path[i].col;
+	}
+	return (int)st;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Tree / kNN (A10) through the reference's own utils/tree.h on top of the brute-force flann
 // stand-in (oracle/shim/flann/flann.hpp).  2-D points (the only instantiation that compiles

@@ -213,6 +213,19 @@ class Context:
         self._check(ppx.ppx_astar_n2(self.handle, nq, _ptr(s), _ptr(g), max_nodes, max_path, _ptr(res), _ptr(paths)))
         return dict(results=res, paths=paths)
 
+    def astar_n2_ex(self, starts, goals, cost_kind=0, heuristic_kind=0, cell_cost=None, bidirectional=False, max_path=0, max_nodes=0):
+        """ppx_astar_n2_ex: AStarN2 / BidirectionalAStarN2 with the device's functor table (see ppx.h)"""
+        from .lib import AstarParamsC
+        s = np.ascontiguousarray(starts, np.int32).reshape(-1, 2)
+        g = np.ascontiguousarray(goals, np.int32).reshape(-1, 2)
+        nq = len(s)
+        res = np.zeros(nq, ASTAR_RESULT)
+        paths = np.zeros((nq, max_path, 2), np.int32) if max_path else None
+        cc = None if cell_cost is None else np.ascontiguousarray(cell_cost, np.float32)
+        prm = AstarParamsC(cost_kind, heuristic_kind, None if cc is None else cc.ctypes.data, 1 if bidirectional else 0, 0)
+        self._check(ppx.ppx_astar_n2_ex(self.handle, nq, _ptr(s), _ptr(g), C.byref(prm), max_nodes, max_path, _ptr(res), _ptr(paths)))
+        return dict(results=res, paths=paths)
+
     def build_map(self, desc: MapDesc, occupancy, pathcost=None, want_sqdist=True):
         """ppx_map_build: occupancy grid in, obstacle squared-distance map computed on the device (N1)."""
         cells = desc.rows * desc.cols

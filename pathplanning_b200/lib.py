@@ -28,6 +28,11 @@ class FootprintParamsC(C.Structure):
                 ("min_step", C.c_float)]
 
 
+class AstarParamsC(C.Structure):
+    _fields_ = [("cost_kind", C.c_int32), ("heuristic_kind", C.c_int32), ("cell_cost", C.c_void_p), ("bidirectional", C.c_int32),
+                ("_pad", C.c_int32)]
+
+
 class RSCostParamsC(C.Structure):
     _fields_ = [("min_turning_radius", C.c_double), ("reverse_cost_multiplier", C.c_float),
                 ("forward_cost_multiplier", C.c_float), ("direction_switching_cost", C.c_float),
@@ -110,6 +115,7 @@ _SIGS = {
     "ppx_smoother_smooth": (C.c_int, [_p, _i64, _p, _p, _p, C.c_int32, _p, _p, _p]),
     "ppx_map_rasterize": (C.c_int, [_p, C.POINTER(MapDescC), C.c_int32, _p, _p, C.c_int32, _p]),
     "ppx_astar_n2": (C.c_int, [_p, _i64, _p, _p, C.c_int32, C.c_int32, _p, _p]),
+    "ppx_astar_n2_ex": (C.c_int, [_p, _i64, _p, _p, C.POINTER(AstarParamsC), C.c_int32, C.c_int32, _p, _p]),
     "ppx_hybrid_search_dev": (C.c_int, [_p, _i64, _p, _p, _p, C.POINTER(HybridLimitsC), _p, _p, _p]),
     "ppx_hybrid_timing": (C.c_int, [_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "ppx_is_state_valid_rect": (C.c_int, [_p, _i64, _p, C.POINTER(FootprintParamsC), _p]),

@@ -131,6 +131,17 @@ class World:
         return dict(status=int(st), cost=cost.value, explored=explored.value, seconds=sec.value, path=path[:min(plen.value, cap)].copy(),
                     path_len=plen.value)
 
+    def astar_n2_ex(self, start, goal, cost_kind=0, heuristic_kind=0, cell_cost=None, bidirectional=False, cap=8192):
+        """AStarN2 / BidirectionalAStarN2 with the functor table of ppx_astar_params"""
+        cost = C.c_double()
+        explored, plen = C.c_long(), C.c_long()
+        path = np.zeros((cap, 2), np.int32)
+        cc = None if cell_cost is None else np.ascontiguousarray(cell_cost, np.float32)
+        st = lib().ref_astar_n2_ex(self.h, C.c_int(int(start[0])), C.c_int(int(start[1])), C.c_int(int(goal[0])), C.c_int(int(goal[1])),
+                                   C.c_int(cost_kind), C.c_int(heuristic_kind), None if cc is None else _p(cc), C.c_int(int(bidirectional)),
+                                   C.byref(cost), C.byref(explored), C.c_long(cap), _p(path), C.byref(plen))
+        return dict(status=int(st), cost=cost.value, explored=explored.value, path=path[:min(plen.value, cap)].copy(), path_len=plen.value)
+
     def remove_obstacle(self, index):
         """RemoveObstacle of the index-th obstacle added to this world"""
         return lib().ref_world_remove_obstacle(self.h, C.c_int(index))

@@ -78,3 +78,32 @@ def test_astar_n2_limits(actx, c1):
     assert int(out["results"][1]["status"]) == -1 and int(out["results"][1]["n_explored"]) == 0  # start outside the grid: Failure
     n = int(out["results"][0]["path_len"])
     assert n > 8 and (out["paths"][0] >= 0).all()  # the first max_path cells of a longer path
+
+
+@pytest.mark.parametrize("bidirectional", [False, True])
+@pytest.mark.parametrize("cost_kind,heuristic_kind", [(0, 0), (1, 1), (2, 2), (0, 3), (3, 0)])
+def test_astar_functors_and_bidirectional(actx, c1, cost_kind, heuristic_kind, bidirectional):
+    """ppx_astar_n2_ex: the functor table (Euclidean / Manhattan / octile / zero heuristic / per-cell cost grid) and
+    BidirectionalAStarN2 (algo/bidirectional_a_star.h:41-204) against the compiled reference running the same functors as
+    C++ std::function objects: status, explored-state count (both searches), optimal cost bit for bit, path cell by cell
+    (forward path + reversed reverse path, the meeting cell twice)."""
+    occ, sq = c1.grids()
+    actx.upload_map(c1.map_desc(), sq, occ, None)
+    rng = np.random.default_rng(23 + cost_kind)
+    cell_cost = (1.0 + rng.uniform(0, 3, occ.shape)).astype(np.float32) if cost_kind == 3 else None
+    free = np.argwhere(occ < 0)
+    pairs = [((1, 1), (198, 198)), ((100, 100), (100, 100))]
+    for _ in range(10):
+        a, b = free[rng.integers(len(free))], free[rng.integers(len(free))]
+        pairs.append((tuple(a), tuple(b)))
+    wall = np.argwhere(occ >= 0)
+    pairs.append(((1, 1), tuple(wall[len(wall) // 3])))
+    starts = np.array([p[0] for p in pairs], np.int32)
+    goals = np.array([p[1] for p in pairs], np.int32)
+    out = actx.astar_n2_ex(starts, goals, cost_kind, heuristic_kind, cell_cost, bidirectional, max_path=2048)
+    solved = 0
+    for i, (s, g) in enumerate(pairs):
+        r = c1.astar_n2_ex(s, g, cost_kind, heuristic_kind, cell_cost, bidirectional)
+        _check(r, out["results"][i], out["paths"][i])
+        solved += r["status"] == 0
+    assert solved >= 9
