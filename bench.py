@@ -460,6 +460,196 @@ def hybrid_section(args, rank, world, local_rank, stream):
     return section
 
 
+def _ref_extras_worker(conn, c5_nodes):
+    """Child process (one core): the reference's side of the extra configurations -- C1 grid A*, C2 single Hybrid A* query,
+    C5 restated RRT* (bounded), C3 solve + check and the rectangular-footprint port on a bounded sample."""
+    import refapi
+    synth = _synth()
+    out = {}
+    try:
+        # C1: AStarN2 on the 200 x 200 grid with 60 rectangle outlines, Euclidean functors
+        w = refapi.World((-50.0, -50.0, -math.pi), (50.0, 50.0, math.pi), 0.5)
+        rng = np.random.default_rng(3)
+        for _ in range(60):
+            w.add_rectangle(2.0 + 10.0 * rng.uniform(), 1.0, rng.uniform(-45, 45), rng.uniform(-45, 45), rng.uniform(-math.pi, math.pi))
+        w.update()
+        r = w.astar_n2((1, 1), (198, 198))
+        out["c1"] = dict(ms=r["seconds"] * 1e3, explored=r["explored"], cost=r["cost"], status=r["status"])
+        w.close()
+        # C2: one Hybrid A* query on the 400 x 400 parking lot (wavefront + GVD update + graph search)
+        cfg = synth.C2
+        w = refapi.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+        for rect in synth.config_rects(cfg):
+            w.add_rectangle(*rect)
+        w.gvd_update()
+        w.set_validator_params(RADIUS, MIN_STEP)
+        H = refapi.Hybrid(w)
+        t0 = time.perf_counter()
+        r = H.search((-18.0, -18.0, 0.0), (17.0, 17.5, math.pi / 2), 42)
+        out["c2"] = dict(ms=(time.perf_counter() - t0) * 1e3, status=r["status"], cost=r["cost"], n_expanded=r["n_expanded"],
+                         phases_ms=[t * 1e3 for t in r["times"]])
+        H.close()
+        w.close()
+        # C3 map: solve + check and the rectangle port on 100k pairs; C5 restated RRT* to c5_nodes nodes
+        cfg = synth.C3
+        w = refapi.World(cfg["lb"], cfg["ub"], cfg["resolution"])
+        for rect in synth.config_rects(cfg):
+            w.add_rectangle(*rect)
+        w.update()
+        w.set_validator_params(RADIUS, MIN_STEP)
+        s, g = synth.random_rs_queries(100000, seed=1000)
+        r = w.check_rs_edges(s, g, RMIN, full=False)
+        out["solve_check"] = dict(edges=100000, seconds=r["seconds"])
+        r2 = w.check_rs_edges(s[:20000], g[:20000], RMIN)
+        rr = w.check_rs_segments_rect(s[:20000], r2["steer"], r2["dir"], r2["len"], RMIN, RECT_FOOTPRINT)
+        out["rect"] = dict(edges=20000, seconds=rr["seconds"], valid=int(rr["valid"].sum()), samples=int(rr["samples"].sum()))
+        for conn_kind, name in ((0, "straight"), (1, "reeds_shepp")):
+            r = refapi.rrtstar_se2_restated(w, cfg["lb"], cfg["ub"], C5_START, C5_GOAL, 7, 10**7, c5_nodes, 1.0, 0.05, conn_kind, RMIN)
+            out["c5_" + name] = dict(nodes=r["n_nodes"], iterations=r["iterations"], edges=r["edges_checked"], seconds=r["seconds"])
+        w.close()
+        conn.send(out)
+    except Exception as e:  # pragma: no cover
+        conn.send(e)
+    conn.close()
+
+
+RECT_FOOTPRINT = (4.5, 2.0, 1.3, 3, 0.1)  # length, width, rear axle -> centre, covering discs, min step
+C5_START, C5_GOAL = (-90.0, -90.0, 0.0), (90.0, 90.0, 1.0)
+
+
+def extras_section(args, local_rank, stream):
+    """The other BASELINE configurations in the driver-run line (N = 1, rank 0): C1 grid A*, C2 single Hybrid A* query, C3
+    solve + check and the rectangular-footprint variant, C5 one RRT* tree to 100 k nodes -- each beside the reference (or
+    its restated loop, kind "port") timed in this run on one host core, results compared where both exist."""
+    import multiprocessing as mp
+    import torch
+    import pathplanning_b200 as pp
+    from pathplanning_b200 import synth
+    from pathplanning_b200.lib import ppx
+    out = {}
+    ref = None
+    if not args.no_cpu_baseline:
+        ctxmp = mp.get_context("fork")
+        a, b = ctxmp.Pipe(duplex=False)
+        proc = ctxmp.Process(target=_ref_extras_worker, args=(b, args.cpu_c5_nodes))
+        proc.start()
+    ctx = pp.Context(local_rank)
+    ctx.set_stream(stream.cuda_stream)
+    vp = pp.ValidatorParams(RADIUS, MIN_STEP)
+
+    def timed(fn, reps=3):
+        fn()
+        t = []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r = fn()
+            torch.cuda.synchronize()
+            t.append(time.perf_counter() - t0)
+        return min(t), r
+    # C1
+    rng = np.random.default_rng(3)
+    rects = [(2.0 + 10.0 * rng.uniform(), 1.0, rng.uniform(-45, 45), rng.uniform(-45, 45), rng.uniform(-math.pi, math.pi)) for _ in range(60)]
+    lb, ub = (-50.0, -50.0, -math.pi), (50.0, 50.0, math.pi)
+    occ = synth.rasterize_rectangles(rects, lb, ub, 0.5)
+    rows, cols, origin = synth.map_geometry(lb, ub, 0.5)
+    ctx.build_map(pp.MapDesc(rows=rows, cols=cols, resolution=0.5, world_origin=origin, lb=lb, ub=ub), occ)
+    sec, r = timed(lambda: ctx.astar_n2([(1, 1)], [(198, 198)], max_path=1024))
+    nb = 4096
+    free = np.argwhere(occ < 0)
+    pick = np.random.default_rng(4).integers(len(free), size=(2, nb))
+    secb, rb = timed(lambda: ctx.astar_n2(free[pick[0]], free[pick[1]]))
+    out["c1"] = {"workload": "C1: grid A* (AStarN2, Euclidean functors) on a 200x200 grid, 60 rectangle outlines, (1,1)->(198,198)",
+                 "ms_single_query": sec * 1e3, "explored": int(r["results"][0]["n_explored"]), "cost": float(r["results"][0]["cost"]),
+                 "batch": {"queries": nb, "value": nb / secb, "unit": "plans/s", "solved": int((rb["results"]["status"] == 0).sum())},
+                 "note": "host call: H2D + kernel + D2H; a single query is one chain of dependent expansions on one warp"}
+    # C2
+    cfg = synth.C2
+    occ = synth.rasterize_rectangles(synth.config_rects(cfg), cfg["lb"], cfg["ub"], cfg["resolution"])
+    rows, cols, origin = synth.map_geometry(cfg["lb"], cfg["ub"], cfg["resolution"])
+    ctx.build_gvd(pp.MapDesc(rows=rows, cols=cols, resolution=cfg["resolution"], world_origin=origin, lb=cfg["lb"], ub=cfg["ub"]), occ, voronoi=True)
+    planner = pp.HybridAStar(ctx, pp.HybridParams(), vp)
+    sec, r = timed(lambda: planner.search(np.array([[-18.0, -18.0, 0.0]]), np.array([[17.0, 17.5, math.pi / 2]]), np.array([42], np.uint64), max_path=256))
+    wf_ms, se_ms = planner.timing()
+    out["c2"] = {"workload": "C2: one Hybrid A* query on the 400x400 parking lot, (-18,-18,0) -> (17,17.5,pi/2), seed 42, Voronoi field built on the device",
+                 "ms": sec * 1e3, "wavefront_ms": wf_ms, "search_ms": se_ms, "status": int(r["results"][0]["status"]),
+                 "cost": float(r["results"][0]["cost"]), "n_expanded": int(r["results"][0]["n_expanded"])}
+    planner.close()
+    # C3 map: solve + check, rectangle variant, C5
+    cfg = synth.C3
+    occ = synth.rasterize_rectangles(synth.config_rects(cfg), cfg["lb"], cfg["ub"], cfg["resolution"])
+    rows, cols, origin = synth.map_geometry(cfg["lb"], cfg["ub"], cfg["resolution"])
+    ctx.build_map(pp.MapDesc(rows=rows, cols=cols, resolution=cfg["resolution"], world_origin=origin, lb=cfg["lb"], ub=cfg["ub"]), occ)
+    n = N_EDGES
+    s, g = synth.random_rs_queries(n, seed=1000)
+    dev = torch.device("cuda", local_rank)
+    d_s, d_g = torch.from_numpy(s).to(dev), torch.from_numpy(g).to(dev)
+    d_valid = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_last = torch.empty(n, dtype=torch.float32, device=dev)
+    cp, vpc = pp.RSCostParams(RMIN).to_c(), vp.to_c()
+
+    def dev_ms(fn, reps=10):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+    ms = dev_ms(lambda: ppx.ppx_connect_check_rs_dev(ctx.handle, n, d_s.data_ptr(), d_g.data_ptr(), ctypes.byref(cp), ctypes.byref(vpc),
+                                                      d_valid.data_ptr(), d_last.data_ptr(), None, None, None))
+    hs, hg = torch.from_numpy(s).pin_memory(), torch.from_numpy(g).pin_memory()
+    hv, hl = torch.empty(n, dtype=torch.uint8).pin_memory(), torch.empty(n, dtype=torch.float32).pin_memory()
+    esec, _ = timed(lambda: ppx.ppx_connect_check_rs(ctx.handle, n, hs.data_ptr(), hg.data_ptr(), ctypes.byref(cp), ctypes.byref(vpc),
+                                                      hv.data_ptr(), hl.data_ptr(), None, None, None))
+    out["solve_check"] = {"workload": "C3 solve + check: PathConnectionReedsShepp::Connect + IsPathValid from 1M (start, goal) pairs",
+                          "value": n / (ms * 1e-3), "unit": "edges/s", "ms_per_step": ms,
+                          "e2e": {"value": n / esec, "unit": "edges/s", "h2d_bytes_per_step": n * 48, "d2h_bytes_per_step": n * 5},
+                          "valid_fraction": float(d_valid.float().mean().item())}
+    sol = ctx.rs_solve(s[:200000], g[:200000], pp.RSCostParams(RMIN))
+    rsec, rr = timed(lambda: ctx.check_edges_rs_rect(sol["edges"], RMIN, RECT_FOOTPRINT))
+    out["rect_footprint"] = {"workload": "C3 check-only with the rectangular footprint variant (4.5 x 2.0 m, 3 covering discs; NOT a reference "
+                             "behaviour, defined in include/ppx.h)", "value": 200000 / rsec, "unit": "edges/s (host call, 200k edges)",
+                             "valid_fraction": float(rr[0].mean()), "mean_samples": float(rr[2].mean())}
+    c5 = {}
+    for conn_kind, name in ((0, "straight"), (1, "reeds_shepp")):
+        t0 = time.perf_counter()
+        r = ctx.rrt_run(np.array([C5_START]), np.array([C5_GOAL]), np.array([7], np.uint64), cfg["lb"], cfg["ub"], dim=3, connection=conn_kind,
+                        star=1, validator=1, max_iteration=10**7, max_nodes=100000, max_connection_distance=1.0, goal_bias=0.05,
+                        min_turning_radius=RMIN, vp=vp, want_trees=False)["results"][0]
+        dt = time.perf_counter() - t0
+        c5[name] = {"nodes": int(r["n_nodes"]), "iterations": int(r["iterations"]), "edges_checked": int(r["n_edges_checked"]), "seconds": dt,
+                    "nodes_per_s": float(r["n_nodes"]) / dt, "nn_queries_per_s": 2.0 * float(r["iterations"]) / dt,
+                    "edges_per_s": float(r["n_edges_checked"]) / dt}
+    out["c5"] = {"workload": "C5: ONE RRT* tree over SE(2) on the C3 map to 100k nodes, maxConnectionDistance 1.0, goalBias 0.05, seed 7, "
+                 "occupancy validator, brute-force kNN in the loop", **c5}
+    ctx.close()
+    if not args.no_cpu_baseline:
+        ref = a.recv()
+        proc.join()
+        if isinstance(ref, Exception):
+            out["cpu_baseline_error"] = f"{type(ref).__name__}: {ref}"
+        else:
+            out["c1"]["cpu_baseline"] = {"ms": ref["c1"]["ms"], "cores": 1, "kind": "reference", "explored": ref["c1"]["explored"], "cost": ref["c1"]["cost"],
+                                         "matches": bool(ref["c1"]["explored"] == out["c1"]["explored"] and ref["c1"]["cost"] == out["c1"]["cost"])}
+            out["c2"]["cpu_baseline"] = {"ms": ref["c2"]["ms"], "cores": 1, "kind": "reference", "n_expanded": ref["c2"]["n_expanded"], "cost": ref["c2"]["cost"],
+                                         "matches": bool(ref["c2"]["n_expanded"] == out["c2"]["n_expanded"]
+                                                         and abs(ref["c2"]["cost"] - out["c2"]["cost"]) <= 1e-6 * abs(ref["c2"]["cost"])),
+                                         "note": "the reference searches its own brushfire field here (12 of 160000 Voronoi-distance cells differ from the device's)"}
+            out["solve_check"]["cpu_baseline"] = {"value": ref["solve_check"]["edges"] / ref["solve_check"]["seconds"], "unit": "edges/s", "cores": 1,
+                                                  "kind": "reference", "sample": "first 100000 pairs of the workload"}
+            out["rect_footprint"]["cpu_baseline"] = {"value": ref["rect"]["edges"] / ref["rect"]["seconds"], "unit": "edges/s", "cores": 1, "kind": "port",
+                                                     "sample": "first 20000 edges"}
+            for name in ("straight", "reeds_shepp"):
+                rc = ref["c5_" + name]
+                out["c5"][name]["cpu_baseline"] = {"nodes_per_s": rc["nodes"] / rc["seconds"], "iterations_per_s": rc["iterations"] / rc["seconds"],
+                                                   "cores": 1, "kind": "port", "sample": f"the same tree to {rc['nodes']} nodes (restated loop over the "
+                                                   "reference's sampler / connection / validator; O(n) brute-force neighbours like the device)"}
+    return out
+
+
 def ours_main(args):
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -676,6 +866,13 @@ def ours_main(args):
         except Exception as e:  # pragma: no cover
             hybrid = {"error": f"{type(e).__name__}: {e}"}
 
+    extras = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        try:
+            extras = extras_section(args, local_rank, stream)
+        except Exception as e:  # pragma: no cover
+            extras = {"error": f"{type(e).__name__}: {e}"}
+
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
@@ -713,6 +910,7 @@ def ours_main(args):
             "clocks": sampler.summary(),
             "serial": serial,
             "hybrid": hybrid,
+            "extras": extras,
         }
         _emit(line)
     if world > 1:
@@ -733,6 +931,8 @@ def main():
     ap.add_argument("--no-hybrid", action="store_true", help="skip the Hybrid A* (config C4) section of the JSON line")
     ap.add_argument("--hybrid-queries", type=int, default=4096)
     ap.add_argument("--cpu-plans-per-core", type=int, default=16)
+    ap.add_argument("--no-extras", action="store_true", help="skip the C1 / C2 / C5 / solve+check / rectangle objects of the JSON line")
+    ap.add_argument("--cpu-c5-nodes", type=int, default=20000, help="node budget of the CPU (restated) RRT* baseline")
     args = ap.parse_args()
     _stdout_to_stderr()
     if args.impl == "reference":

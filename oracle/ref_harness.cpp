@@ -1348,31 +1348,59 @@ int ref_rrtstar_se2_restated(void* hw /* null: free-space validator */, const do
 	std::vector<int> parent;
 	std::vector<double> costFromGoal;
 	std::equal_to<Pose2d> equal;
-	auto find = [&](const Pose2d& s) {
-		for (size_t i = 0; i < states.size(); i++)
-			if (equal(states[i], s))
-				return (int)i;
-		return -1;
+	// m_exploredNodeMap (utils/tree.h:127-129): the first node with an equal state.  A hash on the coordinate bits (-0.0
+	// folded onto +0.0, the heading through WrapTheta as equal_to<Pose2d> compares it) keeps the lookup O(1); collisions
+	// are resolved with the reference's equal_to.
+	auto wrap = [](double t) {
+		while (t > M_PI) t -= 2 * M_PI;
+		while (t < -M_PI) t += 2 * M_PI;
+		return t;
 	};
+	auto hashState = [&](const Pose2d& s) {
+		uint64_t h = 1469598103934665603ULL;
+		double v[3] = { s.x() + 0.0, s.y() + 0.0, wrap(s.theta) + 0.0 };
+		for (double d : v) {
+			uint64_t b;
+			memcpy(&b, &d, 8);
+			h = (h ^ b) * 1099511628211ULL;
+		}
+		return h;
+	};
+	std::unordered_multimap<uint64_t, int> index;
+	auto find = [&](const Pose2d& s) {
+		int best = -1;
+		auto range = index.equal_range(hashState(s));
+		for (auto it = range.first; it != range.second; ++it)
+			if (equal(states[it->second], s) && (best < 0 || it->second < best))
+				best = it->second;
+		return best;
+	};
+	// flann::L2_Simple over (x, y, theta), k nearest by (distance, insertion index): one pass with a sorted top-k list
 	auto knn = [&](const Pose2d& q, unsigned k) {
-		std::vector<std::pair<double, int>> all(states.size());
+		const size_t n = std::min<size_t>(k, states.size());
+		std::vector<std::pair<double, int>> best;
+		best.reserve(n + 1);
+		const double a[3] = { q.x(), q.y(), q.theta };
 		for (size_t i = 0; i < states.size(); i++) {
-			double a[3] = { q.x(), q.y(), q.theta }, b[3] = { states[i].x(), states[i].y(), states[i].theta };
+			const double b[3] = { states[i].x(), states[i].y(), states[i].theta };
 			double d = 0;
 			for (int c = 0; c < 3; c++) {
 				double diff = a[c] - b[c];
 				d += diff * diff;
 			}
-			all[i] = { d, (int)i };
+			if (best.size() == n && !(d < best.back().first))
+				continue; // a later index never displaces an equal distance
+			auto pos = std::upper_bound(best.begin(), best.end(), std::make_pair(d, (int)i));
+			best.insert(pos, { d, (int)i });
+			if (best.size() > n)
+				best.pop_back();
 		}
-		size_t n = std::min<size_t>(k, all.size());
-		std::partial_sort(all.begin(), all.begin() + n, all.end());
-		all.resize(n);
-		return all;
+		return best;
 	};
 	SeedRandom(seed);
 	auto t0 = std::chrono::steady_clock::now();
 	states.push_back(init);
+	index.emplace(hashState(init), 0);
 	parent.push_back(-1);
 	costFromGoal.push_back(0.0);
 	int count = -1, status = -1;
@@ -1413,6 +1441,7 @@ int ref_rrtstar_se2_restated(void* hw /* null: free-space validator */, const do
 		if (node < 0) {
 			node = (int)states.size();
 			states.push_back(newState);
+			index.emplace(hashState(newState), node);
 			parent.push_back(bestParent >= 0 ? bestParent : near[0].second);
 			costFromGoal.push_back(0.0);
 		}

@@ -205,7 +205,9 @@ struct Conn {
 };
 
 // PathConnection*::Connect(from, to), then Truncate(ratio) when `truncate` (SteerTowards, rrt.h:132-140)
-__device__ void connect(const RrtDev& P, const double* from, const double* to, bool truncate, double distance, Conn& c)
+// `pre`: the optimal segment when the caller has solved it cooperatively (rs_solve_warp / rs_solve_quad), else solved here
+__device__ void connect(const RrtDev& P, const double* from, const double* to, bool truncate, double distance, Conn& c,
+	const RSSolution* pre = nullptr)
 {
 	for (int i = 0; i < 3; i++)
 		c.from[i] = from[i];
@@ -231,7 +233,10 @@ __device__ void connect(const RrtDev& P, const double* from, const double* to, b
 	// PathConnectionReedsShepp::Connect (path_reeds_shepp.cpp:174-179), unit multipliers
 	Pose s = { from[0], from[1], from[2] }, g = { to[0], to[1], to[2] };
 	RSSolution sol;
-	rs_solve(s, g, P.rmin, 1.0f, 1.0f, 0.0f, 0, sol);
+	if (pre)
+		sol = *pre;
+	else
+		rs_solve(s, g, P.rmin, 1.0f, 1.0f, 0.0f, 0, sol);
 	c.seg = sol.seg;
 	c.length = sol.mLength * P.rmin;
 	// m_final = Interpolate(1.0)
@@ -408,10 +413,17 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 			// Tree::GetNearestNode(randomState)
 			cta_knn(W, size, P.dim, s_query, 1, s_nearIdx, s_nearD2, s_wd, s_wi, s_wo, &s_winner);
 			int nearest = -1;
+			RSSolution steerSol;
+			if (P.connection == 1 && threadIdx.x < 32) { // the 48 words of the steering connection on the lanes of warp 0
+				const double* f = W.coords + 3 * (size_t)s_nearIdx[0];
+				const Pose ps = { f[0], f[1], f[2] }, pg = { s_query[0], s_query[1], s_query[2] };
+				rs_solve_warp(ps, pg, P.rmin, 1.0f, 1.0f, 0.0f, steerSol);
+			}
 			if (threadIdx.x == 0) {
 				nearest = s_nearIdx[0];
 				Conn c;
-				connect(P, W.coords + 3 * (size_t)nearest, s_query, true, P.maxConnectionDistance, c); // SteerTowards
+				connect(P, W.coords + 3 * (size_t)nearest, s_query, true, P.maxConnectionDistance, c,
+					P.connection == 1 ? &steerSol : nullptr); // SteerTowards
 				nEdges++;
 				if (!conn_valid(P, map, c)) {
 					s_ctl = CTL_SKIP;
@@ -464,7 +476,38 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 			// RRT*: best parent among the nn nearest nodes of newState, rrt_star.h:84-97
 			const int nn = s_nn;
 			cta_knn(W, size, P.dim, s_new, nn, s_nearIdx, s_nearD2, s_wd, s_wi, s_wo, &s_winner);
-			if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
+			if (P.connection == 1) {
+				// candidate j on the quad of lanes 4j..4j+3 (rs_solve_quad: the 4 mirrored goals on the lanes, the 12 base
+				// formulas in a loop); lane 4j then builds and checks the connection
+				if (threadIdx.x < 4 * kRrtMaxK) {
+					const int j = (int)threadIdx.x >> 2;
+					const bool have = j < nn && s_nearIdx[j] >= 0;
+					const int node = have ? s_nearIdx[j] : 0;
+					const double* f = W.coords + 3 * (size_t)node;
+					const Pose ps = { f[0], f[1], f[2] }, pg = { s_new[0], s_new[1], s_new[2] };
+					int w;
+					double t, u, v;
+					rs_solve_quad(ps, pg, P.rmin, 1.0f, 1.0f, 0.0f, 0, w, t, u, v);
+					if (have && (threadIdx.x & 3) == 0) {
+						RSSolution sol;
+						sol.word = w;
+						if (w >= 0) {
+							sol.mLength = rs_build_segment(w, t, u, v, sol.seg);
+							sol.cost = 0.0f;
+						} else {
+							for (int m = 0; m < 5; m++)
+								sol.seg.len[m] = PPX_INF;
+							sol.seg.code = 0xAAAAA;
+							sol.mLength = 0.0;
+							sol.cost = __int_as_float(0x7f800000);
+						}
+						Conn c;
+						connect(P, f, s_new, false, 0.0, c, &sol); // SteerExactly
+						s_candCost[j] = W.cost[node] + c.length;
+						s_candValid[j] = conn_valid(P, map, c) ? 1 : 0;
+					}
+				}
+			} else if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
 				const int node = s_nearIdx[threadIdx.x];
 				Conn c;
 				connect(P, W.coords + 3 * (size_t)node, s_new, false, 0.0, c); // SteerExactly
