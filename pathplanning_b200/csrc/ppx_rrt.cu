@@ -103,17 +103,30 @@ __device__ void cta_knn(const RrtWs& W, int n, int dim, const double* query, int
 		bi[i] = 0x7fffffff;
 	}
 	double q[3] = { query[0], query[1], query[2] };
-	for (int j = threadIdx.x; j < n; j += blockDim.x) {
-		double d = state_dist2(q, W.coords + 3 * (size_t)j, dim);
-		if (nn_closer(d, j, bd[k - 1], bi[k - 1])) {
-			int p = k - 1;
-			while (p > 0 && nn_closer(d, j, bd[p - 1], bi[p - 1])) {
-				bd[p] = bd[p - 1];
-				bi[p] = bi[p - 1];
-				p--;
+	// four nodes per thread and turn: their coordinate loads are independent and in flight together (the scan is bound by
+	// L2 latency, not bandwidth, when every turn waits for its own load); candidates are taken in ascending index order
+	constexpr int kU = 4;
+	for (int j0 = threadIdx.x; j0 < n; j0 += kU * blockDim.x) {
+		double dd[kU];
+		#pragma unroll
+		for (int u = 0; u < kU; u++) {
+			const int j = j0 + u * (int)blockDim.x;
+			dd[u] = j < n ? state_dist2(q, W.coords + 3 * (size_t)j, dim) : PPX_INF;
+		}
+		#pragma unroll
+		for (int u = 0; u < kU; u++) {
+			const int j = j0 + u * (int)blockDim.x;
+			const double d = dd[u];
+			if (j < n && nn_closer(d, j, bd[k - 1], bi[k - 1])) {
+				int p = k - 1;
+				while (p > 0 && nn_closer(d, j, bd[p - 1], bi[p - 1])) {
+					bd[p] = bd[p - 1];
+					bi[p] = bi[p - 1];
+					p--;
+				}
+				bd[p] = d;
+				bi[p] = j;
 			}
-			bd[p] = d;
-			bi[p] = j;
 		}
 	}
 	int head = 0;
