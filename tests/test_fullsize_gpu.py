@@ -2,11 +2,16 @@
 fractions of these batches in seconds, the full batches in minutes):
 
 * C3, 1 M Reeds-Shepp edges: per-edge results do not depend on the batch they are in (permutation,
-  prefix), the FP32 cell filter changes no bit against the all-exact evaluation, a 50 k sample agrees
-  with the compiled reference, the verdict/sample checksums are those of the bench.
+  prefix), the FP32 cell filter changes no bit against the all-exact evaluation, and ALL 1 M edges are
+  solved and checked by the compiled reference, forked over the host cores (word, verdict, sample count,
+  last ratio).
 * C4, 4096 Hybrid A* queries: a query's record does not depend on the shard it is searched in
-  (what makes sharding by query over 1/2/4/8 GPUs result-neutral), a sample agrees with the reference.
+  (what makes sharding by query over 1/2/4/8 GPUs result-neutral), and the first 1024 queries are searched by
+  the reference on all host cores: status, expansion count and the CRC of the expansion sequence.
 """
+import multiprocessing as mp
+import os
+import zlib
 import numpy as np
 import pytest
 
@@ -16,6 +21,39 @@ from pathplanning_b200 import synth
 
 pytestmark = pytest.mark.gpu
 N = 1_000_000
+
+
+def _cores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def _fork_map(fn, chunks):
+    """fn(chunk) in one forked process per chunk (the reference keeps process-global state: RNG, logger)."""
+    ctxmp = mp.get_context("fork")
+    procs = []
+    for c in chunks:
+        a, b = ctxmp.Pipe(duplex=False)
+
+        def run(conn=b, chunk=c):
+            try:
+                conn.send(fn(chunk))
+            except Exception as e:  # pragma: no cover
+                conn.send(e)
+            conn.close()
+        p = ctxmp.Process(target=run)
+        p.start()
+        procs.append((p, a))
+    out = []
+    for p, a in procs:
+        r = a.recv()
+        p.join()
+        if isinstance(r, Exception):
+            raise r
+        out.append(r)
+    return out
 
 
 @pytest.fixture(scope="module")
@@ -54,18 +92,30 @@ def test_c3_full_batch_properties(ctx, c3_full, ref):
     # fused solve + check agrees with check-only on pre-solved edges
     r = ctx.connect_check_rs(s, g, pp.RSCostParams(2.0), vp)
     assert np.array_equal(r["valid"], v) and np.array_equal(r["last"].view(np.uint32), l.view(np.uint32))
-    # a 50 k sample against the compiled reference
+    # ALL edges against the compiled reference (Connect + IsPathValid), one process per host core
     cfg = synth.C3
     w = ref.World(cfg["lb"], cfg["ub"], cfg["resolution"])
     for rect in synth.config_rects(cfg):
         w.add_rectangle(*rect)
     w.update()
-    idx = np.random.default_rng(1).choice(N, 50000, replace=False)
-    rr = w.check_rs_edges(s[idx], g[idx], 2.0)
+    word = ctx.rs_solve(s, g, pp.RSCostParams(2.0))["word"]
+    k = _cores()
+    bounds = [(i * N // k, (i + 1) * N // k) for i in range(k)]
+
+    def part(b):
+        rr = w.check_rs_edges(s[b[0]:b[1]], g[b[0]:b[1]], 2.0)
+        return rr["valid"], rr["samples"].astype(np.int64), rr["last"], rr["word"]
+    parts = _fork_map(part, bounds)
     w.close()
-    assert np.array_equal(rr["valid"], v[idx])
-    assert np.array_equal(rr["samples"].astype(np.int64), ns[idx].astype(np.int64))
-    assert np.allclose(rr["last"], l[idx], rtol=1e-6, atol=0)
+    rv = np.concatenate([p[0] for p in parts])
+    rs_ = np.concatenate([p[1] for p in parts])
+    rl = np.concatenate([p[2] for p in parts])
+    rw = np.concatenate([p[3] for p in parts])
+    assert len(rv) == N
+    assert np.array_equal(rw, word)
+    assert np.array_equal(rv, v)
+    assert np.array_equal(rs_, ns.astype(np.int64))
+    assert np.allclose(rl, l, rtol=1e-6, atol=0)
 
 
 def test_c4_full_batch_is_shard_independent(ctx, ref):
@@ -89,6 +139,30 @@ def test_c4_full_batch_is_shard_independent(ctx, ref):
     planner = pp.HybridAStar(ctx, pp.HybridParams(), vp)
     full = planner.search(starts, goals, seeds)["results"]
     assert 0.8 < (full["status"] == 0).mean() < 1.0
+    # the first 1024 queries on the reference (same field: the reference's own grids were uploaded), all host cores
+    nref = 1024
+    logged = planner.search(starts[:nref], goals[:nref], seeds[:nref], max_log=12000)
+    assert logged["results"].tobytes() == full[:nref].tobytes()
+    k = _cores()
+
+    def part(c):
+        H = ref.Hybrid(w)
+        out = []
+        for i in range(c, nref, k):
+            r = H.search(starts[i], goals[i], int(seeds[i]))
+            out.append((i, r["status"], r["n_expanded"], zlib.crc32(np.ascontiguousarray(r["exp_keys"][:, :3], np.int32).tobytes())))
+        H.close()
+        return out
+    recs = sorted(x for p in _fork_map(part, list(range(k))) for x in p)
+    assert len(recs) == nref
+    bad = []
+    for i, st, nexp, crc in recs:
+        res = full[i]
+        good = int(res["status"]) == st and int(res["n_expanded"]) == nexp and nexp <= 12000
+        good = good and zlib.crc32(np.ascontiguousarray(logged["log"][i]["key"][:nexp], np.int32).tobytes()) == crc
+        if not good:
+            bad.append(i)
+    assert not bad, f"{len(bad)} of {nref} queries expand differently from the reference: {bad[:10]}"
     # shards of 8 "GPUs", searched one after the other on this one: identical records
     for r in (0, 3, 7):
         lo, hi = r * nq // 8, (r + 1) * nq // 8
