@@ -274,6 +274,31 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def gpu_numa_affinity(index, apply=True):
+    """Binds this process to the CPUs local to GPU `index` (sysfs local_cpulist of its PCI function) so that pinned host
+    buffers are first-touched on the GPU's NUMA node.  Returns the node number, or None when the box does not say."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(index)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bdf}"
+        node = int(open(base + "/numa_node").read().strip())
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if apply and cpus and node >= 0:
+            os.sched_setaffinity(0, cpus)
+        return node
+    except Exception:
+        return None
+
+
 def c4_queries(ctx, pp, n, seed=12345):
     """BASELINE config C4: n (start, goal) pairs uniform in +-18.5 m with uniform heading, rejection-sampled with
     IsStateValid on the C2 map; query q uses RNG seed 1000 + q."""
@@ -822,6 +847,38 @@ def ours_main(args):
                   "what": "the same loop with strictly serial launches (option off): every launch waits for the last sample "
                           "chain of the previous one"}
 
+    # Host side of the e2e figure: pin this rank to the CPUs local to its GPU before the pinned buffers are allocated
+    # (first touch places them on that NUMA node), then measure what the box gives: H2D bandwidth of rank 0 alone and of all
+    # ranks at once -- the ceiling of the host-buffer call, which moves 72 B per edge over PCIe.
+    numa = gpu_numa_affinity(local_rank, apply=world > 1)  # at N = 1 the CPU baselines below use every host core
+    pcie = None
+    if True:
+        hb = torch.empty(72_000_000, dtype=torch.uint8).pin_memory()
+        db = torch.empty(72_000_000, dtype=torch.uint8, device=dev)
+
+        def h2d_gbs(reps=5):
+            db.copy_(hb, non_blocking=True)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                db.copy_(hb, non_blocking=True)
+            torch.cuda.synchronize()
+            return reps * hb.numel() / (time.perf_counter() - t0) / 1e9
+        barrier()
+        alone = h2d_gbs() if rank == 0 else 0.0
+        barrier()
+        together = h2d_gbs()
+        tt = torch.tensor([together, -together, together], dtype=torch.float64, device=dev)
+        if world > 1:
+            tmin = tt[1:2].clone()
+            dist.all_reduce(tmin, op=dist.ReduceOp.MAX)
+            tsum = tt[2:3].clone()
+            dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+            tt = torch.stack([tt[0], tmin[0], tsum[0]])
+        pcie = {"h2d_gbs_rank0_alone": alone, "h2d_gbs_all_ranks_min": float(-tt[1].item()), "h2d_gbs_all_ranks_sum": float(tt[2].item()),
+                "numa_node_rank0": numa, "e2e_ceiling_edges_per_s": float(tt[2].item()) * 1e9 / 72.0,
+                "note": "pinned 72 MB copies; the e2e call cannot exceed sum / 72 B per edge"}
+        del hb, db
     # e2e: the host-buffer C-ABI call a reference-side caller makes (pinned host memory)
     if args.mode == "check":
         h_in = [d_edges[b].cpu().pin_memory() for b in range(2)]
@@ -905,7 +962,7 @@ def ours_main(args):
             "map_build": {"ms": map_build_ms, "cells": int(rows * cols),
                           "what": "ppx_map_build host call: H2D occupancy + device EDT + derived grids + D2H distance map"},
             "e2e": {"value": e2e_value, "unit": "edges/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps},
+                    "steps": e2e_steps, "pcie": pcie},
             "gpu_launches": launches,
             "clocks": sampler.summary(),
             "serial": serial,
