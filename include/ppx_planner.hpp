@@ -11,11 +11,15 @@
 //   Planner::PathReedsShepp / PathConnectionReedsShepp   paths/path_reeds_shepp.h:8-54
 //   Planner::ObstaclesHeuristic           algo/heuristics.h:47-78
 //   Planner::HybridAStar                  algo/hybrid_a_star.h:215-263
+//   Planner::NonHolonomicHeuristic        algo/heuristics.h:9-40
+//   Planner::AStarN2 / BidirectionalAStarN2  algo/a_star_n2.h:29-42
+//   Planner::Tree / RRTR2 / RRTStarR2 / RRTStarSE2  utils/tree.h:27-177, algo/rrt.h:30-155, algo/rrt_star.h:29-181
 // Batch entry points (names ending in Batch) are the additions the device makes worthwhile; the
 // scalar methods keep the reference's signatures and run a batch of one.
 // There is NO CPU fallback: constructing a Device without a CUDA device throws.
 #pragma once
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <cstdint>
 #include <limits>
@@ -693,6 +697,304 @@ private:
 	std::vector<GridCellPosition> m_path;
 	double m_cost = std::numeric_limits<double>::infinity();
 	int m_numExplored = 0;
+};
+
+// BidirectionalAStarN2 (algo/a_star_n2.h:36-42, algo/bidirectional_a_star.h:41-204) and AStarN2 with a functor of the
+// device's table (ppx_astar_params): the reference's std::function callbacks cannot cross the C ABI.
+enum class GridMetric { Euclidean = 0, Manhattan = 1, Octile = 2, ZeroOrCellCost = 3 };
+
+class BidirectionalAStarN2 {
+public:
+	bool Initialize(const Ref<OccupancyMap>& map, GridMetric pathCost = GridMetric::Euclidean, GridMetric heuristic = GridMetric::Euclidean,
+		std::vector<float> cellCost = {})
+	{
+		if (!map)
+			return isInitialized = false;
+		m_map = map;
+		m_cost = pathCost;
+		m_heur = heuristic;
+		m_cellCost = std::move(cellCost);
+		return isInitialized = true;
+	}
+	void SetInitState(const GridCellPosition& s) { m_init = s; }
+	void SetGoalState(const GridCellPosition& s) { m_goal = s; }
+	Status SearchPath()
+	{
+		if (!isInitialized)
+			return Status::Failure;
+		if (m_map->Dirty())
+			m_map->Update();
+		const int maxPath = 8192;
+		const int32_t s[2] = { m_init.row, m_init.col }, g[2] = { m_goal.row, m_goal.col };
+		std::vector<int32_t> cells((size_t)maxPath * 2);
+		ppx_astar_params prm {};
+		prm.cost_kind = (int32_t)m_cost;
+		prm.heuristic_kind = (int32_t)m_heur;
+		prm.cell_cost = m_cellCost.empty() ? nullptr : m_cellCost.data();
+		prm.bidirectional = 1;
+		ppx_astar_result res {};
+		auto& dev = m_map->GetDevice();
+		dev->Check(ppx_astar_n2_ex(dev->Context(), 1, s, g, &prm, 0, maxPath, &res, cells.data()));
+		m_path.clear();
+		for (int k = 0; k < std::min(res.path_len, maxPath); k++)
+			m_path.push_back({ cells[2 * k], cells[2 * k + 1] });
+		m_optimalCost = res.cost;
+		m_numExplored = res.n_explored;
+		return res.status == 0 ? Status::Success : Status::Failure;
+	}
+	std::vector<GridCellPosition> GetPath() const { return m_path; }
+	double GetOptimalCost() const { return m_optimalCost; }
+	int GetNumExploredStates() const { return m_numExplored; } // forward + reverse explored maps
+	bool isInitialized = false;
+
+private:
+	Ref<OccupancyMap> m_map;
+	GridMetric m_cost = GridMetric::Euclidean, m_heur = GridMetric::Euclidean;
+	std::vector<float> m_cellCost;
+	GridCellPosition m_init, m_goal;
+	std::vector<GridCellPosition> m_path;
+	double m_optimalCost = std::numeric_limits<double>::infinity();
+	int m_numExplored = 0;
+};
+
+// NonHolonomicHeuristic (algo/heuristics.h:9-40, heuristics.cpp:7-95): the Reeds-Shepp cost table over (x, y, theta), built
+// on the device by ppx_hybrid_create; GetHeuristicValue is the table lookup of :78-95 (negative heading indices read
+// index + numAngular).
+class NonHolonomicHeuristic {
+public:
+	static Ref<NonHolonomicHeuristic> Build(const Ref<OccupancyMap>& map, double spatialResolution = 1.0, double angularResolution = 0.0872,
+		double minTurningRadius = 2.0, double reverseCostMultiplier = 1.0, double forwardCostMultiplier = 1.0,
+		double directionSwitchingCost = 0.0)
+	{
+		auto h = Ref<NonHolonomicHeuristic>(new NonHolonomicHeuristic());
+		h->m_map = map;
+		if (map->Dirty())
+			map->Update();
+		ppx_hybrid_params hp {};
+		hp.wheelbase = 2.6;
+		hp.min_turning_radius = minTurningRadius;
+		hp.direction_switching_cost = directionSwitchingCost;
+		hp.reverse_cost_multiplier = reverseCostMultiplier;
+		hp.forward_cost_multiplier = forwardCostMultiplier;
+		hp.voronoi_cost_multiplier = 1.0;
+		hp.num_generated_motion = 5;
+		hp.spatial_resolution = spatialResolution;
+		hp.angular_resolution = angularResolution;
+		ppx_validator_params vp { 1.0f, 0.1f };
+		auto& dev = map->GetDevice();
+		dev->Check(ppx_hybrid_create(dev->Context(), &hp, &vp, &h->m_handle));
+		int32_t dims[3];
+		double off[2];
+		dev->Check(ppx_hybrid_table(h->m_handle, dims, off, nullptr));
+		h->numSpatialX = (unsigned)dims[0];
+		h->numSpatialY = (unsigned)dims[1];
+		h->numAngular = (unsigned)dims[2];
+		h->offsetX = off[0];
+		h->offsetY = off[1];
+		return h;
+	}
+	~NonHolonomicHeuristic()
+	{
+		if (m_handle)
+			ppx_hybrid_destroy(m_handle);
+	}
+	void SetGoal(const Pose2d& goal) { m_goal = goal; }
+	double GetHeuristicValue(const Pose2d& state) { return GetHeuristicValues({ state })[0]; }
+	std::vector<double> GetHeuristicValues(const std::vector<Pose2d>& states)
+	{
+		std::vector<double> p(3 * states.size()), out(states.size());
+		for (size_t i = 0; i < states.size(); i++) {
+			p[3 * i] = states[i].x();
+			p[3 * i + 1] = states[i].y();
+			p[3 * i + 2] = states[i].theta;
+		}
+		const double g[3] = { m_goal.x(), m_goal.y(), m_goal.theta };
+		auto& dev = m_map->GetDevice();
+		dev->Check(ppx_hybrid_heuristic(m_handle, g, (int64_t)states.size(), p.data(), nullptr, out.data(), nullptr));
+		return out;
+	}
+	/// m_values[i][j][k], row-major
+	std::vector<double> GetTable()
+	{
+		std::vector<double> v((size_t)numSpatialX * numSpatialY * numAngular);
+		m_map->GetDevice()->Check(ppx_hybrid_table(m_handle, nullptr, nullptr, v.data()));
+		return v;
+	}
+	unsigned numSpatialX = 0, numSpatialY = 0, numAngular = 0;
+	double offsetX = 0, offsetY = 0;
+
+private:
+	NonHolonomicHeuristic() = default;
+	Ref<OccupancyMap> m_map;
+	ppx_hybrid* m_handle = nullptr;
+	Pose2d m_goal;
+};
+
+// Tree<Vertex, Dim> (utils/tree.h:27-177), the nearest-neighbour and bookkeeping part: nodes are indices in insertion
+// order (flann's point order), Extend refuses an existing state like :127-129, the queries are exact brute-force k-NN on
+// the device (ppx_knn, replaces flann::Index<L2_Simple<double>>, ties to the lower index).
+template <int Dim>
+class Tree {
+public:
+	using State = std::array<double, Dim>;
+	explicit Tree(const Ref<Device>& dev) : m_dev(dev) { }
+	void Clear()
+	{
+		m_points.clear();
+		m_parent.clear();
+	}
+	int CreateRootNode(const State& s)
+	{
+		Clear();
+		return Append(s, -1);
+	}
+	/// node index of the new node, or of the existing node with an equal state (whose parent is left unchanged)
+	int Extend(const State& s, int parent)
+	{
+		for (size_t i = 0; i < m_parent.size(); i++)
+			if (std::equal(s.begin(), s.end(), m_points.begin() + i * Dim))
+				return (int)i;
+		return Append(s, parent);
+	}
+	int Size() const { return (int)m_parent.size(); }
+	int GetParent(int node) const { return m_parent[node]; }
+	State GetState(int node) const
+	{
+		State s;
+		std::copy(m_points.begin() + (size_t)node * Dim, m_points.begin() + (size_t)(node + 1) * Dim, s.begin());
+		return s;
+	}
+	int GetNearestNode(const State& s) const { return GetNearestNodes(s, 1)[0]; }
+	std::vector<int> GetNearestNodes(const State& s, unsigned int nn) const
+	{
+		std::vector<int32_t> idx(nn);
+		m_dev->Check(ppx_knn(m_dev->Context(), Dim, Size(), m_points.data(), 1, s.data(), (int32_t)nn, idx.data(), nullptr));
+		std::vector<int> out;
+		for (auto i : idx)
+			if (i >= 0)
+				out.push_back(i);
+		return out;
+	}
+
+private:
+	int Append(const State& s, int parent)
+	{
+		m_points.insert(m_points.end(), s.begin(), s.end());
+		m_parent.push_back(parent);
+		return Size() - 1;
+	}
+	Ref<Device> m_dev;
+	std::vector<double> m_points;
+	std::vector<int> m_parent;
+};
+
+// RRT / RRTStar (algo/rrt.h:30-152, algo/rrt_star.h:29-178): the whole loop runs on the device (ppx_rrt_run), one tree per
+// call here; the reference's template parameters collapse to the state kinds it instantiates or sketches -- R^2 with
+// straight connections (RRTR2 / RRTStarR2) and SE(2) with straight or Reeds-Shepp connections (rrt_star.h:181).
+struct RRTParameters { // rrt.h:12-21
+	unsigned int maxIteration = 100, maxNumberTreeNode = 10000;
+	double maxConnectionDistance = 0.1, goalBias = 0.05;
+};
+struct RRTStarParameters { // rrt_star.h:12-21
+	unsigned int maxIteration = 10000, maxNumberTreeNode = 10000;
+	double maxConnectionDistance = 0.1, goalBias = 0.05;
+};
+
+class RRTBase {
+public:
+	/// free space: bounds only (StateValidatorFree); with a validator: its map (StateValidatorOccupancyMap, SE(2) only)
+	RRTBase(const Ref<Device>& dev, const Pose2d& lb, const Pose2d& ub, int dim, bool star, bool reedsShepp, double minTurningRadius,
+		const Ref<StateValidatorOccupancyMap>& validator) :
+		m_dev(dev), m_lb(lb), m_ub(ub), m_dim(dim), m_star(star), m_rs(reedsShepp), m_rmin(minTurningRadius), m_validator(validator) { }
+	void SetInitState(const Pose2d& s) { m_init = s; }
+	void SetGoalState(const Pose2d& s) { m_goal = s; }
+	uint64_t seed = 0; // the reference draws from an unseeded process-global engine (utils/random.h:14-16)
+	Status SearchPath()
+	{
+		ppx_rrt_params p {};
+		p.dim = m_dim;
+		p.connection = m_rs ? 1 : 0;
+		p.star = m_star ? 1 : 0;
+		p.validator = m_validator ? 1 : 0;
+		p.max_iteration = m_maxIteration;
+		p.max_nodes = m_maxNodes;
+		p.max_connection_distance = m_maxConnectionDistance;
+		p.goal_bias = m_goalBias;
+		p.min_turning_radius = m_rmin;
+		p.lb[0] = m_lb.x(); p.lb[1] = m_lb.y(); p.lb[2] = m_lb.theta;
+		p.ub[0] = m_ub.x(); p.ub[1] = m_ub.y(); p.ub[2] = m_ub.theta;
+		ppx_validator_params vp { 1.0f, 0.1f };
+		if (m_validator) {
+			vp.min_safe_radius = m_validator->minSafeRadius;
+			vp.min_path_interpolation_distance = m_validator->minPathInterpolationDistance;
+		}
+		const double s[3] = { m_init.x(), m_init.y(), m_init.theta }, g[3] = { m_goal.x(), m_goal.y(), m_goal.theta };
+		const int64_t cap = (int64_t)m_maxNodes + 2;
+		std::vector<double> nodes((size_t)cap * 3);
+		std::vector<int32_t> parents((size_t)cap);
+		m_dev->Check(ppx_rrt_run(m_dev->Context(), &p, m_validator ? &vp : nullptr, 1, s, g, &seed, &m_result, cap, nodes.data(), parents.data(),
+			nullptr));
+		m_path.clear();
+		if (m_result.status == 0 && m_result.solution >= 0) { // GetPath, rrt.h:96-113: the chain root .. solution node
+			for (int n = m_result.solution; n >= 0; n = parents[n])
+				m_path.insert(m_path.begin(), Pose2d(nodes[3 * (size_t)n], nodes[3 * (size_t)n + 1], nodes[3 * (size_t)n + 2]));
+		}
+		return m_result.status == 0 ? Status::Success : Status::Failure;
+	}
+	std::vector<Pose2d> GetPath() const { return m_path; }
+	const ppx_rrt_result& GetRecord() const { return m_result; }
+
+protected:
+	unsigned int m_maxIteration = 100, m_maxNodes = 10000;
+	double m_maxConnectionDistance = 0.1, m_goalBias = 0.05;
+
+private:
+	Ref<Device> m_dev;
+	Pose2d m_lb, m_ub, m_init, m_goal;
+	int m_dim;
+	bool m_star, m_rs;
+	double m_rmin;
+	Ref<StateValidatorOccupancyMap> m_validator;
+	ppx_rrt_result m_result {};
+	std::vector<Pose2d> m_path;
+};
+
+class RRTR2 : public RRTBase { // rrt.h:154
+public:
+	RRTR2(const Ref<Device>& dev, const Pose2d& lb, const Pose2d& ub) : RRTBase(dev, lb, ub, 2, false, false, 1.0, nullptr) { }
+	void SetParameters(const RRTParameters& p)
+	{
+		m_maxIteration = p.maxIteration; m_maxNodes = p.maxNumberTreeNode;
+		m_maxConnectionDistance = p.maxConnectionDistance; m_goalBias = p.goalBias;
+	}
+};
+
+class RRTStarR2 : public RRTBase { // rrt_star.h:180
+public:
+	RRTStarR2(const Ref<Device>& dev, const Pose2d& lb, const Pose2d& ub) : RRTBase(dev, lb, ub, 2, true, false, 1.0, nullptr)
+	{
+		SetParameters(RRTStarParameters());
+	}
+	void SetParameters(const RRTStarParameters& p)
+	{
+		m_maxIteration = p.maxIteration; m_maxNodes = p.maxNumberTreeNode;
+		m_maxConnectionDistance = p.maxConnectionDistance; m_goalBias = p.goalBias;
+	}
+};
+
+class RRTStarSE2 : public RRTBase { // rrt_star.h:181 (commented out upstream: it does not compile there)
+public:
+	RRTStarSE2(const Ref<Device>& dev, const Pose2d& lb, const Pose2d& ub, const Ref<StateValidatorOccupancyMap>& validator,
+		bool reedsShepp = true, double minTurningRadius = 1.0) :
+		RRTBase(dev, lb, ub, 3, true, reedsShepp, minTurningRadius, validator)
+	{
+		SetParameters(RRTStarParameters());
+	}
+	void SetParameters(const RRTStarParameters& p)
+	{
+		m_maxIteration = p.maxIteration; m_maxNodes = p.maxNumberTreeNode;
+		m_maxConnectionDistance = p.maxConnectionDistance; m_goalBias = p.goalBias;
+	}
 };
 
 } // namespace Planner

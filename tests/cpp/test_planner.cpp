@@ -173,6 +173,54 @@ void TestValidator(const Ref<Device>& dev)
 
 }
 
+namespace Planner {
+
+// planner/tests/test_rrt.cpp:9-38 and test_rrt_star.cpp:10-39: free space [0,5]^2, (0,0) -> (2,2); the reference asserts the
+// end points within 1.0 (and can fail by chance on its unseeded RNG: here the seed is fixed); test_tree.cpp:91-130.
+void TestRRTAndTree(const Ref<Device>& dev)
+{
+	Tree<2> tree(dev);
+	int a = tree.CreateRootNode({ 0.0, 0.0 });
+	int b = tree.Extend({ 1.0, 0.0 }, a);
+	int c = tree.Extend({ 2.0, 0.0 }, b);
+	int d = tree.Extend({ 3.0, 0.0 }, c);
+	CHECK(tree.Size() == 4 && tree.Extend({ 2.0, 0.0 }, a) == c && tree.GetParent(c) == b);
+	CHECK(tree.GetNearestNode({ 1.2, 0.0 }) == b);
+	auto near = tree.GetNearestNodes({ 2.6, 0.0 }, 2);
+	CHECK(near.size() == 2 && ((near[0] == d && near[1] == c) || (near[0] == c && near[1] == d)));
+	for (int star = 0; star < 2; star++) {
+		Pose2d lb(0, 0, 0), ub(5, 5, 0);
+		Status st;
+		std::vector<Pose2d> path;
+		if (star) {
+			RRTStarR2 rrt(dev, lb, ub);
+			RRTStarParameters p;
+			p.maxIteration = 20000;
+			rrt.SetParameters(p);
+			rrt.seed = 31;
+			rrt.SetInitState(Pose2d(0, 0, 0));
+			rrt.SetGoalState(Pose2d(2, 2, 0));
+			st = rrt.SearchPath();
+			path = rrt.GetPath();
+		} else {
+			RRTR2 rrt(dev, lb, ub);
+			RRTParameters p;
+			p.maxIteration = 20000;
+			rrt.SetParameters(p);
+			rrt.seed = 31;
+			rrt.SetInitState(Pose2d(0, 0, 0));
+			rrt.SetGoalState(Pose2d(2, 2, 0));
+			st = rrt.SearchPath();
+			path = rrt.GetPath();
+		}
+		CHECK(st == Status::Success && path.size() >= 2);
+		CHECK(std::hypot(path.front().x(), path.front().y()) < 1.0);
+		CHECK(std::hypot(path.back().x() - 2.0, path.back().y() - 2.0) < 1.0);
+	}
+}
+
+}
+
 int main()
 {
 	auto dev = std::make_shared<Planner::Device>(0);
@@ -181,6 +229,7 @@ int main()
 	Planner::TestReedsShepp(dev, Planner::Pose2d(0, 0, 0), Planner::Pose2d(0.1, 1.5, M_PI));
 	Planner::TestValidator(dev);
 	Planner::TestHybridAStar(dev);
+	Planner::TestRRTAndTree(dev);
 	std::printf("test_planner: all checks passed\n");
 	return 0;
 }
