@@ -325,7 +325,7 @@ def hybrid_section(args, rank, world, local_rank, stream):
     from pathplanning_b200 import synth
     from pathplanning_b200.lib import ppx, HybridLimitsC
     from pathplanning_b200.api import HYBRID_RESULT
-    from pathplanning_b200.shard import shard_indices, gather_records
+    from pathplanning_b200.shard import shard_indices
     dev = torch.device("cuda", local_rank)
     ctx = pp.Context(local_rank)
     ctx.set_stream(stream.cuda_stream)
@@ -386,18 +386,43 @@ def hybrid_section(args, rank, world, local_rank, stream):
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     same_as_timed = bool(out["results"].tobytes() == local.tobytes())
-    # gather of the fixed-size records: the only collective of the path
+    # gather of the fixed-size records: the only collective of the path.  Through the C ABI (ppx_comm_gather_results: NCCL
+    # on the context's stream, device buffers in, device buffer out, uneven shards); the NCCL id travels over
+    # torch.distributed's store.  One D2H copy of the gathered records afterwards.
     gather_ms = 0.0
     allres = local if world == 1 else None
     if world > 1:
+        uid = [None]
+        if rank == 0:
+            buf = (ctypes.c_char * 128)()
+            assert ppx.ppx_comm_unique_id(buf) == 0
+            uid[0] = bytes(buf)
+        dist.broadcast_object_list(uid, src=0)
+        rc = ppx.ppx_comm_init(ctx.handle, (ctypes.c_char * 128).from_buffer_copy(uid[0]), rank, world)
+        assert rc == 0, ppx.ppx_last_error(ctx.handle)
+        d_all = torch.zeros(nq * HYBRID_RESULT.itemsize, dtype=torch.uint8, device=dev)
+        counts = (ctypes.c_int64 * world)()
+
+        def gather():
+            rc = ppx.ppx_comm_gather_results(ctx.handle, d_res.data_ptr(), m, HYBRID_RESULT.itemsize, d_all.data_ptr(), nq, counts)
+            assert rc == 0, ppx.ppx_last_error(ctx.handle)
+        gather()  # warm-up of the collective
         torch.cuda.synchronize()
-        gather_records(local, nq, device=dev, indices=mine)  # warm-up of the collective
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record()
-        allres = gather_records(local, nq, device=dev, indices=mine)
-        g1.record()
+        g0.record(stream)
+        gather()
+        g1.record(stream)
         torch.cuda.synchronize()
         gather_ms = g0.elapsed_time(g1)
+        flat = d_all.cpu().numpy().view(HYBRID_RESULT)
+        # rank order, interleaved shards: rank r's k-th record is query r + k * world
+        allres = np.empty(nq, HYBRID_RESULT)
+        off = 0
+        for r in range(world):
+            allres[r::world] = flat[off:off + counts[r]]
+            off += counts[r]
+        assert off == nq
+        ppx.ppx_comm_destroy(ctx.handle)
     solved, expanded = int((allres["status"] == 0).sum()), int(allres["n_expanded"].sum())
     section = {
         "metric": "batched Hybrid A* plans/s", "workload": f"C4: {nq} independent start/goal queries on the C2 parking lot (400x400 @0.1m), "
