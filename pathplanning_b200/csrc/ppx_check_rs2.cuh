@@ -409,145 +409,10 @@ __global__ void __launch_bounds__(kThreads, kSolve ? 3 : kCheck2Ctas) k_check_rs
 				break;
 			continue;
 		}
-		// ---- T. tail of the launch: no edge left to hand out and at most four lanes still sampling, typically long chains
-		// that skim an obstacle with less slack than minStep -- their steps are then exactly minStep.  Eight lanes serve one
-		// such chain: lane h of the group evaluates the sample h minStep-steps ahead (the same double accumulation the owner
-		// would do), the eight clearance loads are in flight together, and the group accepts the longest prefix of samples
-		// whose predecessors' steps really were minStep.  Same samples, same order, same arithmetic as one per iteration.
-		if (!kAudit && exhausted && qcount == 0 && __popc(running) <= 4) {
-			const int g = (int)lane_id >> 3, h = (int)lane_id & 7;
-			const int nAct = __popc(running);
-			const int owner = g < nAct ? (int)__fns(running, 0, g + 1) : 0;
-			const int oslot = __shfl_sync(0xffffffffu, slot, owner);
-			const int om = __shfl_sync(0xffffffffu, m, owner);
-			const double olen = __shfl_sync(0xffffffffu, length, owner);
-			const double olast = __shfl_sync(0xffffffffu, lastValidLength, owner);
-			const unsigned ons = __shfl_sync(0xffffffffu, ns, owner);
-			const uint32_t* orec = S.q[oslot];
-			const double pathLength = __hiloint2double((int)orec[1], (int)orec[0]);
-			double myLen = olen;
-			for (int i = 0; i < h; i++)
-				myLen += (double)minStep;
-			// code: 0 certified valid (delta), 1 certified invalid, 2 not certified, 3 beyond the end of the path / no owner
-			int code = 3;
-			float delta = 0.0f;
-			int mm = om;
-			if (g < nAct && myLen < pathLength) {
-				const uint32_t cw = orec[22];
-				const int nm = (int)((cw >> 20) & 7u);
-				const float sf = (float)myLen;
-				while (mm + 1 < nm && sf > __uint_as_float(orec[5 + 4 * (mm + 1)]))
-					mm++;
-				const float kx = __uint_as_float(orec[2 + 4 * mm]), ky = __uint_as_float(orec[3 + 4 * mm]);
-				const float thK = __uint_as_float(orec[4 + 4 * mm]);
-				const float rem = (float)(myLen - (double)__uint_as_float(orec[5 + 4 * mm]));
-				const int st = (cw >> (4 * mm)) & 3, dr = (cw >> (4 * mm + 2)) & 3;
-				const bool straight = st == 1;
-				const float sgnAdv = dr == 1 ? -1.0f : 1.0f, sgnTurn = st == 2 ? -1.0f : 1.0f;
-				const float adv = sgnAdv * rem;
-				const float a = adv * inv_r * sgnTurn;
-				const float phi = 0.5f * a;
-				const float ang = fast_wrap(straight ? thK : thK + phi);
-				const float chord = (2.0f * rc) * PPX_FSIN(sgnTurn * phi);
-				const float Lc = straight ? adv * fm.inv_res : chord;
-				const float px = kx + Lc * PPX_FCOS(ang), py = ky + Lc * PPX_FSIN(ang);
-				const int rowb = (int)(short)(orec[23] & 0xffffu), colb = (int)(short)(orec[23] >> 16);
-				const float fx = floorf(px), fy = floorf(py);
-				const float gx = px - fx, gy = py - fy;
-				const bool near = fminf(gx, gy) < kCellEps || fmaxf(gx, gy) > 1.0f - kCellEps;
-				const int row = rowb + (int)fx, col = colb + (int)fy;
-				const int ib = imin(imin(row - fm.rb0, fm.rb1 - row), imin(col - fm.cb0, fm.cb1 - col));
-				code = 2;
-				if (!near && ib >= 0) {
-					const float d = PPX_LDG(map.clearance + (size_t)row * map.cols + col);
-					if (!(d >= minSafeRadius))
-						code = 1;
-					else {
-						delta = d - minSafeRadius;
-						if (delta <= (float)ib * map.res)
-							code = 0;
-					}
-				}
-			}
-			// sample h is reached iff every earlier sample of the group was certified valid with a step of exactly minStep
-			const bool chains = code == 0 && !(minStep < delta); // std::max(delta, minStep) == minStep
-			const unsigned grpMask = 0xffu << (8 * g);
-			const unsigned chainBits = (__ballot_sync(0xffffffffu, chains) & grpMask) >> (8 * g);
-			const int reach = __ffs(~chainBits & 0xffu) - 1; // first sample that does not chain on (0..7), -1 if all eight do
-			const int stop = reach < 0 ? 8 : reach; // samples 0 .. stop - 1 are accepted with step minStep; sample `stop` decides
-			// the deciding sample's outcome, broadcast from its lane
-			const int dl = 8 * g + (stop < 8 ? stop : 7);
-			const int dcode = __shfl_sync(0xffffffffu, code, dl);
-			const float ddelta = __shfl_sync(0xffffffffu, delta, dl);
-			const double dlen = __shfl_sync(0xffffffffu, myLen, dl);
-			const int dm = __shfl_sync(0xffffffffu, mm, dl);
-			const double prevLen = __shfl_sync(0xffffffffu, myLen, 8 * g + (stop > 0 ? stop - 1 : 0));
-			// the owner lane takes the result of its group: g = its rank among the active lanes
-			if (state == LANE_ACTIVE) {
-				const int myG = __popc(running & lt_mask);
-				const int srcLane = 8 * myG; // any lane of the group holds the broadcast values; read the leader's
-				(void)srcLane;
-			}
-			// every lane of group g holds the group's outcome; hand it to the owner through shared registers: the owner is
-			// lane `owner`, which sits in SOME group -- so write it with a shuffle keyed by the owner's own rank
-			const int myRank = __popc(running & lt_mask);
-			const int from = 8 * (state == LANE_ACTIVE ? myRank : 0);
-			const int fStop = __shfl_sync(0xffffffffu, stop, from);
-			const int fCode = __shfl_sync(0xffffffffu, dcode, from);
-			const float fDelta = __shfl_sync(0xffffffffu, ddelta, from);
-			const double fLen = __shfl_sync(0xffffffffu, dlen, from);
-			const int fM = __shfl_sync(0xffffffffu, dm, from);
-			const double fPrev = __shfl_sync(0xffffffffu, prevLen, from);
-			if (state == LANE_ACTIVE) {
-				const double myPath = __hiloint2double((int)rec[1], (int)rec[0]);
-				bool finished = false, verdict = false;
-				float lastOut = 1.0f;
-				if (fStop > 0)
-					lastValidLength = fPrev; // the last accepted sample
-				ns += (unsigned)fStop;
-				if (fStop == 8) { // all eight chained: the next sample is one more minStep on
-					length = fPrev + (double)minStep;
-					m = fM;
-					if (!(length < myPath)) {
-						finished = true;
-						verdict = true;
-					}
-				} else if (fCode == 3) { // the chain ran past the end of the path: valid
-					length = fLen;
-					finished = true;
-					verdict = true;
-				} else if (fCode == 1) { // the deciding sample is in collision
-					ns++;
-					finished = true;
-					verdict = false;
-					lastOut = lastValidLength == 0.0 ? 0.0f : (float)(lastValidLength / myPath);
-				} else if (fCode == 0) { // valid with a longer step
-					ns++;
-					lastValidLength = fLen;
-					length = fLen + (double)std_maxf(fDelta, minStep);
-					m = fM;
-					if (!(length < myPath)) {
-						finished = true;
-						verdict = true;
-					}
-				} else { // not certified: the exact path evaluates this very sample
-					length = fLen;
-					m = fM;
-					state = LANE_PARKED;
-				}
-				if (finished) {
-					const int64_t idx = (int64_t)rec[24];
-					valid[idx] = verdict ? 1 : 0;
-					last[idx] = lastOut;
-					if (samples)
-						samples[idx] = ns;
-					state = LANE_IDLE;
-				}
-			}
-			(void)olast;
-			(void)ons;
-			continue;
-		}
+		// (A cooperative tail -- eight lanes evaluating the next eight minStep-spaced samples of one remaining chain together,
+		// accepting the prefix whose steps really were minStep -- was built and measured: identical results, 255 instead of
+		// 192 us per 1M edges.  Long chains skim obstacles with a slack of 0.1-0.3 m, i.e. steps just ABOVE minStep, so the
+		// prediction rarely holds and every tail iteration pays the extra shuffles.  Removed.)
 		// ---- D. one sample per active lane
 		if (state == LANE_ACTIVE) {
 			const double pathLength = __hiloint2double((int)rec[1], (int)rec[0]);
