@@ -78,23 +78,85 @@ __device__ void cta_bitonic_sort(unsigned long long* keys, uint32_t* cells, uint
 	}
 }
 
-// Rank by counting for small buckets: rank_i = #{k : key_k < key_i} (keys are unique).
-__device__ void cta_rank_sort(const unsigned long long* inKeys, const uint32_t* inCells, uint32_t L,
-	unsigned long long* outKeys, uint32_t* outCells)
+// Pop order of a bucket of up to sortCap / 4 entries.  Every warp sorts runs of 64 entries in registers (bitonic network
+// over shuffles, two entries per lane, straight from the ring in global memory), then every entry finds its rank: its
+// position in its own run plus, for every other run, the number of smaller keys there (binary search; keys are unique).
+// O(L (log 64)^2 / 32 + L (L / 64) log 64) against the O(L^2) of ranking by counting, which was 58% of the kernel's
+// instructions (profiles/r2k_k_wavefront_4096goals_ncu_full_summary.csv).  Padding keys are ~0: they sort to the end of
+// the last run and are never counted.
+__device__ void cta_run_merge_sort(const unsigned long long* gk, const uint32_t* gc, uint32_t L,
+	unsigned long long* runKeys, uint32_t* runCells, unsigned long long* outKeys, uint32_t* outCells)
 {
+	const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+	const uint32_t nruns = (L + 63) >> 6;
+	unsigned long long* dstK = nruns == 1 ? outKeys : runKeys;
+	uint32_t* dstC = nruns == 1 ? outCells : runCells;
+	for (uint32_t run = warp; run < nruns; run += nwarps) {
+		const uint32_t base = run << 6, i0 = base + 2 * lane;
+		// entry e = 2 * lane + t of the run; the ring slot is a multiple of 1024 entries long: the vector loads stay inside
+		const ulonglong2 kk = ((const ulonglong2*)gk)[(base >> 1) + lane];
+		const uint2 cc = ((const uint2*)gc)[(base >> 1) + lane];
+		unsigned long long k0 = i0 < L ? kk.x : ~0ull, k1 = i0 + 1 < L ? kk.y : ~0ull;
+		uint32_t c0 = cc.x, c1 = cc.y;
+		#pragma unroll
+		for (int k = 2; k <= 64; k <<= 1) {
+			const bool asc = ((2 * lane) & k) == 0; // k = 2: bit 1 of e is bit 0 of the lane; k = 64: always ascending
+			#pragma unroll
+			for (int j = k >> 1; j > 0; j >>= 1) {
+				if (j == 1) {
+					if ((k0 > k1) == asc) {
+						const unsigned long long tk = k0;
+						k0 = k1;
+						k1 = tk;
+						const uint32_t tc = c0;
+						c0 = c1;
+						c1 = tc;
+					}
+				} else {
+					const int pl = j >> 1;
+					const unsigned long long o0 = __shfl_xor_sync(0xffffffffu, k0, pl), o1 = __shfl_xor_sync(0xffffffffu, k1, pl);
+					const uint32_t oc0 = __shfl_xor_sync(0xffffffffu, c0, pl), oc1 = __shfl_xor_sync(0xffffffffu, c1, pl);
+					const bool keepMin = ((lane & pl) == 0) == asc;
+					if (keepMin ? o0 < k0 : o0 > k0) {
+						k0 = o0;
+						c0 = oc0;
+					}
+					if (keepMin ? o1 < k1 : o1 > k1) {
+						k1 = o1;
+						c1 = oc1;
+					}
+				}
+			}
+		}
+		((ulonglong2*)dstK)[(base >> 1) + lane] = make_ulonglong2(k0, k1);
+		((uint2*)dstC)[(base >> 1) + lane] = make_uint2(c0, c1);
+	}
+	__syncthreads();
+	if (nruns == 1)
+		return;
 	for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
-		unsigned long long mine = inKeys[i];
-		uint32_t rank = 0;
-		for (uint32_t k = 0; k < L; k++)
-			rank += inKeys[k] < mine ? 1u : 0u;
+		const unsigned long long mine = runKeys[i];
+		const uint32_t own = i >> 6;
+		uint32_t rank = i & 63u;
+		for (uint32_t r = 0; r < nruns; r++) {
+			if (r == own)
+				continue;
+			const unsigned long long* R = runKeys + (r << 6);
+			uint32_t cnt = 0;
+			#pragma unroll
+			for (uint32_t s = 32; s > 0; s >>= 1)
+				cnt += R[cnt + s - 1] < mine ? s : 0u;
+			cnt += R[cnt] < mine ? 1u : 0u;
+			rank += cnt;
+		}
 		outKeys[rank] = mine;
-		outCells[rank] = inCells[i];
+		outCells[rank] = runCells[i];
 	}
 	__syncthreads();
 }
 
 // Exclusive prefix sum of one value per thread over the CTA; returns the exclusive prefix and the
-// CTA total through *total.  s_warp must hold 32 entries.
+// CTA total through *total.  s_warp must hold 32 entries.  The caller must pass a barrier before the next call.
 __device__ uint32_t cta_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t* total)
 {
 	const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -123,17 +185,15 @@ __device__ uint32_t cta_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t* t
 			*total = wi;
 	}
 	__syncthreads();
-	uint32_t out = s_warp[warp] + incl - v;
-	__syncthreads(); // s_warp may be reused by the caller right away
-	return out;
+	return s_warp[warp] + incl - v; // s_warp / *total are rewritten by the next call only: the caller has a barrier before it
 }
 
 // One goal per CTA at a time; CTAs take goals from a global cursor.
-__global__ void k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_t nGoals, const double* __restrict__ goals,
+__global__ void __launch_bounds__(1024) k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_t nGoals, const double* __restrict__ goals,
 	float* __restrict__ costOut, uint8_t* __restrict__ exploredOut, WfWork work, uint32_t sortCap,
 	unsigned long long* __restrict__ queue, int* __restrict__ status)
 {
-	extern __shared__ unsigned long long s_dyn[];
+	extern __shared__ __align__(16) unsigned long long s_dyn[];
 	unsigned long long* s_keys = s_dyn; // [sortCap]
 	unsigned long long* s_keys2 = s_dyn + sortCap; // [sortCap/4] scratch for the rank sort input
 	uint32_t* s_cells = (uint32_t*)(s_dyn + sortCap + sortCap / 4); // [sortCap]
@@ -209,13 +269,8 @@ __global__ void k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_
 			// ---- 1. pop order of the frozen bucket -------------------------------------------------
 			const unsigned long long* sk;
 			const uint32_t* sc;
-			if (L <= sortCap / 4 && L <= 2 * blockDim.x) {
-				for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
-					s_keys2[i] = gk[i];
-					s_cells2[i] = gc[i];
-				}
-				__syncthreads();
-				cta_rank_sort(s_keys2, s_cells2, L, s_keys, s_cells);
+			if (L <= sortCap / 4) {
+				cta_run_merge_sort(gk, gc, L, s_keys2, s_cells2, s_keys, s_cells);
 				sk = s_keys;
 				sc = s_cells;
 			} else {
@@ -266,6 +321,7 @@ __global__ void k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_
 			__syncthreads();
 			// ---- 3. winners ------------------------------------------------------------------------
 			uint32_t wins = 0;
+			unsigned long long wonMask = 0ull; // bit 8 * (rank - first) + j for the first eight parents of the thread
 			for (uint32_t rank = first; rank < lastp; rank++) {
 				const uint32_t cell = sc[rank];
 				const int r = (int)(cell >> 16), c = (int)(cell & 0xffffu);
@@ -274,7 +330,10 @@ __global__ void k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_
 					const int rr = r + c_dr[j], cc = c + c_dc[j];
 					if (rr < 0 || rr >= rows || cc < 0 || cc >= cols)
 						continue;
-					wins += tag[(size_t)rr * cols + cc] == claim_key(rank, j) ? 1u : 0u;
+					const bool won = tag[(size_t)rr * cols + cc] == claim_key(rank, j);
+					wins += won ? 1u : 0u;
+					if (won && rank - first < 8)
+						wonMask |= 1ull << (8 * (rank - first) + j);
 				}
 			}
 			uint32_t seq = counter + cta_exclusive_scan(wins, s_warp, &s_total);
@@ -283,13 +342,19 @@ __global__ void k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_
 				const uint32_t cell = sc[rank];
 				const int r = (int)(cell >> 16), c = (int)(cell & 0xffffu);
 				const float parentCost = __uint_as_float((uint32_t)(sk[rank] >> 32));
+				const bool cached = rank - first < 8;
+				const uint32_t bits = cached ? (uint32_t)(wonMask >> (8 * (rank - first))) & 0xffu : 0xffu;
+				if (bits == 0)
+					continue;
 				#pragma unroll
 				for (int j = 0; j < 8; j++) {
+					if (!((bits >> j) & 1u))
+						continue;
 					const int rr = r + c_dr[j], cc = c + c_dc[j];
 					if (rr < 0 || rr >= rows || cc < 0 || cc >= cols)
 						continue;
 					const size_t ni = (size_t)rr * cols + cc;
-					if (tag[ni] != claim_key(rank, j))
+					if (!cached && tag[ni] != claim_key(rank, j))
 						continue;
 					const float w = (c_dr[j] == 0 || c_dc[j] == 0) ? 1.0f : sqrt2;
 					const float pathCost = w + parentCost;
@@ -308,14 +373,13 @@ __global__ void k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_
 				}
 			}
 			__syncthreads();
+			// slot b is appended to again in step b + 2 at the earliest (bucket b + 4): barriers in between
 			if (threadIdx.x == 0)
 				s_cnt[slot] = 0;
 			pending = pending - L + total;
 			counter += total;
 			b++;
-			const int err = s_err;
-			__syncthreads();
-			if (err) {
+			if (s_err) { // written before the barrier above; the next write is behind the barriers of the next step
 				pending = 0;
 				if (threadIdx.x == 0)
 					atomicExch(status, 1);
