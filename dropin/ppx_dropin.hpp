@@ -9,6 +9,10 @@
 //                                                                ppx_check_edges_{rs,csteer} (state_validator_occupancy_map.cpp:15-71)
 //   PpxHybridAStar : HybridAStar                                 Initialize / SearchPath / GetPath / GetStats / GetGraphSearch* ->
 //                                                                ppx_hybrid_{create,search,resample}, ppx_smoother_* (hybrid_a_star.cpp:206-304)
+//   PpxObstaclesHeuristic : ObstaclesHeuristic                   Update -> ppx_wavefront into the reference's own m_cost / m_explored
+//                                                                (heuristics.cpp:106-153); GetHeuristicValue is the reference's
+//   PpxBuildNonHolonomicHeuristic(...)                           NonHolonomicHeuristic::Build (heuristics.cpp:36-76) with the table
+//                                                                computed by ppx_hybrid_create and copied into m_values
 // With `-include ppx_dropin.hpp -DPPX_DROPIN_SUBSTITUTE` in front of an UNMODIFIED reference translation unit (the
 // pybind11 module interfaces/python/src/pyplanning.cpp, planner/tests/test_hybrid_a_star.cpp, main.cpp) the identifiers
 // HybridAStar and StateValidatorOccupancyMap in that unit name the adapters: the reference's own binding / test code then
@@ -22,6 +26,7 @@
 #include <vector>
 
 #include "core/base.h"
+#include "algo/heuristics.h"
 #include "algo/hybrid_a_star.h"
 #include "algo/smoother.h"
 #include "geometry/2dplane.h"
@@ -35,6 +40,7 @@
 #include "state_validator/obstacle_list_occupancy_map.h"
 #include "state_validator/occupancy_map.h"
 #include "state_validator/state_validator_occupancy_map.h"
+#include "utils/make_ref_enabler.h"
 
 #include "ppx.h"
 
@@ -195,6 +201,68 @@ private:
 	Ref<StateSpaceSE2> m_space;
 	bool m_synced = false;
 };
+
+// ObstaclesHeuristic with the wavefront on the device.  The world model must be on the device (the validator adapter's
+// Sync, or PpxUploadWorld): the wavefront reads the occupancy grid of the context.
+class PpxObstaclesHeuristic : public ObstaclesHeuristic {
+public:
+	PpxObstaclesHeuristic(const Ref<OccupancyMap>& map, double reverseCostMultiplier, double forwardCostMultiplier) :
+		ObstaclesHeuristic(map, reverseCostMultiplier, forwardCostMultiplier) { }
+
+	// heuristics.cpp:106-153: every cell infinity / unexplored, then the cost-to-go wavefront from the goal's cell
+	void Update(const Pose2d& goal)
+	{
+		const double g[3] = { goal.x(), goal.y(), goal.theta };
+		const size_t cells = (size_t)m_cost.rows * m_cost.columns;
+		std::vector<uint8_t> explored(cells);
+		PpxDevice::Check(ppx_wavefront(PpxDevice::Ctx(), 1, g, m_cost.m_data, explored.data()), "ppx_wavefront");
+		for (size_t i = 0; i < cells; i++)
+			m_explored.m_data[i] = explored[i] != 0;
+	}
+};
+
+// NonHolonomicHeuristic::Build with the 41 x 41 x 73-style table of Reeds-Shepp costs computed on the device.  The table
+// belongs to the bounds of the world model on the device (ppx_hybrid_create reads them): they must be the `bounds` given here.
+inline Ref<NonHolonomicHeuristic> PpxBuildNonHolonomicHeuristic(const std::array<Pose2d, 2>& bounds, double spatialResolution,
+	double angularResolution, double minTurningRadius, double reverseCostMultiplier, double forwardCostMultiplier,
+	double directionSwitchingCost)
+{
+	unsigned int nx = ceil((bounds[1].x() - bounds[0].x()) / spatialResolution);
+	if (nx % 2 == 0)
+		nx++;
+	unsigned int ny = ceil((bounds[1].y() - bounds[0].y()) / spatialResolution);
+	if (ny % 2 == 0)
+		ny++;
+	Ref<NonHolonomicHeuristic> heuristic = makeRef<MakeRefEnabler<NonHolonomicHeuristic>>(spatialResolution, angularResolution,
+		minTurningRadius, reverseCostMultiplier, forwardCostMultiplier, directionSwitchingCost, nx, ny);
+	ppx_hybrid_params hp {};
+	hp.wheelbase = 2.6; // not used by the table
+	hp.min_turning_radius = minTurningRadius;
+	hp.direction_switching_cost = directionSwitchingCost;
+	hp.reverse_cost_multiplier = reverseCostMultiplier;
+	hp.forward_cost_multiplier = forwardCostMultiplier;
+	hp.voronoi_cost_multiplier = 0.0;
+	hp.num_generated_motion = 5;
+	hp.spatial_resolution = spatialResolution;
+	hp.angular_resolution = angularResolution;
+	ppx_validator_params vp { 1.0f, 0.1f };
+	ppx_hybrid* h = nullptr;
+	PpxDevice::Check(ppx_hybrid_create(PpxDevice::Ctx(), &hp, &vp, &h), "ppx_hybrid_create");
+	int32_t dims[3];
+	double offsets[2];
+	PpxDevice::Check(ppx_hybrid_table(h, dims, offsets, nullptr), "ppx_hybrid_table");
+	if ((unsigned)dims[0] != heuristic->numSpatialX || (unsigned)dims[1] != heuristic->numSpatialY || (unsigned)dims[2] != heuristic->numAngular) {
+		ppx_hybrid_destroy(h);
+		throw std::runtime_error("libppx: the world model on the device has other bounds than the heuristic asked for");
+	}
+	std::vector<double> values((size_t)dims[0] * dims[1] * dims[2]);
+	PpxDevice::Check(ppx_hybrid_table(h, dims, offsets, values.data()), "ppx_hybrid_table");
+	for (int i = 0; i < dims[0]; i++)
+		for (int j = 0; j < dims[1]; j++)
+			std::memcpy(heuristic->m_values[i][j], &values[((size_t)i * dims[1] + j) * dims[2]], sizeof(double) * dims[2]);
+	ppx_hybrid_destroy(h);
+	return heuristic;
+}
 
 class PpxHybridAStar : public HybridAStar {
 public:

@@ -3,6 +3,7 @@
 #include "ppx_dropin.hpp"
 #include "models/kinematic_bicycle_model.h"
 #include <cstdio>
+#include <cstring>
 #include <random>
 
 using namespace Planner;
@@ -65,5 +66,32 @@ int main()
 	for (size_t i = 0; i < batch.size() && i < got.size(); i++)
 		bad += (got[i] != 0) != (want[i] != 0) || std::fabs(gotLast[i] - wantLast[i]) > 1e-6f * std::fmax(1.0f, std::fabs(wantLast[i]));
 	std::printf("drop-in validator: 300 states, 600 paths (%d valid), single + batch: %d differences\n", nvalid, bad);
-	return bad ? 1 : 0;
+	// heuristic adapters against the reference's own classes on the same world
+	int badH = 0;
+	{
+		ObstaclesHeuristic refObs(map, 1.0, 1.0);
+		PpxObstaclesHeuristic gpuObs(map, 1.0, 1.0);
+		for (int t = 0; t < 3; t++) {
+			Pose2d goal(U(rng), U(rng), A(rng));
+			refObs.Update(goal);
+			gpuObs.Update(goal);
+			for (int r = 0; r < map->Rows(); r++)
+				for (int c = 0; c < map->Columns(); c++)
+					badH += std::memcmp(&refObs.m_cost[r][c], &gpuObs.m_cost[r][c], sizeof(float)) != 0
+						|| refObs.m_explored[r][c] != gpuObs.m_explored[r][c];
+		}
+		auto refNh = NonHolonomicHeuristic::Build(bounds, 1.0, 2 * M_PI / 72, 2.0, 1.0, 1.0, 0.0);
+		auto gpuNh = PpxBuildNonHolonomicHeuristic(bounds, 1.0, 2 * M_PI / 72, 2.0, 1.0, 1.0, 0.0);
+		double worst = 0.0;
+		for (unsigned i = 0; i < refNh->numSpatialX; i++)
+			for (unsigned j = 0; j < refNh->numSpatialY; j++)
+				for (unsigned k = 0; k < refNh->numAngular; k++) {
+					const double a = refNh->m_values[i][j][k], b = gpuNh->m_values[i][j][k];
+					worst = std::fmax(worst, std::fabs(a - b) / std::fmax(1.0, std::fabs(a)));
+				}
+		badH += worst > 1e-6;
+		std::printf("drop-in heuristics: 3 wavefronts (%d x %d cells, float bits), table %u x %u x %u (worst relative difference %.3g): %d differences\n",
+			map->Rows(), map->Columns(), refNh->numSpatialX, refNh->numSpatialY, refNh->numAngular, worst, badH);
+	}
+	return bad || badH ? 1 : 0;
 }

@@ -926,8 +926,11 @@ PPX_HD void rs_solve(const Pose& start, const Pose& goal, double r, float rev, f
 // order -- the same formula on all 32 lanes at the same time, so the warp does not diverge on the formula switch -- and the
 // quad takes the lexicographic minimum of (float cost, word), which is the reference's "first strict minimum in enum
 // order" (word = base * 4 + mirror).  All four lanes of a quad return the pair's solution.  Must be called converged.
-__device__ __forceinline__ void rs_solve_quad(const Pose& start, const Pose& goal, double r, float rev, float fwd, float sw,
-	int shortest, int& outWord, double& ot, double& ou, double& ov)
+// rs_quad_part: the same over the base formulas baseFirst, baseFirst + baseStep, ... < 12 only, returning the quad's partial
+// minimum (bestWord = 64: none) -- several warps can share the 12 formulas of a pair and combine their parts by the same
+// lexicographic rule (k_rrt: one base formula per warp).
+__device__ __forceinline__ void rs_quad_part(const Pose& start, const Pose& goal, double r, float rev, float fwd, float sw,
+	int shortest, int baseFirst, int baseStep, float& bestCost, double& bestLen, int& bestWord, double& bt, double& bu, double& bv)
 {
 	const int q = (int)(threadIdx.x & 3);
 	double dx = goal.x - start.x, dy = goal.y - start.y;
@@ -958,12 +961,12 @@ __device__ __forceinline__ void rs_solve_quad(const Pose& start, const Pose& goa
 	a.phi = PPX_ATAN2(a.eta, a.xi);
 	b.phi = PPX_ATAN2(b.eta, b.xi);
 	const float INF = __int_as_float(0x7f800000);
-	float bestCost = INF; // GetOptimalPath: float cost; GetShortestPath: the double length (kept in bestLen)
-	double bestLen = PPX_INF;
-	int bestWord = 64;
-	double bt = 0, bu = 0, bv = 0;
+	bestCost = INF; // GetOptimalPath: float cost; GetShortestPath: the double length (kept in bestLen)
+	bestLen = PPX_INF;
+	bestWord = 64;
+	bt = 0, bu = 0, bv = 0;
 	#pragma unroll 1
-	for (int base = 0; base < 12; base++) {
+	for (int base = baseFirst; base < 12; base += baseStep) {
 		double t = 0, u = 0, v = 0;
 		const double length = rs_motion_lengths(base, a, b, t, u, v);
 		const int word = base * 4 + q;
@@ -1000,6 +1003,15 @@ __device__ __forceinline__ void rs_solve_quad(const Pose& start, const Pose& goa
 			bt = t2; bu = u2; bv = v2;
 		}
 	}
+}
+
+__device__ __forceinline__ void rs_solve_quad(const Pose& start, const Pose& goal, double r, float rev, float fwd, float sw,
+	int shortest, int& outWord, double& ot, double& ou, double& ov)
+{
+	float bestCost;
+	double bestLen, bt, bu, bv;
+	int bestWord;
+	rs_quad_part(start, goal, r, rev, fwd, sw, shortest, 0, 1, bestCost, bestLen, bestWord, bt, bu, bv);
 	outWord = bestWord < 48 ? bestWord : -1;
 	ot = bt; ou = bu; ov = bv;
 }

@@ -1,22 +1,35 @@
 // libppx.so: RRT and RRT* (A11) with the brute-force nearest-neighbour scan (A10) in the loop,
-// one tree per CTA, batched over trees (algo/rrt.h:55-95, algo/rrt_star.h:53-112, utils/tree.h).
+// one tree per thread-block CLUSTER, batched over trees (algo/rrt.h:55-95, algo/rrt_star.h:53-112, utils/tree.h).
 //
-// A tree is a chain of dependent iterations, each dominated by one or two nearest-neighbour
-// queries over all current nodes.  The CTA's 256 threads scan the node array in parallel (exact
-// FP64 squared distances, ties to the lower insertion index like the oracle's flann stand-in) and
-// merge with a k-round block argmin; the RRT* parent candidates (k <= 16 Reeds-Shepp connections +
-// collision checks) are evaluated one per thread; the scalar control flow -- RNG draws, steering,
-// duplicate-state rule, goal test -- runs on thread 0 in the reference's statement order.
+// A tree is a chain of dependent iterations, each dominated by one or two nearest-neighbour queries over all current
+// nodes.  The scalar control flow -- RNG draws, steering, duplicate-state rule, goal test -- runs on thread 0 of the
+// cluster's CTA 0 in the reference's statement order; the RRT* parent candidates (k <= 16 connections + collision
+// checks) are evaluated on that CTA's threads.  The scans are the part that grows with the tree, and they are spread
+// over the cluster (1, 2, 4, 8 or 16 CTAs = SMs, by how many trees there are to fill the GPU with):
+//   * node i belongs to CTA (i / 256) % C; every CTA keeps the coordinates of its nodes in its own shared memory
+//     (SoA, up to 200 KB: 136 k nodes for C = 16), so a scan never leaves the SM -- one CTA scanning 100 k nodes out of
+//     L2 was bound by the load latency of a single SM (41 us per scan, profiles/r2l_*);
+//   * CTA 0 publishes a command (query, k, tree size, the node appended since the last command) in its shared memory;
+//     after a cluster barrier every CTA reads it through DSMEM, appends the node if it owns it, scans its slice (exact
+//     FP64 squared distances, ties to the lower insertion index like the oracle's flann stand-in), merges the
+//     per-thread candidate lists by warp shuffles and publishes its k best; after a second cluster barrier CTA 0
+//     gathers the C lists through DSMEM and merges them.  Two cluster barriers (~0.2 us each) per query.
+// Trees too large for the slices are scanned from global memory with the same partition.
 // Independent trees (different seeds / queries) fill the other SMs.
 #include <algorithm>
+#include <cooperative_groups.h>
 #include "ppx_ctx.h"
 
 using namespace ppx;
+namespace cg = cooperative_groups;
 
 namespace {
 
 constexpr int kRrtThreads = 256;
+constexpr int kRrtWarps = kRrtThreads / 32;
 constexpr int kRrtMaxK = 16;
+constexpr int kRrtMaxCluster = 16;
+constexpr int kNoNode = 0x7fffffff;
 
 struct RrtDev {
 	int dim, connection, star, validator;
@@ -92,80 +105,367 @@ __device__ __forceinline__ double state_dist2(const double* a, const double* b, 
 	return r;
 }
 
-// k nearest nodes of `query` among nodes [0, n): results (ascending) into s_idx / s_d2 [k].
-__device__ void cta_knn(const RrtWs& W, int n, int dim, const double* query, int k, int* s_idx, double* s_d2,
-	double* s_wd, int* s_wi, int* s_wo, int* s_winner)
+struct NnEntry { // a neighbour candidate: squared distance and node index (kNoNode: none)
+	double d;
+	int idx;
+	int pad;
+};
+
+enum { OP_SCAN = 0, OP_EXIT = 1, OP_SELECT = 2 };
+constexpr int kCandCap = 64; // candidates per CTA of a threshold selection (overflow: the list scan answers the query)
+
+struct RrtCmd { // CTA 0's command to its cluster, read by the other CTAs through DSMEM after the cluster barrier
+	int op, k, n; // n: tree size the scan covers
+	int newIdx; // node appended since the last command (-1: none); its owner stores it in its slice
+	double q[3], newState[3];
+};
+
+struct RrtSlice { // the cluster's partition of the node coordinates: node i -> CTA (i >> 8) % C, local slot ((i >> 8) / C) << 8 | i & 255
+	double *x, *y, *th; // shared memory of this CTA (SoA) or null: scan W.coords in global memory
+	int rank, C;
+};
+
+struct RrtXch { // exchange areas in shared memory
+	NnEntry warpList[kRrtWarps][kRrtMaxK];
+	NnEntry ctaList[kRrtMaxK]; // read by CTA 0 through DSMEM
+	NnEntry gather[kRrtMaxCluster][kRrtMaxK]; // CTA 0 only
+	// threshold selection (cta_select_*): per-warp minima and the candidates under the threshold, read through DSMEM
+	NnEntry warpMin[kRrtWarps];
+	NnEntry allMin[kRrtMaxCluster * kRrtWarps];
+	NnEntry cand[kCandCap];
+	NnEntry thr;
+	int candCount;
+};
+
+// Warp-wide minimum of (d, idx) under nn_closer; every lane gets it.
+__device__ __forceinline__ void warp_nn_min(double& d, int& idx)
 {
-	double bd[kRrtMaxK];
-	int bi[kRrtMaxK];
-	for (int i = 0; i < k; i++) {
-		bd[i] = PPX_INF;
-		bi[i] = 0x7fffffff;
-	}
-	double q[3] = { query[0], query[1], query[2] };
-	// four nodes per thread and turn: their coordinate loads are independent and in flight together (the scan is bound by
-	// L2 latency, not bandwidth, when every turn waits for its own load); candidates are taken in ascending index order
-	constexpr int kU = 4;
-	for (int j0 = threadIdx.x; j0 < n; j0 += kU * blockDim.x) {
-		double dd[kU];
-		#pragma unroll
-		for (int u = 0; u < kU; u++) {
-			const int j = j0 + u * (int)blockDim.x;
-			dd[u] = j < n ? state_dist2(q, W.coords + 3 * (size_t)j, dim) : PPX_INF;
-		}
-		#pragma unroll
-		for (int u = 0; u < kU; u++) {
-			const int j = j0 + u * (int)blockDim.x;
-			const double d = dd[u];
-			if (j < n && nn_closer(d, j, bd[k - 1], bi[k - 1])) {
-				int p = k - 1;
-				while (p > 0 && nn_closer(d, j, bd[p - 1], bi[p - 1])) {
-					bd[p] = bd[p - 1];
-					bi[p] = bi[p - 1];
-					p--;
-				}
-				bd[p] = d;
-				bi[p] = j;
-			}
+	#pragma unroll
+	for (int o = 16; o > 0; o >>= 1) {
+		const double od = __shfl_xor_sync(0xffffffffu, d, o);
+		const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+		if (nn_closer(od, oi, d, idx)) {
+			d = od;
+			idx = oi;
 		}
 	}
+}
+
+// Merge of up to 32 ascending lists (one per lane, `mine` = this lane's list or null) into out[0..k): k rounds of a warp
+// minimum over the list heads; node indices are unique, so exactly the owner of the minimum advances.
+__device__ __forceinline__ void warp_merge_lists(const NnEntry* mine, int k, NnEntry* out)
+{
 	int head = 0;
 	for (int round = 0; round < k; round++) {
-		double d = head < k ? bd[head] : PPX_INF;
-		int idx = head < k ? bi[head] : 0x7fffffff;
-		int owner = threadIdx.x;
+		const bool have = mine && head < k;
+		const double hd = have ? mine[head].d : PPX_INF;
+		const int hi = have ? mine[head].idx : kNoNode;
+		double d = hd;
+		int idx = hi;
+		warp_nn_min(d, idx);
+		if (idx == hi && hi != kNoNode)
+			head++;
+		if ((threadIdx.x & 31) == 0) {
+			out[round].d = d;
+			out[round].idx = idx;
+		}
+	}
+}
+
+// This CTA's part of a neighbour query: scan the nodes it owns among [0, n), k best (ascending) into X.ctaList.
+// K >= k is the length of the per-thread candidate list: a compile-time constant, so the list is registers with static
+// indexing (sorted insertion = one pass of compare-and-swap with a carried element; pop = shift).  With a run-time
+// length the list sat in local memory and one insertion cost ~1 us of dependent L1 round trips -- the part of an
+// iteration that grew with the tree.  Ends without a barrier: the caller's cluster barrier publishes the list.
+template <int K>
+__device__ void cta_scan_slice(const RrtWs& W, const RrtSlice& S, int n, int dim, const double* query, int k, RrtXch& X)
+{
+	double bd[K];
+	int bi[K];
+	#pragma unroll
+	for (int i = 0; i < K; i++) {
+		bd[i] = PPX_INF;
+		bi[i] = kNoNode;
+	}
+	const double q0 = query[0], q1 = query[1], q2 = query[2];
+	auto offer = [&](double d, int j) {
+		if (!nn_closer(d, j, bd[K - 1], bi[K - 1]))
+			return;
 		#pragma unroll
-		for (int o = 16; o > 0; o >>= 1) {
-			double od = __shfl_down_sync(0xffffffffu, d, o);
-			int oi = __shfl_down_sync(0xffffffffu, idx, o);
-			int oo = __shfl_down_sync(0xffffffffu, owner, o);
-			if (nn_closer(od, oi, d, idx)) {
-				d = od;
-				idx = oi;
-				owner = oo;
+		for (int i = 0; i < K; i++) {
+			if (nn_closer(d, j, bd[i], bi[i])) {
+				const double td = bd[i];
+				const int ti = bi[i];
+				bd[i] = d;
+				bi[i] = j;
+				d = td;
+				j = ti;
 			}
 		}
-		if ((threadIdx.x & 31) == 0) {
-			s_wd[threadIdx.x >> 5] = d;
-			s_wi[threadIdx.x >> 5] = idx;
-			s_wo[threadIdx.x >> 5] = owner;
+	};
+	// flann::L2_Simple over the first `dim` raw coordinates, in its accumulation order
+	auto dist2 = [&](double x, double y, double th) {
+		const double dx = q0 - x, dy = q1 - y;
+		double r = 0.0;
+		r += dx * dx;
+		r += dy * dy;
+		if (dim == 3) {
+			const double dt = q2 - th;
+			r += dt * dt;
 		}
-		__syncthreads();
+		return r;
+	};
+	const int stride = S.C << 8; // node index distance between two blocks of this CTA
+	if (S.x) {
+		int local = threadIdx.x;
+		for (int j = (S.rank << 8) + (int)threadIdx.x; j < n; j += stride, local += 256)
+			offer(dist2(S.x[local], S.y[local], S.th[local]), j);
+	} else {
+		// four nodes per thread and turn: their coordinate loads are independent and in flight together
+		constexpr int kU = 4;
+		for (int j0 = (S.rank << 8) + (int)threadIdx.x; j0 < n; j0 += kU * stride) {
+			double dd[kU];
+			#pragma unroll
+			for (int u = 0; u < kU; u++) {
+				const int j = j0 + u * stride;
+				const double* c = W.coords + 3 * (size_t)j;
+				dd[u] = j < n ? dist2(c[0], c[1], c[2]) : PPX_INF;
+			}
+			#pragma unroll
+			for (int u = 0; u < kU; u++) {
+				const int j = j0 + u * stride;
+				if (j < n)
+					offer(dd[u], j);
+			}
+		}
+	}
+	// the 32 lists of a warp -> one list per warp -> the CTA's list
+	{
+		NnEntry* out = X.warpList[threadIdx.x >> 5];
+		for (int round = 0; round < k; round++) {
+			double d = bd[0];
+			int idx = bi[0];
+			warp_nn_min(d, idx);
+			if (idx == bi[0] && idx != kNoNode) { // node indices are unique: only the owner pops
+				#pragma unroll
+				for (int i = 0; i + 1 < K; i++) {
+					bd[i] = bd[i + 1];
+					bi[i] = bi[i + 1];
+				}
+				bd[K - 1] = PPX_INF;
+				bi[K - 1] = kNoNode;
+			}
+			if ((threadIdx.x & 31) == 0) {
+				out[round].d = d;
+				out[round].idx = idx;
+			}
+		}
+	}
+	__syncthreads();
+	if (threadIdx.x < 32)
+		warp_merge_lists(threadIdx.x < kRrtWarps ? X.warpList[threadIdx.x] : nullptr, k, X.ctaList);
+}
+
+// Threshold selection, the fast form of a k-nearest query for clusters of >= 4 CTAs (>= 32 warps >= 2 k):
+//   pass 1  every warp publishes the nearest node of its threads' nodes (8 * C distinct nodes);
+//   ------  cluster barrier; every CTA reads the 8 * C minima and takes their k-th smallest as threshold T: the k nearest
+//           nodes overall are certainly not farther than T;
+//   pass 2  every thread appends its nodes that are not farther than T to its CTA's candidate list (typically k ... 2 k
+//           candidates in the whole cluster);
+//   ------  cluster barrier; CTA 0 gathers the candidates and ranks them by counting.
+// The list scan above did k rounds of a 5-step shuffle minimum on each of three levels (thread lists -> warp -> CTA ->
+// cluster): 24 k - 30 k cycles per query against 4 k for a nearest-node query (PPX_RRT_STATS); it remains the answer when
+// a candidate list overflows.
+template <typename F>
+__device__ __forceinline__ void for_own_nodes(const RrtWs& W, const RrtSlice& S, int n, F&& f)
+{
+	const int stride = S.C << 8;
+	if (S.x) {
+		int local = threadIdx.x;
+		for (int j = (S.rank << 8) + (int)threadIdx.x; j < n; j += stride, local += 256)
+			f(S.x[local], S.y[local], S.th[local], j);
+	} else {
+		for (int j = (S.rank << 8) + (int)threadIdx.x; j < n; j += stride) {
+			const double* c = W.coords + 3 * (size_t)j;
+			f(c[0], c[1], c[2], j);
+		}
+	}
+}
+
+__device__ __forceinline__ double query_dist2(const double* q, int dim, double x, double y, double th)
+{
+	const double dx = q[0] - x, dy = q[1] - y;
+	double r = 0.0;
+	r += dx * dx;
+	r += dy * dy;
+	if (dim == 3) {
+		const double dt = q[2] - th;
+		r += dt * dt;
+	}
+	return r;
+}
+
+__device__ void cta_select_pass1(const RrtWs& W, const RrtSlice& S, int n, int dim, const double* q, RrtXch& X)
+{
+	double d = PPX_INF;
+	int idx = kNoNode;
+	for_own_nodes(W, S, n, [&](double x, double y, double th, int j) {
+		const double dj = query_dist2(q, dim, x, y, th);
+		if (nn_closer(dj, j, d, idx)) {
+			d = dj;
+			idx = j;
+		}
+	});
+	warp_nn_min(d, idx);
+	if ((threadIdx.x & 31) == 0) {
+		X.warpMin[threadIdx.x >> 5].d = d;
+		X.warpMin[threadIdx.x >> 5].idx = idx;
+	}
+	if (threadIdx.x == 0)
+		X.candCount = 0;
+}
+
+// after the cluster barrier that follows pass 1
+__device__ void cta_select_pass2(cg::cluster_group& cluster, const RrtWs& W, const RrtSlice& S, int n, int dim, const double* q, int k,
+	RrtXch& X)
+{
+	const int m = S.C * kRrtWarps;
+	if ((int)threadIdx.x < m) {
+		const NnEntry* remote = cluster.map_shared_rank(X.warpMin, (int)threadIdx.x / kRrtWarps);
+		X.allMin[threadIdx.x] = remote[threadIdx.x % kRrtWarps];
+	}
+	if (threadIdx.x == 0) { // fewer than k nodes among the minima: everything is a candidate
+		X.thr.d = PPX_INF;
+		X.thr.idx = kNoNode;
+	}
+	__syncthreads();
+	if ((int)threadIdx.x < m) {
+		const NnEntry mine = X.allMin[threadIdx.x];
+		int rank = 0;
+		for (int u = 0; u < m; u++)
+			rank += nn_closer(X.allMin[u].d, X.allMin[u].idx, mine.d, mine.idx) ? 1 : 0;
+		if (rank == k - 1 && mine.idx != kNoNode)
+			X.thr = mine;
+	}
+	__syncthreads();
+	const double td = X.thr.d;
+	const int ti = X.thr.idx;
+	for_own_nodes(W, S, n, [&](double x, double y, double th, int j) {
+		const double dj = query_dist2(q, dim, x, y, th);
+		if (!nn_closer(td, ti, dj, j)) { // (dj, j) <= T
+			const int pos = atomicAdd(&X.candCount, 1);
+			if (pos < kCandCap) {
+				X.cand[pos].d = dj;
+				X.cand[pos].idx = j;
+			}
+		}
+	});
+}
+
+// Every CTA of the cluster, once per command: append the announced node to the slice if this CTA owns it, then scan.
+// OP_SELECT has a cluster barrier in its middle: every CTA of the cluster must call this for the same command.
+__device__ void cta_serve(cg::cluster_group& cluster, const RrtWs& W, const RrtSlice& S, const RrtCmd& cmd, int dim, RrtXch& X)
+{
+	const int newIdx = cmd.newIdx;
+	if (S.x && newIdx >= 0 && ((newIdx >> 8) % S.C) == S.rank) {
 		if (threadIdx.x == 0) {
-			int best = 0;
-			for (int w = 1; w < (int)(blockDim.x >> 5); w++)
-				if (nn_closer(s_wd[w], s_wi[w], s_wd[best], s_wi[best]))
-					best = w;
-			bool have = s_wi[best] != 0x7fffffff;
-			s_idx[round] = have ? s_wi[best] : -1;
-			s_d2[round] = s_wd[best];
-			*s_winner = have ? s_wo[best] : -1;
+			const int local = (((newIdx >> 8) / S.C) << 8) | (newIdx & 255);
+			S.x[local] = cmd.newState[0];
+			S.y[local] = cmd.newState[1];
+			S.th[local] = cmd.newState[2];
 		}
-		__syncthreads();
-		if ((int)threadIdx.x == *s_winner)
-			head++;
 		__syncthreads();
 	}
+	const double q[3] = { cmd.q[0], cmd.q[1], cmd.q[2] };
+	if (cmd.op == OP_SELECT) {
+		cta_select_pass1(W, S, cmd.n, dim, q, X);
+		cluster.sync();
+		cta_select_pass2(cluster, W, S, cmd.n, dim, q, cmd.k, X);
+	} else if (cmd.k == 1)
+		cta_scan_slice<1>(W, S, cmd.n, dim, q, 1, X);
+	else if (cmd.k <= 8)
+		cta_scan_slice<8>(W, S, cmd.n, dim, q, cmd.k, X);
+	else
+		cta_scan_slice<kRrtMaxK>(W, S, cmd.n, dim, q, cmd.k, X);
+}
+
+// CTA 0: k nearest nodes of `query` among nodes [0, n): results (ascending) into s_idx / s_d2 [k], -1 where the tree has
+// fewer than k nodes.  `pendingNew` (node appended since the last query, or -1) travels with the command.
+__device__ void cluster_knn(cg::cluster_group& cluster, const RrtWs& W, const RrtSlice& S, RrtCmd& cmd, RrtXch& X, int n, int dim,
+	const double* query, int k, int pendingNew, int* s_idx, double* s_d2)
+{
+	bool select = k > 1 && S.C >= 4;
+	while (true) {
+		if (threadIdx.x == 0) {
+			cmd.op = select ? OP_SELECT : OP_SCAN;
+			cmd.k = k;
+			cmd.n = n;
+			cmd.newIdx = pendingNew;
+			for (int i = 0; i < 3; i++) {
+				cmd.q[i] = query[i];
+				cmd.newState[i] = pendingNew >= 0 ? W.coords[3 * (size_t)pendingNew + i] : 0.0;
+			}
+		}
+		cluster.sync(); // command published (and CTA 0's global writes of the tree: the other CTAs may scan W.coords)
+		cta_serve(cluster, W, S, cmd, dim, X);
+		cluster.sync(); // every CTA's list published
+		if (!select)
+			break;
+		// candidates of all CTAs -> X.gather (256 entries), ranked by counting
+		NnEntry* flat = &X.gather[0][0];
+		int total = 0, mine = -1, myRank = 0;
+		bool overflow = false;
+		for (int r = 0; r < S.C; r++) {
+			const int cnt = *cluster.map_shared_rank(&X.candCount, r);
+			overflow |= cnt > kCandCap;
+			if (mine < 0 && (int)threadIdx.x < total + cnt) {
+				mine = (int)threadIdx.x - total;
+				myRank = r;
+			}
+			total += cnt;
+		}
+		overflow |= total > kRrtMaxCluster * kRrtMaxK;
+		if (overflow) { // uniform over the CTA: answer the query with the list scan
+			select = false;
+			pendingNew = -1; // already appended
+			continue;
+		}
+		if (mine >= 0)
+			flat[threadIdx.x] = cluster.map_shared_rank(X.cand, myRank)[mine];
+		__syncthreads();
+		if ((int)threadIdx.x < total) {
+			const NnEntry e = flat[threadIdx.x];
+			int rank = 0;
+			for (int u = 0; u < total; u++)
+				rank += nn_closer(flat[u].d, flat[u].idx, e.d, e.idx) ? 1 : 0;
+			if (rank < k) {
+				s_idx[rank] = e.idx;
+				s_d2[rank] = e.d;
+			}
+		}
+		if ((int)threadIdx.x >= total && (int)threadIdx.x < k) { // the tree has fewer than k nodes
+			s_idx[threadIdx.x] = -1;
+			s_d2[threadIdx.x] = PPX_INF;
+		}
+		__syncthreads();
+		return;
+	}
+	if ((int)threadIdx.x < S.C * k) {
+		const int r = (int)threadIdx.x / k, e = (int)threadIdx.x % k;
+		const NnEntry* remote = cluster.map_shared_rank(X.ctaList, r);
+		X.gather[r][e] = remote[e];
+	}
+	__syncthreads();
+	if (threadIdx.x < 32) {
+		warp_merge_lists((int)threadIdx.x < S.C ? X.gather[threadIdx.x] : nullptr, k, X.warpList[0]);
+		__syncwarp();
+		if ((int)threadIdx.x < k) {
+			const NnEntry e = X.warpList[0][threadIdx.x];
+			s_idx[threadIdx.x] = e.idx == kNoNode ? -1 : e.idx;
+			s_d2[threadIdx.x] = e.d;
+		}
+	}
+	__syncthreads();
 }
 
 // std::equal_to<Point2d> / std::equal_to<Pose2d> (geometry/2dplane.h:107-134): exact comparison of
@@ -254,7 +554,7 @@ __device__ void connect(const RrtDev& P, const double* from, const double* to, b
 	c.length = sol.mLength * P.rmin;
 	// m_final = Interpolate(1.0)
 	Pose f = s;
-	if (c.length != 0) {
+	if (c.length != 0 && !(truncate && c.length > 0)) { // (Truncate below replaces m_final: the full-length pose is not needed then)
 		RSWalker w;
 		w.init(s);
 		f = w.at(c.seg, P.rmin, 1.0 * c.length);
@@ -332,26 +632,98 @@ __device__ bool conn_valid(const RrtDev& P, const MapDev& map, const Conn& c)
 
 namespace {
 
+// Reeds-Shepp solves spread over the CTA: warp w evaluates base formulas w and w + 8 (of 12) of up to eight pairs, one pair
+// per quad of lanes (rs_quad_part: the four mirrored goals on the quad's lanes, no divergence on the formula switch); the
+// per-warp partial minima of a pair are combined by the same lexicographic (float cost, word) rule.  One warp walking
+// all 12 formulas took 17 k cycles per steering solve (PPX_RRT_STATS).
+struct RsPart {
+	float cost;
+	int word;
+	double t, u, v;
+};
+
+__device__ void rs_finish(const RsPart* parts /* [kRrtWarps] */, double r, RSSolution& sol)
+{
+	const float INF = __int_as_float(0x7f800000);
+	float bestCost = INF;
+	int bestWord = 64;
+	double t = 0, u = 0, v = 0;
+	for (int w = 0; w < kRrtWarps; w++) {
+		const RsPart p = parts[w];
+		if (p.cost < bestCost || (p.cost == bestCost && p.word < bestWord)) {
+			bestCost = p.cost;
+			bestWord = p.word;
+			t = p.t; u = p.u; v = p.v;
+		}
+	}
+	if (!(bestCost < INF) || bestWord >= 48) {
+		sol.word = -1;
+		for (int m = 0; m < 5; m++)
+			sol.seg.len[m] = PPX_INF;
+		sol.seg.code = 0xAAAAA;
+		sol.mLength = 0.0;
+		sol.cost = INF;
+		return;
+	}
+	sol.word = bestWord;
+	sol.mLength = rs_build_segment(bestWord, t, u, v, sol.seg);
+	sol.cost = rs_compute_cost(sol.seg, sol.mLength, r, 1.0f, 1.0f, 0.0f);
+}
+
+// every thread of the CTA, converged: the part of (from -> to) that this warp's formulas give, pair = quad of lanes
+__device__ __forceinline__ void rs_part_store(const double* from, const double* to, double r, bool store, RsPart* parts /* [kRrtWarps] of the pair */)
+{
+	const Pose ps = { from[0], from[1], from[2] }, pg = { to[0], to[1], to[2] };
+	RsPart p;
+	double len;
+	rs_quad_part(ps, pg, r, 1.0f, 1.0f, 0.0f, 0, (int)(threadIdx.x >> 5), kRrtWarps, p.cost, len, p.word, p.t, p.u, p.v);
+	if (store && (threadIdx.x & 3) == 0)
+		parts[threadIdx.x >> 5] = p;
+}
+
 enum { CTL_RUN = 0, CTL_SKIP = 1, CTL_DONE = 2 };
 
 __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64_t ntrees, const double* __restrict__ starts,
 	const double* __restrict__ goals, const unsigned long long* __restrict__ seeds, char* __restrict__ slabs, size_t slabBytes,
-	int cap, int hashCap, ppx_rrt_result* __restrict__ results, int64_t nodeCapacity, double* __restrict__ outNodes,
-	int32_t* __restrict__ outParents, double* __restrict__ outCosts, unsigned long long* __restrict__ queue)
+	int cap, int hashCap, int sliceCap, ppx_rrt_result* __restrict__ results, int64_t nodeCapacity, double* __restrict__ outNodes,
+	int32_t* __restrict__ outParents, double* __restrict__ outCosts, unsigned long long* __restrict__ queue,
+	unsigned long long* __restrict__ stats)
 {
+	extern __shared__ __align__(16) double s_sliceMem[]; // [3][sliceCap] when the slices live in shared memory
 	__shared__ double s_query[3], s_new[3], s_goal[3];
 	__shared__ int s_nearIdx[kRrtMaxK];
 	__shared__ double s_nearD2[kRrtMaxK];
 	__shared__ double s_candCost[kRrtMaxK];
 	__shared__ int s_candValid[kRrtMaxK];
-	__shared__ double s_wd[8];
-	__shared__ int s_wi[8], s_wo[8];
-	__shared__ int s_winner, s_ctlbuf[2], s_n, s_nn;
+	__shared__ int s_ctlbuf[2], s_n, s_nn, s_pending;
 	__shared__ long long s_tree;
+	__shared__ RrtCmd s_cmd;
+	__shared__ RrtXch s_xch;
+	__shared__ RsPart s_part[kRrtMaxK][kRrtWarps];
+	// PPX_RRT_STATS: cycles of thread 0 of CTA 0 per phase (nearest query, steering solve, connect, its collision check,
+	// neighbourhood query, parent candidates, commit) and the number of iterations / accepted iterations
+	__shared__ unsigned long long s_prof[10];
+	if (threadIdx.x < 10)
+		s_prof[threadIdx.x] = 0;
+	long long tPhase = 0;
+	#define RRT_PHASE(i) \
+		if (stats && threadIdx.x == 0) { \
+			const long long now = clock64(); \
+			s_prof[i] += (unsigned long long)(now - tPhase); \
+			tPhase = now; \
+		}
+
+	cg::cluster_group cluster = cg::this_cluster();
+	RrtSlice S;
+	S.rank = (int)cluster.block_rank();
+	S.C = (int)cluster.num_blocks();
+	S.x = sliceCap > 0 ? s_sliceMem : nullptr;
+	S.y = S.x + sliceCap;
+	S.th = S.y + sliceCap;
 
 	RrtWs W;
 	{
-		char* p = slabs + (size_t)blockIdx.x * slabBytes;
+		char* p = slabs + (size_t)(blockIdx.x / S.C) * slabBytes;
 		W.coords = (double*)p; p += (size_t)cap * 24;
 		W.cost = (double*)p; p += (size_t)cap * 8;
 		W.mt = (unsigned long long*)p; p += 312 * 8;
@@ -361,13 +733,35 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 		W.hashCap = hashCap;
 	}
 
+	if (S.rank != 0) {
+		// scan servers: one command per neighbour query of CTA 0 until it says the cluster's trees are done
+		const RrtCmd* remote = cluster.map_shared_rank(&s_cmd, 0);
+		while (true) {
+			cluster.sync();
+			if (threadIdx.x == 0)
+				s_cmd = *remote;
+			__syncthreads();
+			const int op = s_cmd.op;
+			if (op != OP_EXIT)
+				cta_serve(cluster, W, S, s_cmd, P.dim, s_xch);
+			cluster.sync(); // CTA 0 reads the lists after this one (and does not exit before it)
+			if (op == OP_EXIT)
+				return;
+		}
+	}
+
 	while (true) {
 		if (threadIdx.x == 0)
 			s_tree = (long long)atomicAdd(queue, 1ull);
 		__syncthreads();
 		const long long t = s_tree;
-		if (t >= ntrees)
+		if (t >= ntrees) {
+			if (threadIdx.x == 0)
+				s_cmd.op = OP_EXIT;
+			cluster.sync();
+			cluster.sync();
 			return;
+		}
 		for (int i = threadIdx.x; i < hashCap; i += blockDim.x)
 			W.hash[i] = 0;
 		__syncthreads();
@@ -390,6 +784,7 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 			W.cost[0] = 0.0; // NodeInfo::costFromGoal = 0, rrt_star.h:36
 			tree_insert_hash(W, 0, P.dim); // Tree::CreateRootNode
 			n = 1;
+			s_pending = 0; // the node the next command announces to the cluster
 		}
 		__syncthreads();
 
@@ -423,22 +818,34 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 			if (s_ctl == CTL_DONE)
 				break;
 			const int size = s_n;
+			if (stats && threadIdx.x == 0) {
+				tPhase = clock64();
+				s_prof[8]++;
+			}
 			// Tree::GetNearestNode(randomState)
-			cta_knn(W, size, P.dim, s_query, 1, s_nearIdx, s_nearD2, s_wd, s_wi, s_wo, &s_winner);
+			cluster_knn(cluster, W, S, s_cmd, s_xch, size, P.dim, s_query, 1, s_pending, s_nearIdx, s_nearD2);
+			RRT_PHASE(0)
+			if (threadIdx.x == 0)
+				s_pending = -1; // ordered before the next reader by the barriers below
 			int nearest = -1;
 			RSSolution steerSol;
-			if (P.connection == 1 && threadIdx.x < 32) { // the 48 words of the steering connection on the lanes of warp 0
-				const double* f = W.coords + 3 * (size_t)s_nearIdx[0];
-				const Pose ps = { f[0], f[1], f[2] }, pg = { s_query[0], s_query[1], s_query[2] };
-				rs_solve_warp(ps, pg, P.rmin, 1.0f, 1.0f, 0.0f, steerSol);
+			if (P.connection == 1) { // the 48 words of the steering connection over the CTA's warps
+				rs_part_store(W.coords + 3 * (size_t)s_nearIdx[0], s_query, P.rmin, threadIdx.x < 4 || (threadIdx.x & 31) < 4, s_part[0]);
+				__syncthreads();
+				if (threadIdx.x == 0)
+					rs_finish(s_part[0], P.rmin, steerSol);
 			}
+			RRT_PHASE(1)
 			if (threadIdx.x == 0) {
 				nearest = s_nearIdx[0];
 				Conn c;
 				connect(P, W.coords + 3 * (size_t)nearest, s_query, true, P.maxConnectionDistance, c,
 					P.connection == 1 ? &steerSol : nullptr); // SteerTowards
 				nEdges++;
-				if (!conn_valid(P, map, c)) {
+				RRT_PHASE(2)
+				const bool steerValid = conn_valid(P, map, c);
+				RRT_PHASE(3)
+				if (!steerValid) {
 					s_ctl = CTL_SKIP;
 				} else {
 					s_new[0] = c.final_[0];
@@ -471,6 +878,7 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 							W.parent[node] = nearest;
 							W.cost[node] = 0.0;
 							tree_insert_hash(W, node, P.dim);
+							s_pending = node;
 						}
 					}
 					// RRT::IsSolution: (state - goal).norm() < 1, rrt.h:125-128
@@ -488,37 +896,29 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 			}
 			// RRT*: best parent among the nn nearest nodes of newState, rrt_star.h:84-97
 			const int nn = s_nn;
-			cta_knn(W, size, P.dim, s_new, nn, s_nearIdx, s_nearD2, s_wd, s_wi, s_wo, &s_winner);
+			if (stats && threadIdx.x == 0) {
+				tPhase = clock64();
+				s_prof[9]++;
+			}
+			cluster_knn(cluster, W, S, s_cmd, s_xch, size, P.dim, s_new, nn, -1, s_nearIdx, s_nearD2);
+			RRT_PHASE(4)
 			if (P.connection == 1) {
-				// candidate j on the quad of lanes 4j..4j+3 (rs_solve_quad: the 4 mirrored goals on the lanes, the 12 base
-				// formulas in a loop); lane 4j then builds and checks the connection
-				if (threadIdx.x < 4 * kRrtMaxK) {
-					const int j = (int)threadIdx.x >> 2;
+				// candidate j on quad j % 8 of every warp (warp w: base formulas w, w + 8), then thread j combines the eight
+				// parts, builds and checks the connection
+				for (int jb = 0; jb < nn; jb += 8) {
+					const int j = jb + (int)((threadIdx.x & 31) >> 2);
 					const bool have = j < nn && s_nearIdx[j] >= 0;
-					const int node = have ? s_nearIdx[j] : 0;
-					const double* f = W.coords + 3 * (size_t)node;
-					const Pose ps = { f[0], f[1], f[2] }, pg = { s_new[0], s_new[1], s_new[2] };
-					int w;
-					double t, u, v;
-					rs_solve_quad(ps, pg, P.rmin, 1.0f, 1.0f, 0.0f, 0, w, t, u, v);
-					if (have && (threadIdx.x & 3) == 0) {
-						RSSolution sol;
-						sol.word = w;
-						if (w >= 0) {
-							sol.mLength = rs_build_segment(w, t, u, v, sol.seg);
-							sol.cost = 0.0f;
-						} else {
-							for (int m = 0; m < 5; m++)
-								sol.seg.len[m] = PPX_INF;
-							sol.seg.code = 0xAAAAA;
-							sol.mLength = 0.0;
-							sol.cost = __int_as_float(0x7f800000);
-						}
-						Conn c;
-						connect(P, f, s_new, false, 0.0, c, &sol); // SteerExactly
-						s_candCost[j] = W.cost[node] + c.length;
-						s_candValid[j] = conn_valid(P, map, c) ? 1 : 0;
-					}
+					rs_part_store(W.coords + 3 * (size_t)(have ? s_nearIdx[j] : 0), s_new, P.rmin, have, s_part[have ? j : 0]);
+				}
+				__syncthreads();
+				if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
+					const int j = (int)threadIdx.x, node = s_nearIdx[j];
+					RSSolution sol;
+					rs_finish(s_part[j], P.rmin, sol);
+					Conn c;
+					connect(P, W.coords + 3 * (size_t)node, s_new, false, 0.0, c, &sol); // SteerExactly
+					s_candCost[j] = W.cost[node] + c.length;
+					s_candValid[j] = conn_valid(P, map, c) ? 1 : 0;
 				}
 			} else if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
 				const int node = s_nearIdx[threadIdx.x];
@@ -528,6 +928,7 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 				s_candValid[threadIdx.x] = conn_valid(P, map, c) ? 1 : 0;
 			}
 			__syncthreads();
+			RRT_PHASE(5)
 			if (threadIdx.x == 0) {
 				int bestParent = -1;
 				double bestCost = PPX_INF;
@@ -556,6 +957,7 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 						W.coords[3 * (size_t)node + 2] = s_new[2];
 						W.parent[node] = bestParent >= 0 ? bestParent : s_nearIdx[0];
 						tree_insert_hash(W, node, P.dim);
+						s_pending = node;
 					}
 				}
 				if (s_ctl != CTL_DONE) {
@@ -567,10 +969,14 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 					}
 				}
 			}
+			RRT_PHASE(6)
 			__syncthreads();
 			if (s_ctl == CTL_DONE)
 				break;
 		}
+		if (stats && threadIdx.x == 0)
+			for (int i = 0; i < 10; i++)
+				atomicAdd(&stats[i], s_prof[i]);
 
 		if (threadIdx.x == 0) {
 			ppx_rrt_result r;
@@ -646,7 +1052,50 @@ int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_
 	while (hashCap < 2 * cap)
 		hashCap <<= 1;
 	size_t slab = ((size_t)cap * 36 + 312 * 8 + (size_t)hashCap * 4 + 255) & ~(size_t)255;
-	const int ctas = (int)std::min<int64_t>(ntrees, (int64_t)ctx->num_sms * 2);
+	// Cluster size: as many SMs per tree as the batch leaves free (option "rrt_cluster" / PPX_RRT_CLUSTER overrides: 1..16).
+	int C = 1;
+	while (C < kRrtMaxCluster && ntrees * (2 * C) <= (int64_t)ctx->num_sms)
+		C *= 2;
+	if (const char* e = getenv("PPX_RRT_CLUSTER")) {
+		const int v = atoi(e);
+		if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16)
+			C = v;
+	}
+	PPX_CUDA(ctx, cudaFuncSetAttribute(k_rrt, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+	cudaLaunchConfig_t cfg {};
+	cudaLaunchAttribute attr[1];
+	int sliceCap = 0, clusters = 0;
+	size_t smem = 0;
+	for (;; C /= 2) {
+		// slices in shared memory when they fit (200 KB per CTA; 96 KB without a cluster so that two trees share an SM)
+		sliceCap = ((cap + 256 * C - 1) / (256 * C)) * 256;
+		smem = (size_t)sliceCap * 24;
+		if (smem > (C == 1 ? (size_t)96 : (size_t)200) * 1024) {
+			sliceCap = 0;
+			smem = 0;
+		}
+		PPX_CUDA(ctx, cudaFuncSetAttribute(k_rrt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+		cfg.gridDim = dim3((unsigned)C, 1, 1);
+		cfg.blockDim = dim3(kRrtThreads, 1, 1);
+		cfg.dynamicSmemBytes = smem;
+		cfg.stream = ctx->stream;
+		attr[0].id = cudaLaunchAttributeClusterDimension;
+		attr[0].val.clusterDim.x = (unsigned)C;
+		attr[0].val.clusterDim.y = 1;
+		attr[0].val.clusterDim.z = 1;
+		cfg.attrs = attr;
+		cfg.numAttrs = 1;
+		int maxClusters = 0;
+		cudaError_t err = cudaOccupancyMaxActiveClusters(&maxClusters, k_rrt, &cfg);
+		if (err == cudaSuccess && maxClusters > 0) {
+			clusters = (int)std::min<int64_t>(ntrees, (int64_t)maxClusters);
+			break;
+		}
+		cudaGetLastError();
+		if (C == 1)
+			return ppx_fail(ctx, PPX_ERR_CUDA, "rrt: no launch configuration (%s)", cudaGetErrorString(err));
+	}
+	cfg.gridDim = dim3((unsigned)(clusters * C), 1, 1);
 	size_t off = 0;
 	auto carve = [&](size_t bytes) {
 		size_t o = off;
@@ -654,7 +1103,7 @@ int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_
 		return o;
 	};
 	const bool wantNodes = nodes || parents || costs;
-	size_t oSlabs = carve((size_t)ctas * slab), oStarts = carve(ntrees * 24), oGoals = carve(ntrees * 24), oSeeds = carve(ntrees * 8);
+	size_t oSlabs = carve((size_t)clusters * slab), oStarts = carve(ntrees * 24), oGoals = carve(ntrees * 24), oSeeds = carve(ntrees * 8);
 	size_t oRes = carve(ntrees * sizeof(ppx_rrt_result));
 	size_t oNodes = carve(nodes ? (size_t)ntrees * node_capacity * 24 : 0), oPar = carve(parents ? (size_t)ntrees * node_capacity * 4 : 0);
 	size_t oCost = carve(costs ? (size_t)ntrees * node_capacity * 8 : 0);
@@ -665,10 +1114,27 @@ int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_
 	PPX_CUDA(ctx, cudaMemcpyAsync(base + oSeeds, seeds, ntrees * 8, cudaMemcpyHostToDevice, ctx->stream));
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
 	MapDev map = ctx->has_map ? ctx->map_dev() : MapDev {};
-	k_rrt<<<ctas, kRrtThreads, 0, ctx->stream>>>(P, map, ntrees, (const double*)(base + oStarts), (const double*)(base + oGoals),
-		(const unsigned long long*)(base + oSeeds), base + oSlabs, slab, cap, hashCap, (ppx_rrt_result*)(base + oRes),
-		wantNodes ? node_capacity : 0, nodes ? (double*)(base + oNodes) : nullptr, parents ? (int32_t*)(base + oPar) : nullptr,
-		costs ? (double*)(base + oCost) : nullptr, ctx->d_queue);
+	static const bool statsOn = getenv("PPX_RRT_STATS") != nullptr; // phase cycles to stderr (tools/time_rrt_single.py)
+	static unsigned long long* d_stats = nullptr;
+	if (statsOn && !d_stats)
+		PPX_CUDA(ctx, cudaMalloc(&d_stats, 10 * sizeof(unsigned long long)));
+	if (statsOn)
+		PPX_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 10 * sizeof(unsigned long long), ctx->stream));
+	PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_rrt, P, map, (int64_t)ntrees, (const double*)(base + oStarts), (const double*)(base + oGoals),
+		(const unsigned long long*)(base + oSeeds), base + oSlabs, slab, cap, hashCap, sliceCap, (ppx_rrt_result*)(base + oRes),
+		(int64_t)(wantNodes ? node_capacity : 0), nodes ? (double*)(base + oNodes) : (double*)nullptr,
+		parents ? (int32_t*)(base + oPar) : (int32_t*)nullptr, costs ? (double*)(base + oCost) : (double*)nullptr, ctx->d_queue,
+		d_stats));
+	if (d_stats) {
+		unsigned long long st[10];
+		cudaStreamSynchronize(ctx->stream);
+		cudaMemcpy(st, d_stats, sizeof(st), cudaMemcpyDeviceToHost);
+		const double it = (double)std::max<unsigned long long>(1, st[8]), acc = (double)std::max<unsigned long long>(1, st[9]);
+		fprintf(stderr, "rrt stats (cluster %d, slices in %s): %llu iterations, %llu accepted | cycles per iteration: nearest %.0f, steer solve "
+			"%.0f, connect %.0f, steer check %.0f | per accepted iteration: neighbourhood %.0f, candidates %.0f, commit %.0f\n",
+			C, sliceCap ? "shared memory" : "global memory", st[8], st[9], st[0] / it, st[1] / it, st[2] / it, st[3] / it, st[4] / acc,
+			st[5] / acc, st[6] / acc);
+	}
 	PPX_LAUNCHED(ctx);
 	PPX_CUDA(ctx, cudaMemcpyAsync(results, base + oRes, ntrees * sizeof(ppx_rrt_result), cudaMemcpyDeviceToHost, ctx->stream));
 	if (nodes)

@@ -188,8 +188,10 @@ __device__ uint32_t cta_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t* t
 	return s_warp[warp] + incl - v; // s_warp / *total are rewritten by the next call only: the caller has a barrier before it
 }
 
-// One goal per CTA at a time; CTAs take goals from a global cursor.
-__global__ void __launch_bounds__(1024) k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_t nGoals, const double* __restrict__ goals,
+// One goal per CTA at a time; CTAs take goals from a global cursor.  kThreads / kMinBlocks only set the register budget
+// (the kernel is bound by barrier and load latency per bucket: more resident CTAs per SM hide it).
+template <int kThreads, int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks) k_wavefront(MapDev map, const uint8_t* __restrict__ occ8, int64_t nGoals, const double* __restrict__ goals,
 	float* __restrict__ costOut, uint8_t* __restrict__ exploredOut, WfWork work, uint32_t sortCap,
 	unsigned long long* __restrict__ queue, int* __restrict__ status)
 {
@@ -408,9 +410,18 @@ int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* 
 	int threads = perimeter <= 1024 ? 128 : perimeter <= 2048 ? 256 : perimeter <= 4096 ? 512 : 1024;
 	uint32_t sortCap = (uint32_t)threads * 8;
 	size_t smem = (size_t)sortCap * 8 + sortCap / 4 * 8 + (size_t)sortCap * 4 + sortCap / 4 * 4;
-	PPX_CUDA(ctx, cudaFuncSetAttribute(k_wavefront, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+	using Kernel = void (*)(MapDev, const uint8_t*, int64_t, const double*, float*, uint8_t*, WfWork, uint32_t, unsigned long long*, int*);
+	// 256 threads: 4 CTAs per SM (51 registers) for a batch the GPU holds at once -- shortest single wavefront --, 5 (48
+	// registers) for larger batches: 4096 goals 46.5 against 48.8 ms; 6 and 7 CTAs per SM spill and are slower (51, 79 ms)
+	static const int envBlocks = getenv("PPX_WF_BLOCKS") ? atoi(getenv("PPX_WF_BLOCKS")) : 0;
+	const int wantBlocks = envBlocks ? envBlocks : n > (int64_t)ctx->num_sms * 4 ? 5 : 4;
+	Kernel kernel = threads == 128 ? k_wavefront<128, 8>
+		: threads == 256 ? (wantBlocks <= 4 ? k_wavefront<256, 4> : k_wavefront<256, 5>)
+		: threads == 512 ? k_wavefront<512, 2>
+		: k_wavefront<1024, 1>;
+	PPX_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
 	int perSm = 1;
-	PPX_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_wavefront, threads, smem));
+	PPX_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, threads, smem));
 	if (perSm < 1)
 		perSm = 1;
 	int ctas = (int)std::min<int64_t>(n, (int64_t)ctx->num_sms * perSm);
@@ -431,7 +442,7 @@ int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* 
 	int* d_status = (int*)(base + offStatus);
 	PPX_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int), ctx->stream));
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
-	k_wavefront<<<ctas, threads, smem, ctx->stream>>>(ctx->map_dev(), ctx->d_occ8, n, d_goals, d_cost, d_explored, work, sortCap,
+	kernel<<<ctas, threads, smem, ctx->stream>>>(ctx->map_dev(), ctx->d_occ8, n, d_goals, d_cost, d_explored, work, sortCap,
 		ctx->d_queue, d_status);
 	PPX_LAUNCHED(ctx);
 	ctx->d_wf_status = d_status;
