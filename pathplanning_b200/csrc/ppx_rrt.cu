@@ -137,6 +137,21 @@ struct RrtXch { // exchange areas in shared memory
 	int candCount;
 };
 
+// Cluster barrier.  cg::cluster_group::sync() is arrive.release + wait.acquire: SASS MEMBAR.ALL.GPU + UCGABAR_ARV +
+// UCGABAR_WAIT + CCTL.IVALL.  When everything the CTAs exchange lives in shared memory (commands, slices, candidate lists)
+// the GPU-scope fence is not needed: a CTA-scope fence puts the thread's shared-memory writes in its SM's shared memory,
+// which is where the other CTAs' DSMEM reads look, and the arrive can be relaxed.  With slices in global memory CTA 0's
+// node writes must be visible to the scanning CTAs: full release there.
+__device__ __forceinline__ void cluster_barrier(bool globalData)
+{
+	if (globalData) {
+		asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+	} else {
+		__threadfence_block();
+		asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+	}
+}
+
 // Warp-wide minimum of (d, idx) under nn_closer; every lane gets it.
 __device__ __forceinline__ void warp_nn_min(double& d, int& idx)
 {
@@ -379,7 +394,7 @@ __device__ void cta_serve(cg::cluster_group& cluster, const RrtWs& W, const RrtS
 	const double q[3] = { cmd.q[0], cmd.q[1], cmd.q[2] };
 	if (cmd.op == OP_SELECT) {
 		cta_select_pass1(W, S, cmd.n, dim, q, X);
-		cluster.sync();
+		cluster_barrier(!S.x);
 		cta_select_pass2(cluster, W, S, cmd.n, dim, q, cmd.k, X);
 	} else if (cmd.k == 1)
 		cta_scan_slice<1>(W, S, cmd.n, dim, q, 1, X);
@@ -406,9 +421,9 @@ __device__ void cluster_knn(cg::cluster_group& cluster, const RrtWs& W, const Rr
 				cmd.newState[i] = pendingNew >= 0 ? W.coords[3 * (size_t)pendingNew + i] : 0.0;
 			}
 		}
-		cluster.sync(); // command published (and CTA 0's global writes of the tree: the other CTAs may scan W.coords)
+		cluster_barrier(!S.x); // command published (and CTA 0's global writes of the tree when the CTAs scan W.coords)
 		cta_serve(cluster, W, S, cmd, dim, X);
-		cluster.sync(); // every CTA's list published
+		cluster_barrier(!S.x); // every CTA's list published
 		if (!select)
 			break;
 		// candidates of all CTAs -> X.gather (256 entries), ranked by counting
@@ -737,14 +752,14 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 		// scan servers: one command per neighbour query of CTA 0 until it says the cluster's trees are done
 		const RrtCmd* remote = cluster.map_shared_rank(&s_cmd, 0);
 		while (true) {
-			cluster.sync();
+			cluster_barrier(!S.x);
 			if (threadIdx.x == 0)
 				s_cmd = *remote;
 			__syncthreads();
 			const int op = s_cmd.op;
 			if (op != OP_EXIT)
 				cta_serve(cluster, W, S, s_cmd, P.dim, s_xch);
-			cluster.sync(); // CTA 0 reads the lists after this one (and does not exit before it)
+			cluster_barrier(!S.x); // CTA 0 reads the lists after this one (and does not exit before it)
 			if (op == OP_EXIT)
 				return;
 		}
@@ -758,8 +773,8 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 		if (t >= ntrees) {
 			if (threadIdx.x == 0)
 				s_cmd.op = OP_EXIT;
-			cluster.sync();
-			cluster.sync();
+			cluster_barrier(!S.x);
+			cluster_barrier(!S.x);
 			return;
 		}
 		for (int i = threadIdx.x; i < hashCap; i += blockDim.x)

@@ -45,10 +45,11 @@ def test_no_cpu_fallback():
 
 def test_product_does_not_touch_oracle():
     """The product path must never import / link / execute anything under oracle/."""
-    pkg = os.path.join(ROOT, "pathplanning_b200")
-    for dirpath, _, files in os.walk(pkg):
-        for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp")) or f == "Makefile":
-                text = open(os.path.join(dirpath, f), errors="ignore").read()
-                assert "refapi" not in text and "pp_oracle" not in text and "libpp_ref" not in text, f
-                assert not re.search(r"[\"'/]oracle/", text), f
+    for tree in ("pathplanning_b200", "include", "dropin"):
+        for dirpath, dirs, files in os.walk(os.path.join(ROOT, tree)):
+            dirs[:] = [d for d in dirs if d != "_build"]
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp")) or f == "Makefile":
+                    text = open(os.path.join(dirpath, f), errors="ignore").read()
+                    assert "refapi" not in text and "pp_oracle" not in text and "libpp_ref" not in text, f
+                    assert not re.search(r"[\"'/]oracle/", text), f
