@@ -111,13 +111,16 @@ struct NnEntry { // a neighbour candidate: squared distance and node index (kNoN
 	int pad;
 };
 
-enum { OP_SCAN = 0, OP_EXIT = 1, OP_SELECT = 2 };
+enum { OP_SCAN = 0, OP_EXIT = 1, OP_SELECT = 2, OP_NEAREST = 3 };
+constexpr int kSpec = 8; // samples of a speculation batch (one per warp of CTA 0)
 constexpr int kCandCap = 64; // candidates per CTA of a threshold selection (overflow: the list scan answers the query)
 
-struct RrtCmd { // CTA 0's command to its cluster, read by the other CTAs through DSMEM after the cluster barrier
+struct alignas(8) RrtCmd { // CTA 0's command to its cluster, read by the other CTAs through DSMEM after the cluster barrier
 	int op, k, n; // n: tree size the scan covers
-	int newIdx; // node appended since the last command (-1: none); its owner stores it in its slice
-	double q[3], newState[3];
+	int nq; // OP_NEAREST: number of queries (nearest node of each); else 1
+	int nNew, pad; // nodes appended since the last command; their owners store them in their slices
+	int newIdx[kSpec];
+	double q[kSpec][3], newState[kSpec][3];
 };
 
 struct RrtSlice { // the cluster's partition of the node coordinates: node i -> CTA (i >> 8) % C, local slot ((i >> 8) / C) << 8 | i & 255
@@ -379,20 +382,26 @@ __device__ void cta_select_pass2(cg::cluster_group& cluster, const RrtWs& W, con
 
 // Every CTA of the cluster, once per command: append the announced node to the slice if this CTA owns it, then scan.
 // OP_SELECT has a cluster barrier in its middle: every CTA of the cluster must call this for the same command.
+__device__ void cta_nearest_batch(const RrtWs& W, const RrtSlice& S, const RrtCmd& cmd, int dim, RrtXch& X);
+
 __device__ void cta_serve(cg::cluster_group& cluster, const RrtWs& W, const RrtSlice& S, const RrtCmd& cmd, int dim, RrtXch& X)
 {
-	const int newIdx = cmd.newIdx;
-	if (S.x && newIdx >= 0 && ((newIdx >> 8) % S.C) == S.rank) {
-		if (threadIdx.x == 0) {
-			const int local = (((newIdx >> 8) / S.C) << 8) | (newIdx & 255);
-			S.x[local] = cmd.newState[0];
-			S.y[local] = cmd.newState[1];
-			S.th[local] = cmd.newState[2];
+	if (S.x && cmd.nNew > 0) {
+		if ((int)threadIdx.x < cmd.nNew) {
+			const int newIdx = cmd.newIdx[threadIdx.x];
+			if (((newIdx >> 8) % S.C) == S.rank) {
+				const int local = (((newIdx >> 8) / S.C) << 8) | (newIdx & 255);
+				S.x[local] = cmd.newState[threadIdx.x][0];
+				S.y[local] = cmd.newState[threadIdx.x][1];
+				S.th[local] = cmd.newState[threadIdx.x][2];
+			}
 		}
 		__syncthreads();
 	}
-	const double q[3] = { cmd.q[0], cmd.q[1], cmd.q[2] };
-	if (cmd.op == OP_SELECT) {
+	const double q[3] = { cmd.q[0][0], cmd.q[0][1], cmd.q[0][2] };
+	if (cmd.op == OP_NEAREST)
+		cta_nearest_batch(W, S, cmd, dim, X);
+	else if (cmd.op == OP_SELECT) {
 		cta_select_pass1(W, S, cmd.n, dim, q, X);
 		cluster_barrier(!S.x);
 		cta_select_pass2(cluster, W, S, cmd.n, dim, q, cmd.k, X);
@@ -404,23 +413,102 @@ __device__ void cta_serve(cg::cluster_group& cluster, const RrtWs& W, const RrtS
 		cta_scan_slice<kRrtMaxK>(W, S, cmd.n, dim, q, cmd.k, X);
 }
 
+// OP_NEAREST: the nearest node of each of cmd.nq queries in one pass over this CTA's nodes -> X.ctaList[0..nq)
+__device__ void cta_nearest_batch(const RrtWs& W, const RrtSlice& S, const RrtCmd& cmd, int dim, RrtXch& X)
+{
+	const int nq = cmd.nq;
+	double bd[kSpec];
+	int bi[kSpec];
+	#pragma unroll
+	for (int b = 0; b < kSpec; b++) {
+		bd[b] = PPX_INF;
+		bi[b] = kNoNode;
+	}
+	for_own_nodes(W, S, cmd.n, [&](double x, double y, double th, int j) {
+		#pragma unroll
+		for (int b = 0; b < kSpec; b++) {
+			if (b < nq) {
+				const double dj = query_dist2(cmd.q[b], dim, x, y, th);
+				if (nn_closer(dj, j, bd[b], bi[b])) {
+					bd[b] = dj;
+					bi[b] = j;
+				}
+			}
+		}
+	});
+	#pragma unroll
+	for (int b = 0; b < kSpec; b++) {
+		if (b < nq) {
+			warp_nn_min(bd[b], bi[b]);
+			if ((threadIdx.x & 31) == 0) {
+				X.warpList[threadIdx.x >> 5][b].d = bd[b];
+				X.warpList[threadIdx.x >> 5][b].idx = bi[b];
+			}
+		}
+	}
+	__syncthreads();
+	if ((int)threadIdx.x < nq) {
+		NnEntry best = X.warpList[0][threadIdx.x];
+		for (int w = 1; w < kRrtWarps; w++) {
+			const NnEntry e = X.warpList[w][threadIdx.x];
+			if (nn_closer(e.d, e.idx, best.d, best.idx))
+				best = e;
+		}
+		X.ctaList[threadIdx.x] = best;
+	}
+}
+
+// thread 0 of CTA 0: the command of the next query; takes (and empties) the list of nodes appended since the last one
+__device__ void cmd_fill(RrtCmd& cmd, const RrtWs& W, int op, int k, int n, int nq, const double (*q)[3], int* pendCount, const int* pendIdx)
+{
+	cmd.op = op;
+	cmd.k = k;
+	cmd.n = n;
+	cmd.nq = nq;
+	for (int b = 0; b < nq; b++)
+		for (int i = 0; i < 3; i++)
+			cmd.q[b][i] = q[b][i];
+	const int nNew = *pendCount;
+	cmd.nNew = nNew;
+	for (int e = 0; e < nNew; e++) {
+		cmd.newIdx[e] = pendIdx[e];
+		for (int i = 0; i < 3; i++)
+			cmd.newState[e][i] = W.coords[3 * (size_t)pendIdx[e] + i];
+	}
+	*pendCount = 0;
+}
+
+// CTA 0: nearest node of each of nq queries among nodes [0, n) -> outIdx / outD2 [nq]
+__device__ void cluster_nearest(cg::cluster_group& cluster, const RrtWs& W, const RrtSlice& S, RrtCmd& cmd, RrtXch& X, int n, int dim,
+	const double (*q)[3], int nq, int* pendCount, const int* pendIdx, int* outIdx, double* outD2)
+{
+	if (threadIdx.x == 0)
+		cmd_fill(cmd, W, OP_NEAREST, 1, n, nq, q, pendCount, pendIdx);
+	cluster_barrier(!S.x);
+	cta_serve(cluster, W, S, cmd, dim, X);
+	cluster_barrier(!S.x);
+	if ((int)threadIdx.x < nq) {
+		NnEntry best = X.ctaList[threadIdx.x];
+		for (int r = 1; r < S.C; r++) {
+			const NnEntry e = cluster.map_shared_rank(X.ctaList, r)[threadIdx.x];
+			if (nn_closer(e.d, e.idx, best.d, best.idx))
+				best = e;
+		}
+		outIdx[threadIdx.x] = best.idx == kNoNode ? -1 : best.idx;
+		outD2[threadIdx.x] = best.d;
+	}
+	__syncthreads();
+}
+
 // CTA 0: k nearest nodes of `query` among nodes [0, n): results (ascending) into s_idx / s_d2 [k], -1 where the tree has
 // fewer than k nodes.  `pendingNew` (node appended since the last query, or -1) travels with the command.
 __device__ void cluster_knn(cg::cluster_group& cluster, const RrtWs& W, const RrtSlice& S, RrtCmd& cmd, RrtXch& X, int n, int dim,
-	const double* query, int k, int pendingNew, int* s_idx, double* s_d2)
+	const double* query, int k, int* pendCount, const int* pendIdx, int* s_idx, double* s_d2)
 {
 	bool select = k > 1 && S.C >= 4;
 	while (true) {
-		if (threadIdx.x == 0) {
-			cmd.op = select ? OP_SELECT : OP_SCAN;
-			cmd.k = k;
-			cmd.n = n;
-			cmd.newIdx = pendingNew;
-			for (int i = 0; i < 3; i++) {
-				cmd.q[i] = query[i];
-				cmd.newState[i] = pendingNew >= 0 ? W.coords[3 * (size_t)pendingNew + i] : 0.0;
-			}
-		}
+		if (threadIdx.x == 0)
+			cmd_fill(cmd, W, select ? OP_SELECT : OP_SCAN, k, n, 1, (const double (*)[3])query, pendCount, pendIdx);
 		cluster_barrier(!S.x); // command published (and CTA 0's global writes of the tree when the CTAs scan W.coords)
 		cta_serve(cluster, W, S, cmd, dim, X);
 		cluster_barrier(!S.x); // every CTA's list published
@@ -441,8 +529,7 @@ __device__ void cluster_knn(cg::cluster_group& cluster, const RrtWs& W, const Rr
 		}
 		overflow |= total > kRrtMaxCluster * kRrtMaxK;
 		if (overflow) { // uniform over the CTA: answer the query with the list scan
-			select = false;
-			pendingNew = -1; // already appended
+			select = false; // (the appended nodes went out with the first command: the list is empty now)
 			continue;
 		}
 		if (mine >= 0)
@@ -705,12 +792,14 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 	unsigned long long* __restrict__ stats)
 {
 	extern __shared__ __align__(16) double s_sliceMem[]; // [3][sliceCap] when the slices live in shared memory
-	__shared__ double s_query[3], s_new[3], s_goal[3];
+	__shared__ double s_goal[3];
 	__shared__ int s_nearIdx[kRrtMaxK];
 	__shared__ double s_nearD2[kRrtMaxK];
 	__shared__ double s_candCost[kRrtMaxK];
 	__shared__ int s_candValid[kRrtMaxK];
-	__shared__ int s_ctlbuf[2], s_n, s_nn, s_pending;
+	__shared__ int s_n, s_done, s_inserted, s_pendCount, s_pendIdx[kSpec];
+	__shared__ double s_bq[kSpec][3], s_bNew[kSpec][3], s_bNearD2[kSpec];
+	__shared__ int s_bNear[kSpec], s_bOk[kSpec], s_bStale[kSpec];
 	__shared__ long long s_tree;
 	__shared__ RrtCmd s_cmd;
 	__shared__ RrtXch s_xch;
@@ -753,8 +842,8 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 		const RrtCmd* remote = cluster.map_shared_rank(&s_cmd, 0);
 		while (true) {
 			cluster_barrier(!S.x);
-			if (threadIdx.x == 0)
-				s_cmd = *remote;
+			for (int i = threadIdx.x; i < (int)(sizeof(RrtCmd) / 8); i += blockDim.x)
+				((unsigned long long*)&s_cmd)[i] = ((const unsigned long long*)remote)[i];
 			__syncthreads();
 			const int op = s_cmd.op;
 			if (op != OP_EXIT)
@@ -781,10 +870,10 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 			W.hash[i] = 0;
 		__syncthreads();
 
-		// thread-0 state of the reference's loop
+		// state of the reference's loop: count / n / nEdges / status in every thread (uniform), RNG and solution on thread 0
 		RrtRng rng { W.mt, 0 };
 		int count = -1, status = 1, solution = -1, nEdges = 0;
-		int n = 0;
+		int n = 1;
 		if (threadIdx.x == 0) {
 			rng.seed(seeds[t]);
 			for (int i = 0; i < 3; i++) {
@@ -798,196 +887,224 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 			W.parent[0] = -1;
 			W.cost[0] = 0.0; // NodeInfo::costFromGoal = 0, rrt_star.h:36
 			tree_insert_hash(W, 0, P.dim); // Tree::CreateRootNode
-			n = 1;
-			s_pending = 0; // the node the next command announces to the cluster
+			s_pendCount = 1; // the nodes the next command announces to the cluster
+			s_pendIdx[0] = 0;
 		}
 		__syncthreads();
 
-		// The control word is double-buffered by iteration parity: thread 0 may already be writing the next
-		// iteration's word (after its last barrier of this iteration) while a late warp still reads this one.
-		unsigned it = 0;
-		while (true) {
-			it++;
-			volatile int& s_ctl = s_ctlbuf[it & 1];
+		// SPECULATION OVER REJECTED ITERATIONS.  An iteration whose steering connection is invalid changes nothing (rrt.h:75-77,
+		// rrt_star.h:78-79: `continue`), and the random numbers an iteration draws do not depend on the tree.  So kSpec
+		// samples are drawn ahead, their nearest nodes come from ONE pass over the tree, their steering connections are
+		// solved and checked in parallel (Reeds-Shepp words over the warps by base formula, one sample per warp for the
+		// rest), and the batch is then resolved IN ORDER: a rejected sample only counts; an accepted one runs the
+		// reference's statements (neighbourhood, best parent, Extend, goal test) against the tree as it is then; after an
+		// insertion the later samples of the batch compare their nearest node with the new one and are re-steered if it
+		// is nearer.  Iteration counts, edge counts and the tree are those of the one-sample-at-a-time loop.
+		auto steer_one = [&](int b, const RsPart* parts) { // one thread: SteerTowards + IsPathValid of sample b
+			RSSolution sol;
+			if (P.connection == 1)
+				rs_finish(parts, P.rmin, sol);
+			Conn c;
+			connect(P, W.coords + 3 * (size_t)s_bNear[b], s_bq[b], true, P.maxConnectionDistance, c, P.connection == 1 ? &sol : nullptr);
+			const bool ok = conn_valid(P, map, c);
+			s_bOk[b] = ok ? 1 : 0;
+			s_bNew[b][0] = c.final_[0];
+			s_bNew[b][1] = c.final_[1];
+			s_bNew[b][2] = P.dim == 3 ? c.final_[2] : 0.0;
+		};
+		bool done = false;
+		while (!done) {
 			if (threadIdx.x == 0) {
-				count++;
-				if (count > (long long)P.maxIteration || (unsigned)n > P.maxNodes) { // rrt.h:64-69
-					status = -1;
-					s_ctl = CTL_DONE;
-				} else {
+				for (int b = 0; b < kSpec; b++) {
 					// Random<double>::SampleUniform(0, 1) < goalBias ? goal : m_stateSpace->SampleUniform()
 					if (rng.uniform(0.0, 1.0) < P.goalBias) {
-						s_query[0] = s_goal[0];
-						s_query[1] = s_goal[1];
-						s_query[2] = s_goal[2];
+						s_bq[b][0] = s_goal[0];
+						s_bq[b][1] = s_goal[1];
+						s_bq[b][2] = s_goal[2];
 					} else {
-						s_query[0] = rng.uniform(P.lb[0], P.ub[0]);
-						s_query[1] = rng.uniform(P.lb[1], P.ub[1]);
-						s_query[2] = P.dim == 3 ? rng.uniform(P.lb[2], P.ub[2]) : 0.0;
+						s_bq[b][0] = rng.uniform(P.lb[0], P.ub[0]);
+						s_bq[b][1] = rng.uniform(P.lb[1], P.ub[1]);
+						s_bq[b][2] = P.dim == 3 ? rng.uniform(P.lb[2], P.ub[2]) : 0.0;
 					}
-					s_ctl = CTL_RUN;
-					s_n = n;
+					s_bStale[b] = 0;
 				}
+				if (stats)
+					tPhase = clock64();
 			}
 			__syncthreads();
-			if (s_ctl == CTL_DONE)
-				break;
-			const int size = s_n;
-			if (stats && threadIdx.x == 0) {
-				tPhase = clock64();
-				s_prof[8]++;
-			}
-			// Tree::GetNearestNode(randomState)
-			cluster_knn(cluster, W, S, s_cmd, s_xch, size, P.dim, s_query, 1, s_pending, s_nearIdx, s_nearD2);
+			// Tree::GetNearestNode(randomState) for the whole batch
+			cluster_nearest(cluster, W, S, s_cmd, s_xch, n, P.dim, s_bq, kSpec, &s_pendCount, s_pendIdx, s_bNear, s_bNearD2);
 			RRT_PHASE(0)
-			if (threadIdx.x == 0)
-				s_pending = -1; // ordered before the next reader by the barriers below
-			int nearest = -1;
-			RSSolution steerSol;
-			if (P.connection == 1) { // the 48 words of the steering connection over the CTA's warps
-				rs_part_store(W.coords + 3 * (size_t)s_nearIdx[0], s_query, P.rmin, threadIdx.x < 4 || (threadIdx.x & 31) < 4, s_part[0]);
+			if (P.connection == 1) {
+				const int g = (int)((threadIdx.x & 31) >> 2); // sample g on quad g of every warp
+				rs_part_store(W.coords + 3 * (size_t)s_bNear[g], s_bq[g], P.rmin, true, s_part[g]);
 				__syncthreads();
-				if (threadIdx.x == 0)
-					rs_finish(s_part[0], P.rmin, steerSol);
 			}
 			RRT_PHASE(1)
-			if (threadIdx.x == 0) {
-				nearest = s_nearIdx[0];
-				Conn c;
-				connect(P, W.coords + 3 * (size_t)nearest, s_query, true, P.maxConnectionDistance, c,
-					P.connection == 1 ? &steerSol : nullptr); // SteerTowards
-				nEdges++;
-				RRT_PHASE(2)
-				const bool steerValid = conn_valid(P, map, c);
-				RRT_PHASE(3)
-				if (!steerValid) {
-					s_ctl = CTL_SKIP;
-				} else {
-					s_new[0] = c.final_[0];
-					s_new[1] = c.final_[1];
-					s_new[2] = P.dim == 3 ? c.final_[2] : 0.0;
-					if (P.star) {
-						unsigned nn = (unsigned)log((double)size); // std::max<unsigned int>(1, log(m_tree.Size()))
-						if (nn < 1u)
-							nn = 1u;
-						s_nn = (int)(nn > (unsigned)kRrtMaxK ? (unsigned)kRrtMaxK : nn);
-					}
-				}
-			}
+			if ((threadIdx.x & 31) == 0)
+				steer_one((int)(threadIdx.x >> 5), s_part[threadIdx.x >> 5]);
 			__syncthreads();
-			if (s_ctl == CTL_SKIP)
-				continue;
-			if (!P.star) {
-				if (threadIdx.x == 0) {
-					// Tree::Extend(newState, nearestNode), tree.h:124-146
-					int node = tree_find(W, s_new, P.dim);
-					if (node < 0) {
-						if (n >= W.cap) {
-							status = PPX_ERR_CAPACITY;
-							s_ctl = CTL_DONE;
-						} else {
-							node = n++;
-							W.coords[3 * (size_t)node] = s_new[0];
-							W.coords[3 * (size_t)node + 1] = s_new[1];
-							W.coords[3 * (size_t)node + 2] = s_new[2];
-							W.parent[node] = nearest;
-							W.cost[node] = 0.0;
-							tree_insert_hash(W, node, P.dim);
-							s_pending = node;
-						}
-					}
-					// RRT::IsSolution: (state - goal).norm() < 1, rrt.h:125-128
-					double dx = s_new[0] - s_goal[0], dy = s_new[1] - s_goal[1];
-					if (s_ctl != CTL_DONE && sqrt(dx * dx + dy * dy) < 1) {
-						solution = node;
-						status = PPX_OK;
-						s_ctl = CTL_DONE;
-					}
-				}
-				__syncthreads();
-				if (s_ctl == CTL_DONE)
+			RRT_PHASE(3)
+			for (int b = 0; b < kSpec; b++) {
+				count++; // every thread keeps the counters: the limits are checked without a broadcast
+				if (count > (long long)P.maxIteration || (unsigned)n > P.maxNodes) { // rrt.h:64-69
+					status = -1;
+					done = true;
 					break;
-				continue;
-			}
-			// RRT*: best parent among the nn nearest nodes of newState, rrt_star.h:84-97
-			const int nn = s_nn;
-			if (stats && threadIdx.x == 0) {
-				tPhase = clock64();
-				s_prof[9]++;
-			}
-			cluster_knn(cluster, W, S, s_cmd, s_xch, size, P.dim, s_new, nn, -1, s_nearIdx, s_nearD2);
-			RRT_PHASE(4)
-			if (P.connection == 1) {
-				// candidate j on quad j % 8 of every warp (warp w: base formulas w, w + 8), then thread j combines the eight
-				// parts, builds and checks the connection
-				for (int jb = 0; jb < nn; jb += 8) {
-					const int j = jb + (int)((threadIdx.x & 31) >> 2);
-					const bool have = j < nn && s_nearIdx[j] >= 0;
-					rs_part_store(W.coords + 3 * (size_t)(have ? s_nearIdx[j] : 0), s_new, P.rmin, have, s_part[have ? j : 0]);
 				}
-				__syncthreads();
-				if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
-					const int j = (int)threadIdx.x, node = s_nearIdx[j];
-					RSSolution sol;
-					rs_finish(s_part[j], P.rmin, sol);
-					Conn c;
-					connect(P, W.coords + 3 * (size_t)node, s_new, false, 0.0, c, &sol); // SteerExactly
-					s_candCost[j] = W.cost[node] + c.length;
-					s_candValid[j] = conn_valid(P, map, c) ? 1 : 0;
+				if (stats && threadIdx.x == 0)
+					s_prof[8]++;
+				if (s_bStale[b]) { // a node inserted earlier in this batch is nearer: steer from it
+					if (P.connection == 1) {
+						rs_part_store(W.coords + 3 * (size_t)s_bNear[b], s_bq[b], P.rmin, (threadIdx.x & 31) < 4, s_part[0]);
+						__syncthreads();
+					}
+					if (threadIdx.x == 0) {
+						steer_one(b, s_part[0]);
+						if (stats)
+							s_prof[2]++;
+					}
+					__syncthreads();
 				}
-			} else if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
-				const int node = s_nearIdx[threadIdx.x];
-				Conn c;
-				connect(P, W.coords + 3 * (size_t)node, s_new, false, 0.0, c); // SteerExactly
-				s_candCost[threadIdx.x] = W.cost[node] + c.length;
-				s_candValid[threadIdx.x] = conn_valid(P, map, c) ? 1 : 0;
-			}
-			__syncthreads();
-			RRT_PHASE(5)
-			if (threadIdx.x == 0) {
-				int bestParent = -1;
-				double bestCost = PPX_INF;
-				for (int j = 0; j < nn; j++) {
-					if (s_nearIdx[j] < 0)
-						break;
-					if (s_candCost[j] < bestCost) {
-						nEdges++; // the reference evaluates IsPathValid only here (short-circuit &&)
-						if (s_candValid[j]) {
-							bestParent = s_nearIdx[j];
-							bestCost = s_candCost[j];
+				nEdges++;
+				if (!s_bOk[b])
+					continue;
+				const double* newState = s_bNew[b];
+				const int nearest = s_bNear[b];
+				const int size = n;
+				if (threadIdx.x == 0) {
+					s_done = 0;
+					s_inserted = -1;
+				}
+				if (!P.star) {
+					if (threadIdx.x == 0) {
+						// Tree::Extend(newState, nearestNode), tree.h:124-146
+						int node = tree_find(W, newState, P.dim);
+						if (node < 0) {
+							if (n >= W.cap) {
+								status = PPX_ERR_CAPACITY;
+								s_done = 1;
+							} else {
+								node = n;
+								W.coords[3 * (size_t)node] = newState[0];
+								W.coords[3 * (size_t)node + 1] = newState[1];
+								W.coords[3 * (size_t)node + 2] = newState[2];
+								W.parent[node] = nearest;
+								W.cost[node] = 0.0;
+								tree_insert_hash(W, node, P.dim);
+								s_pendIdx[s_pendCount++] = node;
+								s_inserted = node;
+							}
+						}
+						// RRT::IsSolution: (state - goal).norm() < 1, rrt.h:125-128
+						double dx = newState[0] - s_goal[0], dy = newState[1] - s_goal[1];
+						if (!s_done && sqrt(dx * dx + dy * dy) < 1) {
+							solution = node;
+							status = PPX_OK;
+							s_done = 1;
 						}
 					}
+				} else {
+					// RRT*: best parent among the nn nearest nodes of newState, rrt_star.h:84-97
+					unsigned nnu = (unsigned)log((double)size); // std::max<unsigned int>(1, log(m_tree.Size()))
+					if (nnu < 1u)
+						nnu = 1u;
+					const int nn = (int)(nnu > (unsigned)kRrtMaxK ? (unsigned)kRrtMaxK : nnu);
+					if (stats && threadIdx.x == 0) {
+						tPhase = clock64();
+						s_prof[9]++;
+					}
+					cluster_knn(cluster, W, S, s_cmd, s_xch, size, P.dim, newState, nn, &s_pendCount, s_pendIdx, s_nearIdx, s_nearD2);
+					RRT_PHASE(4)
+					if (P.connection == 1) {
+						// candidate j on quad j % 8 of every warp (warp w: base formulas w, w + 8), then thread j combines the
+						// eight parts, builds and checks the connection
+						for (int jb = 0; jb < nn; jb += 8) {
+							const int j = jb + (int)((threadIdx.x & 31) >> 2);
+							const bool have = j < nn && s_nearIdx[j] >= 0;
+							rs_part_store(W.coords + 3 * (size_t)(have ? s_nearIdx[j] : 0), newState, P.rmin, have, s_part[have ? j : 0]);
+						}
+						__syncthreads();
+						if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
+							const int j = (int)threadIdx.x, node = s_nearIdx[j];
+							RSSolution sol;
+							rs_finish(s_part[j], P.rmin, sol);
+							Conn c;
+							connect(P, W.coords + 3 * (size_t)node, newState, false, 0.0, c, &sol); // SteerExactly
+							s_candCost[j] = W.cost[node] + c.length;
+							s_candValid[j] = conn_valid(P, map, c) ? 1 : 0;
+						}
+					} else if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
+						const int node = s_nearIdx[threadIdx.x];
+						Conn c;
+						connect(P, W.coords + 3 * (size_t)node, newState, false, 0.0, c); // SteerExactly
+						s_candCost[threadIdx.x] = W.cost[node] + c.length;
+						s_candValid[threadIdx.x] = conn_valid(P, map, c) ? 1 : 0;
+					}
+					__syncthreads();
+					RRT_PHASE(5)
+					if (threadIdx.x == 0) {
+						int bestParent = -1;
+						double bestCost = PPX_INF;
+						for (int j = 0; j < nn; j++) {
+							if (s_nearIdx[j] < 0)
+								break;
+							if (s_candCost[j] < bestCost) {
+								nEdges++; // the reference evaluates IsPathValid only here (short-circuit &&)
+								if (s_candValid[j]) {
+									bestParent = s_nearIdx[j];
+									bestCost = s_candCost[j];
+								}
+							}
+						}
+						// Tree::Extend(newState, bestParentNode): an existing state returns its node unchanged;
+						// a null parent falls back to the nearest node of the target (tree.h:127-135)
+						int node = tree_find(W, newState, P.dim);
+						if (node < 0) {
+							if (n >= W.cap) {
+								status = PPX_ERR_CAPACITY;
+								s_done = 1;
+							} else {
+								node = n;
+								W.coords[3 * (size_t)node] = newState[0];
+								W.coords[3 * (size_t)node + 1] = newState[1];
+								W.coords[3 * (size_t)node + 2] = newState[2];
+								W.parent[node] = bestParent >= 0 ? bestParent : s_nearIdx[0];
+								tree_insert_hash(W, node, P.dim);
+								s_pendIdx[s_pendCount++] = node;
+								s_inserted = node;
+							}
+						}
+						if (!s_done) {
+							W.cost[node] = bestCost; // (*newNode)->info.costFromGoal = bestCost, also for an existing node
+							if (state_equal(newState, s_goal, P.dim)) { // RRTStar::IsSolution, rrt_star.h:136-139
+								solution = node;
+								status = PPX_OK;
+								s_done = 1;
+							}
+						}
+					}
+					RRT_PHASE(6)
 				}
-				// Tree::Extend(newState, bestParentNode): an existing state returns its node unchanged;
-				// a null parent falls back to the nearest node of the target (tree.h:127-135)
-				int node = tree_find(W, s_new, P.dim);
-				if (node < 0) {
-					if (n >= W.cap) {
-						status = PPX_ERR_CAPACITY;
-						s_ctl = CTL_DONE;
-					} else {
-						node = n++;
-						W.coords[3 * (size_t)node] = s_new[0];
-						W.coords[3 * (size_t)node + 1] = s_new[1];
-						W.coords[3 * (size_t)node + 2] = s_new[2];
-						W.parent[node] = bestParent >= 0 ? bestParent : s_nearIdx[0];
-						tree_insert_hash(W, node, P.dim);
-						s_pending = node;
+				__syncthreads();
+				const int ins = s_inserted;
+				if (ins >= 0)
+					n = ins + 1;
+				if (s_done) {
+					done = true;
+					break;
+				}
+				// the later samples of the batch: is the new node nearer than the nearest node they were steered from?
+				if (ins >= 0 && (int)threadIdx.x > b && (int)threadIdx.x < kSpec) {
+					const double d = state_dist2(s_bq[threadIdx.x], W.coords + 3 * (size_t)ins, P.dim);
+					if (d < s_bNearD2[threadIdx.x]) { // the new node has the largest index: it wins strictly only
+						s_bNear[threadIdx.x] = ins;
+						s_bNearD2[threadIdx.x] = d;
+						s_bStale[threadIdx.x] = 1;
 					}
 				}
-				if (s_ctl != CTL_DONE) {
-					W.cost[node] = bestCost; // (*newNode)->info.costFromGoal = bestCost, also for an existing node
-					if (state_equal(s_new, s_goal, P.dim)) { // RRTStar::IsSolution, rrt_star.h:136-139
-						solution = node;
-						status = PPX_OK;
-						s_ctl = CTL_DONE;
-					}
-				}
+				__syncthreads();
 			}
-			RRT_PHASE(6)
-			__syncthreads();
-			if (s_ctl == CTL_DONE)
-				break;
 		}
 		if (stats && threadIdx.x == 0)
 			for (int i = 0; i < 10; i++)
@@ -1145,9 +1262,10 @@ int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_
 		cudaStreamSynchronize(ctx->stream);
 		cudaMemcpy(st, d_stats, sizeof(st), cudaMemcpyDeviceToHost);
 		const double it = (double)std::max<unsigned long long>(1, st[8]), acc = (double)std::max<unsigned long long>(1, st[9]);
-		fprintf(stderr, "rrt stats (cluster %d, slices in %s): %llu iterations, %llu accepted | cycles per iteration: nearest %.0f, steer solve "
-			"%.0f, connect %.0f, steer check %.0f | per accepted iteration: neighbourhood %.0f, candidates %.0f, commit %.0f\n",
-			C, sliceCap ? "shared memory" : "global memory", st[8], st[9], st[0] / it, st[1] / it, st[2] / it, st[3] / it, st[4] / acc,
+		fprintf(stderr, "rrt stats (cluster %d, slices in %s, batches of %d samples): %llu iterations, %llu accepted, %llu re-steered | cycles "
+			"per iteration (batch phases shared by the samples of a batch): nearest %.0f, steer solve %.0f, connect + check %.0f | per accepted "
+			"iteration: neighbourhood %.0f, candidates %.0f, commit %.0f\n",
+			C, sliceCap ? "shared memory" : "global memory", kSpec, st[8], st[9], st[2], st[0] / it, st[1] / it, st[3] / it, st[4] / acc,
 			st[5] / acc, st[6] / acc);
 	}
 	PPX_LAUNCHED(ctx);
