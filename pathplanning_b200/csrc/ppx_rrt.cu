@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <cooperative_groups.h>
 #include "ppx_ctx.h"
+#include "ppx_fastlane.cuh"
 
 using namespace ppx;
 namespace cg = cooperative_groups;
@@ -138,6 +139,7 @@ struct RrtXch { // exchange areas in shared memory
 	NnEntry cand[kCandCap];
 	NnEntry thr;
 	int candCount;
+	int counts[kRrtMaxCluster];
 };
 
 // Cluster barrier.  cg::cluster_group::sync() is arrive.release + wait.acquire: SASS MEMBAR.ALL.GPU + UCGABAR_ARV +
@@ -487,10 +489,15 @@ __device__ void cluster_nearest(cg::cluster_group& cluster, const RrtWs& W, cons
 	cluster_barrier(!S.x);
 	cta_serve(cluster, W, S, cmd, dim, X);
 	cluster_barrier(!S.x);
+	if ((int)threadIdx.x < nq * S.C) { // one DSMEM read per thread, then the minimum over the CTAs from local memory
+		const int r = (int)threadIdx.x / nq, b = (int)threadIdx.x % nq;
+		X.gather[r][b] = cluster.map_shared_rank(X.ctaList, r)[b];
+	}
+	__syncthreads();
 	if ((int)threadIdx.x < nq) {
-		NnEntry best = X.ctaList[threadIdx.x];
+		NnEntry best = X.gather[0][threadIdx.x];
 		for (int r = 1; r < S.C; r++) {
-			const NnEntry e = cluster.map_shared_rank(X.ctaList, r)[threadIdx.x];
+			const NnEntry e = X.gather[r][threadIdx.x];
 			if (nn_closer(e.d, e.idx, best.d, best.idx))
 				best = e;
 		}
@@ -516,10 +523,13 @@ __device__ void cluster_knn(cg::cluster_group& cluster, const RrtWs& W, const Rr
 			break;
 		// candidates of all CTAs -> X.gather (256 entries), ranked by counting
 		NnEntry* flat = &X.gather[0][0];
+		if ((int)threadIdx.x < S.C)
+			X.counts[threadIdx.x] = *cluster.map_shared_rank(&X.candCount, (int)threadIdx.x);
+		__syncthreads();
 		int total = 0, mine = -1, myRank = 0;
 		bool overflow = false;
 		for (int r = 0; r < S.C; r++) {
-			const int cnt = *cluster.map_shared_rank(&X.candCount, r);
+			const int cnt = X.counts[r];
 			overflow |= cnt > kCandCap;
 			if (mine < 0 && (int)threadIdx.x < total + cnt) {
 				mine = (int)threadIdx.x - total;
@@ -734,6 +744,20 @@ __device__ bool conn_valid(const RrtDev& P, const MapDev& map, const Conn& c)
 
 namespace {
 
+// IsPathValid of an UNTRUNCATED connection (SteerExactly: the parent candidates of RRT*).  A whole Reeds-Shepp path with its own
+// length is exactly what the search kernel's shots are: the certified FP32 cell filter of ppx_fastlane.cuh gives the exact
+// loop's verdict (same cells, same steps) at a fraction of the FP64 walker's cost per sample.  Anything else -- straight
+// connections, a stored length that is not the segment's own (truncation, trap H9) -- takes the exact loop.
+__device__ bool conn_valid_exactly(const RrtDev& P, const MapDev& map, const FastMap& fm, const Conn& c)
+{
+	if (P.validator == 1 && P.connection == 1 && c.length > 0.0 && rs_total_length(c.seg) * P.rmin == c.length) {
+		const Pose a = { c.from[0], c.from[1], c.from[2] };
+		float last;
+		return rs_is_path_valid_filtered(map, fm, a, c.seg, P.rmin, P.minSafeRadius, P.minStep, &last, nullptr);
+	}
+	return conn_valid(P, map, c);
+}
+
 // Reeds-Shepp solves spread over the CTA: warp w evaluates base formulas w and w + 8 (of 12) of up to eight pairs, one pair
 // per quad of lanes (rs_quad_part: the four mirrored goals on the quad's lanes, no divergence on the formula switch); the
 // per-warp partial minima of a pair are combined by the same lexicographic (float cost, word) rule.  One warp walking
@@ -785,7 +809,7 @@ __device__ __forceinline__ void rs_part_store(const double* from, const double* 
 
 enum { CTL_RUN = 0, CTL_SKIP = 1, CTL_DONE = 2 };
 
-__global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64_t ntrees, const double* __restrict__ starts,
+__global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, FastMap fm, int64_t ntrees, const double* __restrict__ starts,
 	const double* __restrict__ goals, const unsigned long long* __restrict__ seeds, char* __restrict__ slabs, size_t slabBytes,
 	int cap, int hashCap, int sliceCap, ppx_rrt_result* __restrict__ results, int64_t nodeCapacity, double* __restrict__ outNodes,
 	int32_t* __restrict__ outParents, double* __restrict__ outCosts, unsigned long long* __restrict__ queue,
@@ -1032,7 +1056,7 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, int64
 							Conn c;
 							connect(P, W.coords + 3 * (size_t)node, newState, false, 0.0, c, &sol); // SteerExactly
 							s_candCost[j] = W.cost[node] + c.length;
-							s_candValid[j] = conn_valid(P, map, c) ? 1 : 0;
+							s_candValid[j] = conn_valid_exactly(P, map, fm, c) ? 1 : 0;
 						}
 					} else if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
 						const int node = s_nearIdx[threadIdx.x];
@@ -1252,7 +1276,10 @@ int ppx_rrt_run(ppx_ctx* ctx, const ppx_rrt_params* params, const ppx_validator_
 		PPX_CUDA(ctx, cudaMalloc(&d_stats, 10 * sizeof(unsigned long long)));
 	if (statsOn)
 		PPX_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 10 * sizeof(unsigned long long), ctx->stream));
-	PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_rrt, P, map, (int64_t)ntrees, (const double*)(base + oStarts), (const double*)(base + oGoals),
+	FastMap fm = ctx->has_map ? fast_map_derive(ctx->desc) : FastMap {};
+	if (!ctx->rs_filter)
+		fm.enabled = 0;
+	PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_rrt, P, map, fm, (int64_t)ntrees, (const double*)(base + oStarts), (const double*)(base + oGoals),
 		(const unsigned long long*)(base + oSeeds), base + oSlabs, slab, cap, hashCap, sliceCap, (ppx_rrt_result*)(base + oRes),
 		(int64_t)(wantNodes ? node_capacity : 0), nodes ? (double*)(base + oNodes) : (double*)nullptr,
 		parents ? (int32_t*)(base + oPar) : (int32_t*)nullptr, costs ? (double*)(base + oCost) : (double*)nullptr, ctx->d_queue,
