@@ -292,6 +292,29 @@ int ppx_rs_interpolate(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* edges, double
  */
 int ppx_wavefront(ppx_ctx* ctx, int64_t n, const double* goals, float* cost, uint8_t* explored);
 int ppx_wavefront_dev(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored);
+/*
+ * ppx_wavefront_dev with NO allocation at call time.  It has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernel, same results bit for bit; the kernel's scratch (per goal in flight: a tag word per
+ * cell + the four-slot bucket ring) lives in a file-scope `static __device__` array of PPX_WAVEFRONT_STATIC_BYTES, which
+ * every GPU that loads the library holds until the process exits.  The call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine; it only enqueues on the context's stream (two 8-byte memsets and the kernel).
+ *   limit     the scratch of at least one goal must fit: 4 bytes per cell + 48 bytes x (the power of two >= 8 (rows + cols)).
+ *             Any map of up to PPX_WAVEFRONT_STATIC_MAX_CELLS cells with rows + cols <= 65536 does (C3's 2000 x 2000
+ *             included); a larger map may not, and is then rejected with PPX_ERR_CAPACITY and a message that states
+ *             the bytes needed.  n is not limited: the goals in flight at once are as many as fit (C2, 400 x 400: 64),
+ *             the rest queue behind them, so big batches are slower than through ppx_wavefront_dev.
+ *   d_status  optional caller-owned device word: 0 ok, 1 a frontier bucket overflowed its ring slot, 2 internal
+ *             (what ppx_wavefront turns into PPX_ERR_CAPACITY); NULL keeps it in the static array.
+ *   set-up    the first call on a device resolves the array's device address (cudaGetSymbolAddress, once per device, may
+ *             load the module): make one call outside any graph capture.
+ *   sharing   every call on a device shares the one array, which keeps the previous call's contents (the call clears what
+ *             must start at zero).  Calls that overlap on the GPU -- two contexts or two streams on one device -- race:
+ *             serialise them.  Calls on one context's stream are ordered and safe.
+ */
+#define PPX_WAVEFRONT_STATIC_BYTES (64 << 20)
+#define PPX_WAVEFRONT_STATIC_MAX_CELLS (4 << 20)
+int ppx_wavefront_dev_static(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored, int32_t* d_status);
 
 /* ------------------------------------------------------------------------------------------ */
 /* A1-A6, A9: Hybrid A* successor generation, heuristics and the batched on-device graph search  */

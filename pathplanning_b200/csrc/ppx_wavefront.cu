@@ -26,6 +26,7 @@
 // The frontier is always compact (bucket lists, never a sweep over the grid); one CTA per goal,
 // as many goals in flight as CTAs fit on the 148 SMs.
 #include <algorithm>
+#include <mutex>
 #include "ppx_ctx.h"
 
 using namespace ppx;
@@ -399,7 +400,44 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_wavefront(MapDev map, 
 
 }
 
-int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored)
+// ---- ppx_wavefront_dev_static: the same kernel with its scratch in a file-scope device array (no allocation at call time) ----
+// Every GPU that loads the library holds these 64 MiB until the process exits.  In host code `g_wf_static` is a host-side
+// stand-in for the symbol, not a device address: the address a kernel can use comes from cudaGetSymbolAddress, once per
+// device, with that device current (wf_static_base).
+constexpr size_t kWfStaticBytes = (size_t)PPX_WAVEFRONT_STATIC_BYTES;
+constexpr size_t kWfStaticHeader = 256; // control words: work-queue cursor at +0, status word at +64
+static __device__ __align__(256) unsigned char g_wf_static[kWfStaticBytes];
+
+namespace {
+
+constexpr int kWfMaxDevices = 64;
+std::mutex g_wfStaticMutex;
+unsigned char* g_wfStaticPtr[kWfMaxDevices] = {};
+
+// Device address of g_wf_static on ctx's device (the caller holds PPX_GUARD: that device is current).
+int wf_static_base(ppx_ctx* ctx, unsigned char** out)
+{
+	if (ctx->device < 0 || ctx->device >= kWfMaxDevices)
+		return ppx_fail(ctx, PPX_ERR_INVALID, "wavefront (static scratch): device ordinal %d out of range", ctx->device);
+	std::lock_guard<std::mutex> lock(g_wfStaticMutex);
+	if (!g_wfStaticPtr[ctx->device]) {
+		void* p = nullptr;
+		cudaError_t err = cudaGetSymbolAddress(&p, g_wf_static);
+		if (err != cudaSuccess || !p)
+			return ppx_fail(ctx, PPX_ERR_CUDA, "wavefront (static scratch): cudaGetSymbolAddress: %s", cudaGetErrorString(err));
+		g_wfStaticPtr[ctx->device] = (unsigned char*)p;
+	}
+	*out = g_wfStaticPtr[ctx->device];
+	return PPX_OK;
+}
+
+}
+
+// `staticBase`: nullptr = scratch from the context's grow-only allocation (ppx_scratch), else the device address of
+// g_wf_static: nothing is allocated, the number of goals in flight is what fits into the array, and a map of which not even
+// one goal fits is rejected.  `d_statusOut`: caller-owned device status word (static form only; may be null).
+static int wavefront_launch_impl(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored,
+	unsigned char* staticBase, int* d_statusOut)
 {
 	const int rows = ctx->desc.rows, cols = ctx->desc.cols;
 	if (rows > 65535 || cols > 65535)
@@ -432,21 +470,46 @@ int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* 
 		cap >>= 1;
 	WfWork work;
 	work.cap = cap;
+	if (staticBase) {
+		// per goal in flight: tag grid + ring keys + ring cells, each part rounded to 256 bytes
+		const size_t perCta = (((size_t)ncells * 4 + 255) & ~(size_t)255) + (size_t)kRing * cap * 8 + (((size_t)kRing * cap * 4 + 255) & ~(size_t)255);
+		const size_t room = kWfStaticBytes - kWfStaticHeader;
+		if (perCta > room)
+			return ppx_fail(ctx, PPX_ERR_CAPACITY, "wavefront (static scratch): a %d x %d map needs %zu bytes of scratch per goal in flight, the "
+				"static array holds %zu (maps of up to %d cells with rows + cols <= 65536 always fit); use ppx_wavefront_dev", rows, cols, perCta,
+				room, PPX_WAVEFRONT_STATIC_MAX_CELLS);
+		ctas = (int)std::min<size_t>((size_t)ctas, room / perCta);
+	}
 	char* base;
 	size_t bytesTag = (size_t)ctas * ncells * 4, bytesKeys = (size_t)ctas * kRing * cap * 8, bytesCells = (size_t)ctas * kRing * cap * 4;
 	size_t offKeys = (bytesTag + 255) & ~(size_t)255, offCells = offKeys + bytesKeys, offStatus = offCells + ((bytesCells + 255) & ~(size_t)255);
-	PPX_CHECK(ppx_scratch(ctx, 4, offStatus + 256, (void**)&base));
+	unsigned long long* d_cursor = ctx->d_queue;
+	int* d_status;
+	if (staticBase) {
+		// the array keeps the last call's contents: the cursor and the status word are cleared here, the tag grid of a goal by
+		// the kernel itself before it starts that goal; the ring slots are written before they are read
+		base = (char*)staticBase + kWfStaticHeader;
+		d_cursor = (unsigned long long*)staticBase;
+		d_status = d_statusOut ? d_statusOut : (int*)(staticBase + 64);
+	} else {
+		PPX_CHECK(ppx_scratch(ctx, 4, offStatus + 256, (void**)&base));
+		d_status = (int*)(base + offStatus);
+	}
 	work.tag = (uint32_t*)base;
 	work.keys = (unsigned long long*)(base + offKeys);
 	work.cells = (uint32_t*)(base + offCells);
-	int* d_status = (int*)(base + offStatus);
 	PPX_CUDA(ctx, cudaMemsetAsync(d_status, 0, sizeof(int), ctx->stream));
-	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
+	PPX_CUDA(ctx, cudaMemsetAsync(d_cursor, 0, sizeof(unsigned long long), ctx->stream));
 	kernel<<<ctas, threads, smem, ctx->stream>>>(ctx->map_dev(), ctx->d_occ8, n, d_goals, d_cost, d_explored, work, sortCap,
-		ctx->d_queue, d_status);
+		d_cursor, d_status);
 	PPX_LAUNCHED(ctx);
 	ctx->d_wf_status = d_status;
 	return PPX_OK;
+}
+
+int ppx_wavefront_launch(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored)
+{
+	return wavefront_launch_impl(ctx, n, d_goals, d_cost, d_explored, nullptr, nullptr);
 }
 
 extern "C" {
@@ -462,6 +525,21 @@ int ppx_wavefront_dev(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_c
 	if (n == 0)
 		return PPX_OK;
 	return ppx_wavefront_launch(ctx, n, d_goals, d_cost, d_explored);
+}
+
+int ppx_wavefront_dev_static(ppx_ctx* ctx, int64_t n, const double* d_goals, float* d_cost, uint8_t* d_explored, int32_t* d_status)
+{
+	PPX_GUARD(ctx);
+	if (!ctx)
+		return PPX_ERR_INVALID;
+	if (!ctx->has_map)
+		return ppx_fail(ctx, PPX_ERR_STATE, "no map uploaded (ppx_map_upload)");
+	PPX_REQUIRE(ctx, n >= 0 && (n == 0 || (d_goals && d_cost)), "bad arguments");
+	if (n == 0)
+		return PPX_OK;
+	unsigned char* base = nullptr;
+	PPX_CHECK(wf_static_base(ctx, &base));
+	return wavefront_launch_impl(ctx, n, d_goals, d_cost, d_explored, base, (int*)d_status);
 }
 
 int ppx_wavefront(ppx_ctx* ctx, int64_t n, const double* goals, float* cost, uint8_t* explored)

@@ -98,6 +98,7 @@ _SIGS = {
     "ppx_rs_interpolate": (C.c_int, [_p, _i64, _p, C.c_double, C.c_int32, _p, _p]),
     "ppx_wavefront": (C.c_int, [_p, _i64, _p, _p, _p]),
     "ppx_wavefront_dev": (C.c_int, [_p, _i64, _p, _p, _p]),
+    "ppx_wavefront_dev_static": (C.c_int, [_p, _i64, _p, _p, _p, _p]),
     "ppx_knn": (C.c_int, [_p, C.c_int32, _i64, _p, _i64, _p, C.c_int32, _p, _p]),
     "ppx_knn_dev": (C.c_int, [_p, C.c_int32, _i64, _p, _i64, _p, C.c_int32, _p, _p]),
     "ppx_rrt_run": (C.c_int, [_p, C.POINTER(RRTParamsC), _p, _i64, _p, _p, _p, _p, _i64, _p, _p, _p]),
