@@ -633,7 +633,7 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 	if (ctx->search_engine == 1) {
 		// one CTA per query: master warp + worker warps (ppx_hybrid_cta.cuh).  The key table lives in shared memory
 		// (16-bit entries) when it fits; a batch much larger than the GPU holds runs with one worker per master and
-		// twice the CTAs, a batch the GPU can hold at once with three workers per master (shortest critical path).
+		// twice the CTAs, a smaller batch with three workers per master (shortest critical path).
 		const int nCs = 2 * h->dev.numDeltas;
 		slab = (cta_ws_bytes(L.maxNodes, L.tableSize, nCs) + 255) & ~(size_t)255;
 		const bool smemTable = (size_t)L.tableSize * 2 <= 28 * 1024 && L.maxNodes + 2 <= 65535
@@ -656,7 +656,9 @@ int launch_search(ppx_hybrid* h, int64_t nq, const double* d_starts, const doubl
 		int perSm4 = 1, perSm2 = 1;
 		PPX_CHECK(perSmOf(4, &perSm4));
 		PPX_CHECK(perSmOf(2, &perSm2));
-		ctaWarps = nq >= 2 * (int64_t)ctx->num_sms * perSm4 ? 2 : 4;
+		// measured crossover on C4 (search phase, 2 / 4 warps): 1024 queries 69.6 / 59.3 ms, 1536: 82.3 / 75.7, 2048: 86.4 / 86.8,
+		// 3072: 109 / 118, 4096: 134 / 155
+		ctaWarps = nq > 4 * (int64_t)ctx->num_sms * perSm4 ? 2 : 4;
 		if (getenv("PPX_SEARCH_WARPS"))
 			ctaWarps = atoi(getenv("PPX_SEARCH_WARPS")) == 2 ? 2 : 4;
 		ctaKernel = pick(ctaWarps);
