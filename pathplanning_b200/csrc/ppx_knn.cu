@@ -13,6 +13,11 @@
 // neighbour order must be exact in FP64 (DESIGN.md "kNN").  Few queries (the inner loop of a single
 // RRT tree): one CTA per query, threads stride over the points and a k-round block argmin merges
 // their private lists.
+//
+// The per-thread candidate list has a COMPILE-TIME length K >= k (1, 4, 8, 16 or 32): it lives in registers with static
+// indexing (insertion = one pass of compare-and-swap with a carried element, pop = shift).  With a run-time length it sat
+// in local memory (384-400 byte stack frames) and every pair paid a local load for the threshold compare: the round-1
+// kernels issued on 31 % of the cycles with 3.3 long-scoreboard stall cycles per issue (profiles/r2o_k_knn_*).
 #include <algorithm>
 #include "ppx_ctx.h"
 
@@ -21,25 +26,53 @@ namespace {
 constexpr int kMaxK = 32;
 constexpr int kTile = 1024; // points per shared-memory tile (24 KB at D = 3)
 
-struct Best {
-	double d[kMaxK];
-	int idx[kMaxK];
-};
-
 __device__ __forceinline__ bool closer(double da, int ia, double db, int ib) { return da < db || (da == db && ia < ib); }
 
-// insert (d, idx) into the ascending list of length k (the caller checked it beats the last entry)
-__device__ __forceinline__ void insert_sorted(double* bd, int* bi, int k, double d, int idx)
-{
-	int p = k - 1;
-	while (p > 0 && closer(d, idx, bd[p - 1], bi[p - 1])) {
-		bd[p] = bd[p - 1];
-		bi[p] = bi[p - 1];
-		p--;
+constexpr int kNoIdx = 0x7fffffff;
+
+// ascending candidate list of K entries in registers
+template <int K>
+struct RegList {
+	double d[K];
+	int idx[K];
+	__device__ __forceinline__ void clear()
+	{
+		#pragma unroll
+		for (int i = 0; i < K; i++) {
+			d[i] = __longlong_as_double(0x7ff0000000000000LL);
+			idx[i] = kNoIdx;
+		}
 	}
-	bd[p] = d;
-	bi[p] = idx;
-}
+	// keeps the k smallest (k <= K): entries beyond k are never read, so inserting against the whole list is harmless,
+	// but the early-out threshold is the k-th entry
+	__device__ __forceinline__ void offer(double nd, int nidx, int k)
+	{
+		if (!closer(nd, nidx, d[K - 1], idx[K - 1]))
+			return;
+		#pragma unroll
+		for (int i = 0; i < K; i++) {
+			if (closer(nd, nidx, d[i], idx[i])) {
+				const double td = d[i];
+				const int ti = idx[i];
+				d[i] = nd;
+				idx[i] = nidx;
+				nd = td;
+				nidx = ti;
+			}
+		}
+		(void)k;
+	}
+	__device__ __forceinline__ void pop()
+	{
+		#pragma unroll
+		for (int i = 0; i + 1 < K; i++) {
+			d[i] = d[i + 1];
+			idx[i] = idx[i + 1];
+		}
+		d[K - 1] = __longlong_as_double(0x7ff0000000000000LL);
+		idx[K - 1] = kNoIdx;
+	}
+};
 
 template <int D>
 __device__ __forceinline__ double dist2(const double* __restrict__ a, const double* __restrict__ b)
@@ -53,7 +86,7 @@ __device__ __forceinline__ double dist2(const double* __restrict__ a, const doub
 	return r;
 }
 
-template <int D>
+template <int D, int K>
 __global__ void __launch_bounds__(256) k_knn_thread_per_query(int64_t np, const double* __restrict__ points, int64_t nq,
 	const double* __restrict__ queries, int k, int* __restrict__ indices, double* __restrict__ dists)
 {
@@ -64,12 +97,8 @@ __global__ void __launch_bounds__(256) k_knn_thread_per_query(int64_t np, const 
 	#pragma unroll
 	for (int i = 0; i < D; i++)
 		qv[i] = active ? queries[q * D + i] : 0.0;
-	double bd[kMaxK];
-	int bi[kMaxK];
-	for (int i = 0; i < k; i++) {
-		bd[i] = __longlong_as_double(0x7ff0000000000000LL);
-		bi[i] = 0x7fffffff;
-	}
+	RegList<K> best;
+	best.clear();
 	for (int64_t base = 0; base < np; base += kTile) {
 		const int m = (int)min((int64_t)kTile, np - base);
 		__syncthreads();
@@ -78,87 +107,99 @@ __global__ void __launch_bounds__(256) k_knn_thread_per_query(int64_t np, const 
 		__syncthreads();
 		if (!active)
 			continue;
-		for (int j = 0; j < m; j++) {
-			double d = dist2<D>(qv, s_pts + j * D);
-			int idx = (int)(base + j);
-			if (closer(d, idx, bd[k - 1], bi[k - 1]))
-				insert_sorted(bd, bi, k, d, idx);
+		#pragma unroll 4
+		for (int j = 0; j < m; j++)
+			best.offer(dist2<D>(qv, s_pts + j * D), (int)(base + j), k);
+	}
+	if (active) {
+		#pragma unroll
+		for (int i = 0; i < K; i++) {
+			if (i < k) {
+				const bool have = best.idx[i] != kNoIdx;
+				indices[q * k + i] = have ? best.idx[i] : -1;
+				if (dists)
+					dists[q * k + i] = best.d[i];
+			}
 		}
 	}
-	if (active)
-		for (int i = 0; i < k; i++) {
-			bool have = bi[i] != 0x7fffffff;
-			indices[q * k + i] = have ? bi[i] : -1;
-			if (dists)
-				dists[q * k + i] = bd[i];
-		}
 }
 
 // One CTA per query.
-template <int D>
+template <int D, int K>
 __global__ void __launch_bounds__(256) k_knn_cta_per_query(int64_t np, const double* __restrict__ points, int64_t nq,
 	const double* __restrict__ queries, int k, int* __restrict__ indices, double* __restrict__ dists)
 {
 	__shared__ double s_d[8];
 	__shared__ int s_i[8];
-	__shared__ int s_owner[8];
-	__shared__ int s_winner;
 	for (int64_t q = blockIdx.x; q < nq; q += gridDim.x) {
 		double qv[D];
 		#pragma unroll
 		for (int i = 0; i < D; i++)
 			qv[i] = queries[q * D + i];
-		double bd[kMaxK];
-		int bi[kMaxK];
-		for (int i = 0; i < k; i++) {
-			bd[i] = __longlong_as_double(0x7ff0000000000000LL);
-			bi[i] = 0x7fffffff;
-		}
-		for (int64_t j = threadIdx.x; j < np; j += blockDim.x) {
-			double d = dist2<D>(qv, points + j * D);
-			if (closer(d, (int)j, bd[k - 1], bi[k - 1]))
-				insert_sorted(bd, bi, k, d, (int)j);
-		}
-		// k-way merge of the private ascending lists: k rounds of block argmin over the list heads
-		int head = 0;
+		RegList<K> best;
+		best.clear();
+		for (int64_t j = threadIdx.x; j < np; j += blockDim.x)
+			best.offer(dist2<D>(qv, points + j * D), (int)j, k);
+		// k-way merge of the private ascending lists: k rounds of block argmin over the list heads; point indices are
+		// unique, so exactly the thread whose head is the minimum pops
 		for (int round = 0; round < k; round++) {
-			double d = head < k ? bd[head] : __longlong_as_double(0x7ff0000000000000LL);
-			int idx = head < k ? bi[head] : 0x7fffffff;
-			int owner = threadIdx.x;
+			double d = best.d[0];
+			int idx = best.idx[0];
 			#pragma unroll
 			for (int o = 16; o > 0; o >>= 1) {
-				double od = __shfl_down_sync(0xffffffffu, d, o);
-				int oi = __shfl_down_sync(0xffffffffu, idx, o);
-				int oo = __shfl_down_sync(0xffffffffu, owner, o);
+				const double od = __shfl_xor_sync(0xffffffffu, d, o);
+				const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
 				if (closer(od, oi, d, idx)) {
 					d = od;
 					idx = oi;
-					owner = oo;
 				}
 			}
 			if ((threadIdx.x & 31) == 0) {
 				s_d[threadIdx.x >> 5] = d;
 				s_i[threadIdx.x >> 5] = idx;
-				s_owner[threadIdx.x >> 5] = owner;
 			}
 			__syncthreads();
+			double bd = s_d[0];
+			int bi = s_i[0];
+			#pragma unroll
+			for (int w = 1; w < 8; w++)
+				if (closer(s_d[w], s_i[w], bd, bi)) {
+					bd = s_d[w];
+					bi = s_i[w];
+				}
 			if (threadIdx.x == 0) {
-				int best = 0;
-				for (int w = 1; w < (int)(blockDim.x >> 5); w++)
-					if (closer(s_d[w], s_i[w], s_d[best], s_i[best]))
-						best = w;
-				bool have = s_i[best] != 0x7fffffff;
-				indices[q * k + round] = have ? s_i[best] : -1;
+				indices[q * k + round] = bi != kNoIdx ? bi : -1;
 				if (dists)
-					dists[q * k + round] = s_d[best];
-				s_winner = have ? s_owner[best] : -1;
+					dists[q * k + round] = bd;
 			}
-			__syncthreads();
-			if ((int)threadIdx.x == s_winner)
-				head++;
+			if (bi != kNoIdx && best.idx[0] == bi)
+				best.pop();
 			__syncthreads();
 		}
 	}
+}
+
+template <int D>
+void knn_launch(ppx_ctx* ctx, bool perThread, int blocks, int64_t np, const double* points, int64_t nq, const double* queries, int k,
+	int* indices, double* dists)
+{
+	#define PPX_KNN_CASE(K) \
+		if (perThread) \
+			k_knn_thread_per_query<D, K><<<blocks, 256, 0, ctx->stream>>>(np, points, nq, queries, k, indices, dists); \
+		else \
+			k_knn_cta_per_query<D, K><<<blocks, 256, 0, ctx->stream>>>(np, points, nq, queries, k, indices, dists);
+	if (k == 1) {
+		PPX_KNN_CASE(1)
+	} else if (k <= 4) {
+		PPX_KNN_CASE(4)
+	} else if (k <= 8) {
+		PPX_KNN_CASE(8)
+	} else if (k <= 16) {
+		PPX_KNN_CASE(16)
+	} else {
+		PPX_KNN_CASE(32)
+	}
+	#undef PPX_KNN_CASE
 }
 
 }
@@ -176,19 +217,12 @@ int ppx_knn_dev(ppx_ctx* ctx, int32_t dim, int64_t npoints, const double* d_poin
 	PPX_REQUIRE(ctx, npoints < 0x7fffffff, "knn: too many points");
 	if (nqueries == 0)
 		return PPX_OK;
-	if (nqueries >= 4 * (int64_t)ctx->num_sms) {
-		int blocks = (int)((nqueries + 255) / 256);
-		if (dim == 2)
-			k_knn_thread_per_query<2><<<blocks, 256, 0, ctx->stream>>>(npoints, d_points, nqueries, d_queries, k, d_indices, d_dist2);
-		else
-			k_knn_thread_per_query<3><<<blocks, 256, 0, ctx->stream>>>(npoints, d_points, nqueries, d_queries, k, d_indices, d_dist2);
-	} else {
-		int blocks = (int)nqueries;
-		if (dim == 2)
-			k_knn_cta_per_query<2><<<blocks, 256, 0, ctx->stream>>>(npoints, d_points, nqueries, d_queries, k, d_indices, d_dist2);
-		else
-			k_knn_cta_per_query<3><<<blocks, 256, 0, ctx->stream>>>(npoints, d_points, nqueries, d_queries, k, d_indices, d_dist2);
-	}
+	const bool perThread = nqueries >= 4 * (int64_t)ctx->num_sms;
+	const int blocks = perThread ? (int)((nqueries + 255) / 256) : (int)nqueries;
+	if (dim == 2)
+		knn_launch<2>(ctx, perThread, blocks, npoints, d_points, nqueries, d_queries, k, d_indices, d_dist2);
+	else
+		knn_launch<3>(ctx, perThread, blocks, npoints, d_points, nqueries, d_queries, k, d_indices, d_dist2);
 	PPX_LAUNCHED(ctx);
 	return PPX_OK;
 }
