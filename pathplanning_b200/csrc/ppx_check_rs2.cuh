@@ -189,8 +189,8 @@ struct SolveArgs {
 	int shortest;
 };
 
-template <bool kAudit, bool kSolve>
-__global__ void __launch_bounds__(kThreads, kSolve ? 3 : kCheck2Ctas) k_check_rs2(MapDev map, FastMap fm, int64_t n,
+template <bool kAudit, bool kSolve, int kCtas = (kSolve ? 3 : kCheck2Ctas)>
+__global__ void __launch_bounds__(kThreads, kCtas) k_check_rs2(MapDev map, FastMap fm, int64_t n,
 	const ppx_rs_edge* __restrict__ edgesIn, double r, float minSafeRadius, float minStep, uint8_t* __restrict__ valid,
 	float* __restrict__ last, uint32_t* __restrict__ samples, unsigned long long* __restrict__ queue, AuditOut* audit,
 	unsigned long long* nextQueue, SolveArgs sa)

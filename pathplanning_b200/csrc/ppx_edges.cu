@@ -275,7 +275,8 @@ __device__ __forceinline__ void store_rs_edge(ppx_rs_edge* e, const Pose& start,
 }
 
 // check != 0: fused PathConnectionReedsShepp::Connect + IsPathValid
-__global__ void __launch_bounds__(kThreads) k_rs_solve(MapDev map, int64_t n, const double* __restrict__ starts,
+template <int kMinBlocks, bool kCheck>
+__global__ void __launch_bounds__(kThreads, kMinBlocks) k_rs_solve(MapDev map, int64_t n, const double* __restrict__ starts,
 	const double* __restrict__ goals, ppx_rs_cost_params cp, int check, float minSafeRadius, float minStep,
 	ppx_rs_edge* __restrict__ edges, int32_t* __restrict__ word, double* __restrict__ length, float* __restrict__ cost,
 	uint8_t* __restrict__ valid, float* __restrict__ last)
@@ -296,7 +297,7 @@ __global__ void __launch_bounds__(kThreads) k_rs_solve(MapDev map, int64_t n, co
 			length[i] = sol.mLength * cp.min_turning_radius;
 		if (cost)
 			cost[i] = sol.cost;
-		if (check) {
+		if (kCheck && check) {
 			float l;
 			bool ok = rs_is_path_valid(map, s, sol.seg, cp.min_turning_radius, minSafeRadius, minStep, &l, nullptr);
 			valid[i] = ok ? 1 : 0;
@@ -747,7 +748,9 @@ int ppx_rs_solve_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, const doub
 			d_cost);
 	} else {
 		MapDev none {};
-		k_rs_solve<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(none, n, d_starts, d_goals, *cp, 0, 0.0f, 0.0f,
+		// 4 CTAs per SM (128 registers): 1.25 ms per 1M pairs against 1.61 ms at 2 (236 registers); ncu at 2: FP64 pipe 13 %,
+		// issue slots 35 % busy on 8 warps per SM (profiles/r2t_k_rs_solve_*) -- latency-bound, not FP64-bound
+		k_rs_solve<4, false><<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(none, n, d_starts, d_goals, *cp, 0, 0.0f, 0.0f,
 			d_edges, d_word, d_length, d_cost, nullptr, nullptr);
 	}
 	PPX_LAUNCHED(ctx);
@@ -774,11 +777,13 @@ int ppx_connect_check_rs_dev(ppx_ctx* ctx, int64_t n, const double* d_starts, co
 		SolveArgs sa { d_starts, d_goals, d_solved, d_word, d_length, d_cost, cp->reverse_cost_multiplier, cp->forward_cost_multiplier,
 			cp->direction_switching_cost, cp->shortest };
 		PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));
-		k_check_rs2<false, true><<<grid_for(ctx, n, kThreads, 3), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, nullptr,
+		// 5 CTAs per SM (96 registers, some spills): 2.18 ms per 1M pairs against 2.68 ms at 3 (168 registers) -- the solver
+		// is a chain of dependent FP64 latencies, more warps hide it (sweep 3 / 4 / 5 / 6: 2.68 / 2.32 / 2.18 / 2.32 ms)
+		k_check_rs2<false, true, 5><<<grid_for(ctx, n, kThreads, 5), kThreads, 0, ctx->stream>>>(ctx->map_dev(), fm, n, nullptr,
 			cp->min_turning_radius, vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, nullptr, ctx->d_queue,
 			nullptr, nullptr, sa);
 	} else {
-		k_rs_solve<<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_starts, d_goals, *cp, 1,
+		k_rs_solve<2, true><<<grid_for(ctx, n, kThreads, 16), kThreads, 0, ctx->stream>>>(ctx->map_dev(), n, d_starts, d_goals, *cp, 1,
 			vp->min_safe_radius, vp->min_path_interpolation_distance, nullptr, d_word, d_length, d_cost, d_valid, d_last);
 	}
 	PPX_LAUNCHED(ctx);
