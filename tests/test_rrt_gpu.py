@@ -34,7 +34,10 @@ def test_knn_reference_tree_cases(ctx):
     assert set(idx[0].tolist()) == {2, 3}
 
 
-@pytest.mark.parametrize("dim,npts,nq,k", [(2, 5000, 3, 7), (2, 20000, 4000, 11), (3, 100000, 2000, 11), (3, 7, 600, 10)])
+@pytest.mark.parametrize("dim,npts,nq,k", [(2, 5000, 3, 7), (2, 20000, 4000, 11), (3, 100000, 2000, 11), (3, 7, 600, 10),
+                                           # every compile-time list length of the kernels (1, 4, 8, 16, 32), both mappings
+                                           (3, 3000, 2, 1), (3, 3000, 700, 1), (2, 3000, 2, 4), (3, 3000, 700, 3), (3, 3000, 5, 8),
+                                           (2, 3000, 700, 16), (3, 3000, 4, 17), (3, 3000, 700, 32), (2, 40, 3, 32)])
 def test_knn_matches_bruteforce(ctx, dim, npts, nq, k):
     rng = np.random.default_rng(dim * 1000 + k)
     pts = rng.uniform(-50, 50, (npts, dim))
