@@ -54,9 +54,9 @@ int ppx_ctx_synchronize(ppx_ctx* ctx);
 /* Options: "rs_filter" (default 1; 0 = the Reeds-Shepp edge checker evaluates every sample with the
  * exact FP64 restatement, for A/B tests of the FP32 cell filter).    "rs_overlap" (default 0; 1 = consecutive ppx_check_edges_rs_dev calls on this context may overlap: a call's kernel
  * starts filling the SMs while the last long sample chains of the previous call drain (programmatic dependent
- * launch).  The caller guarantees that the output arrays of a call do not alias those of the previous call and
- * that its inputs are not produced by it; any other work submitted to the stream still waits for every earlier
- * call to complete.) */
+ * launch; up to three calls are resident on the GPU at once).  The caller guarantees that the output arrays of a call do
+ * not alias those of the previous THREE calls and that its inputs are not produced by them; any other work submitted to
+ * the stream still waits for every earlier call to complete.) */
 int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value);
 const char* ppx_last_error(const ppx_ctx* ctx);
 /* Number of kernels this context launched since creation (bench.py's gpu_launches). */

@@ -144,8 +144,8 @@ int ppx_ctx_create(int device, ppx_ctx** out)
 	ctx->stream = ctx->own_stream;
 	PPX_CUDA(ctx, cudaDeviceGetAttribute(&ctx->num_sms, cudaDevAttrMultiProcessorCount, device));
 	PPX_CUDA(ctx, cudaMalloc(&ctx->d_queue, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
-	PPX_CUDA(ctx, cudaMalloc(&ctx->d_rsq, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
-	PPX_CUDA(ctx, cudaMemset(ctx->d_rsq, 0, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
+	PPX_CUDA(ctx, cudaMalloc(&ctx->d_rsq, ppx_ctx::kRsqSlots * sizeof(unsigned long long)));
+	PPX_CUDA(ctx, cudaMemset(ctx->d_rsq, 0, ppx_ctx::kRsqSlots * sizeof(unsigned long long)));
 	*out = ctx;
 	return PPX_OK;
 }
@@ -217,7 +217,7 @@ int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value)
 	}
 	if (!strcmp(name, "rs_overlap")) {
 		PPX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-		PPX_CUDA(ctx, cudaMemset(ctx->d_rsq, 0, ppx_ctx::kMaxChunks * sizeof(unsigned long long)));
+		PPX_CUDA(ctx, cudaMemset(ctx->d_rsq, 0, ppx_ctx::kRsqSlots * sizeof(unsigned long long)));
 		ctx->rs_slot = 0;
 		ctx->rs_overlap = value != 0;
 		return PPX_OK;

@@ -20,7 +20,10 @@ struct ppx_ctx {
 	int rs_overlap = 0; // 1: consecutive ppx_check_edges_rs_dev launches overlap (programmatic dependent launch)
 	int rs_slot = 0; // cursor slot of the next overlapped launch
 	int search_engine = 1; // Hybrid A* graph search: 1 = one CTA per query (master + worker warps), 0 = one warp per query
-	unsigned long long* d_rsq = nullptr; // kMaxChunks cursors of the overlapped launches (each launch zeroes its successor's)
+	// cursors of the overlapped launches, a ring: each launch zeroes its successor's.  More slots than kernels can be resident
+	// at once (128), so a slot is never reused while an earlier launch still reads it, however small the launches are
+	static constexpr int kRsqSlots = 256;
+	unsigned long long* d_rsq = nullptr;
 
 	// multi-GPU (ppx_comm.cu): ncclComm_t of this rank, NULL without ppx_comm_init
 	void* comm = nullptr;

@@ -55,6 +55,7 @@ struct SmemLen {
 // lanes of the warp are parked (or nothing else is runnable) the warp evaluates those samples with
 // the exact FP64 restatement of the reference (rs_exact_sample) in one divergent pass.
 constexpr int kGrab = 128;
+constexpr int kOverlapCtasPerSm = 2; // per launch in rs_overlap mode, see launch_check_rs
 constexpr int kCheckCtasPerSm = 6; // 80 registers (k_check_rs<0,6>: 32 B of spill stores, ppx_edges.ptxas.log); 24 warps/SM measured best (r1g sweep)
 constexpr int kParkBatch = 8;
 constexpr int kRefillBatch = 8;
@@ -474,7 +475,11 @@ static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 	if (overlap) {
 		// programmatic dependent launch: this kernel may start while the previous one on the stream still drains
 		cudaLaunchConfig_t cfg = {};
-		cfg.gridDim = dim3((unsigned)grid_for(ctx, n, kThreads, kCheckCtasPerSm));
+		// Two CTAs per SM and launch (the SM holds six): up to three launches are resident at once, and the warps of a launch
+		// are a third as many -- each works through three times the edges before it reaches its tail of long sample chains,
+		// which is where lanes idle (1M-edge launches, CTAs per SM and launch 6 / 4 / 2 / 1: 7.98 / 8.65 / 9.36-9.59 / 9.92 G
+		// edges/s; 2 rather than 1 so that the last launch of a stream drains at a third of the GPU, not a sixth)
+		cfg.gridDim = dim3((unsigned)grid_for(ctx, n, kThreads, kOverlapCtasPerSm));
 		cfg.blockDim = dim3(kThreads);
 		cfg.dynamicSmemBytes = 0;
 		cfg.stream = ctx->stream;
@@ -484,7 +489,7 @@ static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 		cfg.attrs = attr;
 		cfg.numAttrs = 1;
 		unsigned long long* q = ctx->d_rsq + queueSlot;
-		unsigned long long* next = ctx->d_rsq + (queueSlot + 1) % ppx_ctx::kMaxChunks;
+		unsigned long long* next = ctx->d_rsq + (queueSlot + 1) % ppx_ctx::kRsqSlots;
 		if (ctx->rs_engine >= 1)
 			PPX_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_check_rs2<false, false>, ctx->map_dev(), fm, n, d_edges, min_turning_radius,
 				vp->min_safe_radius, vp->min_path_interpolation_distance, d_valid, d_last, d_samples, q, (AuditOut*)nullptr, next, SolveArgs {}));
@@ -516,7 +521,7 @@ int ppx_check_edges_rs_dev(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 		return PPX_OK;
 	if (ctx->rs_overlap) { // no memset between the kernels: each launch zeroes the cursor of the next one
 		const int slot = ctx->rs_slot;
-		ctx->rs_slot = (slot + 1) % ppx_ctx::kMaxChunks;
+		ctx->rs_slot = (slot + 1) % ppx_ctx::kRsqSlots;
 		return launch_check_rs(ctx, n, d_edges, min_turning_radius, vp, d_valid, d_last, d_samples, slot, true);
 	}
 	PPX_CUDA(ctx, cudaMemsetAsync(ctx->d_queue, 0, sizeof(unsigned long long), ctx->stream));

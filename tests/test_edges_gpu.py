@@ -256,6 +256,24 @@ def test_rs_overlap_option(ctx, c3_edges):
                 ctx._check(ppx.ppx_memcpy_d2h(ctx.handle, l.ctypes.data_as(C.c_void_p), d_last[k], 4 * n))
                 assert np.array_equal(v.astype(bool), want[k % 3][0]), (rep, k)
                 assert np.array_equal(l.view(np.uint32), want[k % 3][1].view(np.uint32)), (rep, k)
+        # many tiny launches: dozens are resident at once, far more than the three of full-size launches -- the ring of
+        # work-queue cursors (256 slots, each launch zeroes its successor's) must never hand two live launches one cursor
+        tiny, count = 200, 600
+        d_tv, d_tl = dalloc(tiny * count), dalloc(4 * tiny * count)
+        for k in range(count):
+            off = (k % (n // tiny)) * tiny
+            ctx._check(ppx.ppx_check_edges_rs_dev(ctx.handle, tiny, C.c_void_p(d_edges[0].value + 72 * off), 2.0, C.byref(vpc),
+                                                  C.c_void_p(d_tv.value + k * tiny), C.c_void_p(d_tl.value + 4 * k * tiny), None))
+        v = np.zeros(tiny * count, np.uint8)
+        l = np.zeros(tiny * count, np.float32)
+        ctx._check(ppx.ppx_memcpy_d2h(ctx.handle, v.ctypes.data_as(C.c_void_p), d_tv, v.nbytes))
+        ctx._check(ppx.ppx_memcpy_d2h(ctx.handle, l.ctypes.data_as(C.c_void_p), d_tl, l.nbytes))
+        for k in range(count):
+            off = (k % (n // tiny)) * tiny
+            assert np.array_equal(v[k * tiny:(k + 1) * tiny].astype(bool), want[0][0][off:off + tiny]), k
+            assert np.array_equal(l[k * tiny:(k + 1) * tiny].view(np.uint32), want[0][1][off:off + tiny].view(np.uint32)), k
+        ppx.ppx_dev_free(ctx.handle, d_tv)
+        ppx.ppx_dev_free(ctx.handle, d_tl)
     finally:
         ctx.set_option("rs_overlap", 0)
     # back to serial launches on the same context
