@@ -53,8 +53,9 @@ __device__ __forceinline__ unsigned long long make_key(float cost, uint32_t seq)
 __device__ __forceinline__ uint32_t claim_key(uint32_t rank, int j) { return 0x7fffffffu - (rank * 8u + (uint32_t)j); }
 
 // neighbour enumeration order of GridCellPosition::GetNeighbors, utils/grid.cpp:29-47
-__constant__ int c_dr[8] = { 0, -1, 1, 0, -1, 1, -1, 1 };
-__constant__ int c_dc[8] = { -1, -1, -1, 1, 1, 1, 0, 0 };
+// { 0, -1, 1, 0, -1, 1, -1, 1 } / { -1, -1, -1, 1, 1, 1, 0, 0 }; functions so that they fold in the unrolled loops over j
+__host__ __device__ constexpr int wf_dr(int j) { return j == 1 || j == 4 || j == 6 ? -1 : j == 2 || j == 5 || j == 7 ? 1 : 0; }
+__host__ __device__ constexpr int wf_dc(int j) { return j <= 2 ? -1 : j <= 5 ? 1 : 0; }
 
 // In-place bitonic sort of n (power of two) (key, cell) pairs by the whole CTA.
 __device__ void cta_bitonic_sort(unsigned long long* keys, uint32_t* cells, uint32_t n)
@@ -304,21 +305,31 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_wavefront(MapDev map, 
 			const uint32_t per = (L + blockDim.x - 1) / blockDim.x;
 			const uint32_t first = threadIdx.x * per;
 			const uint32_t lastp = first + per < L ? first + per : L;
+			// The eight occupancy bytes of a parent's neighbours are loaded together (one latency, not up to ten dependent
+			// ones: the corner rule reads the 4-neighbours, which are among the eight), and so are the tags in step 3, which
+			// looks only at the neighbours this thread claimed (claimMask: bit 8 * (rank - first) + j, first eight parents).
+			unsigned long long claimMask = 0ull;
 			for (uint32_t rank = first; rank < lastp; rank++) {
 				const uint32_t cell = sc[rank];
 				const int r = (int)(cell >> 16), c = (int)(cell & 0xffffu);
+				uint8_t o[8];
 				#pragma unroll
 				for (int j = 0; j < 8; j++) {
-					const int rr = r + c_dr[j], cc = c + c_dc[j];
-					if (rr < 0 || rr >= rows || cc < 0 || cc >= cols)
+					const int rr = r + wf_dr(j), cc = c + wf_dc(j);
+					const bool in = rr >= 0 && rr < rows && cc >= 0 && cc < cols;
+					o[j] = in ? occ8[(size_t)rr * cols + cc] : (uint8_t)1; // outside the map: never a neighbour
+				}
+				#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					if (o[j])
 						continue;
-					const size_t ni = (size_t)rr * cols + cc;
-					if (occ8[ni])
-						continue;
-					if (c_dr[j] != 0 && c_dc[j] != 0 && occ8[(size_t)rr * cols + c] && occ8[(size_t)r * cols + cc])
+					// corner rule (heuristics.cpp:130-132): (rr, c) is neighbour 6 / 7 (dr = -1 / +1), (r, cc) is neighbour 0 / 3
+					if (wf_dr(j) != 0 && wf_dc(j) != 0 && o[wf_dr(j) < 0 ? 6 : 7] && o[wf_dc(j) < 0 ? 0 : 3])
 						continue;
 					// reached cells hold kSeqFlag|seq >= 2^31 > any claim: the atomicMax leaves them alone
-					atomicMax(&tag[ni], claim_key(rank, j));
+					atomicMax(&tag[(size_t)(r + wf_dr(j)) * cols + (c + wf_dc(j))], claim_key(rank, j));
+					if (rank - first < 8)
+						claimMask |= 1ull << (8 * (rank - first) + j);
 				}
 			}
 			__syncthreads();
@@ -328,12 +339,20 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_wavefront(MapDev map, 
 			for (uint32_t rank = first; rank < lastp; rank++) {
 				const uint32_t cell = sc[rank];
 				const int r = (int)(cell >> 16), c = (int)(cell & 0xffffu);
+				const bool cachedClaims = rank - first < 8;
+				const uint32_t cbits = cachedClaims ? (uint32_t)(claimMask >> (8 * (rank - first))) & 0xffu : 0xffu;
+				if (cbits == 0)
+					continue;
+				uint32_t t[8];
 				#pragma unroll
 				for (int j = 0; j < 8; j++) {
-					const int rr = r + c_dr[j], cc = c + c_dc[j];
-					if (rr < 0 || rr >= rows || cc < 0 || cc >= cols)
-						continue;
-					const bool won = tag[(size_t)rr * cols + cc] == claim_key(rank, j);
+					const int rr = r + wf_dr(j), cc = c + wf_dc(j);
+					const bool look = ((cbits >> j) & 1u) && rr >= 0 && rr < rows && cc >= 0 && cc < cols;
+					t[j] = look ? tag[(size_t)rr * cols + cc] : 0u; // 0 is never a claim key
+				}
+				#pragma unroll
+				for (int j = 0; j < 8; j++) {
+					const bool won = t[j] == claim_key(rank, j);
 					wins += won ? 1u : 0u;
 					if (won && rank - first < 8)
 						wonMask |= 1ull << (8 * (rank - first) + j);
@@ -353,13 +372,13 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_wavefront(MapDev map, 
 				for (int j = 0; j < 8; j++) {
 					if (!((bits >> j) & 1u))
 						continue;
-					const int rr = r + c_dr[j], cc = c + c_dc[j];
+					const int rr = r + wf_dr(j), cc = c + wf_dc(j);
 					if (rr < 0 || rr >= rows || cc < 0 || cc >= cols)
 						continue;
 					const size_t ni = (size_t)rr * cols + cc;
 					if (!cached && tag[ni] != claim_key(rank, j))
 						continue;
-					const float w = (c_dr[j] == 0 || c_dc[j] == 0) ? 1.0f : sqrt2;
+					const float w = (wf_dr(j) == 0 || wf_dc(j) == 0) ? 1.0f : sqrt2;
 					const float pathCost = w + parentCost;
 					cost[ni] = pathCost;
 					tag[ni] = kSeqFlag | seq;
