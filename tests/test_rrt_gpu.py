@@ -53,6 +53,23 @@ def test_knn_matches_bruteforce(ctx, dim, npts, nq, k):
         assert (idx[:, npts:] == -1).all()
 
 
+@pytest.mark.parametrize("offset,spread", [(1.0e6, 0.5), (-3.0e4, 40.0), (0.0, 1.0e-3), (1.0e9, 1.0e3)])
+def test_knn_exact_far_from_origin(ctx, offset, spread):
+    """Coordinates far from the origin (float spacing coarser than the point spacing) and tightly clustered points: the
+    neighbour order is exact in FP64 (a guard for any reduced-precision pre-test of the distance tile)."""
+    rng = np.random.default_rng(77)
+    pts = offset + rng.uniform(-spread, spread, (20000, 3))
+    pts[:, 2] = rng.uniform(-np.pi, np.pi, len(pts))
+    q = offset + rng.uniform(-spread, spread, (700, 3))
+    q[:, 2] = rng.uniform(-np.pi, np.pi, len(q))
+    q[5] = pts[17]
+    pts[9000] = pts[17]
+    idx, d2 = ctx.knn(pts, q, 11)
+    ridx, rd2 = _numpy_knn(pts, q[:150], 11)
+    assert np.array_equal(idx[:150], ridx)
+    assert np.array_equal(d2[:150], rd2)
+
+
 def test_knn_reference_tree_random(ctx, ref):
     rng = np.random.default_rng(8)
     pts = rng.uniform(-5, 5, (3000, 2))
