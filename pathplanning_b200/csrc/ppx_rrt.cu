@@ -1049,8 +1049,11 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, FastM
 							rs_part_store(W.coords + 3 * (size_t)(have ? s_nearIdx[j] : 0), newState, P.rmin, have, s_part[have ? j : 0]);
 						}
 						__syncthreads();
-						if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
-							const int j = (int)threadIdx.x, node = s_nearIdx[j];
+						// candidate j on lane j / 8 of warp j % 8: the connections of different candidates take different branches
+						// (segment types, sample counts); side by side in one warp they would run one after the other
+						const int j = (int)(threadIdx.x & 31) * kRrtWarps + (int)(threadIdx.x >> 5);
+						if ((threadIdx.x & 31) < 2 && j < nn && s_nearIdx[j] >= 0) {
+							const int node = s_nearIdx[j];
 							RSSolution sol;
 							rs_finish(s_part[j], P.rmin, sol);
 							Conn c;
@@ -1058,12 +1061,15 @@ __global__ void __launch_bounds__(kRrtThreads) k_rrt(RrtDev P, MapDev map, FastM
 							s_candCost[j] = W.cost[node] + c.length;
 							s_candValid[j] = conn_valid_exactly(P, map, fm, c) ? 1 : 0;
 						}
-					} else if ((int)threadIdx.x < nn && s_nearIdx[threadIdx.x] >= 0) {
-						const int node = s_nearIdx[threadIdx.x];
-						Conn c;
-						connect(P, W.coords + 3 * (size_t)node, newState, false, 0.0, c); // SteerExactly
-						s_candCost[threadIdx.x] = W.cost[node] + c.length;
-						s_candValid[threadIdx.x] = conn_valid(P, map, c) ? 1 : 0;
+					} else {
+						const int j = (int)(threadIdx.x & 31) * kRrtWarps + (int)(threadIdx.x >> 5); // as above
+						if ((threadIdx.x & 31) < 2 && j < nn && s_nearIdx[j] >= 0) {
+							const int node = s_nearIdx[j];
+							Conn c;
+							connect(P, W.coords + 3 * (size_t)node, newState, false, 0.0, c); // SteerExactly
+							s_candCost[j] = W.cost[node] + c.length;
+							s_candValid[j] = conn_valid(P, map, c) ? 1 : 0;
+						}
 					}
 					__syncthreads();
 					RRT_PHASE(5)
