@@ -374,6 +374,12 @@ def hybrid_section(args, rank, world, local_rank, stream):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_dev = float(t.item())
     wf_ms, search_ms = planner.timing()  # this rank's last repetition
+    per_rank = None
+    if world > 1:  # the step is the slowest rank's: show every rank's phases (last repetition) and its shard's work
+        mine_ms = torch.tensor([wf_ms, search_ms, ev0.elapsed_time(ev1) / reps], dtype=torch.float64, device=dev)
+        all_ms = [torch.zeros_like(mine_ms) for _ in range(world)]
+        dist.all_gather(all_ms, mine_ms)
+        per_rank = [{"rank": r, "wavefront_ms": float(a[0]), "search_ms": float(a[1]), "step_ms": float(a[2])} for r, a in enumerate(all_ms)]
     launches = (ctx.launch_count - launches0) // (reps + 3)
     local = d_res.cpu().numpy().view(HYBRID_RESULT).copy()  # the device-timed run's records of this shard
     # through the host-buffer call (goal de-duplication, H2D, wavefronts, search, D2H of results + paths)
@@ -431,7 +437,7 @@ def hybrid_section(args, rank, world, local_rank, stream):
         "e2e": {"value": nq / float(te.item()), "unit": "plans/s", "h2d_bytes": int(m * 56), "d2h_bytes": int(m * (40 + 128 * 40)),
                 "records_equal_device_timed_run": same_as_timed},
         "solved": solved, "expansions": expanded, "longest_query_expansions": int(allres["n_expanded"].max()),
-        "gather_ms": gather_ms, "gpu_launches": int(launches),
+        "gather_ms": gather_ms, "gpu_launches": int(launches), "per_rank": per_rank,
         "field": {"what": "Voronoi potential built on the device (ppx_gvd_build: distance map, Voronoi edges, Voronoi distance "
                           "map, PathCostMap); the CPU arm searches the same field", "build_ms_host_call": gvd_ms,
                   "voronoi_edge_cells": int((field["voro_sqdist"] == 0).sum())},
