@@ -56,7 +56,11 @@ int ppx_ctx_synchronize(ppx_ctx* ctx);
  * starts filling the SMs while the last long sample chains of the previous call drain (programmatic dependent
  * launch; up to three calls are resident on the GPU at once).  The caller guarantees that the output arrays of a call do
  * not alias those of the previous THREE calls and that its inputs are not produced by them; any other work submitted to
- * the stream still waits for every earlier call to complete.) */
+ * the stream still waits for every earlier call to complete.)
+ * "rs_engine" (default 1: k_check_rs2, knot records + bulk-copy staging; 0: the round-1 lane machine k_check_rs; 2: as 1, and
+ * ppx_rs_solve uses the quad-cooperative solver) and "search_engine" (default 1: one CTA per Hybrid A* query, master + worker
+ * warps; 0: one warp per query) are A/B switches: the results are identical (tests/test_edges_gpu.py::test_rs_engines_identical,
+ * tests/test_hybrid_gpu.py::test_search_engines_identical). */
 int ppx_ctx_set_option(ppx_ctx* ctx, const char* name, int64_t value);
 const char* ppx_last_error(const ppx_ctx* ctx);
 /* Number of kernels this context launched since creation (bench.py's gpu_launches). */
