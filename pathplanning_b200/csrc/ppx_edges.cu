@@ -479,7 +479,8 @@ static int launch_check_rs(ppx_ctx* ctx, int64_t n, const ppx_rs_edge* d_edges, 
 		// are a third as many -- each works through three times the edges before it reaches its tail of long sample chains,
 		// which is where lanes idle (1M-edge launches, CTAs per SM and launch 6 / 4 / 2 / 1: 7.98 / 8.65 / 9.36-9.59 / 9.92 G
 		// edges/s; 2 rather than 1 so that the last launch of a stream drains at a third of the GPU, not a sixth)
-		cfg.gridDim = dim3((unsigned)grid_for(ctx, n, kThreads, kOverlapCtasPerSm));
+		static const int overlapCtas = getenv("PPX_OVERLAP_CTAS") ? std::max(1, std::min(6, atoi(getenv("PPX_OVERLAP_CTAS")))) : kOverlapCtasPerSm;
+		cfg.gridDim = dim3((unsigned)grid_for(ctx, n, kThreads, overlapCtas));
 		cfg.blockDim = dim3(kThreads);
 		cfg.dynamicSmemBytes = 0;
 		cfg.stream = ctx->stream;
