@@ -243,29 +243,35 @@ __global__ void __launch_bounds__(kAstarWarps * 32) k_astar_n2(AstarFn F, const 
 				if (exists && nr != r && nc != c && occ8[(size_t)nr * cols + c] && occ8[(size_t)r * cols + nc])
 					exists = false; // diagonal between two occupied cells
 			}
-			double step = 0.0, h = 0.0;
+			// the eight table entries -- and the f of the frontier nodes they name -- are read by the eight lanes at once: the
+			// neighbours are eight different cells, so no commit below can change another neighbour's entry, and read one
+			// after the other by lane 0 they were up to sixteen dependent L2 round trips per expansion
+			double step = 0.0, h = 0.0, oldF = 0.0;
 			uint32_t entry = 0;
 			if (exists) {
 				step = step_cost(F, r, c, nr, nc);
 				h = heuristic(F, nr, nc, gr, gc);
 				entry = W.table[(size_t)nr * cols + nc];
+				if (entry >= 2u)
+					oldF = W.f[entry - 2u];
 			}
 			const double parentG = W.g[n];
 			for (int j = 0; j < 8; j++) { // commit in order (lane 0 holds the search state)
 				const bool ex = __shfl_sync(0xffffffffu, (int)exists, j) != 0;
 				const double st = __shfl_sync(0xffffffffu, step, j), hj = __shfl_sync(0xffffffffu, h, j);
 				const int cr = __shfl_sync(0xffffffffu, nr, j), cc = __shfl_sync(0xffffffffu, nc, j);
+				const uint32_t e = __shfl_sync(0xffffffffu, entry, j);
+				const double ef = __shfl_sync(0xffffffffu, oldF, j);
 				if (!ex || lane != 0 || status != 1)
 					continue;
 				const int ci = cr * cols + cc;
-				const uint32_t e = W.table[ci]; // re-read: an earlier neighbour cannot alias it, but keep it simple
 				const double g = parentG + st, f = g + hj;
 				bool push = false;
 				if (e == 0u)
 					push = true;
 				else if (e >= 2u) { // ProcessPossibleShortcut, a_star.h:412-421
 					const int fn = (int)(e - 2u);
-					if (W.f[fn] > f) {
+					if (ef > f) {
 						W.dead[fn] = 1;
 						push = true;
 					}
@@ -285,7 +291,6 @@ __global__ void __launch_bounds__(kAstarWarps * 32) k_astar_n2(AstarFn F, const 
 					W.table[ci] = (uint32_t)m + 2u;
 				}
 			}
-			(void)entry;
 			__syncwarp();
 			status = __shfl_sync(0xffffffffu, status, 0);
 		}
